@@ -1,0 +1,129 @@
+/*
+ * llie_b200.h — C ABI of the B200-native loss/metric hot path
+ * (drop-in compute boundary for RUA1027/Lowlight_Image_Enhancement).
+ *
+ * The reference has no FFI of its own: its boundary is Python call signatures
+ * (SURVEY.md §8b).  Every entry point below names the reference function whose
+ * arithmetic it replaces (paths relative to the reference repo root).  The
+ * Python mirror in lowlight_image_enhancement_b200/ binds these with ctypes;
+ * INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - all data pointers are DEVICE pointers to contiguous NCHW buffers on the
+ *     current device; `stream` is a cudaStream_t passed as void*;
+ *   - every call is asynchronous on `stream`, never synchronises, never
+ *     allocates, and is CUDA-graph capturable;
+ *   - the return value is 0 (LLIE_OK) or a negative LLIE_E* code; nothing
+ *     throws across the ABI; llie_last_error() returns a static message;
+ *   - `workspace` is a caller-owned device buffer of llie_workspace_bytes()
+ *     bytes that must be ZERO before its first use and must not be shared by
+ *     calls running concurrently on different streams; every call leaves it
+ *     zeroed again (self-resetting tickets), so one cudaMemset at allocation
+ *     time is enough;
+ *   - reductions are deterministic (fixed-order two-stage, no float atomics).
+ */
+#ifndef LLIE_B200_H
+#define LLIE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LLIE_OK 0
+#define LLIE_EINVAL (-1)   /* bad argument / unsupported combination */
+#define LLIE_ECUDA (-2)    /* a CUDA runtime call failed (see llie_last_error) */
+#define LLIE_ENOSM100 (-3) /* device is not sm_100 */
+
+/* padding modes (phys: zeros/reflect/replicate; ssim adds circular) */
+#define LLIE_PAD_ZEROS 0
+#define LLIE_PAD_REFLECT 1
+#define LLIE_PAD_REPLICATE 2
+#define LLIE_PAD_CIRCULAR 3
+
+/* PSF layouts */
+#define LLIE_PSF_DEPTHWISE 0 /* [C,1,kh,kw], output channel c reads input channel c */
+#define LLIE_PSF_DENSE 1     /* [C_out,C_in,kh,kw] cross-channel */
+
+int llie_abi_version(void);
+const char *llie_last_error(void);
+size_t llie_workspace_bytes(void);
+/* 0 if the current device is compute capability 10.x, else LLIE_ENOSM100 */
+int llie_check_device(void);
+
+/* ------------------------------------------------------------------------
+ * Physics-consistency projector  r = clipY(sY * (K (*) padY(pred))) - clipA(sA * obs)
+ *
+ * replaces  metrics/phys_consistency.py:193-255  _phys_cons_core          (rho_side=0)
+ *           NewBP_model/losses.py:173-192        PhysicsConsistencyLoss   (rho_side=1, replicate, same)
+ *           NewBP_model/losses.py:217-220        PhysicalConsistencyLossSRGB (rho_side=1, zeros, same)
+ * ------------------------------------------------------------------------ */
+typedef struct llie_phys_desc {
+    int32_t n, c_in, c_out, h, w;
+    int32_t kh, kw;         /* odd */
+    int32_t psf_layout;     /* LLIE_PSF_* (depthwise requires c_in == c_out) */
+    int32_t pad_mode;       /* LLIE_PAD_ZEROS / REFLECT / REPLICATE */
+    int32_t crop_valid;     /* 1: compare only [kh/2, H-kh/2) x [kw/2, W-kw/2) */
+    int32_t robust;         /* 0: |r|   1: sqrt(r^2 + eps^2) */
+    int32_t rho_side;       /* 0: rho multiplies K*pred (metric)  1: rho multiplies obs (loss) */
+    int32_t clip_y;         /* clamp sY*(K*pred) to [0,1] */
+    int32_t clip_a;         /* clamp sA*obs to [0,1] */
+    float eps;
+    float rho_scalar;       /* used when rho == NULL */
+    /* element strides of the rho tensor for (n, c, y, x); 0 = broadcast */
+    int64_t rho_sn, rho_sc, rho_sh, rho_sw;
+} llie_phys_desc;
+
+/* Forward.
+ *   psf          prepared (normalised) weights, layout per desc
+ *   rho          NULL (use rho_scalar) or device pointer with the strides in desc
+ *   out_mean     [n + 2] floats: per-sample mean of the loss map, then mean over
+ *                samples, then sum over samples (phys_consistency.py:250-251)
+ *   out_sum      NULL or [n + 1] doubles: raw per-sample sums of the loss map, then the total
+ *   out_map      NULL or [n, c_out, h', w'] |r| map (phys_consistency.py:244, return_map)
+ *   out_flags    [1] int: bit0 non-finite value seen in pred, bit1 in obs
+ *                (replaces the two isfinite().all() passes, phys_consistency.py:57-60)
+ */
+int llie_phys_forward(const llie_phys_desc *desc, const float *pred, const float *obs,
+                      const float *psf, const float *rho, float *out_mean, double *out_sum,
+                      float *out_map, int32_t *out_flags, void *workspace, void *stream);
+
+/* Backward (adjoint): grad_pred = padY^T K^T ( sY * 1[clipY passes] * psi(r) * g_n )
+ *   where psi = sign (robust=0, sign(0)=0) or r/sqrt(r^2+eps^2), and
+ *   g_n = gout[gout_stride * n] * gscale  (gscale folds 1/count and the batch reduction).
+ * This is the conv_transpose2d dual of NewBP_model/newbp_layer.py:16-21 fused with the
+ * residual derivative (autograd of losses.py:191, :220 in the reference).
+ *   scratch      NULL, or [n, c_out, h, w] floats; REQUIRED for dense PSFs or kh,kw > 9
+ */
+int llie_phys_backward(const llie_phys_desc *desc, const float *pred, const float *obs,
+                       const float *psf, const float *rho, const float *gout, int64_t gout_stride,
+                       float gscale, float *grad_pred, float *scratch, void *stream);
+
+/* ------------------------------------------------------------------------
+ * NewBP operator: y = conv2d(x, K, padding, groups) and its explicit adjoint
+ * gx = conv_transpose2d(gy, K, padding, groups)
+ * replaces NewBP_model/newbp_layer.py:9-21 (NewBPFunction) and :117-126 (CrosstalkPSF.forward).
+ * groups must be 1 (dense K [c_out,c_in,kh,kw]) or c_in == c_out (depthwise K [c,1,kh,kw]).
+ * dtype: 0 = float32, 1 = float64 (the reference's gradcheck tests run in double).
+ * ------------------------------------------------------------------------ */
+typedef struct llie_conv_desc {
+    int32_t n, c_in, c_out, h, w; /* input spatial size of the FORWARD op */
+    int32_t kh, kw;
+    int32_t pad_h, pad_w;         /* zero padding */
+    int32_t depthwise;            /* 1: groups == c_in == c_out */
+    int32_t dtype;                /* 0 f32, 1 f64 */
+} llie_conv_desc;
+
+/* y: [n, c_out, h + 2*pad_h - kh + 1, w + 2*pad_w - kw + 1] */
+int llie_newbp_forward(const llie_conv_desc *desc, const void *x, const void *kernel, void *y,
+                       void *stream);
+/* gy has the forward OUTPUT shape, gx the forward INPUT shape */
+int llie_newbp_adjoint(const llie_conv_desc *desc, const void *gy, const void *kernel, void *gx,
+                       void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLIE_B200_H */

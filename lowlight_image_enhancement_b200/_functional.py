@@ -1,0 +1,276 @@
+"""Thin functional layer between the reference-shaped Python API and the C ABI.
+
+Everything here is plumbing: argument normalisation, output allocation through torch's caching
+allocator on the current stream, autograd pairing of *_forward / *_backward entry points.
+No arithmetic on image-sized tensors happens in Python.
+"""
+from __future__ import annotations
+
+import warnings
+from dataclasses import dataclass
+from typing import Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _native as nat
+
+PSF_DEPTHWISE, PSF_DENSE = 0, 1
+
+
+# ------------------------------------------------------------------------------------------------
+# PSF preparation (metrics/phys_consistency.py:75-127 semantics, superset of accepted layouts)
+# ------------------------------------------------------------------------------------------------
+@dataclass
+class PreparedPSF:
+    weights: Tensor      # device fp32, [C,1,kh,kw] (layout 0) or [C_out,C_in,kh,kw] (layout 1)
+    layout: int
+    kh: int
+    kw: int
+    zero_sum: bool       # a channel sum was ~0 during normalisation (RuntimeWarning in the reference)
+
+
+_psf_cache: dict = {}
+
+
+def prepare_psf(psf: Tensor, c_in: int, c_out: int, dev: torch.device, *, normalize: bool,
+                nonneg: bool, eps: float, allow_depthwise: bool = True) -> PreparedPSF:
+    """Validate / normalise a PSF once (cached on the tensor's identity + version) and upload it.
+
+    Accepted: 2-D [kh,kw] and [1,1,kh,kw] (mono, broadcast to every channel), [C,1,kh,kw]
+    (per-channel depthwise) and the reference's dense [C_out,C_in,kh,kw].  Error types and messages
+    follow phys_consistency.py:88-111.  A dense PSF whose off-diagonal blocks are all exactly zero is
+    executed on the depthwise path (identical arithmetic, no cross-channel taps).
+    """
+    if not isinstance(psf, Tensor):
+        raise TypeError("`psf` must be a torch.Tensor.")
+    key = (psf.data_ptr(), psf._version, tuple(psf.shape), psf.dtype, str(psf.device), c_in, c_out, str(dev),
+           bool(normalize), bool(nonneg), float(eps), allow_depthwise)
+    hit = _psf_cache.get(key)
+    if hit is not None:
+        return hit
+    p = psf.detach()
+    if p.ndim == 2:
+        p = p.unsqueeze(0).unsqueeze(0)
+    if p.ndim != 4:
+        raise ValueError(
+            f"`psf` must have shape [C_out, C_in, kh, kw]; received tensor with shape {tuple(psf.shape)}.")
+    co, ci, kh, kw = p.shape
+    mono = allow_depthwise and co == 1 and ci == 1 and c_in == c_out and c_out > 1
+    depthwise = allow_depthwise and ci == 1 and co == c_out and c_in == c_out and c_out > 1
+    if not (mono or depthwise):
+        if co != c_out:
+            raise ValueError(f"PSF output channels ({co}) must match observation channels ({c_out}).")
+        if ci != c_in:
+            raise ValueError(f"PSF input channels ({ci}) must match prediction channels ({c_in}).")
+    if kh < 1 or kw < 1:
+        raise ValueError("PSF kernel height/width must be >= 1.")
+    if kh % 2 == 0 or kw % 2 == 0:
+        raise ValueError(
+            "PSF kernels must have odd spatial dimensions to avoid half-pixel shifts. "
+            "Please supply odd-sized kernels (e.g., 3/5/7).")
+    # tiny tensor: prepare on the host in fp32 with the reference's op order, then upload once
+    p = p.to(device="cpu", dtype=torch.float32)
+    if nonneg:
+        p = p.clamp_min(0)
+    zero_sum = False
+    if normalize:
+        sums = p.reshape(p.shape[0], -1).sum(dim=1)
+        dead = sums.abs() < eps
+        zero_sum = bool(dead.any())
+        p = p / torch.where(dead, torch.ones_like(sums), sums).view(-1, 1, 1, 1)
+    if mono:
+        p = p.expand(c_out, 1, kh, kw)
+        layout = PSF_DEPTHWISE
+    elif depthwise:
+        layout = PSF_DEPTHWISE
+    else:
+        layout = PSF_DENSE
+        if allow_depthwise and c_in == c_out and c_out > 1:
+            off = p.clone()
+            for c in range(c_out):
+                off[c, c] = 0
+            if not bool(off.any()):
+                p = torch.stack([p[c, c] for c in range(c_out)]).unsqueeze(1)
+                layout = PSF_DEPTHWISE
+        elif c_in == 1 and c_out == 1:
+            layout = PSF_DEPTHWISE
+    out = PreparedPSF(p.contiguous().to(dev), layout, kh, kw, zero_sum)
+    if len(_psf_cache) > 256:
+        _psf_cache.clear()
+    _psf_cache[key] = out
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# exposure ratio normalisation (phys_consistency.py:160-190)
+# ------------------------------------------------------------------------------------------------
+def normalise_rho(rho, n: int, c: int, h: int, w: int, dev: torch.device
+                  ) -> Tuple[Optional[Tensor], float, Tuple[int, int, int, int]]:
+    """-> (device tensor or None, scalar, element strides for (n,c,y,x))."""
+    if not torch.is_tensor(rho):
+        return None, float(rho), (0, 0, 0, 0)
+    r = nat.stage(rho.detach(), dev, torch.float32)
+    if r.ndim == 0:
+        return r, 0.0, (0, 0, 0, 0)
+    if r.ndim == 1:
+        if r.shape[0] != n:
+            raise ValueError(f"Exposure ratio length ({r.shape[0]}) must match batch size ({n}).")
+        return r, 0.0, (1, 0, 0, 0)
+    if r.ndim == 4:
+        if r.shape[0] != n:
+            raise ValueError(f"Exposure ratio batch dimension ({r.shape[0]}) must match batch size ({n}).")
+        if r.shape[1] not in (1, c):
+            raise ValueError(
+                f"Exposure ratio channel dimension ({r.shape[1]}) incompatible with data channels ({c}).")
+        if r.shape[2] not in (1, h) or r.shape[3] not in (1, w):
+            raise RuntimeError(
+                f"Exposure ratio of shape {tuple(r.shape)} is not broadcastable to {(n, c, h, w)}.")
+        st = r.stride()
+        strides = tuple(0 if r.shape[i] == 1 else int(st[i]) for i in range(4))
+        return r, 0.0, strides  # type: ignore[return-value]
+    raise ValueError("Exposure ratio must be scalar, [N], or [N,1,H,W]/[N,C,H,W] for broadcasting.")
+
+
+# ------------------------------------------------------------------------------------------------
+# physics projector
+# ------------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class PhysCfg:
+    pad_mode: int
+    crop_valid: bool
+    robust: bool
+    eps: float
+    rho_side: int     # 0: rho scales K*pred (metric convention), 1: rho scales obs (loss convention)
+    clip_y: bool
+    clip_a: bool
+
+
+def _desc(cfg: PhysCfg, pred: Tensor, c_out: int, psf: PreparedPSF, rho_scalar: float, strides) -> nat.PhysDesc:
+    n, c_in, h, w = pred.shape
+    return nat.PhysDesc(n, c_in, c_out, h, w, psf.kh, psf.kw, psf.layout, cfg.pad_mode, int(cfg.crop_valid),
+                        int(cfg.robust), cfg.rho_side, int(cfg.clip_y), int(cfg.clip_a), cfg.eps, rho_scalar,
+                        strides[0], strides[1], strides[2], strides[3])
+
+
+def phys_forward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t: Optional[Tensor], rho_scalar: float,
+                 rho_strides, cfg: PhysCfg, want_map: bool):
+    """Launch llie_phys_forward.  pred/obs: contiguous fp32 CUDA NCHW.
+    Returns (vec[N+2] fp32 = per-sample means | batch mean | batch sum, flags int32[1], map or None)."""
+    dev = pred.device
+    n, c_in, h, w = pred.shape
+    c_out = obs.shape[1]
+    ph, pw = (psf.kh // 2, psf.kw // 2) if cfg.crop_valid else (0, 0)
+    if cfg.crop_valid and (h <= 2 * ph or w <= 2 * pw):
+        raise ValueError("crop='valid' leaves an empty comparison region for this PSF/image size.")
+    buf = torch.empty(n + 3, dtype=torch.float32, device=dev)
+    flags = buf[n + 2:].view(torch.int32)
+    amap = torch.empty((n, c_out, h - 2 * ph, w - 2 * pw), dtype=torch.float32, device=dev) if want_map else None
+    d = _desc(cfg, pred, c_out, psf, rho_scalar, rho_strides)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_phys_forward(d, nat.ptr(pred), nat.ptr(obs), nat.ptr(psf.weights), nat.ptr(rho_t),
+                                         nat.ptr(buf), None, nat.ptr(amap), nat.ptr(flags),
+                                         nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+    nat.check(rc, "llie_phys_forward")
+    nat.count_launch()
+    return buf[: n + 2], flags, amap
+
+
+def phys_backward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_scalar, rho_strides, cfg: PhysCfg,
+                  gout: Tensor, gscale: float) -> Tensor:
+    dev = pred.device
+    n, c_in, h, w = pred.shape
+    c_out = obs.shape[1]
+    grad = torch.empty_like(pred)
+    needs_scratch = psf.layout == PSF_DENSE or psf.kh != 3 or psf.kw != 3 or (w % 4) != 0 or \
+        (rho_t is not None and (rho_strides[2] != 0 or rho_strides[3] != 0)) or \
+        pred.data_ptr() % 16 or obs.data_ptr() % 16 or grad.data_ptr() % 16
+    scratch = torch.empty((n, c_out, h, w), dtype=torch.float32, device=dev) if needs_scratch else None
+    d = _desc(cfg, pred, c_out, psf, rho_scalar, rho_strides)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_phys_backward(d, nat.ptr(pred), nat.ptr(obs), nat.ptr(psf.weights), nat.ptr(rho_t),
+                                          nat.ptr(gout), 1 if gout.numel() > 1 else 0, gscale, nat.ptr(grad),
+                                          nat.ptr(scratch), nat.stream_ptr(dev))
+    nat.check(rc, "llie_phys_backward")
+    nat.count_launch(2 if needs_scratch else 1)
+    return grad
+
+
+class PhysProjector(torch.autograd.Function):
+    """vec[N+2] = (per-sample means, batch mean, batch sum) of the loss map; differentiable in pred."""
+
+    @staticmethod
+    def forward(ctx, pred, obs, psf: PreparedPSF, rho_t, rho_scalar, rho_strides, cfg: PhysCfg):
+        p = pred.detach().contiguous()
+        o = obs.detach().contiguous()
+        vec, flags, _ = phys_forward(p, o, psf, rho_t, rho_scalar, rho_strides, cfg, False)
+        ctx.save_for_backward(p, o)
+        ctx.aux = (psf, rho_t, rho_scalar, rho_strides, cfg)
+        ctx.flags = flags
+        return vec
+
+    @staticmethod
+    def backward(ctx, gvec):
+        p, o = ctx.saved_tensors
+        psf, rho_t, rho_scalar, rho_strides, cfg = ctx.aux
+        n, _, h, w = p.shape
+        ph, pw = (psf.kh // 2, psf.kw // 2) if cfg.crop_valid else (0, 0)
+        count = o.shape[1] * (h - 2 * ph) * (w - 2 * pw)
+        g = gvec[:n] + gvec[n] / n + gvec[n + 1]
+        grad = phys_backward(p, o, psf, rho_t, rho_scalar, rho_strides, cfg, g.contiguous().float(), 1.0 / count)
+        return grad, None, None, None, None, None, None
+
+
+# ------------------------------------------------------------------------------------------------
+# NewBP conv / adjoint
+# ------------------------------------------------------------------------------------------------
+def _conv_desc(x_shape, k: Tensor, pad_h: int, pad_w: int, groups: int, dtype) -> nat.ConvDesc:
+    n, c_in, h, w = x_shape
+    c_out, c_in_g, kh, kw = k.shape
+    if groups == 1:
+        if c_in_g != c_in:
+            raise RuntimeError(f"kernel expects {c_in_g} input channels, input has {c_in}")
+        depthwise = 1 if (c_in == 1 and c_out == 1) else 0
+    elif groups == c_in and c_out == c_in and c_in_g == 1:
+        depthwise = 1
+    else:
+        raise NotImplementedError(
+            "NewBP conv kernels support groups == 1 or depthwise (groups == C_in == C_out) only.")
+    return nat.ConvDesc(n, c_in, c_out, h, w, kh, kw, pad_h, pad_w, depthwise, 0 if dtype == torch.float32 else 1)
+
+
+def _pair(p):
+    return (int(p), int(p)) if not isinstance(p, (tuple, list)) else (int(p[0]), int(p[1]))
+
+
+def newbp_conv(x: Tensor, k: Tensor, padding, groups: int) -> Tensor:
+    dev = x.device
+    ph, pw = _pair(padding)
+    d = _conv_desc(x.shape, k, ph, pw, groups, x.dtype)
+    ho, wo = d.h + 2 * ph - d.kh + 1, d.w + 2 * pw - d.kw + 1
+    if ho <= 0 or wo <= 0:
+        raise RuntimeError("Kernel size can't be greater than actual input size")
+    y = torch.empty((d.n, d.c_out, ho, wo), dtype=x.dtype, device=dev)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_newbp_forward(d, nat.ptr(x), nat.ptr(k), nat.ptr(y), nat.stream_ptr(dev))
+    nat.check(rc, "llie_newbp_forward")
+    nat.count_launch()
+    return y
+
+
+def newbp_adjoint(gy: Tensor, k: Tensor, padding, groups: int, x_shape) -> Tensor:
+    dev = gy.device
+    ph, pw = _pair(padding)
+    d = _conv_desc(x_shape, k, ph, pw, groups, gy.dtype)
+    gx = torch.empty(tuple(x_shape), dtype=gy.dtype, device=dev)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_newbp_adjoint(d, nat.ptr(gy), nat.ptr(k), nat.ptr(gx), nat.stream_ptr(dev))
+    nat.check(rc, "llie_newbp_adjoint")
+    nat.count_launch()
+    return gx
+
+
+def warn_zero_sum():
+    warnings.warn(
+        "PSF channel sums near zero detected during normalisation; clamping to preserve stability.",
+        RuntimeWarning, stacklevel=3)

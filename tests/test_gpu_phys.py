@@ -1,0 +1,244 @@
+"""GPU parity: fused phys-consistency kernels and the NewBP operator vs the CPU oracle and the
+reference-generated golden vectors.  Tolerances from BASELINE.json: 1e-5 relative for fp32 losses
+and gradients."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import psf_ops
+from tests.golden_inputs import PHYS_CASES, dense_from_spec, depthwise_from_spec, loss_inputs, phys_inputs
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available()
+    return torch.device("cuda:0")
+
+
+def _rel(a, b):
+    a = a.detach().double().cpu()
+    b = torch.as_tensor(b).double()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def _run_case(case, psf, dev):
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw, phys_cons_srgb
+    pred, obs, rho = phys_inputs(case)
+    fn = phys_cons_srgb if case["srgb"] else phys_cons_raw
+    kw = dict(reduction=case["reduction"], padding=case["padding"], crop=case["crop"], robust=case["robust"],
+              eps=case["eps"], return_map=True, normalize_psf=case.get("normalize_psf", True))
+    if case["srgb"]:
+        kw["clamp01"] = case["clamp01"]
+    rho_d = rho.to(dev) if torch.is_tensor(rho) else rho
+    return fn(pred.to(dev), obs.to(dev), psf.to(dev), rho_d, **kw)
+
+
+@pytest.mark.parametrize("i", range(len(PHYS_CASES)))
+def test_phys_metric_vs_golden_dense(golden, dev, i):
+    """Dense [3,3,kh,kw] PSFs exactly as the reference accepts them."""
+    val, mp = _run_case(PHYS_CASES[i], dense_from_spec(PHYS_CASES[i]["psf"]), dev)
+    assert _rel(val, golden[f"phys{i}_val"]) < RTOL
+    np.testing.assert_allclose(mp.cpu().numpy(), golden[f"phys{i}_map"], atol=2e-6, rtol=0)
+
+
+@pytest.mark.parametrize("i", [k for k, c in enumerate(PHYS_CASES) if c["psf"][0] == "diag"])
+def test_phys_metric_depthwise_form(golden, dev, i):
+    """Same cases with the PSF given in the depthwise [3,1,kh,kw] form (superset of the reference)."""
+    val, mp = _run_case(PHYS_CASES[i], depthwise_from_spec(PHYS_CASES[i]["psf"][1]), dev)
+    assert _rel(val, golden[f"phys{i}_val"]) < RTOL
+    np.testing.assert_allclose(mp.cpu().numpy(), golden[f"phys{i}_map"], atol=2e-6, rtol=0)
+
+
+@pytest.mark.parametrize("padding", ["reflect", "replicate", "zeros"])
+@pytest.mark.parametrize("crop", ["valid", "same"])
+@pytest.mark.parametrize("robust,eps", [("none", 1e-12), ("charbonnier", 1e-3)])
+@pytest.mark.parametrize("shape", [(2, 3, 64, 128), (1, 3, 70, 252), (3, 3, 33, 8)])
+def test_phys_tile_path_fwd_bwd(dev, padding, crop, robust, eps, shape):
+    """Tile path (depthwise 3x3, W % 4 == 0): forward value, map and the adjoint gradient vs autograd of
+    the oracle.  Shapes straddle tile edges (120-wide tiles, 32-high)."""
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_srgb
+    g = torch.Generator().manual_seed(sum(shape) + len(padding))
+    pred = torch.rand(shape, generator=g)
+    k = depthwise_from_spec("B2")
+    rho = torch.tensor([0.9, 1.1, 1.3][: shape[0]])
+    obs = (psf_ops.crosstalk_forward(pred, k) * rho.view(-1, 1, 1, 1) + 0.05 * torch.randn(shape, generator=g)).clamp(0, 1.2)
+    dense = psf_ops.embed_dense(k)
+    kw = dict(padding=padding, crop=crop, robust=robust, eps=eps, reduction="mean")
+    xr = pred.clone().requires_grad_(True)
+    with torch.enable_grad():
+        ref = _oracle_diff(xr, obs, dense, rho, clamp01=True, **kw)
+        ref.backward()
+    x = pred.to(dev).requires_grad_(True)
+    val, mp = phys_cons_srgb(x.detach(), obs.to(dev), k.to(dev), rho.to(dev), return_map=True, **kw)
+    assert _rel(val, ref) < RTOL
+    out = phys_cons_srgb(x, obs.to(dev), k.to(dev), rho.to(dev), differentiable=True, **kw)
+    assert out.requires_grad
+    out.backward()
+    assert _rel(out, ref) < RTOL
+    assert _rel(x.grad, xr.grad) < RTOL
+
+
+def _oracle_diff(pred, obs, dense, rho, *, padding, crop, robust, eps, reduction, clamp01):
+    """Differentiable restatement (the oracle's phys_metric detaches like the reference does)."""
+    import torch.nn.functional as F
+    k = psf_ops.prepare_dense_psf(dense, 3, 3, torch.float32, True, False, eps)
+    ph, pw = k.shape[-2] // 2, k.shape[-1] // 2
+    if padding == "zeros":
+        y = F.conv2d(pred, k, padding=(ph, pw))
+    else:
+        y = F.conv2d(F.pad(pred, (pw, pw, ph, ph), mode=padding), k)
+    y = y * psf_ops.expand_rho(rho, y)
+    if clamp01:
+        y = y.clamp(0.0, 1.0)
+    o = obs
+    if crop == "valid":
+        y, o = y[..., ph:-ph, pw:-pw], o[..., ph:-ph, pw:-pw]
+    d = y - o
+    lm = torch.sqrt(d * d + eps * eps) if robust == "charbonnier" else d.abs()
+    per = lm.flatten(1).mean(1)
+    return per.mean(0) if reduction == "mean" else per.sum(0)
+
+
+@pytest.mark.parametrize("case_i", [5, 6, 7, 8])
+def test_phys_generic_path_gradient(dev, case_i):
+    """Generic path (dense / 5x5 / 3x5 / spatial rho): gradient vs oracle autograd."""
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw, phys_cons_srgb
+    case = PHYS_CASES[case_i]
+    pred, obs, rho = phys_inputs(case)
+    dense = dense_from_spec(case["psf"])
+    xr = pred.clone().requires_grad_(True)
+    red = "mean" if case["reduction"] == "none" else case["reduction"]
+    ref = _oracle_diff(xr, obs, dense, rho, padding=case["padding"], crop=case["crop"], robust=case["robust"],
+                       eps=case["eps"], reduction=red, clamp01=case["clamp01"])
+    ref.backward()
+    x = pred.to(dev).requires_grad_(True)
+    fn = phys_cons_srgb if case["srgb"] else phys_cons_raw
+    kw = dict(padding=case["padding"], crop=case["crop"], robust=case["robust"], eps=case["eps"], reduction=red,
+              differentiable=True)
+    if case["srgb"]:
+        kw["clamp01"] = case["clamp01"]
+    out = fn(x, obs.to(dev), dense.to(dev), rho.to(dev) if torch.is_tensor(rho) else rho, **kw)
+    out.backward()
+    assert _rel(out, ref) < RTOL
+    assert _rel(x.grad, xr.grad) < 2e-5
+
+
+@pytest.mark.parametrize("mode", ["mono", "rgb"])
+def test_crosstalk_newbp_and_losses_vs_golden(golden, dev, mode):
+    from lowlight_image_enhancement_b200.NewBP_model.losses import PhysicalConsistencyLossSRGB, PhysicsConsistencyLoss
+    from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import CrosstalkPSF, NewBPFunction, build_psf_kernels
+    k = build_psf_kernels(mode, "P2" if mode == "mono" else "B2")
+    np.testing.assert_array_equal(k.numpy(), golden[f"kern_{mode}"])
+    psf = CrosstalkPSF(mode, k).to(dev)
+    np.testing.assert_allclose(psf.kernel.cpu().numpy(), golden[f"kern_{mode}_norm"], rtol=1e-7)
+    bhat, a, rho = loss_inputs(mode)
+    gy = torch.randn(bhat.shape, generator=torch.Generator().manual_seed(77))
+    x = bhat.to(dev).requires_grad_(True)
+    y = psf(x)
+    y.backward(gy.to(dev))
+    assert _rel(y, golden[f"xtalk_{mode}_y"]) < RTOL
+    assert _rel(x.grad, golden[f"xtalk_{mode}_gx"]) < RTOL
+    kd = psf.kernel.expand(3, 1, 3, 3).contiguous()
+    x2 = bhat.to(dev).requires_grad_(True)
+    y2 = NewBPFunction.apply(x2, kd, 1, 3)
+    y2.backward(gy.to(dev))
+    assert _rel(y2, golden[f"newbp_{mode}_fwd"]) < RTOL
+    assert _rel(x2.grad, golden[f"newbp_{mode}_gx"]) < RTOL
+    # fused sRGB physics loss: value and gradient
+    x3 = bhat.to(dev).requires_grad_(True)
+    ls = PhysicalConsistencyLossSRGB(psf)(x3, a.to(dev), rho.to(dev))
+    ls.backward()
+    assert _rel(ls, golden[f"physloss_srgb_{mode}_val"]) < RTOL
+    assert _rel(x3.grad, golden[f"physloss_srgb_{mode}_grad"]) < RTOL
+    # unfused route (forward hook present) must agree
+    calls = []
+    h = psf.register_forward_hook(lambda *_: calls.append(1))
+    x4 = bhat.to(dev).requires_grad_(True)
+    ls2 = PhysicalConsistencyLossSRGB(psf)(x4, a.to(dev), rho.to(dev))
+    ls2.backward()
+    h.remove()
+    assert len(calls) == 1
+    assert _rel(ls2, golden[f"physloss_srgb_{mode}_val"]) < RTOL
+    assert _rel(x4.grad, golden[f"physloss_srgb_{mode}_grad"]) < RTOL
+    # RAW physics loss, 3x3 and 5x5
+    for tag, kk in (("k3", k), ("k5", torch.ones(k.shape[0], 1, 5, 5) / 25.0)):
+        x5 = bhat.to(dev).requires_grad_(True)
+        lr = PhysicsConsistencyLoss(kk, device=dev)(x5, a.to(dev), rho.view(-1).to(dev))
+        lr.backward()
+        assert _rel(lr, golden[f"physloss_raw_{mode}_{tag}_val"]) < RTOL
+        assert _rel(x5.grad, golden[f"physloss_raw_{mode}_{tag}_grad"]) < RTOL
+
+
+def test_newbp_double_precision_and_gradcheck(dev):
+    """core_tests/test_physics_loss_grad.py semantics: fp64 adjoint == conv_transpose2d; gradcheck."""
+    import torch.nn.functional as F
+    from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import CrosstalkPSF
+    torch.manual_seed(0)
+    for mode in ("mono", "rgb"):
+        k = torch.rand(1 if mode == "mono" else 3, 1, 3, 3, dtype=torch.double)
+        psf = CrosstalkPSF(mode, k).to(dev).to(torch.double)
+        z = torch.randn(1, 3, 6, 6, dtype=torch.double, device=dev, requires_grad=True)
+        ref = torch.randn(1, 3, 6, 6, dtype=torch.double, device=dev)
+        assert torch.autograd.gradcheck(lambda t: (psf(t) - ref).abs().sum(), (z,), eps=1e-6, atol=1e-4)
+        y = psf(z)
+        ga = torch.randn_like(y)
+        (gz,) = torch.autograd.grad(y, z, ga)
+        kd = psf.kernel.expand(3, -1, -1, -1).contiguous().cpu()
+        want = F.conv_transpose2d(ga.cpu(), kd, padding=1, groups=3)
+        assert torch.allclose(gz.cpu(), want, atol=1e-12)
+
+
+def test_reference_contract_errors_and_flags(dev):
+    """test_phys_consistency.py of the reference: ValueErrors, zero-PSF warning, NaN detection, shapes."""
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw, phys_cons_srgb
+    x = torch.rand(1, 3, 24, 24, device=dev)
+    with pytest.raises(ValueError):
+        phys_cons_raw(x, x, torch.ones(3, 3, 4, 4, device=dev), 1.0)
+    with pytest.raises(ValueError):
+        phys_cons_raw(x, x, torch.ones(2, 3, 3, 3, device=dev), 1.0)
+    with pytest.warns(RuntimeWarning):
+        v = phys_cons_raw(x, x, torch.zeros(3, 3, 3, 3, device=dev), 1.0)
+    assert torch.isfinite(v)
+    bad = x.clone()
+    bad[0, 1, 0, 0] = float("nan")  # on the cropped border: still must be detected
+    with pytest.raises(ValueError, match="pred"):
+        phys_cons_raw(bad, x, dense_from_spec(("delta", 3)).to(dev), 1.0)
+    with pytest.raises(ValueError, match="obs"):
+        phys_cons_raw(x, bad, dense_from_spec(("delta", 3)).to(dev), 1.0)
+    # delta PSF, obs = rho * gt -> ~0
+    v = phys_cons_raw(x, 0.7 * x, dense_from_spec(("delta", 3)).to(dev), 0.7, crop="same")
+    assert abs(float(v)) <= 1e-7
+    _, m = phys_cons_raw(x, x, dense_from_spec(("delta", 5)).to(dev), 1.0, crop="valid", padding="zeros", return_map=True)
+    assert tuple(m.shape) == (1, 3, 20, 20)
+    # clamp caps the residual
+    p9, o8 = torch.full((1, 3, 24, 24), 0.9, device=dev), torch.full((1, 3, 24, 24), 0.8, device=dev)
+    _, m = phys_cons_srgb(p9, o8, dense_from_spec(("delta", 3)).to(dev), 1.5, crop="same", return_map=True)
+    assert float(m.max()) <= 0.25 + 1e-6
+    # host tensors are uploaded and the result comes back on the host
+    out = phys_cons_raw(x.cpu(), x.cpu(), dense_from_spec(("delta", 3)), 1.0)
+    assert out.device.type == "cpu"
+
+
+def test_full_size_properties(dev):
+    """BASELINE C2 size (8x3x512x512): linearity in rho and the delta-PSF identity, size-independent."""
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw
+    g = torch.Generator(device=dev).manual_seed(102)
+    pred = torch.rand(8, 3, 512, 512, device=dev, generator=g)
+    k = depthwise_from_spec("B2").to(dev)
+    zero = torch.zeros_like(pred)
+    rho = torch.tensor([100., 250., 300., 100., 250., 300., 100., 250.], device=dev)
+    a = phys_cons_raw(pred / 300, zero, k, rho, reduction="none", crop="same", padding="zeros")
+    b = phys_cons_raw(pred / 300, zero, k, 2 * rho, reduction="none", crop="same", padding="zeros")
+    assert torch.allclose(2 * a, b, rtol=1e-6)
+    ident = torch.zeros(3, 1, 3, 3, device=dev)
+    ident[:, 0, 1, 1] = 1
+    v = phys_cons_raw(pred, pred * 0.5, ident, 0.5, crop="same")
+    assert float(v) <= 1e-7
+    # deterministic: bitwise identical on repeat
+    a2 = phys_cons_raw(pred / 300, zero, k, rho, reduction="none", crop="same", padding="zeros")
+    assert torch.equal(a, a2)
