@@ -1,0 +1,297 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the B200-native loss/metric hot path (contract: see DESIGN.md §Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload phys_c2]
+
+A *step* is one pass of the hot path over one synthetic batch of BASELINE.json configs[1]:
+`phys_cons_raw` (rgb B2 depthwise PSF, per-image rho in {100,250,300}, reflect pad, valid crop, L1)
+forward + the adjoint backward on 8x3x512x512 fp32.  value = Mpix/s (pixels = N*H*W) with inputs
+resident in HBM; e2e = the same through the public Python API from pinned HOST buffers (H2D of
+pred/obs and D2H of the loss inside the timed region).  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+RHO = [100.0, 250.0, 300.0, 100.0, 250.0, 300.0, 100.0, 250.0]
+SHAPE = (8, 3, 512, 512)
+POOL = 8  # rotating buffer sets: 8 x (pred+obs+grad = 75.5 MB) = 604 MB >> 126 MB L2
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+def synth_batch(seed, device):
+    """pred = U[0,1)/rho_n, obs = clamp(rho_n*(B2 (*) pred) + 0.01 N, 0, 1)."""
+    from oracle import psf_ops  # input synthesis only (not timed, not the product path)
+    g = torch.Generator().manual_seed(seed)
+    rho = torch.tensor(RHO)
+    pred = torch.rand(SHAPE, generator=g) / rho.view(-1, 1, 1, 1)
+    k = psf_ops.normalise_crosstalk(psf_ops.canonical_kernels("rgb"))
+    obs = (rho.view(-1, 1, 1, 1) * psf_ops.crosstalk_forward(pred, k) + 0.01 * torch.randn(SHAPE, generator=g)).clamp(0, 1)
+    return pred.to(device), obs.to(device), rho.to(device)
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop = index, [], threading.Event()
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.t.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.t.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if len(r) >= 6 and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) >= 6 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i].lower() == "active"})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's algorithm (oracle restatement of metrics/phys_consistency.py, same torch ops)
+# ------------------------------------------------------------------------------------------------
+def cpu_step_fn():
+    from oracle import psf_ops
+    dense = psf_ops.embed_dense(psf_ops.canonical_kernels("rgb"))
+
+    def step(pred, obs, rho):
+        x = pred.detach().clone().requires_grad_(True)
+        loss = psf_ops.phys_metric(x, obs, dense, rho, keep_graph=True)
+        loss.backward()
+        return float(loss.detach())
+    return step
+
+
+def time_cpu(steps, warmup):
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sets = [synth_batch(102 + i, "cpu") for i in range(2)]
+    step = cpu_step_fn()
+    for i in range(warmup):
+        step(*sets[i % 2])
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step(*sets[i % 2])
+    dt = time.perf_counter() - t0
+    mpix = SHAPE[0] * SHAPE[2] * SHAPE[3] / 1e6
+    return mpix * steps / dt, dt / steps * 1e3, cores
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return None
+    steps = max(1, args.steps)
+    val, ms, cores = time_cpu(steps, max(1, min(args.warmup, 3)))
+    sample = f"{steps} full C2 batches (8x3x512x512) fwd+bwd, oracle port of phys_cons_raw, torch CPU {cores} threads"
+    return {
+        "impl": "reference", "metric": "Mpix/s phys-cons fwd+bwd", "value": round(val, 3), "unit": "Mpix/s",
+        "n_gpus": args.gpus, "steps": steps, "warmup": args.warmup, "ms_per_step": round(ms, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "phys_cons_raw rgb B2 depthwise PSF, per-image rho, 8x3x512x512 fp32, fwd+bwd (BASELINE configs[1])"},
+        "cpu_baseline": {"value": round(val, 3), "unit": "Mpix/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(val, 3), "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def timed(fn, iters, dev):
+    """CUDA-event time (ms) of `iters` calls of fn(i) on the current stream, synchronised both sides."""
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(dev)
+    s.record()
+    for i in range(iters):
+        fn(i)
+    e.record()
+    torch.cuda.synchronize(dev)
+    return s.elapsed_time(e)
+
+
+def run_ours(args, rank, world, dev):
+    import torch.distributed as dist
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    from lowlight_image_enhancement_b200 import _native as nat
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw
+    from oracle import psf_ops  # kernel constants for input synthesis only
+
+    sets = [synth_batch(1000 * rank + 102 + i, dev) for i in range(POOL)]
+    grads = [torch.empty(SHAPE, device=dev) for _ in range(POOL)]
+    kern = psf_ops.canonical_kernels("rgb").to(dev)
+    psf = Fn.prepare_psf(kern, 3, 3, dev, normalize=True, nonneg=False, eps=1e-12)
+    cfg = Fn.PhysCfg(nat.PAD["reflect"], True, False, 1e-12, 0, False, False)
+    n, c, h, w = SHAPE
+    count = c * (h - 2) * (w - 2)
+    gout = torch.ones(1, device=dev)
+    gscale = 1.0 / (n * count)
+    st = (1, 0, 0, 0)
+
+    def fwd(i):
+        p, o, r = sets[i % POOL]
+        return Fn.phys_forward(p, o, psf, r, 0.0, st, cfg, False)
+
+    def bwd(i):
+        p, o, r = sets[i % POOL]
+        return Fn.phys_backward(p, o, psf, r, 0.0, st, cfg, gout, gscale, out=grads[i % POOL])
+
+    def step(i):
+        fwd(i)
+        bwd(i)
+
+    K, W = args.steps, max(3, args.warmup)
+    for i in range(W):
+        step(i)
+    # per-kernel timings (live, CUDA events on the launching stream)
+    t_f = timed(fwd, K, dev) / K
+    t_b = timed(bwd, K, dev) / K
+    if world > 1:
+        dist.barrier()
+    l0 = nat.launches
+    with ClockSampler(dev.index) as clk:
+        ms = timed(step, K, dev)
+    launches = nat.launches - l0
+    if world > 1:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.barrier()
+        ms = float(t)
+    mpix = n * h * w / 1e6
+    value = world * mpix * K / (ms / 1e3)
+
+    # ---- e2e: public API, pinned host inputs, H2D + D2H inside the timed region
+    hp = [(s[0].cpu().pin_memory(), s[1].cpu().pin_memory()) for s in sets[:4]]
+    rho_d = sets[0][2]
+
+    def e2e_step(i):
+        ph_, oh_ = hp[i % 4]
+        x = ph_.to(dev, non_blocking=True).requires_grad_(True)
+        o = oh_.to(dev, non_blocking=True)
+        loss = phys_cons_raw(x, o, kern, rho_d, differentiable=True)
+        loss.backward()
+        return loss.item()
+
+    Ke = max(3, min(K, 50))
+    if args.skip_e2e:
+        Ke = 1
+    for i in range(1 if args.skip_e2e else 3):
+        e2e_step(i)
+    ms_e = timed(e2e_step, Ke, dev)
+    if world > 1:
+        t = torch.tensor([ms_e], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_e = float(t)
+    e2e_val = world * mpix * Ke / (ms_e / 1e3)
+
+    if rank != 0:
+        return None
+    peak, peak_src = peaks()
+    elems = n * c * h * w
+    bytes_f, bytes_b = 8 * elems, 12 * elems
+    ach_b = bytes_b / (t_b * 1e-3) / 1e9
+    ach_f = bytes_f / (t_f * 1e-3) / 1e9
+    line = {
+        "metric": "Mpix/s phys-cons fwd+bwd", "value": round(value, 1), "unit": "Mpix/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 5), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "phys_cons_raw rgb B2 depthwise PSF, per-image rho, 8x3x512x512 fp32, fwd+bwd (BASELINE configs[1])",
+                   "l2": f"inputs rotate over {POOL} resident buffer sets (604 MB per GPU) > 126 MB L2",
+                   "per_gpu_batch": list(SHAPE)},
+        "roofline": {"bound": "hbm", "kernel": "phys_bwd_tile3", "achieved": round(ach_b, 1), "peak": peak,
+                     "unit": "GB/s", "frac": round(ach_b / peak, 4), "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": bytes_b, "us_per_launch": round(t_b * 1e3, 2)},
+        "kernels": [
+            {"kernel": "phys_fwd_tile3", "us": round(t_f * 1e3, 2), "algorithmic_bytes": bytes_f,
+             "achieved_gbs": round(ach_f, 1), "frac": round(ach_f / peak, 4)},
+            {"kernel": "phys_bwd_tile3", "us": round(t_b * 1e3, 2), "algorithmic_bytes": bytes_b,
+             "achieved_gbs": round(ach_b, 1), "frac": round(ach_b / peak, 4)}],
+        "e2e": {"value": round(e2e_val, 1), "unit": "Mpix/s", "h2d_bytes_per_step": 2 * 4 * elems,
+                "d2h_bytes_per_step": 4, "steps": Ke, "api": "metrics.phys_consistency.phys_cons_raw(differentiable=True)+backward"},
+        "gpu_launches": launches,
+        "clocks": clk.summary(),
+    }
+    if world == 1 and not args.skip_cpu:
+        v, ms_c, cores = time_cpu(3, 1)
+        line["cpu_baseline"] = {"value": round(v, 3), "unit": "Mpix/s", "cores": cores, "kind": "port",
+                                "sample": "3 full C2 batches fwd+bwd after 1 warm-up, oracle port, torch CPU all threads"}
+    return line
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="phys_c2")
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: 1 untimed-quality e2e step only")
+    ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: no cpu_baseline leg")
+    args = ap.parse_args()
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.impl == "reference":
+        line = run_reference(args, rank)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    line = run_ours(args, rank, world, dev)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

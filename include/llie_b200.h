@@ -123,6 +123,36 @@ int llie_newbp_forward(const llie_conv_desc *desc, const void *x, const void *ke
 int llie_newbp_adjoint(const llie_conv_desc *desc, const void *gy, const void *kernel, void *gx,
                        void *stream);
 
+/* ------------------------------------------------------------------------
+ * PSNR family: per-(n,c) sums of squared differences in float64, finalised on the device.
+ * replaces metrics/linear.py:139-210 (psnr_linear: subtract in the input dtype, THEN cast to f64),
+ *          metrics/channelwise.py:113-222 (rgb_psnr / cpsnr_rgb: cast to f64, clamp, subtract),
+ *          metrics/psnr.py:39-88 (calculate_psnr: f64 global mean, n=c=1 over the whole tensor).
+ * ------------------------------------------------------------------------ */
+typedef struct llie_psnr_desc {
+    int32_t n, c;
+    int64_t plane;        /* h*w elements per (n,c) plane */
+    int32_t dtype;        /* 0 f32, 1 f64 inputs */
+    int32_t cast_first;   /* 0: diff in input dtype then f64 (linear.py:197); 1: f64 first (channelwise.py:146-150) */
+    int32_t clamp;        /* clamp both inputs to [0, clamp_hi] before the difference */
+    double clamp_hi;
+    double data_range;
+    double eps;
+} llie_psnr_desc;
+
+/* columns of the [n + 2, LLIE_PSNR_COLS(c)] float64 result matrix (rows n / n+1: batch mean / sum) */
+#define LLIE_PSNR_COLS(c) (2 * (c) + 3)
+/* [0,c)      per-channel MSE
+ * [c,2c)     per-channel PSNR = 10 log10(L^2 / max(mse_c, eps))           (channelwise.py:153-155)
+ * 2c         mean over channels of the per-channel PSNR                     (channelwise.py:156)
+ * 2c+1       CPSNR from the mean of channel MSEs, eps floor                  (channelwise.py:211-216)
+ * 2c+2       PSNR of the whole sample, +inf where mse <= eps                 (linear.py:198-208, psnr.py:84-85)
+ *   out_minmax  NULL or [2] floats (dtype f32) / doubles (f64): global min / max over BOTH tensors
+ *               (metrics/ssim.py:62-71 auto data range)
+ *   out_flags   [1] int: bit0 non-finite in x, bit1 non-finite in y */
+int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const void *y, double *out,
+                    void *out_minmax, int32_t *out_flags, void *workspace, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,7 +52,7 @@ class PhysicsConsistencyLoss(nn.Module):
 
     def _psf(self, c: int, dev: torch.device) -> Fn.PreparedPSF:
         k = self.K
-        key = (k.data_ptr(), k._version, tuple(k.shape), c, str(dev))
+        key = (id(k), k._version, tuple(k.shape), c, str(dev))
         if self._prepared is None or self._prepared[0] != key:
             kh, kw = k.shape[-2:]
             kk = k.detach().to(torch.float32)

@@ -30,9 +30,6 @@ class PreparedPSF:
     zero_sum: bool       # a channel sum was ~0 during normalisation (RuntimeWarning in the reference)
 
 
-_psf_cache: dict = {}
-
-
 def prepare_psf(psf: Tensor, c_in: int, c_out: int, dev: torch.device, *, normalize: bool,
                 nonneg: bool, eps: float, allow_depthwise: bool = True) -> PreparedPSF:
     """Validate / normalise a PSF once (cached on the tensor's identity + version) and upload it.
@@ -44,11 +41,12 @@ def prepare_psf(psf: Tensor, c_in: int, c_out: int, dev: torch.device, *, normal
     """
     if not isinstance(psf, Tensor):
         raise TypeError("`psf` must be a torch.Tensor.")
-    key = (psf.data_ptr(), psf._version, tuple(psf.shape), psf.dtype, str(psf.device), c_in, c_out, str(dev),
-           bool(normalize), bool(nonneg), float(eps), allow_depthwise)
-    hit = _psf_cache.get(key)
-    if hit is not None:
-        return hit
+    # The cache lives ON the tensor object (dies with it; an address-keyed cache would alias
+    # recycled allocations) and is invalidated by in-place edits through the version counter.
+    key = (psf._version, c_in, c_out, str(dev), bool(normalize), bool(nonneg), float(eps), allow_depthwise)
+    slot = getattr(psf, "_llie_prepared", None)
+    if slot is not None and key in slot:
+        return slot[key]
     p = psf.detach()
     if p.ndim == 2:
         p = p.unsqueeze(0).unsqueeze(0)
@@ -96,9 +94,13 @@ def prepare_psf(psf: Tensor, c_in: int, c_out: int, dev: torch.device, *, normal
         elif c_in == 1 and c_out == 1:
             layout = PSF_DEPTHWISE
     out = PreparedPSF(p.contiguous().to(dev), layout, kh, kw, zero_sum)
-    if len(_psf_cache) > 256:
-        _psf_cache.clear()
-    _psf_cache[key] = out
+    try:
+        if slot is None or len(slot) > 16:
+            slot = {}
+            psf._llie_prepared = slot
+        slot[key] = out
+    except Exception:  # tensor subclasses without a __dict__: just skip caching
+        pass
     return out
 
 
@@ -177,11 +179,11 @@ def phys_forward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t: Optional[Te
 
 
 def phys_backward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_scalar, rho_strides, cfg: PhysCfg,
-                  gout: Tensor, gscale: float) -> Tensor:
+                  gout: Tensor, gscale: float, out: Optional[Tensor] = None) -> Tensor:
     dev = pred.device
     n, c_in, h, w = pred.shape
     c_out = obs.shape[1]
-    grad = torch.empty_like(pred)
+    grad = torch.empty_like(pred) if out is None else out
     needs_scratch = psf.layout == PSF_DENSE or psf.kh != 3 or psf.kw != 3 or (w % 4) != 0 or \
         (rho_t is not None and (rho_strides[2] != 0 or rho_strides[3] != 0)) or \
         pred.data_ptr() % 16 or obs.data_ptr() % 16 or grad.data_ptr() % 16

@@ -117,11 +117,13 @@ def expand_rho(rho, ref):
 
 def phys_metric(pred, obs, psf, rho, *, reduction="mean", padding="reflect", normalize_psf=True,
                 enforce_nonnegative=False, crop="valid", robust="none", clamp01=False,
-                return_map=False, eps=1e-12):
-    """phys_consistency.py:193-255 with the wrappers' fp32 cast (:300-301, :349-350)."""
+                return_map=False, eps=1e-12, keep_graph=False):
+    """phys_consistency.py:193-255 with the wrappers' fp32 cast (:300-301, :349-350).
+    keep_graph=True skips the reference's detach so autograd of the same ops gives d/d pred (used as
+    the gradient oracle and as the CPU fwd+bwd baseline)."""
     if pred.ndim == 3:
         pred, obs = pred[None], obs[None]
-    pred = pred.detach().to(torch.float32)
+    pred = (pred if keep_graph else pred.detach()).to(torch.float32)
     obs = obs.detach().to(torch.float32)
     k = prepare_dense_psf(psf, pred.shape[1], obs.shape[1], pred.dtype, normalize_psf,
                           enforce_nonnegative, eps)

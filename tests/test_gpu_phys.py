@@ -80,13 +80,21 @@ def test_phys_tile_path_fwd_bwd(dev, padding, crop, robust, eps, shape):
     assert out.requires_grad
     out.backward()
     assert _rel(out, ref) < RTOL
-    assert _rel(x.grad, xr.grad) < RTOL
+    if robust == "none":
+        assert _rel(x.grad, xr.grad) < RTOL
+    else:
+        # Charbonnier with eps=1e-3 is ill-conditioned where |r| ~ eps (d psi/dr = 1/eps): fp32 eager is
+        # itself ~1e-4 away from an fp64 run of the same oracle.  Judge both against fp64.
+        x64 = pred.double().requires_grad_(True)
+        _oracle_diff(x64, obs.double(), dense.double(), rho.double(), clamp01=True, dtype=torch.float64, **kw).backward()
+        ours, eager = _rel(x.grad, x64.grad), _rel(xr.grad, x64.grad)
+        assert ours < max(RTOL, 3.0 * eager), (ours, eager)
 
 
-def _oracle_diff(pred, obs, dense, rho, *, padding, crop, robust, eps, reduction, clamp01):
+def _oracle_diff(pred, obs, dense, rho, *, padding, crop, robust, eps, reduction, clamp01, dtype=torch.float32):
     """Differentiable restatement (the oracle's phys_metric detaches like the reference does)."""
     import torch.nn.functional as F
-    k = psf_ops.prepare_dense_psf(dense, 3, 3, torch.float32, True, False, eps)
+    k = psf_ops.prepare_dense_psf(dense, 3, 3, dtype, True, False, eps)
     ph, pw = k.shape[-2] // 2, k.shape[-1] // 2
     if padding == "zeros":
         y = F.conv2d(pred, k, padding=(ph, pw))
