@@ -101,6 +101,10 @@ int llie_phys_backward(const llie_phys_desc *desc, const float *pred, const floa
                        const float *psf, const float *rho, const float *gout, int64_t gout_stride,
                        float gscale, float *grad_pred, float *scratch, void *stream);
 
+/* 1 if llie_phys_backward needs `scratch` for this problem (generic path), 0 for the TMA tile path */
+int llie_phys_backward_needs_scratch(const llie_phys_desc *desc, const float *pred, const float *obs,
+                                     const float *rho, const float *grad_pred);
+
 /* ------------------------------------------------------------------------
  * NewBP operator: y = conv2d(x, K, padding, groups) and its explicit adjoint
  * gx = conv_transpose2d(gy, K, padding, groups)

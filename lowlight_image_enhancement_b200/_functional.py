@@ -184,11 +184,10 @@ def phys_backward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_scalar
     n, c_in, h, w = pred.shape
     c_out = obs.shape[1]
     grad = torch.empty_like(pred) if out is None else out
-    needs_scratch = psf.layout == PSF_DENSE or psf.kh != 3 or psf.kw != 3 or (w % 4) != 0 or \
-        (rho_t is not None and (rho_strides[2] != 0 or rho_strides[3] != 0)) or \
-        pred.data_ptr() % 16 or obs.data_ptr() % 16 or grad.data_ptr() % 16
-    scratch = torch.empty((n, c_out, h, w), dtype=torch.float32, device=dev) if needs_scratch else None
     d = _desc(cfg, pred, c_out, psf, rho_scalar, rho_strides)
+    needs_scratch = bool(nat.lib().llie_phys_backward_needs_scratch(d, nat.ptr(pred), nat.ptr(obs), nat.ptr(rho_t),
+                                                                    nat.ptr(grad)))
+    scratch = torch.empty((n, c_out, h, w), dtype=torch.float32, device=dev) if needs_scratch else None
     with torch.cuda.device(dev):
         rc = nat.lib().llie_phys_backward(d, nat.ptr(pred), nat.ptr(obs), nat.ptr(psf.weights), nat.ptr(rho_t),
                                           nat.ptr(gout), 1 if gout.numel() > 1 else 0, gscale, nat.ptr(grad),
@@ -270,6 +269,30 @@ def newbp_adjoint(gy: Tensor, k: Tensor, padding, groups: int, x_shape) -> Tenso
     nat.check(rc, "llie_newbp_adjoint")
     nat.count_launch()
     return gx
+
+
+# ------------------------------------------------------------------------------------------------
+# PSNR family
+# ------------------------------------------------------------------------------------------------
+def psnr_stats(x: Tensor, y: Tensor, n: int, c: int, plane: int, *, cast_first: bool, clamp_hi,
+               data_range: float, eps: float, want_minmax: bool = False):
+    """Launch llie_psnr_stats on contiguous same-dtype (f32/f64) CUDA tensors.
+    Returns (table float64 [n+2, 2c+3], flags int32[1], minmax or None); see include/llie_b200.h."""
+    dev = x.device
+    cols = 2 * c + 3
+    table = torch.empty((n + 2, cols), dtype=torch.float64, device=dev)
+    aux = torch.empty(4, dtype=torch.float64, device=dev)
+    flags = aux[:1].view(torch.int32)[:1]
+    mm = aux[1:3].view(x.dtype)[:2] if want_minmax else None
+    d = nat.PsnrDesc(n, c, plane, 0 if x.dtype == torch.float32 else 1, int(cast_first),
+                     0 if clamp_hi is None else 1, 0.0 if clamp_hi is None else float(clamp_hi),
+                     float(data_range), float(eps))
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_psnr_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(table), nat.ptr(mm), nat.ptr(flags),
+                                       nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+    nat.check(rc, "llie_psnr_stats")
+    nat.count_launch()
+    return table, flags, mm
 
 
 def warn_zero_sum():

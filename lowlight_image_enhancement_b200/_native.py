@@ -40,6 +40,14 @@ class ConvDesc(C.Structure):
     ]
 
 
+class PsnrDesc(C.Structure):
+    _fields_ = [
+        ("n", C.c_int32), ("c", C.c_int32), ("plane", C.c_int64), ("dtype", C.c_int32),
+        ("cast_first", C.c_int32), ("clamp", C.c_int32), ("clamp_hi", C.c_double),
+        ("data_range", C.c_double), ("eps", C.c_double),
+    ]
+
+
 PAD = {"zeros": 0, "constant": 0, "reflect": 1, "replicate": 2, "circular": 3}
 
 _VP = C.c_void_p
@@ -51,8 +59,10 @@ _SIGNATURES = {
     "llie_phys_forward": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_phys_backward": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, C.c_int64, C.c_float,
                                      _VP, _VP, _VP]),
+    "llie_phys_backward_needs_scratch": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_forward": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_adjoint": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
+    "llie_psnr_stats": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
 }
 
 

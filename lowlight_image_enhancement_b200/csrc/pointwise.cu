@@ -1,0 +1,260 @@
+// PSNR family (sm_100a): one streaming pass producing float64 sums of squared differences per (n,c)
+// plane, global min/max and finiteness flags; the last block finalises every PSNR flavour the
+// reference defines (metrics/linear.py:139-210, metrics/channelwise.py:113-222, metrics/psnr.py:39-88).
+// HBM-bound: 8 B/element (f32) read once, 128-bit loads, fixed-order two-stage reduction.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace llie {
+
+struct PsnrArgs {
+    llie_psnr_desc d;
+    const void *x, *y;
+    double *out;
+    void *out_minmax;
+    int *out_flags;
+    double *part_sum;  // [n*c][G]
+    double *part_min;  // [n*c][G]
+    double *part_max;
+    int *part_flag;
+    unsigned *ticket;
+    int vec_ok;
+};
+
+template <typename T>
+struct Vec;
+template <>
+struct Vec<float> {
+    using type = float4;
+    static constexpr int N = 4;
+};
+template <>
+struct Vec<double> {
+    using type = double2;
+    static constexpr int N = 2;
+};
+
+template <typename T>
+__device__ __forceinline__ bool is_finite(T v);
+template <>
+__device__ __forceinline__ bool is_finite<float>(float v) { return finite_f(v); }
+template <>
+__device__ __forceinline__ bool is_finite<double>(double v) {
+    return (__double2hiint(v) & 0x7ff00000) != 0x7ff00000;
+}
+
+template <typename T>
+struct Acc {
+    double s = 0.0;
+    T mn, mx;
+    int flag = 0;
+    const llie_psnr_desc &d;
+    T hi_t;
+    __device__ Acc(const llie_psnr_desc &dd) : d(dd) {
+        mn = (T)INFINITY;
+        mx = (T)-INFINITY;
+        hi_t = (T)dd.clamp_hi;
+    }
+    __device__ __forceinline__ void add(T xv, T yv) {
+        if (!is_finite(xv)) flag |= 1;
+        if (!is_finite(yv)) flag |= 2;
+        mn = min(mn, min(xv, yv));
+        mx = max(mx, max(xv, yv));
+        double df;
+        if (d.cast_first) {
+            double a = (double)xv, b = (double)yv;
+            if (d.clamp) {
+                a = fmin(fmax(a, 0.0), d.clamp_hi);
+                b = fmin(fmax(b, 0.0), d.clamp_hi);
+            }
+            df = a - b;
+        } else {
+            T a = xv, b = yv;
+            if (d.clamp) {
+                a = min(max(a, (T)0), hi_t);
+                b = min(max(b, (T)0), hi_t);
+            }
+            df = (double)(a - b);
+        }
+        s = fma(df, df, s);
+    }
+};
+
+__device__ __forceinline__ void unpack(const float4 &v, float o[4]) { o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+__device__ __forceinline__ void unpack(const double2 &v, double o[2]) { o[0] = v.x; o[1] = v.y; }
+
+__device__ double psnr_db(double range2, double mse, double eps) { return 10.0 * log10(range2 / fmax(mse, eps)); }
+
+template <typename T>
+__global__ void __launch_bounds__(256) psnr_stats_kernel(const PsnrArgs a) {
+    __shared__ double red[32];
+    using V = typename Vec<T>::type;
+    constexpr int VN = Vec<T>::N;
+    const llie_psnr_desc &d = a.d;
+    const int nc = blockIdx.y;
+    const int G = gridDim.x;
+    const T *xp = static_cast<const T *>(a.x) + (long long)nc * d.plane;
+    const T *yp = static_cast<const T *>(a.y) + (long long)nc * d.plane;
+    Acc<T> acc(d);
+    const long long stride = (long long)G * blockDim.x;
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (a.vec_ok) {
+        const long long nv = d.plane / VN;
+        const V *xv = reinterpret_cast<const V *>(xp);
+        const V *yv = reinterpret_cast<const V *>(yp);
+        // 2 independent 128-bit loads per tensor in flight per thread
+        for (; i + stride < nv; i += 2 * stride) {
+            const V x0 = __ldcs(xv + i), x1 = __ldcs(xv + i + stride);
+            const V y0 = __ldcs(yv + i), y1 = __ldcs(yv + i + stride);
+            T xa[VN], ya[VN];
+            unpack(x0, xa); unpack(y0, ya);
+#pragma unroll
+            for (int k = 0; k < VN; ++k) acc.add(xa[k], ya[k]);
+            unpack(x1, xa); unpack(y1, ya);
+#pragma unroll
+            for (int k = 0; k < VN; ++k) acc.add(xa[k], ya[k]);
+        }
+        for (; i < nv; i += stride) {
+            T xa[VN], ya[VN];
+            unpack(__ldcs(xv + i), xa); unpack(__ldcs(yv + i), ya);
+#pragma unroll
+            for (int k = 0; k < VN; ++k) acc.add(xa[k], ya[k]);
+        }
+        // tail (plane % VN elements)
+        for (long long t = nv * VN + blockIdx.x * blockDim.x + threadIdx.x; t < d.plane; t += stride)
+            acc.add(xp[t], yp[t]);
+    } else {
+        for (; i < d.plane; i += stride) acc.add(__ldcs(xp + i), __ldcs(yp + i));
+    }
+    // block reduce: sum, min, max, flags
+    const double s = block_sum<double>(acc.s, red);
+    double mn = (double)acc.mn, mx = (double)acc.mx;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+        mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    }
+    __shared__ double smn[8], smx[8];
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) { smn[threadIdx.x >> 5] = mn; smx[threadIdx.x >> 5] = mx; }
+    const int f = block_or(acc.flag, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { mn = fmin(mn, smn[w]); mx = fmax(mx, smx[w]); }
+        const size_t slot = (size_t)nc * G + blockIdx.x;
+        a.part_sum[slot] = s;
+        a.part_min[slot] = mn;
+        a.part_max[slot] = mx;
+        a.part_flag[slot] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x * gridDim.y)) return;
+
+    // ---------------- finalize (one block): per-(n,c) totals, then the PSNR table
+    const int NC = d.n * d.c;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    double *tot = a.part_sum;  // reuse slot [row*G + 0] for the row total after reading the row
+    double gmn = INFINITY, gmx = -INFINITY;
+    int gf = 0;
+    for (int row = wid; row < NC; row += 8) {
+        double ss = 0.0;
+        for (int b = lane; b < G; b += 32) {
+            const size_t slot = (size_t)row * G + b;
+            ss += __ldcg(a.part_sum + slot);
+            gmn = fmin(gmn, __ldcg(a.part_min + slot));
+            gmx = fmax(gmx, __ldcg(a.part_max + slot));
+            gf |= __ldcg(a.part_flag + slot);
+        }
+        ss = warp_sum(ss);
+        __syncwarp();
+        if (lane == 0) tot[(size_t)row * G] = ss;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        gmn = fmin(gmn, __shfl_xor_sync(0xffffffffu, gmn, o));
+        gmx = fmax(gmx, __shfl_xor_sync(0xffffffffu, gmx, o));
+    }
+    __syncthreads();
+    if (lane == 0) { smn[wid] = gmn; smx[wid] = gmx; }
+    const int ff = block_or(gf, reinterpret_cast<int *>(red));
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) { gmn = fmin(gmn, smn[w]); gmx = fmax(gmx, smx[w]); }
+        if (a.out_minmax) {
+            if (d.dtype == 0) {
+                static_cast<float *>(a.out_minmax)[0] = (float)gmn;
+                static_cast<float *>(a.out_minmax)[1] = (float)gmx;
+            } else {
+                static_cast<double *>(a.out_minmax)[0] = gmn;
+                static_cast<double *>(a.out_minmax)[1] = gmx;
+            }
+        }
+        *a.out_flags = ff;
+    }
+    // table rows: one thread per sample
+    const int C = d.c, cols = 2 * C + 3;
+    const double r2 = d.data_range * d.data_range;
+    for (int n = threadIdx.x; n < d.n; n += blockDim.x) {
+        double *o = a.out + (size_t)n * cols;
+        double msum = 0.0, psum = 0.0;
+        for (int c = 0; c < C; ++c) {
+            const double mse = tot[(size_t)(n * C + c) * G] / (double)d.plane;
+            o[c] = mse;
+            const double p = psnr_db(r2, mse, d.eps);
+            o[C + c] = p;
+            msum += mse;
+            psum += p;
+        }
+        o[2 * C] = psum / C;
+        o[2 * C + 1] = psnr_db(r2, msum / C, d.eps);
+        const double mall = msum / C;  // equal plane sizes: mean over C*H*W == mean of channel means
+        o[2 * C + 2] = (mall <= d.eps) ? INFINITY : psnr_db(r2, mall, d.eps);
+    }
+    __syncthreads();
+    for (int col = threadIdx.x; col < cols; col += blockDim.x) {
+        double sacc = 0.0;
+        for (int n = 0; n < d.n; ++n) sacc += a.out[(size_t)n * cols + col];
+        a.out[(size_t)d.n * cols + col] = sacc / d.n;
+        a.out[(size_t)(d.n + 1) * cols + col] = sacc;
+    }
+}
+
+}  // namespace llie
+
+using namespace llie;
+
+extern "C" int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const void *y, double *out,
+                               void *out_minmax, int32_t *out_flags, void *workspace, void *stream) {
+    LLIE_REQUIRE(desc && x && y && out && out_flags && workspace, "psnr_stats: null pointer");
+    LLIE_REQUIRE(desc->n > 0 && desc->c > 0 && desc->plane > 0, "psnr_stats: empty tensor");
+    LLIE_REQUIRE((long long)desc->n * desc->c <= 65535, "psnr_stats: n*c too large for grid.y");
+    LLIE_REQUIRE(desc->dtype == 0 || desc->dtype == 1, "psnr_stats: dtype must be 0 (f32) or 1 (f64)");
+    LLIE_REQUIRE(desc->data_range > 0 && desc->eps > 0, "psnr_stats: data_range and eps must be positive");
+    PsnrArgs a{};
+    a.d = *desc;
+    a.x = x; a.y = y; a.out = out; a.out_minmax = out_minmax; a.out_flags = out_flags;
+    const int nc = desc->n * desc->c;
+    const int vn = desc->dtype ? 2 : 4;
+    const size_t esz = desc->dtype ? 8 : 4;
+    a.vec_ok = aligned16(x) && aligned16(y) && ((desc->plane * esz) % 16 == 0);
+    long long per_block = 256LL * vn * 4;
+    int G = div_up(kNumSM * 8, nc);
+    long long maxg = (desc->plane + per_block - 1) / per_block;
+    if (G > maxg) G = (int)maxg;
+    if (G < 1) G = 1;
+    Workspace ws(workspace);
+    const size_t slots = (size_t)nc * G;
+    LLIE_REQUIRE(slots * (3 * sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "psnr_stats: workspace too small");
+    a.part_sum = reinterpret_cast<double *>(ws.scratch);
+    a.part_min = a.part_sum + slots;
+    a.part_max = a.part_min + slots;
+    a.part_flag = reinterpret_cast<int *>(a.part_max + slots);
+    a.ticket = ws.tickets;
+    dim3 grid(G, nc);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (desc->dtype == 0)
+        psnr_stats_kernel<float><<<grid, 256, 0, st>>>(a);
+    else
+        psnr_stats_kernel<double><<<grid, 256, 0, st>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
