@@ -53,6 +53,11 @@ size_t llie_workspace_bytes(void);
 /* 0 if the current device is compute capability 10.x, else LLIE_ENOSM100 */
 int llie_check_device(void);
 
+/* Diagnostic knobs for A/B measurements (process-wide, not thread-safe; defaults are the product). */
+#define LLIE_TUNE_PHYS_PATH 1 /* 0 TMA row ring (default) | 1 TMA tile ring | 2 generic only | 3 register prefetch */
+#define LLIE_TUNE_PHYS_ROWS 2 /* rows per warp chunk of the rolling path; 0 = heuristic */
+int llie_tune(int key, int value);
+
 /* ------------------------------------------------------------------------
  * Physics-consistency projector  r = clipY(sY * (K (*) padY(pred))) - clipA(sA * obs)
  *

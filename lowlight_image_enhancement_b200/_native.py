@@ -12,7 +12,8 @@ import threading
 import torch
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "_lib", "libllie_b200.so")
+# LLIE_B200_LIB selects an alternative build of the SAME library (A/B variants made by tools/); default in-tree
+LIB_PATH = os.environ.get("LLIE_B200_LIB") or os.path.join(_PKG, "_lib", "libllie_b200.so")
 
 _lib = None
 _lock = threading.Lock()
@@ -56,6 +57,7 @@ _SIGNATURES = {
     "llie_last_error": (C.c_char_p, []),
     "llie_workspace_bytes": (C.c_size_t, []),
     "llie_check_device": (C.c_int, []),
+    "llie_tune": (C.c_int, [C.c_int, C.c_int]),
     "llie_phys_forward": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_phys_backward": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, C.c_int64, C.c_float,
                                      _VP, _VP, _VP]),

@@ -209,9 +209,21 @@ static int grid_x_for(int n, int work_items) {
     return per_sample;
 }
 
+int g_phys_path = 0;  // 0 TMA row ring (default), 1 TMA tile ring, 2 generic only, 3 register prefetch (llie_tune)
+
 }  // namespace llie
 
 using namespace llie;
+
+extern "C" int llie_tune(int key, int value) {
+    switch (key) {
+        case LLIE_TUNE_PHYS_PATH: g_phys_path = value; return LLIE_OK;
+        case LLIE_TUNE_PHYS_ROWS: phys_roll_set_rows(value); phys_ring_set_rows(value); return LLIE_OK;
+        default: break;
+    }
+    llie::set_error("llie_tune: unknown key %d", key);
+    return LLIE_EINVAL;
+}
 
 extern "C" int llie_phys_forward(const llie_phys_desc *desc, const float *pred, const float *obs, const float *psf,
                                  const float *rho, float *out_mean, double *out_sum, float *out_map,
@@ -226,7 +238,9 @@ extern "C" int llie_phys_forward(const llie_phys_desc *desc, const float *pred, 
     Workspace ws(workspace);
     a.ticket = ws.tickets;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (phys_tma_eligible(a)) return launch_phys_fwd_tma(a, workspace, st);
+    if (g_phys_path == 0 && phys_ring_eligible(a)) return launch_phys_fwd_ring(a, workspace, st);
+    if (g_phys_path == 3 && phys_roll_eligible(a)) return launch_phys_fwd_roll(a, workspace, st);
+    if (g_phys_path == 1 && phys_tma_eligible(a)) return launch_phys_fwd_tma(a, workspace, st);
     long long items = (long long)desc->c_out * desc->h * desc->w;
     const int gx = grid_x_for(desc->n, (int)((items + 255) / 256));
     const size_t need = (size_t)desc->n * gx * (sizeof(double) + sizeof(int));
@@ -245,7 +259,10 @@ extern "C" int llie_phys_backward_needs_scratch(const llie_phys_desc *desc, cons
     PhysArgs a{};
     a.d = *desc;
     a.pred = pred; a.obs = obs; a.rho = rho;
-    return (phys_tma_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
+    if (g_phys_path == 0) return (phys_ring_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
+    if (g_phys_path == 3) return (phys_roll_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
+    if (g_phys_path == 1) return (phys_tma_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
+    return 1;
 }
 
 extern "C" int llie_phys_backward(const llie_phys_desc *desc, const float *pred, const float *obs, const float *psf,
@@ -260,7 +277,11 @@ extern "C" int llie_phys_backward(const llie_phys_desc *desc, const float *pred,
     a.grad = grad_pred; a.scratch = scratch;
     fill_domain(a);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (phys_tma_eligible(a) && aligned16(grad_pred)) {
+    if (g_phys_path == 0 && phys_ring_eligible(a) && aligned16(grad_pred)) {
+        return launch_phys_bwd_ring(a, st);
+    } else if (g_phys_path == 3 && phys_roll_eligible(a) && aligned16(grad_pred)) {
+        return launch_phys_bwd_roll(a, st);
+    } else if (g_phys_path == 1 && phys_tma_eligible(a) && aligned16(grad_pred)) {
         return launch_phys_bwd_tma(a, nullptr, st);
     } else {
         LLIE_REQUIRE(scratch != nullptr, "phys_backward: this PSF/shape needs the scratch buffer");

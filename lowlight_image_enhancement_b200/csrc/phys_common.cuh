@@ -80,6 +80,18 @@ __device__ __forceinline__ int preimages(int i, int n, int p, int mode, int out[
     return k;
 }
 
+// TMA row-ring path (phys_ring.cu)
+bool phys_ring_eligible(const PhysArgs &a);
+int launch_phys_fwd_ring(PhysArgs &a, void *workspace, cudaStream_t st);
+int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st);
+void phys_ring_set_rows(int r);
+
+// register-rolling path (phys_roll.cu)
+bool phys_roll_eligible(const PhysArgs &a);
+int launch_phys_fwd_roll(PhysArgs &a, void *workspace, cudaStream_t st);
+int launch_phys_bwd_roll(PhysArgs &a, cudaStream_t st);
+void phys_roll_set_rows(int r);
+
 // tile path entry points (phys_tma.cu); return LLIE_OK or an error code
 bool phys_tma_eligible(const PhysArgs &a);
 int launch_phys_fwd_tma(PhysArgs &a, void *workspace, cudaStream_t st);
