@@ -88,8 +88,10 @@ typedef struct llie_phys_desc {
  *                samples, then sum over samples (phys_consistency.py:250-251)
  *   out_sum      NULL or [n + 1] doubles: raw per-sample sums of the loss map, then the total
  *   out_map      NULL or [n, c_out, h', w'] |r| map (phys_consistency.py:244, return_map)
- *   out_flags    [1] int: bit0 non-finite value seen in pred, bit1 in obs
- *                (replaces the two isfinite().all() passes, phys_consistency.py:57-60)
+ *   out_flags    [1] int: bit0 non-finite value seen in pred, bit1 in obs, bit2 a per-sample sum
+ *                is non-finite but the source tensor is unknown (un-clipped fast path: the caller
+ *                resolves it on the error path); replaces the two isfinite().all() passes,
+ *                phys_consistency.py:57-60
  */
 int llie_phys_forward(const llie_phys_desc *desc, const float *pred, const float *obs,
                       const float *psf, const float *rho, float *out_mean, double *out_sum,

@@ -2,15 +2,20 @@
 // planes) -- the HBM-bound production path for the reference's CrosstalkPSF shapes.
 //
 // Persistent CTAs of 4 consumer warps + 1 producer warp.  A work item is a chunk of rows of a
-// 512-column strip of one (n, c) plane.  The producer's elected lane streams the item row by row
-// with 1-D TMA bulk copies (cp.async.bulk global -> shared, 2 KB per row and tensor, completion on
-// an mbarrier) into a ring of kRing row slots, so ~45 KB per CTA (180 KB per SM at 4 CTAs) are in
-// flight without holding a single register; consumers wait on a slot's full barrier, pull their 4
-// pixels (+ neighbours) into registers with LDS, release the slot through its empty barrier and
-// run the 3x3 stencil in rolling ("scatter") form on registers.  No CTA-wide barrier in the loop.
-// Padding: zero rows are synthesised by the consumer, reflect / replicate rows are simply fetched
-// from the mapped source row by the producer, and the image-edge lanes select their outside
-// neighbour from their own pixels.
+// 512-column strip of one (n, c) plane.  The producer's elected lane streams the item with 1-D TMA
+// bulk copies (cp.async.bulk global -> shared, one 2 KB row segment per copy, completion on an
+// mbarrier) into a ring of kSlots slots of kG rows each, so the bytes in flight (~130 KB per SM)
+// live in shared memory and not in registers; consumers wait on a slot's full barrier, run kG rows
+// of the 3x3 stencil in rolling ("scatter") form on registers with straight-line code, and release
+// the slot through its empty barrier.  No CTA-wide barrier in the loop.
+//
+// The per-row consumer code is branch-free:
+//   * padded rows: reflect / replicate rows are fetched from the mapped source row by the producer;
+//     zero rows are read from a permanently-zero row buffer (pointer select);
+//   * padded columns: the two image-edge lanes read their outside neighbour from a per-thread
+//     precomputed shared-memory index (own pixel for reflect / replicate, a zero word for zeros);
+//   * crop, warm-up rows and lanes beyond W are float masks folded into the accumulation;
+//   * rho on the conv side is folded into the 9 weights once per item.
 //
 //   forward   r = clipY(sY*(K(*)pred)) - clipA(sA*obs), |r| or Charbonnier, fp64 partial per warp
 //             and item, fixed-order finalize in the last CTA (bitwise reproducible).
@@ -19,22 +24,28 @@
 //             (mirror / edge fold) is applied in-register on the image-edge lanes and through two
 //             virtual rows on the first / last chunk of a plane.
 #include "phys_common.cuh"
+#include <type_traits>
+
 #include "tma.cuh"
 
 namespace llie {
 
-constexpr int kRing = 12;            // row slots per CTA
+constexpr int kG = 4;                // rows per ring slot (one mbarrier pair per slot)
+constexpr int kSlots = 3;            // ring depth
 constexpr int kCons = 128;           // consumer threads (4 warps side by side = 512 columns)
 constexpr int kRingThreads = kCons + 32;
 constexpr int kCols = kCons * 4;     // 512
-constexpr int kRowF = kCols + 8;     // floats per halo'd row segment: columns x0-4 .. x0+515
-constexpr int kSlotF = 2 * kRowF;    // pred segment + obs segment
+constexpr int kRowD = kCols + 8;     // data floats per halo'd row segment: columns x0-4 .. x0+515
+constexpr int kRowF = kRowD + 4;     // + 4 always-zero floats (index kRowD = "the zero word")
+constexpr int kPairF = 2 * kRowF;    // pred row + obs row
+constexpr int kSlotF = kG * kPairF;
 constexpr int kCtasPerSM = 4;
+constexpr size_t kRingSmem = ((size_t)kSlots * kSlotF + kRowF) * sizeof(float);  // ring + zero row
 
 struct RingGeom {
     int groups, chunks;  // column groups of 512 px, row chunks per plane (even split of H)
     int items, items_per_sample;
-    double *part;  // [items][4] per-warp partial sums
+    double *part;  // [items] per-item partial sums
     double *samp;  // [n] per-sample sums (finalize scratch)
     int *pflag;    // [gridDim.x]
 };
@@ -82,53 +93,6 @@ __device__ __forceinline__ int src_row(int r, int H, int mode) {
     return -1;
 }
 
-// One ring entry = (pred row pr, obs row orow), either may be absent (-1).  Producer side.
-__device__ __forceinline__ void produce(float *slot, uint64_t *full, const float *pred_plane, const float *obs_plane,
-                                        int pr, int orow, int x0, int W) {
-    const int cs = x0 - 4 < 0 ? 0 : x0 - 4;
-    const int ce = x0 + kCols + 4 > W ? W : x0 + kCols + 4;
-    const uint32_t bytes = (uint32_t)(ce - cs) * 4u;
-    const int doff = cs - (x0 - 4);
-    const uint32_t total = (pr >= 0 ? bytes : 0u) + (orow >= 0 ? bytes : 0u);
-    mbar_expect_tx(full, total);
-    if (pr >= 0) bulk_g2s(slot + doff, pred_plane + (long long)pr * W + cs, bytes, full);
-    if (orow >= 0) bulk_g2s(slot + kRowF + doff, obs_plane + (long long)orow * W + cs, bytes, full);
-}
-
-template <bool ROBUST, bool CLIPY, bool CLIPA>
-__device__ __forceinline__ float loss_r(float conv, float a, float ry, float ra, float eps2) {
-    float y = conv * ry, t = a * ra;
-    if (CLIPY) y = fminf(fmaxf(y, 0.f), 1.f);
-    if (CLIPA) t = fminf(fmaxf(t, 0.f), 1.f);
-    const float r = y - t;
-    return ROBUST ? sqrtf(fmaf(r, r, eps2)) : fabsf(r);
-}
-template <bool CLIPY, bool CLIPA>
-__device__ __forceinline__ float absres_r(float conv, float a, float ry, float ra) {
-    float y = conv * ry, t = a * ra;
-    if (CLIPY) y = fminf(fmaxf(y, 0.f), 1.f);
-    if (CLIPA) t = fminf(fmaxf(t, 0.f), 1.f);
-    return fabsf(y - t);
-}
-// upstream-weighted derivative of the loss w.r.t. conv; gs = g_n * (rho if rho scales the conv side)
-template <bool ROBUST, bool CLIPY, bool CLIPA>
-__device__ __forceinline__ float dloss_r(float conv, float a, float ry, float ra, float eps2, float gs) {
-    float y = conv * ry, t = a * ra;
-    bool pass = true;
-    if (CLIPY) {
-        pass = (y >= 0.f) && (y <= 1.f);  // torch.clamp backward: gradient where lo <= y <= hi
-        y = fminf(fmaxf(y, 0.f), 1.f);
-    }
-    if (CLIPA) t = fminf(fmaxf(t, 0.f), 1.f);
-    const float r = y - t;
-    float q;
-    if (ROBUST)
-        q = gs * (r / sqrtf(fmaf(r, r, eps2)));
-    else
-        q = (r > 0.f) ? gs : ((r < 0.f) ? -gs : 0.f);
-    return pass ? q : 0.f;
-}
-
 // Rolling ("scatter") form of the 9-tap chain over NC output columns; r has NC + 2 entries (one
 // neighbour on each side).  When input row rho arrives it completes output row rho-1 (kernel row
 // 2), extends output row rho (kernel row 1) and opens output row rho+1 (kernel row 0).  The
@@ -153,16 +117,58 @@ __device__ __forceinline__ void roll3(const float (&r)[NC + 2], const float (&w)
     }
 }
 
+// fminf / fmaxf drop NaN: non-finite values are caught by the chk_* accumulators before the clip
+__device__ __forceinline__ float clamp01(float v) { return fminf(fmaxf(v, 0.f), 1.f); }
+
 struct RingState {
     int slot;
     uint32_t phase;
     __device__ __forceinline__ void advance() {
-        if (++slot == kRing) {
+        if (++slot == kSlots) {
             slot = 0;
             phase ^= 1u;
         }
     }
 };
+
+// common prologue: zero the ring (stale words are read by masked lanes / rows and must be finite),
+// the zero row and the zero words; init the barriers
+__device__ __forceinline__ void ring_setup(float *ring, uint64_t *full, uint64_t *empty) {
+    float4 *r4 = reinterpret_cast<float4 *>(ring);
+    const int n4 = (int)(kRingSmem / 16);
+    for (int i = threadIdx.x; i < n4; i += kRingThreads) r4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kSlots; ++s) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], kCons / 32);
+        }
+        mbar_fence_init();
+    }
+    fence_proxy_async();  // generic-proxy zero fill before the async-proxy (TMA) writes
+    __syncthreads();
+}
+
+// Producer: fill one slot.  rows[u] = (pred source row or -1, obs row or -1) for u < kG.
+struct SlotRows {
+    int pr[kG], orow[kG];
+};
+__device__ __forceinline__ void produce_slot(float *slot, uint64_t *full, const float *pred_plane,
+                                             const float *obs_plane, const SlotRows &sr, int x0, int W) {
+    const int cs = x0 - 4 < 0 ? 0 : x0 - 4;
+    const int ce = x0 + kCols + 4 > W ? W : x0 + kCols + 4;
+    const uint32_t bytes = (uint32_t)(ce - cs) * 4u;
+    const int doff = cs - (x0 - 4);
+    uint32_t total = 0;
+#pragma unroll
+    for (int u = 0; u < kG; ++u) total += (sr.pr[u] >= 0 ? bytes : 0u) + (sr.orow[u] >= 0 ? bytes : 0u);
+    mbar_expect_tx(full, total);
+#pragma unroll
+    for (int u = 0; u < kG; ++u) {
+        float *dst = slot + u * kPairF + doff;
+        if (sr.pr[u] >= 0) bulk_g2s(dst, pred_plane + (long long)sr.pr[u] * W + cs, bytes, full);
+        if (sr.orow[u] >= 0) bulk_g2s(dst + kRowF, obs_plane + (long long)sr.orow[u] * W + cs, bytes, full);
+    }
+}
 
 // Thread 0 publishes the CTA's results; returns true in ALL threads of the last CTA to arrive.
 __device__ __forceinline__ bool ring_last_block(unsigned *ticket, unsigned total_blocks) {
@@ -181,33 +187,56 @@ __device__ __forceinline__ bool ring_last_block(unsigned *ticket, unsigned total
     return s_last;
 }
 
-// last CTA: per-sample sums by one warp per sample (all loads of a pass in flight together),
-// fixed summation order -> bitwise reproducible
-__device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i) {
+// last CTA: fixed-order per-sample sums of the per-item partials.  Many samples: one warp per sample
+// (samples in flight together); few samples: the whole CTA per sample with 8 loads in flight per
+// thread.  Either way the summation order only depends on the launch geometry.
+__device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, double *red_d) {
     const int N = a.d.n;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    const int per = g.items_per_sample * 4;
-    for (int n = wrp; n < N; n += nw) {
-        const double *p = g.part + (size_t)n * per;
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-        int b = lane;
-        for (; b + 96 < per; b += 128) {
-            s0 += __ldcg(p + b);
-            s1 += __ldcg(p + b + 32);
-            s2 += __ldcg(p + b + 64);
-            s3 += __ldcg(p + b + 96);
+    const int per = g.items_per_sample;
+    if (N >= nw) {
+        for (int n = wrp; n < N; n += nw) {
+            const double *p = g.part + (size_t)n * per;
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int b = lane;
+            for (; b + 96 < per; b += 128) {
+                s0 += __ldcg(p + b);
+                s1 += __ldcg(p + b + 32);
+                s2 += __ldcg(p + b + 64);
+                s3 += __ldcg(p + b + 96);
+            }
+            for (; b < per; b += 32) s0 += __ldcg(p + b);
+            const double s = warp_sum((s0 + s1) + (s2 + s3));
+            if (lane == 0) g.samp[n] = s;
         }
-        for (; b < per; b += 32) s0 += __ldcg(p + b);
-        const double s = warp_sum((s0 + s1) + (s2 + s3));
-        if (lane == 0) g.samp[n] = s;
+    } else {
+        const int NT = blockDim.x;
+        for (int n = 0; n < N; ++n) {
+            const double *p = g.part + (size_t)n * per;
+            double acc[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] = 0.0;
+            int b = threadIdx.x;
+            for (; b + 7 * NT < per; b += 8 * NT) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] += __ldcg(p + b + k * NT);
+            }
+            for (int k = 0; b < per; b += NT, ++k) acc[k & 7] += __ldcg(p + b);
+            const double s = block_sum<double, false>(((acc[0] + acc[1]) + (acc[2] + acc[3])) +
+                                                          ((acc[4] + acc[5]) + (acc[6] + acc[7])), red_d);
+            if (threadIdx.x == 0) g.samp[n] = s;
+        }
     }
     int fl = 0;
     for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) fl |= __ldcg(g.pflag + b);
     const int ff = block_or(fl, red_i);  // contains the __syncthreads that publishes samp[]
     if (threadIdx.x == 0) {
         double batch = 0.0, total = 0.0;
+        int f = ff;
         for (int n = 0; n < N; ++n) {
             const double s = g.samp[n];
+            // an un-clipped non-finite input surfaces as a non-finite sum (source unknown: bit 2)
+            if ((__double2hiint(s) & 0x7ff00000) == 0x7ff00000) f |= 4;
             const float m = (float)(s * a.inv_count);
             a.out_mean[n] = m;
             if (a.out_sum) a.out_sum[n] = s;
@@ -217,33 +246,38 @@ __device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i) 
         a.out_mean[N] = (float)(batch / N);
         a.out_mean[N + 1] = (float)batch;
         if (a.out_sum) a.out_sum[N] = total;
-        *a.out_flags = ff;
+        *a.out_flags = f;
     }
 }
 
+// per-thread shared-memory indices of the horizontal neighbours (see header comment)
+__device__ __forceinline__ void edge_indices(int tid, bool is_left, bool is_right, int mode, int &lidx, int &ridx) {
+    lidx = 4 * tid + 3;
+    ridx = 4 * tid + 8;
+    if (is_left) lidx = mode == LLIE_PAD_REFLECT ? 4 * tid + 5 : (mode == LLIE_PAD_REPLICATE ? 4 * tid + 4 : kRowD);
+    if (is_right) ridx = mode == LLIE_PAD_REFLECT ? 4 * tid + 6 : (mode == LLIE_PAD_REPLICATE ? 4 * tid + 7 : kRowD);
+}
+
 // ------------------------------------------------------------------------------------------------
-// forward
+// forward.  Entry e of an item: pred row ya-1+e (mapped), obs row ya-2+e (for e >= 2); it completes
+// output row ya-2+e.  E = rows + 2 entries, kG entries per slot.
 // ------------------------------------------------------------------------------------------------
 template <bool ROBUST, bool CLIPY, bool CLIPA>
 __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const PhysArgs a, const RingGeom g) {
     extern __shared__ __align__(128) unsigned char smraw[];
     float *ring = reinterpret_cast<float *>(smraw);
-    __shared__ uint64_t full[kRing], empty[kRing];
+    const float *zrow = ring + kSlots * kSlotF;
+    __shared__ uint64_t full[kSlots], empty[kSlots];
     __shared__ int red_i[32];
+    __shared__ double red_d[32];
+    __shared__ double red_w[8];
     const llie_phys_desc &d = a.d;
     const int H = d.h, W = d.w, mode = d.pad_mode;
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+    ring_setup(ring, full, empty);
+    int iter = 0;
 
-    if (tid == 0) {
-        for (int s = 0; s < kRing; ++s) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], kCons / 32);
-        }
-        mbar_fence_init();
-    }
-    __syncthreads();
-
-    float chk_p = 0.f, chk_o = 0.f;  // x*0 accumulators: NaN iff a non-finite value was read
+    float chk_p = 0.f, chk_o = 0.f;  // x*0 accumulators: NaN iff a non-finite value went through a clip
     RingState rs{0, 0u};
 
     if (wrp == kCons / 32) {
@@ -253,12 +287,17 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
                 const Item it = decode_item(item, g, d.c_out, H);
                 const float *pplane = a.pred + (long long)it.plane * H * W;
                 const float *oplane = a.obs + (long long)it.plane * H * W;
-                // entry e: pred row ya-1+e (mapped), obs row ya-2+e (for e >= 2)
                 const int E = it.yb - it.ya + 2;
-                for (int e = 0; e < E; ++e) {
+                for (int e0 = 0; e0 < E; e0 += kG) {
+                    SlotRows sr;
+#pragma unroll
+                    for (int u = 0; u < kG; ++u) {
+                        const int e = e0 + u;
+                        sr.pr[u] = e < E ? src_row(it.ya - 1 + e, H, mode) : -1;
+                        sr.orow[u] = (e < E && e >= 2) ? it.ya - 2 + e : -1;
+                    }
                     mbar_wait(&empty[rs.slot], rs.phase ^ 1u);
-                    produce(ring + rs.slot * kSlotF, &full[rs.slot], pplane, oplane, src_row(it.ya - 1 + e, H, mode),
-                            e >= 2 ? it.ya - 2 + e : -1, it.x0, W);
+                    produce_slot(ring + rs.slot * kSlotF, &full[rs.slot], pplane, oplane, sr, it.x0, W);
                     rs.advance();
                 }
             }
@@ -269,80 +308,99 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
             const Item it = decode_item(item, g, d.c_out, H);
             const int xr = it.x0 + tid * 4;
             const bool active = xr < W;
-            const int x = active ? xr : W - 4;
-            const bool is_left = xr == 0, is_right = xr + 4 == W;
-            float w[9];
-#pragma unroll
-            for (int q = 0; q < 9; ++q) w[q] = __ldg(a.psf + it.c * 9 + q);
+            int lidx, ridx;
+            edge_indices(tid, xr == 0, xr + 4 == W, mode, lidx, ridx);
             const float rho = (a.rho == nullptr)
                                   ? d.rho_scalar
                                   : __ldg(a.rho + (long long)it.n * d.rho_sn + (long long)it.c * d.rho_sc);
             const float ry = d.rho_side == 0 ? rho : 1.f, ra = d.rho_side == 1 ? rho : 1.f;
+            float w[9];  // rho on the conv side is folded into the weights
+#pragma unroll
+            for (int q = 0; q < 9; ++q) w[q] = __ldg(a.psf + it.c * 9 + q) * ry;
             const float eps2 = d.eps * d.eps;
             float cm[4];  // 1 where the column belongs to the compared domain of an active lane
 #pragma unroll
             for (int i = 0; i < 4; ++i) cm[i] = (active && xr + i >= a.x_lo && xr + i < a.x_lo + a.wo) ? 1.f : 0.f;
+            const bool map_on = a.out_map != nullptr && active;
             const bool map_vec = (a.wo & 3) == 0 && a.x_lo == 0;
             float sA[4] = {0.f, 0.f, 0.f, 0.f}, sB[4] = {0.f, 0.f, 0.f, 0.f};
             float acc = 0.f;
             const int E = it.yb - it.ya + 2;
-            for (int e = 0; e < E; ++e) {
-                const int prow = it.ya - 1 + e;  // pred row of this entry; completes output row prow-1
-                const float *sp = ring + rs.slot * kSlotF;
-                mbar_wait(&full[rs.slot], rs.phase);
-                float4 v = make_float4(0.f, 0.f, 0.f, 0.f), ob = v;
-                float l = 0.f, r = 0.f;
-                if (src_row(prow, H, mode) >= 0) {  // CTA-uniform; absent rows are zeros
-                    v = reinterpret_cast<const float4 *>(sp)[tid + 1];
-                    l = sp[4 * tid + 3];
-                    r = sp[4 * tid + 8];
-                }
-                if (e >= 2) ob = reinterpret_cast<const float4 *>(sp + kRowF)[tid + 1];
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&empty[rs.slot]);
-                rs.advance();
-
-                if (!active) {  // lanes beyond W read stale smem
-                    v = make_float4(0.f, 0.f, 0.f, 0.f);
-                    ob = v;
-                    l = r = 0.f;
-                }
-                if (is_left) l = mode == LLIE_PAD_REFLECT ? v.y : (mode == LLIE_PAD_REPLICATE ? v.x : 0.f);
-                if (is_right) r = mode == LLIE_PAD_REFLECT ? v.z : (mode == LLIE_PAD_REPLICATE ? v.w : 0.f);
-                const float r6[6] = {l, v.x, v.y, v.z, v.w, r};
-                chk_p = fmaf(v.x, 0.f, chk_p);
-                chk_p = fmaf(v.y, 0.f, chk_p);
-                chk_p = fmaf(v.z, 0.f, chk_p);
-                chk_p = fmaf(v.w, 0.f, chk_p);
-                float cv[4];
-                roll3<4>(r6, w, sA, sB, cv);
-                if (e >= 2) {  // CTA-uniform
-                    const int y = prow - 1;
+            // one slot = kG entries.  GENERAL handles partial slots, zero-padding rows, warm-up and
+            // cropped rows; the interior slots of an item (all rows real, in-domain) take the lean path.
+            auto do_slot = [&](auto general_tag, int e0, const float *sp) {
+                constexpr bool GENERAL = decltype(general_tag)::value;
+#pragma unroll
+                for (int u = 0; u < kG; ++u) {
+                    const int e = e0 + u;
+                    if (GENERAL && e >= E) break;  // CTA-uniform (only the last slot of an item is partial)
+                    const int y = it.ya - 2 + e;   // output row completed by this entry (pred row y+1)
+                    const float *rowp = sp + u * kPairF;
+                    const float *pz = rowp;
+                    float rowmask = 1.f;
+                    if (GENERAL) {
+                        if (src_row(y + 1, H, mode) < 0) pz = zrow;
+                        rowmask = (e >= 2 && y >= a.y_lo && y < a.y_lo + a.ho) ? 1.f : 0.f;
+                    }
+                    const float4 v = reinterpret_cast<const float4 *>(pz)[tid + 1];
+                    const float r6[6] = {pz[lidx], v.x, v.y, v.z, v.w, pz[ridx]};
+                    const float4 ob = reinterpret_cast<const float4 *>(rowp + kRowF)[tid + 1];
+                    float cv[4];
+                    roll3<4>(r6, w, sA, sB, cv);
                     const float av[4] = {ob.x, ob.y, ob.z, ob.w};
+                    float mv[4], racc = 0.f;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) chk_o = fmaf(av[i], 0.f, chk_o);
-                    if (y >= a.y_lo && y < a.y_lo + a.ho) {  // CTA-uniform
+                    for (int i = 0; i < 4; ++i) {
+                        float yv = cv[i], t = av[i] * ra;
+                        if (CLIPY) {
+                            chk_p = fmaf(yv, 0.f, chk_p);
+                            yv = clamp01(yv);
+                        }
+                        if (CLIPA) {
+                            chk_o = fmaf(t, 0.f, chk_o);
+                            t = clamp01(t);
+                        }
+                        const float r = yv - t;
+                        mv[i] = fabsf(r);
+                        racc = fmaf(ROBUST ? sqrtf(fmaf(r, r, eps2)) : mv[i], cm[i], racc);
+                    }
+                    acc = GENERAL ? fmaf(racc, rowmask, acc) : acc + racc;
+                    if (map_on && rowmask != 0.f) {
+                        float *mrow = a.out_map + (((long long)it.plane) * a.ho + (y - a.y_lo)) * a.wo;
+                        if (map_vec) {
+                            *reinterpret_cast<float4 *>(mrow + xr) = make_float4(mv[0], mv[1], mv[2], mv[3]);
+                        } else {
 #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            acc = fmaf(loss_r<ROBUST, CLIPY, CLIPA>(cv[i], av[i], ry, ra, eps2), cm[i], acc);
-                        if (a.out_map != nullptr && active) {
-                            float mv[4];
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) mv[i] = absres_r<CLIPY, CLIPA>(cv[i], av[i], ry, ra);
-                            float *mrow = a.out_map + (((long long)it.plane) * a.ho + (y - a.y_lo)) * a.wo;
-                            if (map_vec) {
-                                *reinterpret_cast<float4 *>(mrow + x) = make_float4(mv[0], mv[1], mv[2], mv[3]);
-                            } else {
-#pragma unroll
-                                for (int i = 0; i < 4; ++i)
-                                    if (cm[i] != 0.f) mrow[x + i - a.x_lo] = mv[i];
-                            }
+                            for (int i = 0; i < 4; ++i)
+                                if (cm[i] != 0.f) mrow[xr + i - a.x_lo] = mv[i];
                         }
                     }
                 }
+            };
+            // entries [e_lo, e_hi) are interior: real pred rows, e >= 2, output row inside the domain
+            const int y_first = it.ya > a.y_lo ? it.ya : a.y_lo;  // first compared output row of the item
+            int y_end = it.yb < a.y_lo + a.ho ? it.yb : a.y_lo + a.ho;
+            if (y_end > H - 1) y_end = H - 1;                      // pred row y+1 must be a real row
+            const int e_lo = y_first - it.ya + 2, e_hi = y_end - it.ya + 2;
+            for (int e0 = 0; e0 < E; e0 += kG) {
+                const float *sp = ring + rs.slot * kSlotF;
+                mbar_wait(&full[rs.slot], rs.phase);
+                if (e0 >= e_lo && e0 + kG <= e_hi)
+                    do_slot(std::false_type{}, e0, sp);
+                else
+                    do_slot(std::true_type{}, e0, sp);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&empty[rs.slot]);
+                rs.advance();
             }
+            // one partial per item: the 4 consumer warps meet on named barrier 1 (red_w is double-
+            // buffered by item parity, so one barrier per item suffices)
             const double ws = warp_sum((double)acc);
-            if (lane == 0) g.part[(size_t)item * 4 + wrp] = ws;
+            double *rw = red_w + (iter & 1) * 4;
+            if (lane == 0) rw[wrp] = ws;
+            asm volatile("bar.sync 1, %0;" ::"n"(kCons) : "memory");
+            if (tid == 0) g.part[item] = (rw[0] + rw[1]) + (rw[2] + rw[3]);
+            ++iter;
         }
     }
 
@@ -351,37 +409,31 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
     if (!(chk_o == 0.f)) flag |= 2;
     const int f = block_or(flag, red_i);
     if (tid == 0) g.pflag[blockIdx.x] = f;
-    if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i);
+    if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i, red_d);
 }
 
 // ------------------------------------------------------------------------------------------------
-// backward: grad = padY^T K^T q,  q = g_n * dLoss/dconv on the compared domain (0 elsewhere)
+// backward: grad = padY^T K^T q,  q = g_n * dLoss/dconv on the compared domain (0 elsewhere).
+// An item emits the (virtual) grad rows ja .. jb-1; the first / last chunk of a plane also produce
+// the padded rows -1 / H.  Entry k (k = 0 .. jb-ja+3) is j = ja-4+k: it carries pred row j+2 and obs
+// row j+1, completes conv / q row j+1 and grad row j.  The first two entries only warm up the conv
+// partial sums (q forced to 0 by the row mask), the next two the grad partial sums.
 // ------------------------------------------------------------------------------------------------
 template <bool ROBUST, bool CLIPY, bool CLIPA>
 __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const PhysArgs a, const RingGeom g) {
     extern __shared__ __align__(128) unsigned char smraw[];
     float *ring = reinterpret_cast<float *>(smraw);
-    __shared__ uint64_t full[kRing], empty[kRing];
+    const float *zrow = ring + kSlots * kSlotF;
+    __shared__ uint64_t full[kSlots], empty[kSlots];
     const llie_phys_desc &d = a.d;
     const int H = d.h, W = d.w, mode = d.pad_mode;
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
     const bool fold = mode != LLIE_PAD_ZEROS;
     const int fold_top = mode == LLIE_PAD_REFLECT ? 1 : 0;          // image row that padded row -1 reads
     const int fold_bot = mode == LLIE_PAD_REFLECT ? H - 2 : H - 1;  // image row that padded row H reads
-
-    if (tid == 0) {
-        for (int s = 0; s < kRing; ++s) {
-            mbar_init(&full[s], 1);
-            mbar_init(&empty[s], kCons / 32);
-        }
-        mbar_fence_init();
-    }
-    __syncthreads();
+    ring_setup(ring, full, empty);
     RingState rs{0, 0u};
 
-    // An item emits the (virtual) grad rows ja .. jb-1; the first / last chunk of a plane also produce
-    // the padded rows -1 / H.  Entry j (j = ja-4 .. jb-1) carries pred row j+2 and obs row j+1; the
-    // first two entries only warm up the conv partial sums, the next two the grad partial sums.
     if (wrp == kCons / 32) {
         if (lane == 0) {
             for (int item = blockIdx.x; item < g.items; item += gridDim.x) {
@@ -390,12 +442,17 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                 const float *oplane = a.obs + (long long)it.plane * H * W;
                 const int ja = (it.first && fold) ? -1 : it.ya;
                 const int jb = (it.last && fold) ? H + 1 : it.yb;
-                for (int j = ja - 4; j < jb; ++j) {
-                    const int qr = j + 1;  // q row this entry completes
-                    const bool need_obs = j >= ja - 2 && qr >= a.y_lo && qr < a.y_lo + a.ho;
+                const int E = jb - ja + 4;
+                for (int k0 = 0; k0 < E; k0 += kG) {
+                    SlotRows sr;
+#pragma unroll
+                    for (int u = 0; u < kG; ++u) {
+                        const int k = k0 + u, j = ja - 4 + k, qr = j + 1;
+                        sr.pr[u] = k < E ? src_row(j + 2, H, mode) : -1;
+                        sr.orow[u] = (k < E && k >= 2 && qr >= a.y_lo && qr < a.y_lo + a.ho) ? qr : -1;
+                    }
                     mbar_wait(&empty[rs.slot], rs.phase ^ 1u);
-                    produce(ring + rs.slot * kSlotF, &full[rs.slot], pplane, oplane, src_row(j + 2, H, mode),
-                            need_obs ? qr : -1, it.x0, W);
+                    produce_slot(ring + rs.slot * kSlotF, &full[rs.slot], pplane, oplane, sr, it.x0, W);
                     rs.advance();
                 }
             }
@@ -409,23 +466,31 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         const bool active = xr < W;
         const int x = active ? xr : W - 4;
         const bool is_left = xr == 0, is_right = xr + 4 == W;
+        // what the image-edge lanes substitute for their outside neighbour (1: .y/.z  2: .x/.w  3: zero)
+        const int lsel = is_left ? (mode == LLIE_PAD_REFLECT ? 1 : (mode == LLIE_PAD_REPLICATE ? 2 : 3)) : 0;
+        const int rsel = is_right ? (mode == LLIE_PAD_REFLECT ? 1 : (mode == LLIE_PAD_REPLICATE ? 2 : 3)) : 0;
         const int ja = (it.first && fold) ? -1 : it.ya;
         const int jb = (it.last && fold) ? H + 1 : it.yb;
         float *gp = a.grad + (long long)it.plane * H * W + x;
-        float w[9], wf[9];
-#pragma unroll
-        for (int q = 0; q < 9; ++q) w[q] = __ldg(a.psf + it.c * 9 + q);
-#pragma unroll
-        for (int q = 0; q < 9; ++q) wf[q] = w[8 - q];
         const float rho = (a.rho == nullptr)
                               ? d.rho_scalar
                               : __ldg(a.rho + (long long)it.n * d.rho_sn + (long long)it.c * d.rho_sc);
         const float ry = d.rho_side == 0 ? rho : 1.f, ra = d.rho_side == 1 ? rho : 1.f;
-        const float eps2 = d.eps * d.eps;
-        const float gs = __ldg(a.gout + a.gout_stride * it.n) * a.gscale * ry;
-        bool colok[6];  // columns x-1 .. x+4 inside the compared domain
+        float w[9], wf[9];  // rho on the conv side is folded into the weights (forward and adjoint)
 #pragma unroll
-        for (int i = 0; i < 6; ++i) colok[i] = active && (xr - 1 + i >= a.x_lo) && (xr - 1 + i < a.x_lo + a.wo);
+        for (int q = 0; q < 9; ++q) w[q] = __ldg(a.psf + it.c * 9 + q) * ry;
+#pragma unroll
+        for (int q = 0; q < 9; ++q) wf[q] = w[8 - q];
+        const float eps2 = d.eps * d.eps;
+        const float gs = __ldg(a.gout + a.gout_stride * it.n) * a.gscale;
+        float qm[6];  // gs where column x-1+i is inside the compared domain, else 0
+#pragma unroll
+        for (int i = 0; i < 6; ++i)
+            qm[i] = (active && (xr - 1 + i >= a.x_lo) && (xr - 1 + i < a.x_lo + a.wo)) ? gs : 0.f;
+        // edge-fold weights (image-edge lanes): column -1 gets K[.][0] q(., 0), column W gets K[.][2] q(., W-1)
+        const float k0 = is_left ? w[0] : w[2], k1 = is_left ? w[3] : w[5], k2 = is_left ? w[6] : w[8];
+        const int tgt = is_left ? (mode == LLIE_PAD_REFLECT ? 1 : 0) : (mode == LLIE_PAD_REFLECT ? 2 : 3);
+        const bool edge_fold = fold && (is_left || is_right);
 
         float cA[6], cB[6];
 #pragma unroll
@@ -433,89 +498,93 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         float gA[4] = {0.f, 0.f, 0.f, 0.f}, gB[4] = {0.f, 0.f, 0.f, 0.f};
         float eA = 0.f, eB = 0.f;  // partial sums of the folded padded column (image-edge lanes only)
         float carry[4] = {0.f, 0.f, 0.f, 0.f};
+        const int E = jb - ja + 4;
 
-        for (int j = ja - 4; j < jb; ++j) {
-            const int prow = j + 2, qr = j + 1;
-            const bool have_q = j >= ja - 2 && qr >= a.y_lo && qr < a.y_lo + a.ho;  // CTA-uniform
+        for (int k0e = 0; k0e < E; k0e += kG) {
             const float *sp = ring + rs.slot * kSlotF;
             mbar_wait(&full[rs.slot], rs.phase);
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f), ob = v;
-            float2 pl = make_float2(0.f, 0.f), pr = pl;
-            float ol = 0.f, orr = 0.f;
-            if (src_row(prow, H, mode) >= 0) {
-                v = reinterpret_cast<const float4 *>(sp)[tid + 1];
-                pl = reinterpret_cast<const float2 *>(sp)[2 * tid + 1];
-                pr = reinterpret_cast<const float2 *>(sp)[2 * tid + 4];
-            }
-            if (have_q) {
-                const float *so = sp + kRowF;
-                ob = reinterpret_cast<const float4 *>(so)[tid + 1];
-                ol = so[4 * tid + 3];
-                orr = so[4 * tid + 8];
+#pragma unroll
+            for (int u = 0; u < kG; ++u) {
+                const int k = k0e + u;
+                if (k < E) {  // CTA-uniform
+                    const int j = ja - 4 + k, prow = j + 2, qr = j + 1;
+                    const float *rowp = sp + u * kPairF;
+                    const float *pz = src_row(prow, H, mode) >= 0 ? rowp : zrow;
+                    const float4 v = reinterpret_cast<const float4 *>(pz)[tid + 1];
+                    const float2 pl = reinterpret_cast<const float2 *>(pz)[2 * tid + 1];
+                    const float2 pr = reinterpret_cast<const float2 *>(pz)[2 * tid + 4];
+                    const float *so = rowp + kRowF;
+                    const float4 ob = reinterpret_cast<const float4 *>(so)[tid + 1];
+                    const float ol = so[4 * tid + 3], orr = so[4 * tid + 8];
+                    float l1 = pl.y, r0 = pr.x;
+                    l1 = lsel == 1 ? v.y : l1;
+                    l1 = lsel == 2 ? v.x : l1;
+                    l1 = lsel == 3 ? 0.f : l1;
+                    r0 = rsel == 1 ? v.z : r0;
+                    r0 = rsel == 2 ? v.w : r0;
+                    r0 = rsel == 3 ? 0.f : r0;
+                    const float r8[8] = {pl.x, l1, v.x, v.y, v.z, v.w, r0, pr.y};
+                    float cv[6];
+                    roll3<6>(r8, w, cA, cB, cv);  // conv row qr over columns x-1 .. x+4
+                    // q row qr (0 on warm-up entries, outside the compared rows / columns)
+                    const float rowm = (k >= 2 && qr >= a.y_lo && qr < a.y_lo + a.ho) ? 1.f : 0.f;
+                    const float av[6] = {ol, ob.x, ob.y, ob.z, ob.w, orr};
+                    float qc[6];
+#pragma unroll
+                    for (int i = 0; i < 6; ++i) {
+                        float yv = cv[i], t = av[i] * ra;
+                        float m = qm[i] * rowm;
+                        if (CLIPY) {
+                            m = (yv >= 0.f && yv <= 1.f) ? m : 0.f;  // torch.clamp backward passes lo <= y <= hi
+                            yv = clamp01(yv);
+                        }
+                        if (CLIPA) t = clamp01(t);
+                        const float r = yv - t;
+                        float psi;
+                        if (ROBUST)
+                            psi = r / sqrtf(fmaf(r, r, eps2));
+                        else
+                            psi = (r > 0.f) ? 1.f : ((r < 0.f) ? -1.f : 0.f);
+                        qc[i] = (m != 0.f) ? m * psi : 0.f;  // select: stale rows may hold anything finite
+                    }
+                    // ---- grad (virtual) row j: q row j+1 completes it (flipped kernel, rolling form)
+                    float gr[4];
+                    roll3<4>(qc, wf, gA, gB, gr);
+                    if (edge_fold) {
+                        const float qe = is_left ? qc[1] : qc[4];
+                        const float ecol = fmaf(k0, qe, eA);
+                        eA = fmaf(k1, qe, eB);
+                        eB = k2 * qe;
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (i == tgt) gr[i] += ecol;
+                    }
+                    if (k >= 4) {  // CTA-uniform: entries 0..3 are warm-up
+                        if (j == -1) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) carry[i] = gr[i];
+                        } else if (j == H) {
+                            if (active) {
+                                float4 *dst = reinterpret_cast<float4 *>(gp + (long long)fold_bot * W);
+                                float4 t = *dst;  // written by this very thread two / one entries ago
+                                t.x += gr[0]; t.y += gr[1]; t.z += gr[2]; t.w += gr[3];
+                                *dst = t;
+                            }
+                        } else {
+                            if (it.first && fold && j == fold_top) {
+#pragma unroll
+                                for (int i = 0; i < 4; ++i) gr[i] += carry[i];
+                            }
+                            if (active)
+                                *reinterpret_cast<float4 *>(gp + (long long)j * W) =
+                                    make_float4(gr[0], gr[1], gr[2], gr[3]);
+                        }
+                    }
+                }
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[rs.slot]);
             rs.advance();
-
-            if (!active) {  // lanes beyond W read stale smem
-                v = make_float4(0.f, 0.f, 0.f, 0.f);
-                pl = pr = make_float2(0.f, 0.f);
-            }
-            float l0 = pl.x, l1 = pl.y, r0 = pr.x, r1 = pr.y;
-            if (is_left) {  // column -1 is padded; column -2 only feeds a discarded q
-                l1 = mode == LLIE_PAD_REFLECT ? v.y : (mode == LLIE_PAD_REPLICATE ? v.x : 0.f);
-                l0 = 0.f;
-            }
-            if (is_right) {
-                r0 = mode == LLIE_PAD_REFLECT ? v.z : (mode == LLIE_PAD_REPLICATE ? v.w : 0.f);
-                r1 = 0.f;
-            }
-            const float r8[8] = {l0, l1, v.x, v.y, v.z, v.w, r0, r1};
-            float cv[6];
-            roll3<6>(r8, w, cA, cB, cv);  // conv row qr over columns x-1 .. x+4
-            if (j < ja - 2) continue;     // conv warm-up entries (CTA-uniform)
-            float qc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (have_q) {
-                const float av[6] = {ol, ob.x, ob.y, ob.z, ob.w, orr};
-#pragma unroll
-                for (int i = 0; i < 6; ++i)
-                    qc[i] = colok[i] ? dloss_r<ROBUST, CLIPY, CLIPA>(cv[i], av[i], ry, ra, eps2, gs) : 0.f;
-            }
-            // ---- grad (virtual) row j: q row j+1 completes it (flipped kernel, rolling form)
-            float gr[4];
-            roll3<4>(qc, wf, gA, gB, gr);
-            if (fold && (is_left || is_right)) {
-                // padded column -1 (W) = sum_ky K[ky][0] q(j-ky+1, 0)  (K[ky][2] q(.., W-1)), rolling too
-                const float qe = is_left ? qc[1] : qc[4];
-                const float k0 = is_left ? w[0] : w[2], k1 = is_left ? w[3] : w[5], k2 = is_left ? w[6] : w[8];
-                const float ecol = fmaf(k0, qe, eA);
-                eA = fmaf(k1, qe, eB);
-                eB = k2 * qe;
-                // folds onto column 1 / 0 (left: reflect / replicate) or W-2 / W-1 (right)
-                const int tgt = is_left ? (mode == LLIE_PAD_REFLECT ? 1 : 0) : (mode == LLIE_PAD_REFLECT ? 2 : 3);
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (i == tgt) gr[i] += ecol;
-            }
-            if (j < ja) continue;  // grad warm-up entries (CTA-uniform)
-            if (j == -1) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i) carry[i] = gr[i];
-            } else if (j == H) {
-                if (active) {
-                    float4 *dst = reinterpret_cast<float4 *>(gp + (long long)fold_bot * W);
-                    float4 t = *dst;  // written by this very thread two / one iterations ago
-                    t.x += gr[0]; t.y += gr[1]; t.z += gr[2]; t.w += gr[3];
-                    *dst = t;
-                }
-            } else {
-                if (it.first && fold && j == fold_top) {
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) gr[i] += carry[i];
-                }
-                if (active)
-                    *reinterpret_cast<float4 *>(gp + (long long)j * W) = make_float4(gr[0], gr[1], gr[2], gr[3]);
-            }
         }
     }
 }
@@ -561,42 +630,40 @@ bool phys_ring_eligible(const PhysArgs &a) {
     if (items > 0x3fffffffLL) return false;
     int grid;
     const RingGeom g = make_geom(d, grid);
-    const size_t need = (size_t)g.items * 4 * sizeof(double) + (size_t)d.n * sizeof(double) + (size_t)grid * sizeof(int);
+    const size_t need = (size_t)g.items * sizeof(double) + (size_t)d.n * sizeof(double) + (size_t)grid * sizeof(int);
     return need <= kWsBytes - kWsHeaderBytes;
 }
 
-#define LLIE_RING_DISPATCH(KERNEL, d, GRID, SMEM, ST, ...)                                                  \
-    do {                                                                                                    \
-        const int key = ((d).robust ? 4 : 0) | ((d).clip_y ? 2 : 0) | ((d).clip_a ? 1 : 0);                 \
-        switch (key) {                                                                                      \
-            case 0: LLIE_RING_ONE((KERNEL<false, false, false>), GRID, SMEM, ST, __VA_ARGS__); break;       \
-            case 1: LLIE_RING_ONE((KERNEL<false, false, true>), GRID, SMEM, ST, __VA_ARGS__); break;        \
-            case 2: LLIE_RING_ONE((KERNEL<false, true, false>), GRID, SMEM, ST, __VA_ARGS__); break;        \
-            case 3: LLIE_RING_ONE((KERNEL<false, true, true>), GRID, SMEM, ST, __VA_ARGS__); break;         \
-            case 4: LLIE_RING_ONE((KERNEL<true, false, false>), GRID, SMEM, ST, __VA_ARGS__); break;        \
-            case 5: LLIE_RING_ONE((KERNEL<true, false, true>), GRID, SMEM, ST, __VA_ARGS__); break;         \
-            case 6: LLIE_RING_ONE((KERNEL<true, true, false>), GRID, SMEM, ST, __VA_ARGS__); break;         \
-            default: LLIE_RING_ONE((KERNEL<true, true, true>), GRID, SMEM, ST, __VA_ARGS__); break;         \
-        }                                                                                                   \
+#define LLIE_RING_ONE(K, GRID, ST, ...)                                                                          \
+    do {                                                                                                         \
+        auto kern = K;                                                                                           \
+        LLIE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem));   \
+        kern<<<GRID, kRingThreads, kRingSmem, ST>>>(__VA_ARGS__);                                                \
     } while (0)
-#define LLIE_RING_ONE(K, GRID, SMEM, ST, ...)                                                               \
-    do {                                                                                                    \
-        auto kern = K;                                                                                      \
-        LLIE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(SMEM))); \
-        kern<<<GRID, kRingThreads, SMEM, ST>>>(__VA_ARGS__);                                                \
+#define LLIE_RING_DISPATCH(KERNEL, d, GRID, ST, ...)                                               \
+    do {                                                                                           \
+        const int key = ((d).robust ? 4 : 0) | ((d).clip_y ? 2 : 0) | ((d).clip_a ? 1 : 0);        \
+        switch (key) {                                                                             \
+            case 0: LLIE_RING_ONE((KERNEL<false, false, false>), GRID, ST, __VA_ARGS__); break;    \
+            case 1: LLIE_RING_ONE((KERNEL<false, false, true>), GRID, ST, __VA_ARGS__); break;     \
+            case 2: LLIE_RING_ONE((KERNEL<false, true, false>), GRID, ST, __VA_ARGS__); break;     \
+            case 3: LLIE_RING_ONE((KERNEL<false, true, true>), GRID, ST, __VA_ARGS__); break;      \
+            case 4: LLIE_RING_ONE((KERNEL<true, false, false>), GRID, ST, __VA_ARGS__); break;     \
+            case 5: LLIE_RING_ONE((KERNEL<true, false, true>), GRID, ST, __VA_ARGS__); break;      \
+            case 6: LLIE_RING_ONE((KERNEL<true, true, false>), GRID, ST, __VA_ARGS__); break;      \
+            default: LLIE_RING_ONE((KERNEL<true, true, true>), GRID, ST, __VA_ARGS__); break;      \
+        }                                                                                          \
     } while (0)
-
-constexpr size_t kRingSmem = (size_t)kRing * kSlotF * sizeof(float);
 
 int launch_phys_fwd_ring(PhysArgs &a, void *workspace, cudaStream_t st) {
     int grid;
     RingGeom g = make_geom(a.d, grid);
     Workspace ws(workspace);
     g.part = reinterpret_cast<double *>(ws.scratch);
-    g.samp = g.part + (size_t)g.items * 4;
+    g.samp = g.part + (size_t)g.items;
     g.pflag = reinterpret_cast<int *>(g.samp + a.d.n);
     a.ticket = ws.tickets;
-    LLIE_RING_DISPATCH(phys_fwd_ring, a.d, grid, kRingSmem, st, a, g);
+    LLIE_RING_DISPATCH(phys_fwd_ring, a.d, grid, st, a, g);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
@@ -604,7 +671,7 @@ int launch_phys_fwd_ring(PhysArgs &a, void *workspace, cudaStream_t st) {
 int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st) {
     int grid;
     const RingGeom g = make_geom(a.d, grid);
-    LLIE_RING_DISPATCH(phys_bwd_ring, a.d, grid, kRingSmem, st, a, g);
+    LLIE_RING_DISPATCH(phys_bwd_ring, a.d, grid, st, a, g);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

@@ -88,6 +88,11 @@ def _core(pred, obs, *, psf, expo_ratio, reduction, padding, normalize_psf, enfo
         vec, flags, amap = Fn.phys_forward(p.detach(), o, prepared, rho_t, rho_s, rho_st, cfg, return_map)
     if flags is not None:
         f = int(flags.item())  # the one host sync (the reference pays two isfinite().all() syncs)
+        if f & 4 and not f & 3:
+            # un-clipped paths detect non-finite inputs through the (non-finite) sum, which cannot say
+            # which tensor it came from: resolve on this error path only
+            f |= 1 if not bool(torch.isfinite(p).all()) else 0
+            f |= 2 if not bool(torch.isfinite(o).all()) else 0
         if f & 1:
             raise ValueError("`pred` contains NaN or Inf values.")
         if f & 2:
