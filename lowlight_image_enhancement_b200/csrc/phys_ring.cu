@@ -191,9 +191,14 @@ __device__ __forceinline__ bool ring_last_block(unsigned *ticket, unsigned total
 // (samples in flight together); few samples: the whole CTA per sample with 8 loads in flight per
 // thread.  Either way the summation order only depends on the launch geometry.
 __device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, double *red_d) {
+    constexpr int kSmemSamples = 64;
+    __shared__ double s_samp[kSmemSamples];
     const int N = a.d.n;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int per = g.items_per_sample;
+    double *samp = N <= kSmemSamples ? s_samp : g.samp;
+    int fl = 0;  // flag loads go first so that they overlap the partial-sum loads
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) fl |= __ldcg(g.pflag + b);
     if (N >= nw) {
         for (int n = wrp; n < N; n += nw) {
             const double *p = g.part + (size_t)n * per;
@@ -207,7 +212,7 @@ __device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, 
             }
             for (; b < per; b += 32) s0 += __ldcg(p + b);
             const double s = warp_sum((s0 + s1) + (s2 + s3));
-            if (lane == 0) g.samp[n] = s;
+            if (lane == 0) samp[n] = s;
         }
     } else {
         const int NT = blockDim.x;
@@ -221,20 +226,18 @@ __device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, 
 #pragma unroll
                 for (int k = 0; k < 8; ++k) acc[k] += __ldcg(p + b + k * NT);
             }
-            for (int k = 0; b < per; b += NT, ++k) acc[k & 7] += __ldcg(p + b);
+            for (; b < per; b += NT) acc[0] += __ldcg(p + b);
             const double s = block_sum<double, false>(((acc[0] + acc[1]) + (acc[2] + acc[3])) +
                                                           ((acc[4] + acc[5]) + (acc[6] + acc[7])), red_d);
-            if (threadIdx.x == 0) g.samp[n] = s;
+            if (threadIdx.x == 0) samp[n] = s;
         }
     }
-    int fl = 0;
-    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) fl |= __ldcg(g.pflag + b);
     const int ff = block_or(fl, red_i);  // contains the __syncthreads that publishes samp[]
     if (threadIdx.x == 0) {
         double batch = 0.0, total = 0.0;
         int f = ff;
         for (int n = 0; n < N; ++n) {
-            const double s = g.samp[n];
+            const double s = samp[n];
             // an un-clipped non-finite input surfaces as a non-finite sum (source unknown: bit 2)
             if ((__double2hiint(s) & 0x7ff00000) == 0x7ff00000) f |= 4;
             const float m = (float)(s * a.inv_count);
@@ -466,9 +469,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         const bool active = xr < W;
         const int x = active ? xr : W - 4;
         const bool is_left = xr == 0, is_right = xr + 4 == W;
-        // what the image-edge lanes substitute for their outside neighbour (1: .y/.z  2: .x/.w  3: zero)
-        const int lsel = is_left ? (mode == LLIE_PAD_REFLECT ? 1 : (mode == LLIE_PAD_REPLICATE ? 2 : 3)) : 0;
-        const int rsel = is_right ? (mode == LLIE_PAD_REFLECT ? 1 : (mode == LLIE_PAD_REPLICATE ? 2 : 3)) : 0;
+        int lidx, ridx;  // smem index of column x-1 / x+4 (own pixel or the zero word on image-edge lanes)
+        edge_indices(tid, is_left, is_right, mode, lidx, ridx);
         const int ja = (it.first && fold) ? -1 : it.ya;
         const int jb = (it.last && fold) ? H + 1 : it.yb;
         float *gp = a.grad + (long long)it.plane * H * W + x;
@@ -500,88 +502,102 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         float carry[4] = {0.f, 0.f, 0.f, 0.f};
         const int E = jb - ja + 4;
 
-        for (int k0e = 0; k0e < E; k0e += kG) {
-            const float *sp = ring + rs.slot * kSlotF;
-            mbar_wait(&full[rs.slot], rs.phase);
+        // GENERAL slots: partial slots, zero-padding rows, warm-up entries, cropped q rows, virtual rows;
+        // interior slots (all pred rows real, q row compared, grad row a plain image row) run lean.
+        auto do_slot = [&](auto general_tag, int kb, const float *sp) {
+            constexpr bool GENERAL = decltype(general_tag)::value;
 #pragma unroll
             for (int u = 0; u < kG; ++u) {
-                const int k = k0e + u;
-                if (k < E) {  // CTA-uniform
-                    const int j = ja - 4 + k, prow = j + 2, qr = j + 1;
-                    const float *rowp = sp + u * kPairF;
-                    const float *pz = src_row(prow, H, mode) >= 0 ? rowp : zrow;
-                    const float4 v = reinterpret_cast<const float4 *>(pz)[tid + 1];
-                    const float2 pl = reinterpret_cast<const float2 *>(pz)[2 * tid + 1];
-                    const float2 pr = reinterpret_cast<const float2 *>(pz)[2 * tid + 4];
-                    const float *so = rowp + kRowF;
-                    const float4 ob = reinterpret_cast<const float4 *>(so)[tid + 1];
-                    const float ol = so[4 * tid + 3], orr = so[4 * tid + 8];
-                    float l1 = pl.y, r0 = pr.x;
-                    l1 = lsel == 1 ? v.y : l1;
-                    l1 = lsel == 2 ? v.x : l1;
-                    l1 = lsel == 3 ? 0.f : l1;
-                    r0 = rsel == 1 ? v.z : r0;
-                    r0 = rsel == 2 ? v.w : r0;
-                    r0 = rsel == 3 ? 0.f : r0;
-                    const float r8[8] = {pl.x, l1, v.x, v.y, v.z, v.w, r0, pr.y};
-                    float cv[6];
-                    roll3<6>(r8, w, cA, cB, cv);  // conv row qr over columns x-1 .. x+4
-                    // q row qr (0 on warm-up entries, outside the compared rows / columns)
-                    const float rowm = (k >= 2 && qr >= a.y_lo && qr < a.y_lo + a.ho) ? 1.f : 0.f;
-                    const float av[6] = {ol, ob.x, ob.y, ob.z, ob.w, orr};
-                    float qc[6];
+                const int k = kb + u;
+                if (GENERAL && k >= E) break;  // CTA-uniform
+                const int j = ja - 4 + k, qr = j + 1;
+                const float *rowp = sp + u * kPairF;
+                const float *pz = rowp;
+                float rowm = 1.f;
+                if (GENERAL) {
+                    if (src_row(j + 2, H, mode) < 0) pz = zrow;
+                    rowm = (k >= 2 && qr >= a.y_lo && qr < a.y_lo + a.ho) ? 1.f : 0.f;
+                }
+                const float4 v = reinterpret_cast<const float4 *>(pz)[tid + 1];
+                const float r8[8] = {pz[4 * tid + 2], pz[lidx], v.x, v.y, v.z, v.w, pz[ridx], pz[4 * tid + 9]};
+                const float *so = rowp + kRowF;
+                const float4 ob = reinterpret_cast<const float4 *>(so)[tid + 1];
+                const float av[6] = {so[4 * tid + 3], ob.x, ob.y, ob.z, ob.w, so[4 * tid + 8]};
+                float cv[6];
+                roll3<6>(r8, w, cA, cB, cv);  // conv row qr over columns x-1 .. x+4
+                float qc[6];
 #pragma unroll
-                    for (int i = 0; i < 6; ++i) {
-                        float yv = cv[i], t = av[i] * ra;
-                        float m = qm[i] * rowm;
-                        if (CLIPY) {
-                            m = (yv >= 0.f && yv <= 1.f) ? m : 0.f;  // torch.clamp backward passes lo <= y <= hi
-                            yv = clamp01(yv);
-                        }
-                        if (CLIPA) t = clamp01(t);
-                        const float r = yv - t;
-                        float psi;
-                        if (ROBUST)
-                            psi = r / sqrtf(fmaf(r, r, eps2));
-                        else
-                            psi = (r > 0.f) ? 1.f : ((r < 0.f) ? -1.f : 0.f);
-                        qc[i] = (m != 0.f) ? m * psi : 0.f;  // select: stale rows may hold anything finite
+                for (int i = 0; i < 6; ++i) {
+                    float yv = cv[i], t = av[i] * ra;
+                    float m = GENERAL ? qm[i] * rowm : qm[i];
+                    if (CLIPY) {
+                        m = (yv >= 0.f && yv <= 1.f) ? m : 0.f;  // torch.clamp backward passes lo <= y <= hi
+                        yv = clamp01(yv);
                     }
-                    // ---- grad (virtual) row j: q row j+1 completes it (flipped kernel, rolling form)
-                    float gr[4];
-                    roll3<4>(qc, wf, gA, gB, gr);
-                    if (edge_fold) {
-                        const float qe = is_left ? qc[1] : qc[4];
-                        const float ecol = fmaf(k0, qe, eA);
-                        eA = fmaf(k1, qe, eB);
-                        eB = k2 * qe;
-#pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (i == tgt) gr[i] += ecol;
+                    if (CLIPA) t = clamp01(t);
+                    const float r = yv - t;
+                    if (ROBUST) {
+                        qc[i] = (m != 0.f) ? m * (r / sqrtf(fmaf(r, r, eps2))) : 0.f;
+                    } else {
+                        // m * sign(r), sign(0) = 0 (stale rows hold finite values; m == 0 masks them)
+                        qc[i] = (r != 0.f) ? copysignf(m, r) : 0.f;
                     }
-                    if (k >= 4) {  // CTA-uniform: entries 0..3 are warm-up
-                        if (j == -1) {
+                }
+                // ---- grad (virtual) row j: q row j+1 completes it (flipped kernel, rolling form)
+                float gr[4];
+                roll3<4>(qc, wf, gA, gB, gr);
+                if (edge_fold) {
+                    const float qe = is_left ? qc[1] : qc[4];
+                    const float ecol = fmaf(k0, qe, eA);
+                    eA = fmaf(k1, qe, eB);
+                    eB = k2 * qe;
 #pragma unroll
-                            for (int i = 0; i < 4; ++i) carry[i] = gr[i];
-                        } else if (j == H) {
-                            if (active) {
-                                float4 *dst = reinterpret_cast<float4 *>(gp + (long long)fold_bot * W);
-                                float4 t = *dst;  // written by this very thread two / one entries ago
-                                t.x += gr[0]; t.y += gr[1]; t.z += gr[2]; t.w += gr[3];
-                                *dst = t;
-                            }
-                        } else {
-                            if (it.first && fold && j == fold_top) {
+                    for (int i = 0; i < 4; ++i)
+                        if (i == tgt) gr[i] += ecol;
+                }
+                if (!GENERAL) {
+                    if (active)
+                        *reinterpret_cast<float4 *>(gp + (long long)j * W) = make_float4(gr[0], gr[1], gr[2], gr[3]);
+                } else if (k >= 4) {  // CTA-uniform: entries 0..3 are warm-up
+                    if (j == -1) {
 #pragma unroll
-                                for (int i = 0; i < 4; ++i) gr[i] += carry[i];
-                            }
-                            if (active)
-                                *reinterpret_cast<float4 *>(gp + (long long)j * W) =
-                                    make_float4(gr[0], gr[1], gr[2], gr[3]);
+                        for (int i = 0; i < 4; ++i) carry[i] = gr[i];
+                    } else if (j == H) {
+                        if (active) {
+                            float4 *dst = reinterpret_cast<float4 *>(gp + (long long)fold_bot * W);
+                            float4 t = *dst;  // written by this very thread two / one entries ago
+                            t.x += gr[0]; t.y += gr[1]; t.z += gr[2]; t.w += gr[3];
+                            *dst = t;
                         }
+                    } else {
+                        if (it.first && fold && j == fold_top) {
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) gr[i] += carry[i];
+                        }
+                        if (active)
+                            *reinterpret_cast<float4 *>(gp + (long long)j * W) =
+                                make_float4(gr[0], gr[1], gr[2], gr[3]);
                     }
                 }
             }
+        };
+        // interior entries: k >= 4, grad row j in [max(ja, fold_top + 1), ...), q row j+1 compared and
+        // pred row j+2 a real image row:  j >= max(0, y_lo - 1, fold_top + 1 if first),  j + 2 <= H - 1,
+        // j + 1 < y_lo + ho
+        int j_lo = ja + 0 > 0 ? ja : 0;
+        if (j_lo < a.y_lo - 1) j_lo = a.y_lo - 1;
+        if (it.first && fold && j_lo < fold_top + 1) j_lo = fold_top + 1;
+        int j_hi = jb < H - 2 ? jb : H - 2;  // exclusive
+        if (j_hi > a.y_lo + a.ho - 1) j_hi = a.y_lo + a.ho - 1;
+        const int k_lo = (j_lo - ja + 4) > 4 ? (j_lo - ja + 4) : 4, k_hi = j_hi - ja + 4;
+
+        for (int kb = 0; kb < E; kb += kG) {
+            const float *sp = ring + rs.slot * kSlotF;
+            mbar_wait(&full[rs.slot], rs.phase);
+            if (kb >= k_lo && kb + kG <= k_hi)
+                do_slot(std::false_type{}, kb, sp);
+            else
+                do_slot(std::true_type{}, kb, sp);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[rs.slot]);
             rs.advance();
@@ -604,9 +620,11 @@ static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     if (g_ring_rows > 0) {
         chunks = d.h / g_ring_rows;
     } else {
-        // items = k * (resident CTA slots) for the smallest k that keeps chunks >= ~24 rows: every
-        // persistent CTA gets the same number of items (no tail wave), rows split evenly
-        long long k = ((long long)d.h * cols + (long long)slots * 24 - 1) / ((long long)slots * 24);
+        // items = k * (resident CTA slots): every persistent CTA gets the same number of items (no
+        // tail wave) and the rows of a plane are split evenly; k aims at ~48-row chunks (warm-up rows
+        // cost 2 (forward) / 4 (backward) extra row reads per chunk), but never leaves slots idle
+        const long long per_k = (long long)slots * 48;
+        long long k = ((long long)d.h * cols + per_k / 2) / per_k;
         if (k < 1) k = 1;
         chunks = (int)((k * slots) / cols);
     }
