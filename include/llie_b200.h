@@ -164,6 +164,72 @@ typedef struct llie_psnr_desc {
 int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const void *y, double *out,
                     void *out_minmax, int32_t *out_flags, void *workspace, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Gaussian / uniform-window SSIM statistics: per-(n, c) float64 sums of the SSIM map (or of the DSSIM
+ * loss map) over the full image or its interior, one fused separable-filter kernel.
+ * replaces metrics/linear.py:213-324 (ssim_linear), metrics/channelwise.py:226-302 (rgb_ssim),
+ *          metrics/ssim.py:246-311 (SSIMEvaluator -> torchmetrics 1.2.0 _ssim_update),
+ *          NewBP_model/losses.py:146-155 (SSIMLoss -> kornia 0.6.12 ssim_loss), forward value.
+ * The K x K window of all three is the outer product of `win1d` (K normalised taps, device memory).
+ * ------------------------------------------------------------------------ */
+#define LLIE_SSIM_MAX_K 15
+typedef struct llie_ssim_desc {
+    int32_t n, c, h, w;   /* c = channels of the input tensors */
+    int32_t ksize;        /* odd, <= LLIE_SSIM_MAX_K, <= min(h, w) */
+    int32_t pad_mode;     /* LLIE_PAD_* (ZEROS == 'constant') */
+    int32_t luma;         /* 1: c == 3 and SSIM runs on 0.2989 R + 0.5870 G + 0.1140 B (ssim.py:116-127) */
+    int32_t clamp_in;     /* clamp both inputs to [0,1] first (losses.py:155) */
+    int32_t clamp_var;    /* sigma_x^2, sigma_y^2 clamped >= 0 (linear.py:307-308) */
+    int32_t interior;     /* 1: reduce over [K/2, H-K/2) x [K/2, W-K/2) only (torchmetrics crop) */
+    int32_t loss_map;     /* 1: reduce clamp((1 - S) / 2, 0, 1) instead of S (kornia ssim_loss) */
+    float c1, c2, eps;    /* (k1 L)^2, (k2 L)^2, denominator eps (0 for torchmetrics) */
+} llie_ssim_desc;
+/*   out_sum   [n * co] doubles, co = luma ? 1 : c;  out_map NULL or [n, co, h, w] SSIM map
+ *   out_flags [1] int: bit0 non-finite in x, bit1 in y */
+int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                    double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream);
+
+/* ------------------------------------------------------------------------
+ * sRGB -> Lab(D65/2deg) -> CIEDE2000, per-image float64 sums (+ optional map / L plane of x).
+ * replaces metrics/color_error.py:68-97,105-210,235-266 (variant 0, metric) and
+ *          NewBP_model/losses.py:99-143 (variant 1, loss: eps 1e-6, inputs clamped to [0,1]).
+ * ------------------------------------------------------------------------ */
+typedef struct llie_deltae_desc {
+    int32_t n, h, w;      /* inputs are [n, 3, h, w] */
+    int32_t variant;      /* 0 metric (color_error.py) | 1 loss (losses.py) */
+    int32_t input_lab;    /* 1: inputs already hold (L, a, b) planes (stage-level parity tests) */
+    int32_t clamp_in;     /* clamp sRGB inputs to [0,1] first (losses.py:140-141) */
+    float kL, kC, kH, eps;
+} llie_deltae_desc;
+/*   out_sum [n] doubles; out_map NULL or [n, h, w]; out_l NULL or [n, h, w] (L of x, for the edge mask) */
+int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum, float *out_map,
+                float *out_l, int32_t *out_flags, void *workspace, void *stream);
+
+/* Sobel magnitude sqrt(gx^2 + gy^2 + 1e-12) of [planes, h, w], zero padding (color_error.py:23-30, 296-301) */
+int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Exact torch.quantile(..., 'linear') by radix select, optionally gated by `gate[i] >= gate_thr[image]`.
+ * replaces the full sorts of metrics/color_error.py:213-231 (percentiles), :334-335 (edge threshold),
+ * :336-342 (boolean gather + mean + p95 of the edge region).
+ * ------------------------------------------------------------------------ */
+typedef struct llie_select_desc {
+    int32_t images;       /* values is [images, per_image] */
+    int64_t per_image;
+    int32_t nq;           /* 1 or 2 quantiles */
+    int32_t joint;        /* 0: one population per image | 1: all images form ONE population */
+} llie_select_desc;
+/* bytes of the caller-owned `select_ws`: ZERO before first use, self-resetting like `workspace`, and to be
+ * used with the SAME `images` on every call (its internal layout depends on it) */
+size_t llie_select_workspace_bytes(int32_t images, int32_t reserved);
+/*   q          HOST array of nq fractions in [0,1]
+ *   out_q      [segments, nq] floats (segments = joint ? 1 : images); NaN for an empty population
+ *   out_count  [images] int64: participating elements per image (the edge-mask pixel count)
+ *   out_sum    NULL or [segments] doubles: sum of the participating values */
+int llie_select_quantiles(const llie_select_desc *desc, const float *values, const float *gate,
+                          const float *gate_thr, const double *q, float *out_q, int64_t *out_count,
+                          double *out_sum, void *select_ws, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

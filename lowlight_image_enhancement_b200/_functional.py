@@ -299,3 +299,140 @@ def warn_zero_sum():
     warnings.warn(
         "PSF channel sums near zero detected during normalisation; clamping to preserve stability.",
         RuntimeWarning, stacklevel=3)
+
+
+# ------------------------------------------------------------------------------------------------
+# SSIM statistics
+# ------------------------------------------------------------------------------------------------
+_win_cache: dict = {}
+
+
+def window_1d(kind: str, k: int, sigma: float, dev: torch.device) -> Tensor:
+    """Normalised separable window taps on `dev` (cached).  The outer product equals the reference's
+    normalised 2-D window up to fp32 rounding:
+      'linear'       metrics/linear.py:82-121 (coords - (k-1)/2 in float64, cast, normalised)
+      'uniform'      linear.py gaussian=False
+      'torchmetrics' arange((1-k)/2, (1+k)/2), exp(-(d/sigma)^2/2), normalised (fp32)
+      'kornia'       arange(k) - k//2, exp(-x^2/(2 sigma^2)), normalised (fp32)"""
+    key = (kind, int(k), float(sigma), str(dev))
+    w = _win_cache.get(key)
+    if w is None:
+        if kind == "uniform":
+            g = torch.full((k,), 1.0 / k, dtype=torch.float64)
+        elif kind == "linear":
+            c = torch.arange(k, dtype=torch.float64) - (k - 1) / 2.0
+            g = torch.exp(-(c ** 2) / (2 * sigma ** 2))
+            g = g / g.sum()
+        elif kind == "torchmetrics":
+            d = torch.arange(start=(1 - k) / 2, end=(1 + k) / 2, step=1, dtype=torch.float32)
+            g = torch.exp(-torch.pow(d / sigma, 2) / 2)
+            g = g / g.sum()
+        elif kind == "kornia":
+            x = torch.arange(k, dtype=torch.float32) - k // 2
+            g = torch.exp(-x.pow(2.0) / (2 * sigma ** 2))
+            g = g / g.sum()
+        else:
+            raise ValueError(kind)
+        w = g.to(torch.float32).contiguous().to(dev)
+        _win_cache[key] = w
+    return w
+
+
+def ssim_stats(x: Tensor, y: Tensor, win: Tensor, *, pad_mode: int, c1: float, c2: float, eps: float,
+               luma: bool = False, clamp_in: bool = False, clamp_var: bool = False, interior: bool = False,
+               loss_map: bool = False, want_map: bool = False):
+    """Launch llie_ssim_stats on contiguous fp32 CUDA [N,C,H,W] tensors.
+    Returns (sums float64 [N, Co], flags int32[1], map or None)."""
+    dev = x.device
+    n, c, h, w = x.shape
+    co = 1 if luma else c
+    sums = torch.empty((n, co), dtype=torch.float64, device=dev)
+    flags = torch.empty(1, dtype=torch.int32, device=dev)
+    smap = torch.empty((n, co, h, w), dtype=torch.float32, device=dev) if want_map else None
+    d = nat.SsimDesc(n, c, h, w, int(win.numel()), pad_mode, int(luma), int(clamp_in), int(clamp_var),
+                     int(interior), int(loss_map), float(c1), float(c2), float(eps))
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(sums), nat.ptr(smap),
+                                       nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+    nat.check(rc, "llie_ssim_stats")
+    nat.count_launch()
+    return sums, flags, smap
+
+
+# ------------------------------------------------------------------------------------------------
+# CIEDE2000, Sobel, quantile select
+# ------------------------------------------------------------------------------------------------
+def deltae(x: Tensor, y: Tensor, *, variant: int, kL: float = 1.0, kC: float = 1.0, kH: float = 1.0,
+           eps: float = 1e-12, input_lab: bool = False, clamp_in: bool = False, want_map: bool = False,
+           want_l: bool = False):
+    """Launch llie_deltae on contiguous fp32 CUDA [N,3,H,W].  Returns (sums f64[N], flags, map|None, L|None)."""
+    dev = x.device
+    n, _, h, w = x.shape
+    sums = torch.empty(n, dtype=torch.float64, device=dev)
+    flags = torch.empty(1, dtype=torch.int32, device=dev)
+    dmap = torch.empty((n, h, w), dtype=torch.float32, device=dev) if want_map else None
+    lpl = torch.empty((n, h, w), dtype=torch.float32, device=dev) if want_l else None
+    d = nat.DeltaEDesc(n, h, w, variant, int(input_lab), int(clamp_in), float(kL), float(kC), float(kH), float(eps))
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_deltae(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(dmap), nat.ptr(lpl),
+                                   nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+    nat.check(rc, "llie_deltae")
+    nat.count_launch()
+    return sums, flags, dmap, lpl
+
+
+def sobel_magnitude(l_planes: Tensor) -> Tensor:
+    """[..., H, W] fp32 CUDA -> Sobel magnitude of every plane (zero padding)."""
+    dev = l_planes.device
+    h, w = l_planes.shape[-2:]
+    planes = l_planes.numel() // (h * w)
+    out = torch.empty_like(l_planes)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_sobel_magnitude(nat.ptr(l_planes), nat.ptr(out), planes, h, w, nat.stream_ptr(dev))
+    nat.check(rc, "llie_sobel_magnitude")
+    nat.count_launch()
+    return out
+
+
+_sel_ws: dict = {}
+
+
+def _select_ws(dev: torch.device, images: int) -> Tensor:
+    stream = torch.cuda.current_stream(dev)
+    # the layout inside the buffer depends on `images`, and only part of it self-resets to zero:
+    # one buffer per (device, stream, images)
+    key = (dev.index, stream.cuda_stream, images)
+    ws = _sel_ws.get(key)
+    if ws is None:
+        if len(_sel_ws) > 64:
+            _sel_ws.clear()
+        ws = torch.zeros(nat.lib().llie_select_workspace_bytes(images, 0), dtype=torch.uint8, device=dev)
+        _sel_ws[key] = ws
+    return ws
+
+
+def select_quantiles(values: Tensor, qs, *, joint: bool, gate: Optional[Tensor] = None,
+                     gate_thr: Optional[Tensor] = None, want_sum: bool = False):
+    """torch.quantile(values[i].flatten(), q, interpolation='linear') per image (joint=False) or over all
+    images together (joint=True), optionally only over elements with gate >= gate_thr[image].
+    values / gate: contiguous fp32 CUDA [images, ...].  Returns (quantiles f32 [segments, nq],
+    counts int64 [images], sums f64 [segments] or None)."""
+    import ctypes as C
+    dev = values.device
+    images = values.shape[0]
+    per = values.numel() // images
+    nq = len(qs)
+    segs = 1 if joint else images
+    out_q = torch.empty((segs, nq), dtype=torch.float32, device=dev)
+    cnt = torch.empty(images, dtype=torch.int64, device=dev)
+    sums = torch.empty(segs, dtype=torch.float64, device=dev) if want_sum else None
+    d = nat.SelectDesc(images, per, nq, int(joint))
+    qarr = (C.c_double * nq)(*[float(q) for q in qs])
+    ws = _select_ws(dev, images)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_select_quantiles(d, nat.ptr(values), nat.ptr(gate), nat.ptr(gate_thr), qarr,
+                                             nat.ptr(out_q), nat.ptr(cnt), nat.ptr(sums), nat.ptr(ws),
+                                             nat.stream_ptr(dev))
+    nat.check(rc, "llie_select_quantiles")
+    nat.count_launch(6)
+    return out_q, cnt, sums

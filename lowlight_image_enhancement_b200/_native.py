@@ -49,6 +49,20 @@ class PsnrDesc(C.Structure):
     ]
 
 
+class SsimDesc(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in ("n", "c", "h", "w", "ksize", "pad_mode", "luma", "clamp_in", "clamp_var",
+                                         "interior", "loss_map")] + [(k, C.c_float) for k in ("c1", "c2", "eps")]
+
+
+class DeltaEDesc(C.Structure):
+    _fields_ = [(k, C.c_int32) for k in ("n", "h", "w", "variant", "input_lab", "clamp_in")] + \
+               [(k, C.c_float) for k in ("kL", "kC", "kH", "eps")]
+
+
+class SelectDesc(C.Structure):
+    _fields_ = [("images", C.c_int32), ("per_image", C.c_int64), ("nq", C.c_int32), ("joint", C.c_int32)]
+
+
 PAD = {"zeros": 0, "constant": 0, "reflect": 1, "replicate": 2, "circular": 3}
 
 _VP = C.c_void_p
@@ -65,6 +79,12 @@ _SIGNATURES = {
     "llie_newbp_forward": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_adjoint": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_psnr_stats": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_ssim_stats": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_deltae": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),
+    "llie_select_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "llie_select_quantiles": (C.c_int, [C.POINTER(SelectDesc), _VP, _VP, _VP, C.POINTER(C.c_double), _VP, _VP, _VP,
+                                        _VP, _VP]),
 }
 
 

@@ -1,0 +1,274 @@
+// sRGB -> Lab(D65/2deg) -> CIEDE2000 maps and sums (sm_100a), both variants of the reference, fused into
+// one pass over the two images (24 B/px read) instead of ~50 eager pointwise kernels:
+//   * metrics/color_error.py:105-210  _deltaE00_lab_map  METRIC variant (eps 1e-12, unwrapped hue,
+//                                      piecewise dh / hbar under `valid`, sin(2 dtheta), clamp >= 0)
+//   * NewBP_model/losses.py:99-136    DeltaE00Loss._ciede2000  LOSS variant (eps 1e-6 everywhere, hue
+//                                      mod 2pi, boolean-mask wraps, sin(dtheta), + eps under the sqrt)
+//   * kornia 0.6.12 rgb_to_lab (color_error.py:79-85, losses.py:140-141) restated, see oracle/colour.py
+// plus the Sobel magnitude of the L plane (color_error.py:296-301) for the edge mask.
+// Precise transcendentals (powf / atan2f / sinf / cosf / expf, no fast-math): the tolerance is 1e-4
+// absolute on dE00.  This kernel is bound by the FP32/SFU pipes (~600 instructions per pixel against
+// 24 bytes), not by HBM.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace llie {
+
+constexpr float kPi = 3.14159265358979323846f;
+
+__device__ __forceinline__ float srgb_to_linear(float c) {
+    return c > 0.04045f ? powf((c + 0.055f) / 1.055f, 2.4f) : c / 12.92f;
+}
+__device__ __forceinline__ float lab_f(float t) {
+    return t > 0.008856f ? powf(fmaxf(t, 0.008856f), 1.0f / 3.0f) : 7.787f * t + 4.0f / 29.0f;
+}
+// kornia 0.6.12 rgb_to_lab
+__device__ __forceinline__ void rgb_to_lab(float r, float g, float b, float &L, float &A, float &B) {
+    r = srgb_to_linear(r);
+    g = srgb_to_linear(g);
+    b = srgb_to_linear(b);
+    const float x = 0.412453f * r + 0.357580f * g + 0.180423f * b;
+    const float y = 0.212671f * r + 0.715160f * g + 0.072169f * b;
+    const float z = 0.019334f * r + 0.119193f * g + 0.950227f * b;
+    const float fx = lab_f(x / 0.95047f), fy = lab_f(y / 1.0f), fz = lab_f(z / 1.08883f);
+    L = 116.0f * fy - 16.0f;
+    A = 500.0f * (fx - fy);
+    B = 200.0f * (fy - fz);
+}
+
+__device__ __forceinline__ float pow7(float v) {
+    const float v2 = v * v, v4 = v2 * v2;
+    return v4 * v2 * v;
+}
+__device__ __forceinline__ float deg2rad(float d) { return d * (kPi / 180.0f); }
+
+// METRIC variant (color_error.py:105-210)
+__device__ float de00_metric(float L1, float a1, float b1, float L2, float a2, float b2, float kL, float kC, float kH,
+                             float eps) {
+    const float c1 = sqrtf(a1 * a1 + b1 * b1 + eps), c2 = sqrtf(a2 * a2 + b2 * b2 + eps);
+    const float cb = 0.5f * (c1 + c2);
+    const float cb7 = pow7(cb);
+    const float k25 = 6103515625.0f;
+    const float g = 0.5f * (1.0f - sqrtf(cb7 / (cb7 + k25 + eps)));
+    const float a1p = (1.0f + g) * a1, a2p = (1.0f + g) * a2;
+    const float c1p = sqrtf(a1p * a1p + b1 * b1 + eps), c2p = sqrtf(a2p * a2p + b2 * b2 + eps);
+    const float h1 = atan2f(b1, a1p), h2 = atan2f(b2, a2p);
+    const float dL = L2 - L1, dC = c2p - c1p;
+    const bool ok = (c1p * c2p) != 0.0f;
+    const float df = h2 - h1;
+    float dh = 0.0f;
+    if (ok && fabsf(df) <= kPi) dh = df;
+    if (ok && df > kPi) dh = df - 2.0f * kPi;
+    if (ok && df < -kPi) dh = df + 2.0f * kPi;
+    const float dH = 2.0f * sqrtf(c1p * c2p + eps) * sinf(dh / 2.0f);
+    const float Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
+    const float hs = h1 + h2, ad = fabsf(h1 - h2);
+    float hb;
+    if (!ok)
+        hb = hs;
+    else if (ad <= kPi)
+        hb = 0.5f * hs;
+    else if (hs < 2.0f * kPi)
+        hb = 0.5f * (hs + 2.0f * kPi);
+    else
+        hb = 0.5f * (hs - 2.0f * kPi);
+    const float t = 1.0f - 0.17f * cosf(hb - deg2rad(30.0f)) + 0.24f * cosf(2.0f * hb) +
+                    0.32f * cosf(3.0f * hb + deg2rad(6.0f)) - 0.20f * cosf(4.0f * hb - deg2rad(63.0f));
+    const float q = ((hb * 180.0f / kPi) - 275.0f) / 25.0f;
+    const float dth = deg2rad(30.0f) * expf(-(q * q));
+    const float Cb7 = pow7(Cb);
+    const float rc = 2.0f * sqrtf(Cb7 / (Cb7 + k25 + eps));
+    const float rt = -sinf(2.0f * dth) * rc;
+    const float l50 = (Lb - 50.0f) * (Lb - 50.0f);
+    const float sL = 1.0f + (0.015f * l50) / sqrtf(20.0f + l50 + eps);
+    const float sC = 1.0f + 0.045f * Cb;
+    const float sH = 1.0f + 0.015f * Cb * t;
+    const float lt = dL / (kL * sL + eps), ct = dC / (kC * sC + eps), ht = dH / (kH * sH + eps);
+    return sqrtf(fmaxf(lt * lt + ct * ct + ht * ht + rt * ct * ht, 0.0f));
+}
+
+// torch's `%` on floats (python modulo: result takes the sign of the divisor)
+__device__ __forceinline__ float pymod(float a, float m) {
+    float r = fmodf(a, m);
+    if (r != 0.0f && ((r < 0.0f) != (m < 0.0f))) r += m;
+    return r;
+}
+
+// LOSS variant (losses.py:99-136)
+__device__ float de00_loss(float L1, float a1, float b1, float L2, float a2, float b2, float eps) {
+    const float c1 = sqrtf(a1 * a1 + b1 * b1 + eps), c2 = sqrtf(a2 * a2 + b2 * b2 + eps);
+    const float cb = 0.5f * (c1 + c2);
+    const float cb7 = pow7(cb);
+    const float k25 = 6103515625.0f;
+    const float g = 0.5f * (1.0f - sqrtf(cb7 / (cb7 + k25 + eps)));
+    const float a1p = (1.0f + g) * a1, a2p = (1.0f + g) * a2;
+    const float c1p = sqrtf(a1p * a1p + b1 * b1 + eps), c2p = sqrtf(a2p * a2p + b2 * b2 + eps);
+    const float h1 = pymod(atan2f(b1, a1p), 2.0f * kPi), h2 = pymod(atan2f(b2, a2p), 2.0f * kPi);
+    const float dL = L2 - L1, dC = c2p - c1p;
+    float dh = h2 - h1;
+    dh = dh - (dh > kPi ? 2.0f * kPi : 0.0f) + (dh < -kPi ? 2.0f * kPi : 0.0f);
+    const float dH = 2.0f * sqrtf(c1p * c2p + eps) * sinf(dh / 2.0f);
+    const float Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
+    const float hs = h1 + h2;
+    const float hb = hs / 2.0f - (fabsf(h1 - h2) > kPi ? kPi : 0.0f) + (hs < 0.0f ? 2.0f * kPi : 0.0f);
+    const float t = 1.0f - 0.17f * cosf(hb - deg2rad(30.0f)) + 0.24f * cosf(2.0f * hb) +
+                    0.32f * cosf(3.0f * hb + deg2rad(6.0f)) - 0.20f * cosf(4.0f * hb - deg2rad(63.0f));
+    const float q = ((hb * (180.0f / kPi)) - 275.0f) / 25.0f;
+    const float dro = 30.0f * expf(-(q * q));
+    const float Cb7 = pow7(Cb);
+    const float rc = 2.0f * sqrtf(Cb7 / (Cb7 + k25 + eps));
+    const float l50 = (Lb - 50.0f) * (Lb - 50.0f);
+    const float sL = 1.0f + (0.015f * l50) / sqrtf(20.0f + l50 + eps);
+    const float sC = 1.0f + 0.045f * Cb;
+    const float sH = 1.0f + 0.015f * Cb * t;
+    const float rt = -sinf(deg2rad(dro)) * rc;
+    const float lt = dL / sL, ct = dC / sC, ht = dH / sH;
+    return sqrtf(lt * lt + ct * ct + ht * ht + rt * ct * ht + eps);
+}
+
+struct DeArgs {
+    llie_deltae_desc d;
+    const float *x, *y;
+    double *out_sum;
+    float *out_map, *out_l;
+    int *out_flags;
+    double *part;  // [n][G]
+    int *pflag;    // [n][G]
+    unsigned *ticket;
+};
+
+__global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
+    __shared__ double red[32];
+    const llie_deltae_desc &d = a.d;
+    const int n = blockIdx.y, G = gridDim.x;
+    const long long plane = (long long)d.h * d.w;
+    const float *x0 = a.x + (long long)n * 3 * plane, *y0 = a.y + (long long)n * 3 * plane;
+    float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
+         i += (long long)G * blockDim.x) {
+        float p0 = __ldcs(x0 + i), p1 = __ldcs(x0 + plane + i), p2 = __ldcs(x0 + 2 * plane + i);
+        float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
+        chk_x = fmaf(p0, 0.f, fmaf(p1, 0.f, fmaf(p2, 0.f, chk_x)));
+        chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
+        float L1, A1, B1, L2, A2, B2;
+        if (d.input_lab) {
+            L1 = p0; A1 = p1; B1 = p2;
+            L2 = t0; A2 = t1; B2 = t2;
+        } else {
+            if (d.clamp_in) {
+                p0 = fminf(fmaxf(p0, 0.f), 1.f); p1 = fminf(fmaxf(p1, 0.f), 1.f); p2 = fminf(fmaxf(p2, 0.f), 1.f);
+                t0 = fminf(fmaxf(t0, 0.f), 1.f); t1 = fminf(fmaxf(t1, 0.f), 1.f); t2 = fminf(fmaxf(t2, 0.f), 1.f);
+            }
+            rgb_to_lab(p0, p1, p2, L1, A1, B1);
+            rgb_to_lab(t0, t1, t2, L2, A2, B2);
+        }
+        const float de = d.variant == 0 ? de00_metric(L1, A1, B1, L2, A2, B2, d.kL, d.kC, d.kH, d.eps)
+                                        : de00_loss(L1, A1, B1, L2, A2, B2, d.eps);
+        acc += de;
+        if (a.out_map) a.out_map[(long long)n * plane + i] = de;
+        if (a.out_l) a.out_l[(long long)n * plane + i] = L1;
+    }
+    const double bs = block_sum<double>((double)acc, red);
+    int flag = 0;
+    if (!(chk_x == 0.f)) flag |= 1;
+    if (!(chk_y == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        a.part[(size_t)n * G + blockIdx.x] = bs;
+        a.pflag[(size_t)n * G + blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x * gridDim.y)) return;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    for (int s = wrp; s < d.n; s += 8) {
+        const double *p = a.part + (size_t)s * G;
+        double s0 = 0.0, s1 = 0.0;
+        int b = lane;
+        for (; b + 32 < G; b += 64) {
+            s0 += __ldcg(p + b);
+            s1 += __ldcg(p + b + 32);
+        }
+        for (; b < G; b += 32) s0 += __ldcg(p + b);
+        const double t = warp_sum(s0 + s1);
+        if (lane == 0) a.out_sum[s] = t;
+    }
+    int fl = 0;
+    for (int b = threadIdx.x; b < G * d.n; b += blockDim.x) fl |= __ldcg(a.pflag + b);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) *a.out_flags = ff;
+}
+
+// Sobel magnitude of a [planes, H, W] stack, zero padding (color_error.py:23-30, 296-301).  Products and
+// sums are kept un-contracted (no FMA) so that the result is the IEEE value torch computes.
+__global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, int H, int W, long long planes) {
+    const long long plane = (long long)H * W, total = plane * planes;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long pl = i / plane;
+        const int rem = (int)(i - pl * plane);
+        const int y = rem / W, x = rem - y * W;
+        const float *p = L + pl * plane;
+        auto at = [&](int yy, int xx) -> float {
+            return (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(p + (long long)yy * W + xx) : 0.f;
+        };
+        const float v00 = at(y - 1, x - 1), v01 = at(y - 1, x), v02 = at(y - 1, x + 1);
+        const float v10 = at(y, x - 1), v12 = at(y, x + 1);
+        const float v20 = at(y + 1, x - 1), v21 = at(y + 1, x), v22 = at(y + 1, x + 1);
+        // gx = sum_k Kx[k] * v[k] in row-major tap order, gy likewise (zero taps contribute exactly 0)
+        float gx = __fmul_rn(-1.f, v00);
+        gx = __fadd_rn(gx, v02);
+        gx = __fadd_rn(gx, __fmul_rn(-2.f, v10));
+        gx = __fadd_rn(gx, __fmul_rn(2.f, v12));
+        gx = __fadd_rn(gx, __fmul_rn(-1.f, v20));
+        gx = __fadd_rn(gx, v22);
+        float gy = __fmul_rn(-1.f, v00);
+        gy = __fadd_rn(gy, __fmul_rn(-2.f, v01));
+        gy = __fadd_rn(gy, __fmul_rn(-1.f, v02));
+        gy = __fadd_rn(gy, v20);
+        gy = __fadd_rn(gy, __fmul_rn(2.f, v21));
+        gy = __fadd_rn(gy, v22);
+        const float s = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), 1e-12f);
+        g[i] = __fsqrt_rn(s);
+    }
+}
+
+}  // namespace llie
+
+using namespace llie;
+
+extern "C" int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                           float *out_map, float *out_l, int32_t *out_flags, void *workspace, void *stream) {
+    LLIE_REQUIRE(desc && x && y && out_sum && out_flags && workspace, "deltae: null pointer");
+    LLIE_REQUIRE(desc->n > 0 && desc->h > 0 && desc->w > 0, "deltae: empty tensor");
+    LLIE_REQUIRE(desc->n <= 65535, "deltae: batch too large for grid.y");
+    LLIE_REQUIRE(desc->variant == 0 || desc->variant == 1, "deltae: variant must be 0 (metric) or 1 (loss)");
+    DeArgs a{};
+    a.d = *desc;
+    a.x = x; a.y = y; a.out_sum = out_sum; a.out_map = out_map; a.out_l = out_l; a.out_flags = out_flags;
+    const long long plane = (long long)desc->h * desc->w;
+    int G = div_up(kNumSM * 8, desc->n);
+    const long long maxg = (plane + 255) / 256;
+    if (G > maxg) G = (int)maxg;
+    if (G < 1) G = 1;
+    Workspace ws(workspace);
+    const size_t slots = (size_t)G * desc->n;
+    LLIE_REQUIRE(slots * (sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "deltae: workspace too small");
+    a.part = reinterpret_cast<double *>(ws.scratch);
+    a.pflag = reinterpret_cast<int *>(ws.scratch + slots * sizeof(double));
+    a.ticket = ws.tickets;
+    dim3 grid(G, desc->n);
+    deltae_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+extern "C" int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w,
+                                    void *stream) {
+    LLIE_REQUIRE(l_planes && out_g && planes > 0 && h > 0 && w > 0, "sobel: bad arguments");
+    const long long total = (long long)planes * h * w;
+    long long blocks = (total + 255) / 256;
+    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
+    sobel_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w, planes);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}

@@ -1,0 +1,257 @@
+// Exact order statistics / torch.quantile(..., interpolation='linear') on the device by a 3-pass radix
+// select over the float bit patterns (11 + 11 + 10 bits), replacing the full sorts the reference
+// pays for the edge threshold, the edge p95 and the dE00 percentiles
+// (metrics/color_error.py:213-231, 334-342).  Optionally the population is gated by a second array
+// (`gate[i] >= gate_thr[image]`, the Sobel edge mask of color_error.py:336-339), in which case the
+// first pass also yields the gated count (the bit-exact integer of the edge mask) and the gated sum.
+//
+// torch semantics reproduced exactly: rank = float(q) * float(n-1) in FLOAT32, lo = floor, hi = ceil,
+// result = lerp(v[lo], v[hi], rank - lo) with torch.lerp's two-sided formula.
+// All counting is integer (atomics on integers are order-independent) -> bit-reproducible.
+#include "common.cuh"
+
+namespace llie {
+
+constexpr int kBins = 2048;
+constexpr int kMaxQ = 2;            // quantiles per call
+constexpr int kMaxR = 2 * kMaxQ;    // ranks tracked (lo / hi of every quantile)
+
+struct SelState {                    // per segment, lives in the workspace
+    unsigned long long count;        // population size
+    unsigned long long k[kMaxR];     // remaining rank inside the current prefix
+    unsigned prefix[kMaxR];          // decided high bits (monotone-mapped)
+    float w[kMaxQ];                  // interpolation weights
+};
+
+struct SelArgs {
+    llie_select_desc d;
+    const float *values, *gate, *gate_thr;
+    float q[kMaxQ];
+    float *out_q;                    // [segments][nq]
+    long long *out_count;            // [images] gated (or plain) element count per image
+    double *out_sum;                 // [segments] sum of the participating values (or NULL)
+    unsigned long long *hist;        // [segments][kMaxR][kBins]
+    unsigned long long *img_count;   // [images]
+    double *psum;                    // [images][gridDim.x]
+    SelState *state;                 // [segments]
+    int pass;                        // 0, 1, 2
+};
+
+// monotone map float bits -> unsigned (total order incl. negatives)
+__device__ __forceinline__ unsigned fkey(float v) {
+    const unsigned b = __float_as_uint(v);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float funkey(unsigned k) {
+    return __uint_as_float((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k);
+}
+__device__ __forceinline__ int pass_shift(int pass) { return pass == 0 ? 21 : (pass == 1 ? 10 : 0); }
+__device__ __forceinline__ unsigned pass_bins(int pass) { return pass == 2 ? 1024u : 2048u; }
+__device__ __forceinline__ unsigned pass_himask(int pass) {  // bits already decided before this pass
+    return pass == 0 ? 0u : (pass == 1 ? 0xffe00000u : 0xfffffc00u);
+}
+
+// grid (bx, images).  Segment = image, or 0 when d.joint.
+__global__ void __launch_bounds__(256) select_hist_kernel(const SelArgs a) {
+    extern __shared__ unsigned sh[];  // [nr][bins]
+    __shared__ double red[32];
+    const llie_select_desc &d = a.d;
+    const int img = blockIdx.y, seg = d.joint ? 0 : img;
+    const int nr = 2 * d.nq;
+    const unsigned bins = pass_bins(a.pass);
+    for (unsigned i = threadIdx.x; i < nr * bins; i += blockDim.x) sh[i] = 0u;
+    __syncthreads();
+    const int shift = pass_shift(a.pass);
+    const unsigned himask = pass_himask(a.pass);
+    unsigned pre[kMaxR];
+#pragma unroll
+    for (int r = 0; r < kMaxR; ++r) pre[r] = (a.pass > 0 && r < nr) ? a.state[seg].prefix[r] : 0u;
+    const bool same01 = nr >= 2 && pre[0] == pre[1], same23 = nr >= 4 && pre[2] == pre[3];
+    const float thr = a.gate ? __ldg(a.gate_thr + img) : 0.f;
+    const float *v = a.values + (long long)img * d.per_image;
+    const float *gt = a.gate ? a.gate + (long long)img * d.per_image : nullptr;
+    unsigned long long cnt = 0;
+    double sum = 0.0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < d.per_image;
+         i += (long long)gridDim.x * blockDim.x) {
+        if (gt && !(__ldg(gt + i) >= thr)) continue;
+        const float val = __ldg(v + i);
+        const unsigned key = fkey(val);
+        if (a.pass == 0) {
+            ++cnt;
+            sum += (double)val;
+        }
+        const unsigned digit = (key >> shift) & (bins - 1u);
+        const unsigned hi = key & himask;
+        // ranks that share a prefix share a histogram row (the common case: lo and hi are adjacent ranks)
+        if (hi == pre[0]) atomicAdd(&sh[digit], 1u);
+        if (nr >= 2 && !same01 && hi == pre[1]) atomicAdd(&sh[bins + digit], 1u);
+        if (nr >= 4 && hi == pre[2]) atomicAdd(&sh[2 * bins + digit], 1u);
+        if (nr >= 4 && !same23 && hi == pre[3]) atomicAdd(&sh[3 * bins + digit], 1u);
+    }
+    __syncthreads();
+    unsigned long long *gh = a.hist + (size_t)seg * kMaxR * kBins;
+    for (unsigned i = threadIdx.x; i < nr * bins; i += blockDim.x) {
+        const unsigned c = sh[i];
+        if (c) atomicAdd(&gh[(i / bins) * kBins + (i % bins)], (unsigned long long)c);
+    }
+    if (a.pass == 0) {
+        // gated count per image (integer) and a deterministic per-block partial of the gated sum
+        unsigned long long wc = cnt;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) wc += __shfl_xor_sync(0xffffffffu, wc, o);
+        if ((threadIdx.x & 31) == 0 && wc) atomicAdd(&a.img_count[img], wc);
+        const double bs = block_sum<double>(sum, red);
+        if (threadIdx.x == 0) a.psum[(size_t)img * gridDim.x + blockIdx.x] = bs;
+    }
+}
+
+// one block per segment: walk the histogram rows, fix the next digit of every rank
+__global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int images, int blocks_x) {
+    __shared__ unsigned long long chunk[256];
+    __shared__ unsigned long long newk[kMaxR];
+    __shared__ unsigned newp[kMaxR];
+    __shared__ double red[32];
+    const llie_select_desc &d = a.d;
+    const int seg = blockIdx.x;
+    const int nr = 2 * d.nq;
+    SelState &st = a.state[seg];
+    const unsigned bins = pass_bins(a.pass);
+    const int shift = pass_shift(a.pass);
+    unsigned long long *gh = a.hist + (size_t)seg * kMaxR * kBins;
+
+    if (a.pass == 0) {
+        // population, ranks and weights (torch.quantile float32 arithmetic)
+        const int i0 = d.joint ? 0 : seg, i1 = d.joint ? images : seg + 1;
+        if (threadIdx.x == 0) {
+            unsigned long long c = 0;
+            for (int i = i0; i < i1; ++i) {
+                c += a.img_count[i];
+                a.out_count[i] = (long long)a.img_count[i];
+            }
+            st.count = c;
+            for (int qi = 0; qi < d.nq; ++qi) {
+                const float rank = a.q[qi] * (float)((long long)c - 1);
+                const float lo = floorf(rank), hi = ceilf(rank);
+                st.k[2 * qi] = c ? (unsigned long long)lo : 0ull;
+                st.k[2 * qi + 1] = c ? (unsigned long long)hi : 0ull;
+                st.w[qi] = rank - lo;
+                st.prefix[2 * qi] = st.prefix[2 * qi + 1] = 0u;
+            }
+        }
+        if (a.out_sum) {  // fixed-order sum of the per-block partials
+            double s = 0.0;
+            const long long tot = (long long)(i1 - i0) * blocks_x;
+            const double *p = a.psum + (size_t)i0 * blocks_x;
+            for (long long b = threadIdx.x; b < tot; b += blockDim.x) s += p[b];
+            s = block_sum<double>(s, red);
+            if (threadIdx.x == 0) a.out_sum[seg] = s;
+        }
+        __syncthreads();
+    }
+    for (int r = 0; r < nr; ++r) {
+        // rows are shared when the two ranks of a quantile had the same prefix going into this pass
+        const bool shared_row = (r & 1) && st.prefix[r] == st.prefix[r - 1] && a.pass >= 0;
+        const unsigned long long *row = gh + (size_t)(shared_row ? r - 1 : r) * kBins;
+        const unsigned long long k = st.k[r];
+        // 256 threads x (bins / 256) bins: chunk sums, then thread 0 walks chunks, then bins
+        const int per = bins / 256;
+        unsigned long long cs = 0;
+        for (int j = 0; j < per; ++j) cs += row[threadIdx.x * per + j];
+        chunk[threadIdx.x] = cs;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned long long cum = 0;
+            int c = 0;
+            while (c < 255 && cum + chunk[c] <= k) cum += chunk[c++];
+            int b = c * per;
+            while (b < c * per + per - 1 && cum + row[b] <= k) cum += row[b++];
+            chunk[0] = (unsigned long long)b;
+            chunk[1] = k - cum;
+        }
+        __syncthreads();
+        const unsigned digit = (unsigned)chunk[0];
+        const unsigned long long knew = chunk[1];
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            // NOTE: prefix[r] is updated only after a possible sharing partner (r+1) compared against
+            // the OLD prefix[r]; handled by deferring the write through `newp`
+            newp[r] = st.prefix[r] | (digit << shift);
+            newk[r] = knew;
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        for (int r = 0; r < nr; ++r) {
+            st.prefix[r] = newp[r];
+            st.k[r] = newk[r];
+        }
+    }
+    __syncthreads();
+    // clear the histogram rows for the next pass / next call
+    for (unsigned i = threadIdx.x; i < (unsigned)kMaxR * kBins; i += blockDim.x) gh[i] = 0ull;
+    if (a.pass == 2 && threadIdx.x == 0) {
+        for (int qi = 0; qi < d.nq; ++qi) {
+            float res = __int_as_float(0x7fc00000);  // empty population -> NaN (color_error.py:340-341)
+            if (st.count) {
+                const float lo = funkey(st.prefix[2 * qi]), hi = funkey(st.prefix[2 * qi + 1]);
+                const float w = st.w[qi];
+                // torch.lerp: w < 0.5 ? a + w (b - a) : b - (b - a) (1 - w)
+                const float df = hi - lo;
+                res = w < 0.5f ? lo + w * df : hi - df * (1.f - w);
+            }
+            a.out_q[seg * d.nq + qi] = res;
+        }
+        const int i0 = d.joint ? 0 : seg, i1 = d.joint ? images : seg + 1;
+        for (int i = i0; i < i1; ++i) a.img_count[i] = 0ull;  // self-reset
+    }
+}
+
+}  // namespace llie
+
+using namespace llie;
+
+extern "C" size_t llie_select_workspace_bytes(int32_t images, int32_t blocks_hint) {
+    (void)blocks_hint;
+    const size_t segs = (size_t)images;
+    return segs * kMaxR * kBins * sizeof(unsigned long long) + segs * sizeof(unsigned long long) +
+           segs * sizeof(SelState) + segs * (size_t)(kNumSM * 8) * sizeof(double) + 256;
+}
+
+extern "C" int llie_select_quantiles(const llie_select_desc *desc, const float *values, const float *gate,
+                                     const float *gate_thr, const double *q, float *out_q, int64_t *out_count,
+                                     double *out_sum, void *select_ws, void *stream) {
+    LLIE_REQUIRE(desc && values && q && out_q && out_count && select_ws, "select: null pointer");
+    const llie_select_desc &d = *desc;
+    LLIE_REQUIRE(d.images > 0 && d.images <= 65535 && d.per_image > 0, "select: bad population");
+    LLIE_REQUIRE(d.nq >= 1 && d.nq <= kMaxQ, "select: 1..%d quantiles per call", kMaxQ);
+    LLIE_REQUIRE((gate == nullptr) == (gate_thr == nullptr), "select: gate and gate_thr go together");
+    for (int i = 0; i < d.nq; ++i) LLIE_REQUIRE(q[i] >= 0.0 && q[i] <= 1.0, "select: q must be in [0,1]");
+    SelArgs a{};
+    a.d = d;
+    a.values = values; a.gate = gate; a.gate_thr = gate_thr;
+    for (int i = 0; i < d.nq; ++i) a.q[i] = (float)q[i];
+    a.out_q = out_q; a.out_count = reinterpret_cast<long long *>(out_count); a.out_sum = out_sum;
+    const int segs = d.joint ? 1 : d.images;
+    int bx = div_up(kNumSM * 8, d.images);
+    const long long maxb = (d.per_image + 1023) / 1024;
+    if (bx > maxb) bx = (int)maxb;
+    if (bx < 1) bx = 1;
+    unsigned char *w = static_cast<unsigned char *>(select_ws);
+    a.hist = reinterpret_cast<unsigned long long *>(w);
+    w += (size_t)d.images * kMaxR * kBins * sizeof(unsigned long long);
+    a.img_count = reinterpret_cast<unsigned long long *>(w);
+    w += (size_t)d.images * sizeof(unsigned long long);
+    a.state = reinterpret_cast<SelState *>(w);
+    w += (size_t)d.images * sizeof(SelState);
+    a.psum = reinterpret_cast<double *>(((uintptr_t)w + 7) & ~(uintptr_t)7);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const size_t smem = (size_t)2 * d.nq * kBins * sizeof(unsigned);
+    for (int pass = 0; pass < 3; ++pass) {
+        a.pass = pass;
+        select_hist_kernel<<<dim3(bx, d.images), 256, smem, st>>>(a);
+        select_scan_kernel<<<segs, 256, 0, st>>>(a, d.images, bx);
+    }
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
