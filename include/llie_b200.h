@@ -189,6 +189,19 @@ typedef struct llie_ssim_desc {
 int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
                     double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream);
 
+/* Differentiable (D)SSIM, kornia policy (reflect border, same size, no variance clamp): forward as
+ * llie_ssim_stats plus out_coef [3][n*c][h][w] = grad_scale * dLossMap/dS * (A1, A2, A3), the per-window
+ * sensitivities of S to (mu_x, E[x^2], E[xy]); backward folds them through the adjoint of reflect-pad o
+ * separable correlation:  out_grad = mask_[0,1](x) * g * (G^T c1 + 2 x G^T c2 + y G^T c3).
+ * `grad_out` is a DEVICE pointer: one float (gradient of the reduced loss) or, with grad_out_is_map, a
+ * [n,c,h,w] map (reduction 'none').  replaces kornia.losses.SSIMLoss autograd (losses.py:146-155). */
+int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                           float grad_scale, double *out_sum, float *out_map, float *out_coef, int32_t *out_flags,
+                           void *workspace, void *stream);
+int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                            const float *coef, const float *grad_out, int32_t grad_out_is_map, float *out_grad,
+                            void *stream);
+
 /* ------------------------------------------------------------------------
  * sRGB -> Lab(D65/2deg) -> CIEDE2000, per-image float64 sums (+ optional map / L plane of x).
  * replaces metrics/color_error.py:68-97,105-210,235-266 (variant 0, metric) and
@@ -204,6 +217,12 @@ typedef struct llie_deltae_desc {
 /*   out_sum [n] doubles; out_map NULL or [n, h, w]; out_l NULL or [n, h, w] (L of x, for the edge mask) */
 int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum, float *out_map,
                 float *out_l, int32_t *out_flags, void *workspace, void *stream);
+
+/* DeltaE00Loss forward + analytic backward in ONE pass (variant 1, sRGB inputs): per-image sums of dE00 and
+ * out_grad[n,3,h,w] = grad_scale * d dE00(pixel) / d x (clamp pass-through mask included), i.e. the gradient
+ * of `dE.mean()` when grad_scale = 1 / (n h w).  replaces losses.py:138-143 + its autograd graph. */
+int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const float *y, float grad_scale,
+                          double *out_sum, float *out_grad, int32_t *out_flags, void *workspace, void *stream);
 
 /* Sobel magnitude sqrt(gx^2 + gy^2 + 1e-12) of [planes, h, w], zero padding (color_error.py:23-30, 296-301) */
 int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w, void *stream);

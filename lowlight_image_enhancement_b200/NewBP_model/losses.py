@@ -4,13 +4,17 @@ Implemented on sm_100a kernels (fused forward + analytic backward):
     PhysicsConsistencyLoss        losses.py:158-192   | K * Bhat_raw (replicate pad) - clamp(A*rho) |_1
     PhysicalConsistencyLossSRGB   losses.py:206-220   | CrosstalkPSF(Bhat) - clamp(A*rho, 0, 1) |_1
     align_exposure_srgb           losses.py:195-203
+    DeltaE00Loss                  losses.py:92-143    mean CIEDE2000 (loss variant) on clamp(.,0,1) sRGB
+    SSIMLoss                      losses.py:146-155   kornia-policy DSSIM, no kornia dependency
+    HybridLossPlus                losses.py:223-372   L1 + dE00 + DSSIM + physics (+ injected extras)
 
-Out of scope (stay stock PyTorch in the reference; SURVEY.md §2 rows 3, 11): the VGG19
-`PerceptualLoss` and LPIPS.
+Out of scope (stay stock PyTorch in the reference; SURVEY.md §2 rows 3, 11 and §8a R11): the VGG19
+`PerceptualLoss` and LPIPS.  `HybridLossPlus` takes them as injected modules (`perceptual_module`,
+`lpips_module`); without one the term is skipped and logged as 0 — nothing here downloads weights.
 """
 from __future__ import annotations
 
-from typing import Optional
+from typing import Dict, Optional, Union
 
 import torch
 import torch.nn as nn
@@ -137,3 +141,173 @@ class PhysicalConsistencyLossSRGB(nn.Module):
         cfg = Fn.PhysCfg(nat.PAD["zeros"], False, False, 1e-12, 1, False, True)
         out = Fn.PhysProjector.apply(x, a, psf, rho_t, rho_s, rho_st, cfg)[n]
         return out if home == dev else out.to(home)
+
+
+def _resolve_device(device: Union[str, torch.device]) -> torch.device:
+    """losses.py:20-29 ('auto' -> cuda when available)."""
+    if isinstance(device, torch.device):
+        return device
+    if isinstance(device, str):
+        if device == "auto":
+            return torch.device("cuda" if torch.cuda.is_available() else "cpu")
+        return torch.device(device)
+    raise TypeError(f"Unsupported device spec: {device!r}")
+
+
+def _pair_on_device(gen: Tensor, tgt: Tensor):
+    if gen.shape != tgt.shape or gen.ndim != 4:
+        raise ValueError(f"expected two [N,C,H,W] tensors of equal shape, got {tuple(gen.shape)} vs {tuple(tgt.shape)}")
+    dev = nat.cuda_device_for(gen, tgt)
+    return nat.stage(gen, dev, torch.float32), nat.stage(tgt.detach(), dev, torch.float32), gen.device, dev
+
+
+class DeltaE00Loss(nn.Module):
+    """Mean CIEDE2000 (the reference's *loss* formula: eps inside every sqrt, wrapped hue, sin(d_theta)) between
+    two sRGB [0,1] images; one fused kernel yields the value and the gradient w.r.t. `gen_srgb01`
+    (losses.py:92-143).  Identical images give sqrt(eps) = 1e-3, not 0, exactly as the reference."""
+
+    def __init__(self, eps: float = 1e-6):
+        super().__init__()
+        self.eps = eps
+
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(self, gen_srgb01: Tensor, tgt_srgb01: Tensor) -> Tensor:
+        x, y, home, dev = _pair_on_device(gen_srgb01, tgt_srgb01)
+        if x.shape[1] != 3:
+            raise ValueError(f"DeltaE00Loss expects 3-channel sRGB inputs, got {x.shape[1]} channels")
+        out = Fn.DeltaE00LossFn.apply(x, y, float(self.eps))
+        return out if home == dev else out.to(home)
+
+
+class SSIMLoss(nn.Module):
+    """DSSIM = reduction(clamp((1 - SSIM) / 2, 0, 1)) with kornia 0.6.12's conventions (11-tap sigma-1.5
+    Gaussian, reflect border, C1 = (0.01 max_val)^2, C2 = (0.03 max_val)^2, eps 1e-12); inputs are clamped
+    to [0,1] (losses.py:146-155).  Forward is one separable-filter kernel, backward one adjoint-filter
+    kernel (csrc/ssim.cu)."""
+
+    def __init__(self, window_size: int = 11, max_val: float = 1.0, reduction: str = "mean"):
+        super().__init__()
+        if window_size <= 0 or window_size % 2 == 0:
+            raise ValueError(f"window_size must be a positive odd integer; received {window_size}.")
+        if window_size > 15:
+            raise NotImplementedError("the CUDA SSIM kernels support odd windows up to 15")
+        if reduction not in ("mean", "sum", "none"):
+            raise ValueError(f"Invalid reduction option: {reduction}")
+        self.window_size, self.max_val, self.reduction = int(window_size), float(max_val), reduction
+
+    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
+    def forward(self, gen_srgb01: Tensor, tgt_srgb01: Tensor) -> Tensor:
+        x, y, home, dev = _pair_on_device(gen_srgb01, tgt_srgb01)
+        p = self.window_size // 2
+        if p >= x.shape[2] or p >= x.shape[3] or self.window_size > x.shape[2] or self.window_size > x.shape[3]:
+            raise RuntimeError("Padding size should be less than the corresponding input dimension")
+        out = Fn.SSIMLossFn.apply(x, y, self.window_size, self.max_val, self.reduction)
+        return out if home == dev else out.to(home)
+
+
+class _L1Mean(nn.Module):
+    """nn.L1Loss() (global mean) with its sign/numel gradient: the physics projector with a 1x1 identity
+    stencil, i.e. one read of each tensor forward and one backward (losses.py:249, 332)."""
+
+    def forward(self, a: Tensor, b: Tensor) -> Tensor:
+        x, y, home, dev = _pair_on_device(a, b)
+        n, c = x.shape[:2]
+        psf = Fn.PreparedPSF(torch.ones(c, 1, 1, 1, dtype=torch.float32, device=dev), Fn.PSF_DEPTHWISE, 1, 1, False)
+        cfg = Fn.PhysCfg(nat.PAD["zeros"], False, False, 1e-12, 1, False, False)
+        out = Fn.PhysProjector.apply(x, y, psf, None, 1.0, (0, 0, 0, 0), cfg)[n]
+        return out if home == dev else out.to(home)
+
+
+class HybridLossPlus(nn.Module):
+    """Pluggable hybrid loss, same constructor / kwargs-only forward / `(total, logs)` contract as
+    losses.py:223-372.  L1, DeltaE00, DSSIM and the physics term run on the sm_100a kernels; the VGG
+    perceptual and LPIPS terms are NOT built here (no weight download) — pass `perceptual_module` /
+    `lpips_module` (any nn.Module mapping (gen, tgt) -> scalar / per-sample tensor) to include them.
+
+    The reference checks every term for finiteness as it goes (5-7 host syncs per step); here the terms are
+    checked together after the last one (a single sync), raising the same RuntimeError that names the first
+    offending term.  `check_finite=False` removes that sync (CUDA-graph capture)."""
+
+    def __init__(self, device: str = "cuda", w_l1_raw: float = 1.0, w_perc: float = 0.02, w_lpips: float = 0.0,
+                 w_deltaE: float = 0.02, w_ssim: float = 0.05, w_phys: float = 0.10, use_deltaE: bool = True,
+                 use_ssim: bool = True, use_lpips: bool = False, use_phys: bool = True, use_uncertainty: bool = False,
+                 physics_kernel: Optional[Tensor] = None, physics_psf_module: Optional[nn.Module] = None, *,
+                 perceptual_module: Optional[nn.Module] = None, lpips_module: Optional[nn.Module] = None,
+                 check_finite: bool = True):
+        super().__init__()
+        device = _resolve_device(device)
+        self.register_buffer("_zero", torch.tensor(0.0), persistent=False)
+        self._zero: Tensor
+        self.l1_raw = _L1Mean()
+        self.perc = perceptual_module
+        self.deltaE = DeltaE00Loss() if use_deltaE else None
+        self.ssim = SSIMLoss() if use_ssim else None
+        self.lpips = lpips_module if use_lpips else None
+        self.phys = (PhysicsConsistencyLoss(physics_kernel, device=device)
+                     if use_phys and physics_kernel is not None else None)
+        if use_phys and physics_psf_module is not None:
+            self.phys_srgb = PhysicalConsistencyLossSRGB(physics_psf_module.to(device))
+        else:
+            self.phys_srgb = None
+        self.use_uncertainty = use_uncertainty
+        self.check_finite = check_finite
+        if use_uncertainty:
+            self.log_sigma = nn.ParameterDict({k: nn.Parameter(torch.zeros(()))
+                                               for k in ("l1", "perc", "lpips", "de", "ssim", "phys")})
+        else:
+            self.w = dict(l1=w_l1_raw, perc=w_perc, lpips=w_lpips, de=w_deltaE, ssim=w_ssim, phys=w_phys)
+
+    @staticmethod
+    def _ensure_finite(name: str, value: Tensor):
+        """losses.py:298-306."""
+        if not torch.isfinite(value).all():
+            finite_vals = value[torch.isfinite(value)]
+            stats = ""
+            if finite_vals.numel() > 0:
+                stats = f" (finite min={finite_vals.min().item():.4e}, max={finite_vals.max().item():.4e})"
+            raise RuntimeError(f"HybridLossPlus detected non-finite values in term '{name}'.{stats}")
+
+    def _weighted(self, name: str, val: Optional[Tensor]):
+        """losses.py:308-316."""
+        if val is None:
+            zero = self._zero.clone()
+            return zero, zero.detach()
+        if self.use_uncertainty:
+            s = self.log_sigma[name]
+            return (val * torch.exp(-2 * s.to(val.device)) + s.to(val.device)), val.detach()
+        return self.w[name] * val, val.detach()
+
+    def forward(self, *, Bhat_raw: Tensor, B_raw: Tensor, A_raw: Tensor, expo_ratio: Tensor, Bhat_srgb01: Tensor,
+                B_srgb01: Tensor, A_srgb01: Optional[Tensor] = None):
+        logs: Dict[str, Tensor] = {}
+        terms = []          # (check name, value) in the reference's order
+        total = 0.0
+
+        def add(check_name, key, log_name, val):
+            nonlocal total
+            terms.append((check_name, val))
+            lw, logs[log_name] = self._weighted(key, val)
+            total = total + lw
+
+        add("L1_raw", "l1", "L1_raw", self.l1_raw(Bhat_raw, B_raw))
+        if self.perc is not None:
+            add("Perc", "perc", "Perc", self.perc(Bhat_srgb01, B_srgb01))
+        else:
+            logs["Perc"] = self._zero.clone().to(Bhat_raw.device)
+        if self.lpips is not None:
+            add("LPIPS", "lpips", "LPIPS", self.lpips(Bhat_srgb01, B_srgb01).mean())
+        if self.deltaE is not None:
+            add("DeltaE", "de", "DeltaE", self.deltaE(Bhat_srgb01, B_srgb01))
+        if self.ssim is not None:
+            add("SSIM", "ssim", "SSIM", self.ssim(Bhat_srgb01, B_srgb01))
+        if self.phys is not None:
+            add("Phys_raw", "phys", "Phys", self.phys(Bhat_raw, A_raw, expo_ratio))
+        elif self.phys_srgb is not None and A_srgb01 is not None:
+            add("Phys_srgb", "phys", "Phys", self.phys_srgb(Bhat_srgb01, A_srgb01, expo_ratio))
+        if self.check_finite:
+            vals = torch.stack([v.detach().reshape(()).float() for _, v in terms])
+            if not bool(torch.isfinite(vals).all()):                      # the one host sync of the step
+                for (name, v) in terms:
+                    self._ensure_finite(name, v.detach())
+        logs["Total"] = total.detach()
+        return total, logs

@@ -436,3 +436,97 @@ def select_quantiles(values: Tensor, qs, *, joint: bool, gate: Optional[Tensor] 
     nat.check(rc, "llie_select_quantiles")
     nat.count_launch(6)
     return out_q, cnt, sums
+
+
+# ------------------------------------------------------------------------------------------------
+# Differentiable loss terms (NewBP_model/losses.py:92-155)
+# ------------------------------------------------------------------------------------------------
+class DeltaE00LossFn(torch.autograd.Function):
+    """mean dE00 (loss variant) of clamp(gen,0,1) vs clamp(tgt,0,1); the gradient w.r.t. `gen` is produced by
+    the same kernel pass as the value (llie_deltae_loss_grad) and only scaled in backward."""
+
+    @staticmethod
+    def forward(ctx, gen: Tensor, tgt: Tensor, eps: float):
+        x = gen.detach().contiguous()
+        y = tgt.detach().contiguous()
+        dev = x.device
+        n, _, h, w = x.shape
+        sums = torch.empty(n, dtype=torch.float64, device=dev)
+        flags = torch.empty(1, dtype=torch.int32, device=dev)
+        d = nat.DeltaEDesc(n, h, w, 1, 0, 1, 1.0, 1.0, 1.0, float(eps))
+        if ctx.needs_input_grad[0]:
+            grad = torch.empty_like(x)
+            with torch.cuda.device(dev):
+                rc = nat.lib().llie_deltae_loss_grad(d, nat.ptr(x), nat.ptr(y), 1.0 / (n * h * w), nat.ptr(sums),
+                                                     nat.ptr(grad), nat.ptr(flags), nat.ptr(nat.workspace(dev)),
+                                                     nat.stream_ptr(dev))
+            nat.check(rc, "llie_deltae_loss_grad")
+            ctx.save_for_backward(grad)
+        else:
+            with torch.cuda.device(dev):
+                rc = nat.lib().llie_deltae(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), None, None, nat.ptr(flags),
+                                           nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+            nat.check(rc, "llie_deltae")
+        nat.count_launch()
+        # float32 mean over N*H*W like dE.mean(); the sum itself is carried in float64
+        return (sums.sum() / float(n * h * w)).to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, gout):
+        (grad,) = ctx.saved_tensors
+        return grad * gout, None, None
+
+
+class SSIMLossFn(torch.autograd.Function):
+    """kornia-policy DSSIM: reduction(clamp((1 - SSIM(clamp(x), clamp(y))) / 2, 0, 1)), reduction in
+    {'mean','sum','none'}; forward stores three coefficient planes, backward is one adjoint-filter kernel."""
+
+    @staticmethod
+    def forward(ctx, gen: Tensor, tgt: Tensor, window_size: int, max_val: float, reduction: str):
+        x = gen.detach().contiguous()
+        y = tgt.detach().contiguous()
+        dev = x.device
+        n, c, h, w = x.shape
+        win = window_1d("kornia", int(window_size), 1.5, dev)
+        c1, c2 = (0.01 * max_val) ** 2, (0.03 * max_val) ** 2
+        d = nat.SsimDesc(n, c, h, w, int(window_size), nat.PAD["reflect"], 0, 1, 0, 0, 1, c1, c2, 1e-12)
+        sums = torch.empty((n, c), dtype=torch.float64, device=dev)
+        flags = torch.empty(1, dtype=torch.int32, device=dev)
+        want_map = reduction == "none"
+        smap = torch.empty((n, c, h, w), dtype=torch.float32, device=dev) if want_map else None
+        scale = 1.0 / (n * c * h * w) if reduction == "mean" else 1.0
+        need_grad = ctx.needs_input_grad[0]
+        with torch.cuda.device(dev):
+            if need_grad:
+                coef = torch.empty((3, n, c, h, w), dtype=torch.float32, device=dev)
+                rc = nat.lib().llie_ssim_loss_forward(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), scale, nat.ptr(sums),
+                                                      nat.ptr(smap), nat.ptr(coef), nat.ptr(flags),
+                                                      nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+                ctx.save_for_backward(x, y, win, coef)
+                ctx.desc = d
+            else:
+                rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(sums), nat.ptr(smap),
+                                               nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+        nat.check(rc, "llie_ssim_loss_forward")
+        nat.count_launch()
+        ctx.reduction = reduction
+        if want_map:
+            return torch.clamp((1.0 - smap) * 0.5, 0.0, 1.0)
+        tot = sums.sum()
+        if reduction == "mean":
+            tot = tot / float(n * c * h * w)
+        return tot.to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, y, win, coef = ctx.saved_tensors
+        dev = x.device
+        is_map = ctx.reduction == "none"
+        g = gout.detach().to(torch.float32).contiguous()
+        out = torch.empty_like(x)
+        with torch.cuda.device(dev):
+            rc = nat.lib().llie_ssim_loss_backward(ctx.desc, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(coef),
+                                                   nat.ptr(g), int(is_map), nat.ptr(out), nat.stream_ptr(dev))
+        nat.check(rc, "llie_ssim_loss_backward")
+        nat.count_launch()
+        return out, None, None, None, None

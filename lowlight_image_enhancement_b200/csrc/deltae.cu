@@ -198,6 +198,199 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
     if (threadIdx.x == 0) *a.out_flags = ff;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// LOSS variant with its gradient w.r.t. (L1, a1, b1): forward-mode duals with three tangents carried in
+// registers next to the value, so the ~60-op chain of losses.py:99-136 is differentiated in the same pass
+// that evaluates it (autograd: ~40 saved planes and ~90 replayed kernels).  Each rule is the one ATen's
+// autograd applies (sqrt: g/(2 sqrt); atan2: (x dy - y dx)/(x^2 + y^2), 0 at the origin like ATen;
+// `%`, comparisons and masks carry no gradient).
+struct D3 {
+    float v, x, y, z;
+};
+__device__ __forceinline__ D3 dconst(float v) { return {v, 0.f, 0.f, 0.f}; }
+__device__ __forceinline__ D3 operator+(D3 a, D3 b) { return {a.v + b.v, a.x + b.x, a.y + b.y, a.z + b.z}; }
+__device__ __forceinline__ D3 operator-(D3 a, D3 b) { return {a.v - b.v, a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ D3 operator+(D3 a, float b) { return {a.v + b, a.x, a.y, a.z}; }
+__device__ __forceinline__ D3 operator-(D3 a, float b) { return {a.v - b, a.x, a.y, a.z}; }
+__device__ __forceinline__ D3 operator-(float a, D3 b) { return {a - b.v, -b.x, -b.y, -b.z}; }
+__device__ __forceinline__ D3 operator-(D3 a) { return {-a.v, -a.x, -a.y, -a.z}; }
+__device__ __forceinline__ D3 operator*(float s, D3 a) { return {s * a.v, s * a.x, s * a.y, s * a.z}; }
+__device__ __forceinline__ D3 operator*(D3 a, D3 b) {
+    return {a.v * b.v, fmaf(a.x, b.v, a.v * b.x), fmaf(a.y, b.v, a.v * b.y), fmaf(a.z, b.v, a.v * b.z)};
+}
+__device__ __forceinline__ D3 operator/(D3 a, D3 b) {
+    const float inv = 1.0f / b.v, q = a.v * inv;
+    return {q, (a.x - q * b.x) * inv, (a.y - q * b.y) * inv, (a.z - q * b.z) * inv};
+}
+__device__ __forceinline__ D3 dchain(float v, float dv, D3 a) { return {v, dv * a.x, dv * a.y, dv * a.z}; }
+__device__ __forceinline__ D3 dsqrt(D3 a) {
+    const float r = sqrtf(a.v);
+    return dchain(r, 0.5f / r, a);
+}
+__device__ __forceinline__ D3 dsin(D3 a) {
+    float s, c;
+    sincosf(a.v, &s, &c);
+    return dchain(s, c, a);
+}
+__device__ __forceinline__ D3 dcos(D3 a) {
+    float s, c;
+    sincosf(a.v, &s, &c);
+    return dchain(c, -s, a);
+}
+__device__ __forceinline__ D3 dexp(D3 a) {
+    const float e = expf(a.v);
+    return dchain(e, e, a);
+}
+__device__ __forceinline__ D3 dpow7(D3 a) {
+    const float v2 = a.v * a.v, v3 = v2 * a.v, v6 = v3 * v3;
+    return dchain(v6 * a.v, 7.0f * v6, a);
+}
+__device__ __forceinline__ D3 datan2(D3 y, D3 x) {
+    const float den = x.v * x.v + y.v * y.v;
+    const float r = den == 0.0f ? 0.0f : 1.0f / den;  // ATen: zero gradient at the origin
+    return {atan2f(y.v, x.v), (x.v * y.x - y.v * x.x) * r, (x.v * y.y - y.v * x.y) * r, (x.v * y.z - y.v * x.z) * r};
+}
+
+// dE00 (loss variant) and d dE00 / d(L1, a1, b1); (L2, a2, b2) are constants
+__device__ D3 de00_loss_dual(float L1f, float a1f, float b1f, float L2, float a2, float b2, float eps) {
+    const D3 L1{L1f, 1.f, 0.f, 0.f}, a1{a1f, 0.f, 1.f, 0.f}, b1{b1f, 0.f, 0.f, 1.f};
+    const float k25 = 6103515625.0f;
+    const D3 c1 = dsqrt(a1 * a1 + b1 * b1 + eps);
+    const float c2 = sqrtf(a2 * a2 + b2 * b2 + eps);
+    const D3 cb = 0.5f * (c1 + c2);
+    const D3 cb7 = dpow7(cb);
+    const D3 g = 0.5f * (1.0f - dsqrt(cb7 / (cb7 + (k25 + eps))));
+    const D3 g1 = g + 1.0f;
+    const D3 a1p = g1 * a1, a2p = a2 * g1;
+    const D3 c1p = dsqrt(a1p * a1p + b1 * b1 + eps), c2p = dsqrt(a2p * a2p + (b2 * b2 + eps));
+    D3 h1 = datan2(b1, a1p), h2 = datan2(dconst(b2), a2p);
+    h1.v = pymod(h1.v, 2.0f * kPi);
+    h2.v = pymod(h2.v, 2.0f * kPi);
+    const D3 dL = L2 - L1, dC = c2p - c1p;
+    D3 dh = h2 - h1;
+    dh.v = dh.v - (dh.v > kPi ? 2.0f * kPi : 0.0f) + (dh.v < -kPi ? 2.0f * kPi : 0.0f);
+    const D3 dH = 2.0f * (dsqrt(c1p * c2p + eps) * dsin(0.5f * dh));
+    const D3 Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
+    const D3 hs = h1 + h2;
+    D3 hb = 0.5f * hs;
+    hb.v = hs.v / 2.0f - (fabsf(h1.v - h2.v) > kPi ? kPi : 0.0f) + (hs.v < 0.0f ? 2.0f * kPi : 0.0f);
+    const D3 t = (1.0f - 0.17f * dcos(hb - deg2rad(30.0f))) + 0.24f * dcos(2.0f * hb) +
+                 0.32f * dcos(3.0f * hb + deg2rad(6.0f)) - 0.20f * dcos(4.0f * hb - deg2rad(63.0f));
+    const D3 q = (1.0f / 25.0f) * ((180.0f / kPi) * hb - 275.0f);
+    const D3 dro = 30.0f * dexp(-(q * q));
+    const D3 Cb7 = dpow7(Cb);
+    const D3 rc = 2.0f * dsqrt(Cb7 / (Cb7 + (k25 + eps)));
+    const D3 l50 = (Lb - 50.0f) * (Lb - 50.0f);
+    const D3 sL = (0.015f * l50) / dsqrt(l50 + (20.0f + eps)) + 1.0f;
+    const D3 sC = 0.045f * Cb + 1.0f;
+    const D3 sH = 0.015f * (Cb * t) + 1.0f;
+    const D3 rt = -(dsin((kPi / 180.0f) * dro) * rc);
+    const D3 lt = dL / sL, ct = dC / sC, ht = dH / sH;
+    return dsqrt(lt * lt + ct * ct + ht * ht + rt * (ct * ht) + eps);
+}
+
+// sRGB channel -> linear with derivative (autograd of where(c > .04045, pow(.., 2.4), c / 12.92))
+__device__ __forceinline__ float srgb_to_linear_d(float c, float &dc) {
+    if (c > 0.04045f) {
+        const float base = (c + 0.055f) / 1.055f, v = powf(base, 2.4f);
+        dc = (2.4f / 1.055f) * (v / base);  // 2.4 base^1.4 / 1.055
+        return v;
+    }
+    dc = 1.0f / 12.92f;
+    return c / 12.92f;
+}
+__device__ __forceinline__ float lab_f_d(float t, float &dt) {
+    if (t > 0.008856f) {
+        const float v = powf(t, 1.0f / 3.0f);  // the reference's exponent is float(1/3), not an exact cube root
+        dt = (1.0f / 3.0f) * (v / t);          // t^(-2/3) / 3
+        return v;
+    }
+    dt = 7.787f;
+    return 7.787f * t + 4.0f / 29.0f;
+}
+
+struct DeGradArgs {
+    int n, h, w, clamp_in;
+    float eps, scale;
+    const float *x, *y;
+    double *out_sum;
+    float *out_grad;
+    int *out_flags;
+    double *part;
+    int *pflag;
+    unsigned *ticket;
+};
+
+// losses.py:138-143 value (per-image sums) + `scale` * d dE / d x, one pass: 24 B/px read, 12 B/px written
+__global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs a) {
+    __shared__ double red[32];
+    const int n = blockIdx.y, G = gridDim.x;
+    const long long plane = (long long)a.h * a.w;
+    const float *x0 = a.x + (long long)n * 3 * plane, *y0 = a.y + (long long)n * 3 * plane;
+    float *g0 = a.out_grad + (long long)n * 3 * plane;
+    float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
+         i += (long long)G * blockDim.x) {
+        const float r0 = __ldcs(x0 + i), r1 = __ldcs(x0 + plane + i), r2 = __ldcs(x0 + 2 * plane + i);
+        float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
+        chk_x = fmaf(r0, 0.f, fmaf(r1, 0.f, fmaf(r2, 0.f, chk_x)));
+        chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
+        float p0 = r0, p1 = r1, p2 = r2;
+        float m0 = 1.f, m1 = 1.f, m2 = 1.f;  // clamp pass-through masks (ATen: min <= x <= max)
+        if (a.clamp_in) {
+            m0 = (r0 >= 0.f && r0 <= 1.f) ? 1.f : 0.f;
+            m1 = (r1 >= 0.f && r1 <= 1.f) ? 1.f : 0.f;
+            m2 = (r2 >= 0.f && r2 <= 1.f) ? 1.f : 0.f;
+            p0 = fminf(fmaxf(p0, 0.f), 1.f); p1 = fminf(fmaxf(p1, 0.f), 1.f); p2 = fminf(fmaxf(p2, 0.f), 1.f);
+            t0 = fminf(fmaxf(t0, 0.f), 1.f); t1 = fminf(fmaxf(t1, 0.f), 1.f); t2 = fminf(fmaxf(t2, 0.f), 1.f);
+        }
+        float d0, d1, d2;
+        const float l0 = srgb_to_linear_d(p0, d0), l1 = srgb_to_linear_d(p1, d1), l2 = srgb_to_linear_d(p2, d2);
+        const float X = 0.412453f * l0 + 0.357580f * l1 + 0.180423f * l2;
+        const float Y = 0.212671f * l0 + 0.715160f * l1 + 0.072169f * l2;
+        const float Z = 0.019334f * l0 + 0.119193f * l1 + 0.950227f * l2;
+        float dfx, dfy, dfz;
+        const float fx = lab_f_d(X / 0.95047f, dfx), fy = lab_f_d(Y / 1.0f, dfy), fz = lab_f_d(Z / 1.08883f, dfz);
+        const float L1 = 116.0f * fy - 16.0f, A1 = 500.0f * (fx - fy), B1 = 200.0f * (fy - fz);
+        float L2, A2, B2;
+        rgb_to_lab(t0, t1, t2, L2, A2, B2);
+        const D3 de = de00_loss_dual(L1, A1, B1, L2, A2, B2, a.eps);
+        acc += de.v;
+        // reverse through Lab -> f -> XYZ -> linear -> sRGB
+        const float gfx = 500.0f * de.y, gfy = 116.0f * de.x - 500.0f * de.y + 200.0f * de.z, gfz = -200.0f * de.z;
+        const float gX = gfx * dfx / 0.95047f, gY = gfy * dfy, gZ = gfz * dfz / 1.08883f;
+        const float gl0 = 0.412453f * gX + 0.212671f * gY + 0.019334f * gZ;
+        const float gl1 = 0.357580f * gX + 0.715160f * gY + 0.119193f * gZ;
+        const float gl2 = 0.180423f * gX + 0.072169f * gY + 0.950227f * gZ;
+        // where()-style masking: a clamped-away channel gets exactly 0 even when the chain holds NaN
+        __stcs(g0 + i, m0 != 0.f ? a.scale * gl0 * d0 : 0.f);
+        __stcs(g0 + plane + i, m1 != 0.f ? a.scale * gl1 * d1 : 0.f);
+        __stcs(g0 + 2 * plane + i, m2 != 0.f ? a.scale * gl2 * d2 : 0.f);
+    }
+    const double bs = block_sum<double>((double)acc, red);
+    int flag = 0;
+    if (!(chk_x == 0.f)) flag |= 1;
+    if (!(chk_y == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        a.part[(size_t)n * G + blockIdx.x] = bs;
+        a.pflag[(size_t)n * G + blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x * gridDim.y)) return;
+    const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
+    for (int s = wrp; s < a.n; s += 8) {
+        const double *p = a.part + (size_t)s * G;
+        double s0 = 0.0;
+        for (int b = lane; b < G; b += 32) s0 += __ldcg(p + b);
+        const double t = warp_sum(s0);
+        if (lane == 0) a.out_sum[s] = t;
+    }
+    int fl = 0;
+    for (int b = threadIdx.x; b < G * a.n; b += blockDim.x) fl |= __ldcg(a.pflag + b);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) *a.out_flags = ff;
+}
+
 // Sobel magnitude of a [planes, H, W] stack, zero padding (color_error.py:23-30, 296-301).  Products and
 // sums are kept un-contracted (no FMA) so that the result is the IEEE value torch computes.
 __global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, int H, int W, long long planes) {
@@ -258,6 +451,34 @@ extern "C" int llie_deltae(const llie_deltae_desc *desc, const float *x, const f
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
     deltae_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const float *y, float grad_scale,
+                                     double *out_sum, float *out_grad, int32_t *out_flags, void *workspace,
+                                     void *stream) {
+    LLIE_REQUIRE(desc && x && y && out_sum && out_grad && out_flags && workspace, "deltae_loss_grad: null pointer");
+    LLIE_REQUIRE(desc->n > 0 && desc->h > 0 && desc->w > 0, "deltae_loss_grad: empty tensor");
+    LLIE_REQUIRE(desc->n <= 65535, "deltae_loss_grad: batch too large for grid.y");
+    LLIE_REQUIRE(desc->variant == 1 && !desc->input_lab, "deltae_loss_grad: loss variant on sRGB inputs only");
+    DeGradArgs a{};
+    a.n = desc->n; a.h = desc->h; a.w = desc->w; a.clamp_in = desc->clamp_in;
+    a.eps = desc->eps; a.scale = grad_scale;
+    a.x = x; a.y = y; a.out_sum = out_sum; a.out_grad = out_grad; a.out_flags = out_flags;
+    const long long plane = (long long)desc->h * desc->w;
+    int G = div_up(kNumSM * 8, desc->n);
+    const long long maxg = (plane + 255) / 256;
+    if (G > maxg) G = (int)maxg;
+    if (G < 1) G = 1;
+    Workspace ws(workspace);
+    const size_t slots = (size_t)G * desc->n;
+    LLIE_REQUIRE(slots * (sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "deltae_loss_grad: workspace too small");
+    a.part = reinterpret_cast<double *>(ws.scratch);
+    a.pflag = reinterpret_cast<int *>(ws.scratch + slots * sizeof(double));
+    a.ticket = ws.tickets;
+    dim3 grid(G, desc->n);
+    deltae_loss_grad_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

@@ -22,6 +22,8 @@ struct SsimArgs {
     const float *x, *y, *win;
     double *out_sum;
     float *out_map;
+    float *coef;       // NULL or [3][planes][H][W]: dLoss/dS * (A1, A2, A3) for ssim_loss_bwd_kernel
+    float coef_scale;  // 1 / numel for reduction 'mean'
     int *out_flags;
     double *part;  // [planes][tiles_per_plane]
     int *pflag;    // [gridDim.x]
@@ -165,6 +167,23 @@ __global__ void __launch_bounds__(SNT, 2) ssim_stats_kernel(const SsimArgs a) {
         const float den = (mx2 + my2 + d.c1) * (sx + sy + d.c2) + d.eps;
         float s = num / den;
         if (a.out_map != nullptr && gy < H && gx < W) a.out_map[((long long)plane * H + gy) * W + gx] = s;
+        if (a.coef != nullptr && gy < H && gx < W) {
+            // S as a function of (mu_x, E[x^2], E[xy]) at this window:
+            //   A3 = dS/dsigma_xy, A2 = dS/dsigma_x^2, A1 = dS/dmu_x - 2 mu_x A2 - mu_y A3
+            const float l = (1.f - s) * 0.5f;
+            const float up = (!d.loss_map) ? a.coef_scale : ((l >= 0.f && l <= 1.f) ? -0.5f * a.coef_scale : 0.f);
+            const float inv = 1.f / den;
+            const float n1 = 2.f * mxy + d.c1, n2 = 2.f * sxy + d.c2, d1 = mx2 + my2 + d.c1, d2 = sx + sy + d.c2;
+            const float a3 = 2.f * n1 * inv;
+            const float a2 = -s * d1 * inv;
+            const float dmu = 2.f * (my * n2 - s * mx * d2) * inv;
+            const float a1 = dmu - 2.f * mx * a2 - my * a3;
+            const long long stride = (long long)d.n * a.co * plane_elems;
+            float *cp = a.coef + ((long long)plane * H + gy) * W + gx;
+            cp[0] = up * a1;
+            cp[stride] = up * a2;
+            cp[2 * stride] = up * a3;
+        }
         if (d.loss_map) s = fminf(fmaxf((1.f - s) * 0.5f, 0.f), 1.f);
         if (gy >= lo_y && gy < hi_y && gx >= lo_x && gx < hi_x) facc += s;
     }
@@ -213,12 +232,185 @@ static int launch_ssim(const SsimArgs &a, int grid, cudaStream_t st) {
     return LLIE_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Backward of the (D)SSIM sum w.r.t. x (kornia policy: reflect border, "same" size):
+//   dL/dx(q) = mask(q) * g_up * [ (G^T c1)(q) + 2 x(q) (G^T c2)(q) + y(q) (G^T c3)(q) ]
+// where c1..c3 are the coefficient maps the forward kernel stored and G^T is the adjoint of
+// reflect-pad o separable correlation: a zero-extended correlation t(j) on j in [-P, W+P) whose out-of-image
+// taps fold back, out(q) = t(q) + [1 <= q <= P] t(-q) + [W-1-P <= q <= W-2] t(2W-2-q), per axis.
+// Same tiling as the forward kernel: (A) coefficient tile with halo (zeros outside the image) -> smem,
+// (B) horizontal pass + column folds, (C) vertical pass + row folds, combine with x, y (8 B/elem read).
+struct SsimBwdArgs {
+    int n, c, h, w, clamp_in, gout_is_map;
+    const float *x, *y, *win, *coef;
+    const float *gout;  // device scalar (upstream gradient of the reduced loss) or a [n,c,h,w] map
+    float *out_grad;
+    int tiles_x, tiles_y;
+};
+
+template <int K>
+__device__ __forceinline__ float fold_extra(const float *line, int stride, int q, int o0, int L, const float *sg) {
+    // line[(p - o0) * stride] holds the zero-extended sequence at image coordinate p
+    constexpr int P = K / 2;
+    float e = 0.f;
+    if (q >= 1 && q <= P)
+        for (int p = 0; p <= P - q && p < L; ++p) e = fmaf(sg[p + q + P], line[(p - o0) * stride], e);
+    if (q >= L - 1 - P && q <= L - 2) {
+        const int qq = 2 * L - 2 - q;
+        for (int p = max(qq - P, 0); p <= L - 1; ++p) e = fmaf(sg[p - qq + P], line[(p - o0) * stride], e);
+    }
+    return e;
+}
+
+template <int K>
+__global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs a) {
+    constexpr int P = K / 2;
+    constexpr int XR = STH + 2 * P;
+    constexpr int XP = (STW + 2 * P) | 1;
+    constexpr int HP = STW + 1;
+    extern __shared__ __align__(16) float sm[];
+    float *sC = sm;                   // [3][XR][XP]
+    float *sH = sC + 3 * XR * XP;     // [3][XR][HP]
+    __shared__ float sg[K];
+    const int H = a.h, W = a.w, tid = threadIdx.x;
+    const int tpp = a.tiles_x * a.tiles_y;
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int ty = trem / a.tiles_x, tx = trem - ty * a.tiles_x;
+    const int y0 = ty * STH, x0 = tx * STW;
+    const long long plane_elems = (long long)H * W;
+    const long long stride = (long long)a.n * a.c * plane_elems;
+    const float *cb = a.coef + (long long)plane * plane_elems;
+    const float *gm = a.gout_is_map ? a.gout + (long long)plane * plane_elems : nullptr;
+    const float gs = a.gout_is_map ? 1.f : __ldg(a.gout);
+
+    float g[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
+    if (tid < K) sg[tid] = __ldg(a.win + tid);
+
+    // ---- (A) coefficient tiles, zero outside the image
+    for (int idx = tid; idx < XR * (STW + 2 * P); idx += SNT) {
+        const int r = idx / (STW + 2 * P), cc = idx - r * (STW + 2 * P);
+        const int sy = y0 - P + r, sx = x0 - P + cc;
+        float v1 = 0.f, v2 = 0.f, v3 = 0.f;
+        if (sy >= 0 && sy < H && sx >= 0 && sx < W) {
+            const long long off = (long long)sy * W + sx;
+            const float up = gm ? __ldg(gm + off) : gs;
+            v1 = up * __ldg(cb + off);
+            v2 = up * __ldg(cb + stride + off);
+            v3 = up * __ldg(cb + 2 * stride + off);
+        }
+        sC[r * XP + cc] = v1;
+        sC[XR * XP + r * XP + cc] = v2;
+        sC[2 * XR * XP + r * XP + cc] = v3;
+    }
+    __syncthreads();
+
+    // ---- (B) horizontal pass (+ column folds on the tiles that touch the left / right image border)
+    const bool fold_x = (x0 <= P) || (x0 + STW > W - 1 - P);
+    for (int t = tid; t < XR * (STW / 4); t += SNT) {
+        const int cg = t / XR, r = t - cg * XR;
+        float acc[3][4];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const float *px = sC + q * XR * XP + r * XP + cg * 4;
+#pragma unroll
+            for (int o = 0; o < 4; ++o) acc[q][o] = 0.f;
+#pragma unroll
+            for (int u = 0; u < K + 3; ++u) {
+                const float v = px[u];
+#pragma unroll
+                for (int o = 0; o < 4; ++o) {
+                    const int j = u - o;
+                    if (j >= 0 && j < K) acc[q][o] = fmaf(g[j], v, acc[q][o]);
+                }
+            }
+        }
+        if (fold_x) {
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                const int qx = x0 + cg * 4 + o;
+                if (qx < W && (qx <= P || qx >= W - 1 - P)) {
+#pragma unroll
+                    for (int q = 0; q < 3; ++q)
+                        acc[q][o] += fold_extra<K>(sC + q * XR * XP + r * XP, 1, qx, x0 - P, W, sg);
+                }
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            float *h = sH + q * XR * HP + r * HP + cg * 4;
+#pragma unroll
+            for (int o = 0; o < 4; ++o) h[o] = acc[q][o];
+        }
+    }
+    __syncthreads();
+
+    // ---- (C) vertical pass (+ row folds), combine
+    const int col = tid & (STW - 1), rg = tid / STW;
+    const int gx = x0 + col;
+    float m[3][8];
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        const float *h = sH + q * XR * HP + (rg * 8) * HP + col;
+#pragma unroll
+        for (int o = 0; o < 8; ++o) m[q][o] = 0.f;
+#pragma unroll
+        for (int u = 0; u < K + 7; ++u) {
+            const float v = h[u * HP];
+#pragma unroll
+            for (int o = 0; o < 8; ++o) {
+                const int j = u - o;
+                if (j >= 0 && j < K) m[q][o] = fmaf(g[j], v, m[q][o]);
+            }
+        }
+    }
+    const bool fold_y = (y0 <= P) || (y0 + STH > H - 1 - P);
+    if (gx >= W) return;
+    const float *xb = a.x + (long long)plane * plane_elems, *yb = a.y + (long long)plane * plane_elems;
+    float *ob = a.out_grad + (long long)plane * plane_elems;
+#pragma unroll
+    for (int o = 0; o < 8; ++o) {
+        const int gy = y0 + rg * 8 + o;
+        if (gy >= H) break;
+        float g1 = m[0][o], g2 = m[1][o], g3 = m[2][o];
+        if (fold_y && (gy <= P || gy >= H - 1 - P)) {
+            g1 += fold_extra<K>(sH + col, HP, gy, y0 - P, H, sg);
+            g2 += fold_extra<K>(sH + XR * HP + col, HP, gy, y0 - P, H, sg);
+            g3 += fold_extra<K>(sH + 2 * XR * HP + col, HP, gy, y0 - P, H, sg);
+        }
+        const long long off = (long long)gy * W + gx;
+        const float xr = __ldg(xb + off);
+        float xv = xr, yv = __ldg(yb + off);
+        bool pass = true;
+        if (a.clamp_in) {
+            pass = (xr >= 0.f && xr <= 1.f);
+            xv = fminf(fmaxf(xv, 0.f), 1.f);
+            yv = fminf(fmaxf(yv, 0.f), 1.f);
+        }
+        const float gr = g1 + 2.f * xv * g2 + yv * g3;
+        ob[off] = pass ? gr : 0.f;
+    }
+}
+
+template <int K>
+static int launch_ssim_bwd(const SsimBwdArgs &a, int grid, cudaStream_t st) {
+    constexpr int P = K / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
+    const size_t smem = (size_t)(3 * XR * XP + 3 * XR * HP) * sizeof(float);
+    LLIE_CUDA_OK(cudaFuncSetAttribute(ssim_loss_bwd_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ssim_loss_bwd_kernel<K><<<grid, SNT, smem, st>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
 }  // namespace llie
 
 using namespace llie;
 
-extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                               double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream) {
+static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d, double *out_sum,
+                        float *out_map, float *coef, float coef_scale, int32_t *out_flags, void *workspace,
+                        void *stream) {
     LLIE_REQUIRE(desc && x && y && win1d && out_sum && out_flags && workspace, "ssim_stats: null pointer");
     const llie_ssim_desc &d = *desc;
     LLIE_REQUIRE(d.n > 0 && d.c > 0 && d.h > 0 && d.w > 0, "ssim_stats: empty tensor");
@@ -232,6 +424,7 @@ extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const
     a.d = d;
     a.x = x; a.y = y; a.win = win1d;
     a.out_sum = out_sum; a.out_map = out_map; a.out_flags = out_flags;
+    a.coef = coef; a.coef_scale = coef_scale;
     a.co = d.luma ? 1 : d.c;
     a.tiles_x = div_up(d.w, STW);
     a.tiles_y = div_up(d.h, STH);
@@ -252,5 +445,51 @@ extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const
         case 11: return launch_ssim<11>(a, (int)grid, st);
         case 13: return launch_ssim<13>(a, (int)grid, st);
         default: return launch_ssim<15>(a, (int)grid, st);
+    }
+}
+
+extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                               double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream) {
+    return ssim_forward(desc, x, y, win1d, out_sum, out_map, nullptr, 0.f, out_flags, workspace, stream);
+}
+
+extern "C" int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                                      float grad_scale, double *out_sum, float *out_map, float *out_coef,
+                                      int32_t *out_flags, void *workspace, void *stream) {
+    LLIE_REQUIRE(desc && out_coef, "ssim_loss_forward: null pointer");
+    LLIE_REQUIRE(desc->pad_mode == LLIE_PAD_REFLECT && !desc->luma && !desc->clamp_var && !desc->interior,
+                 "ssim_loss_forward: the differentiable path is the kornia policy (reflect, same size, no clamps)");
+    LLIE_REQUIRE(desc->ksize / 2 < desc->h && desc->ksize / 2 < desc->w, "ssim_loss_forward: reflect pad >= image");
+    return ssim_forward(desc, x, y, win1d, out_sum, out_map, out_coef, grad_scale, out_flags, workspace, stream);
+}
+
+extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                                       const float *coef, const float *grad_out, int32_t grad_out_is_map,
+                                       float *out_grad, void *stream) {
+    LLIE_REQUIRE(desc && x && y && win1d && coef && grad_out && out_grad, "ssim_loss_backward: null pointer");
+    const llie_ssim_desc &d = *desc;
+    LLIE_REQUIRE(d.n > 0 && d.c > 0 && d.h > 0 && d.w > 0, "ssim_loss_backward: empty tensor");
+    LLIE_REQUIRE(d.ksize >= 1 && (d.ksize & 1) && d.ksize <= LLIE_SSIM_MAX_K, "ssim_loss_backward: bad window");
+    LLIE_REQUIRE(d.pad_mode == LLIE_PAD_REFLECT && !d.luma && !d.clamp_var && !d.interior,
+                 "ssim_loss_backward: kornia policy only");
+    LLIE_REQUIRE(d.ksize / 2 < d.h && d.ksize / 2 < d.w && d.ksize <= d.h && d.ksize <= d.w,
+                 "ssim_loss_backward: window larger than the image");
+    SsimBwdArgs a{};
+    a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map;
+    a.x = x; a.y = y; a.win = win1d; a.coef = coef; a.gout = grad_out; a.out_grad = out_grad;
+    a.tiles_x = div_up(d.w, STW);
+    a.tiles_y = div_up(d.h, STH);
+    const long long grid = (long long)d.n * d.c * a.tiles_x * a.tiles_y;
+    LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    switch (d.ksize) {
+        case 1: return launch_ssim_bwd<1>(a, (int)grid, st);
+        case 3: return launch_ssim_bwd<3>(a, (int)grid, st);
+        case 5: return launch_ssim_bwd<5>(a, (int)grid, st);
+        case 7: return launch_ssim_bwd<7>(a, (int)grid, st);
+        case 9: return launch_ssim_bwd<9>(a, (int)grid, st);
+        case 11: return launch_ssim_bwd<11>(a, (int)grid, st);
+        case 13: return launch_ssim_bwd<13>(a, (int)grid, st);
+        default: return launch_ssim_bwd<15>(a, (int)grid, st);
     }
 }

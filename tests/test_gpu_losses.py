@@ -1,0 +1,213 @@
+"""GPU parity: DeltaE00Loss / SSIMLoss / HybridLossPlus (value + analytic gradient) vs autograd through the
+CPU oracle.  Tolerance from BASELINE.json: 1e-5 relative for fp32 losses and gradients; a gradient is
+compared max-norm-wise against the float64 run of the oracle.  dE00 gradients are ill-conditioned where
+the two colours are close (dE ~ 1: every term is a difference of nearly equal fp32 numbers) or neutral
+(1 / (a^2 + b^2) amplification); there fp32 autograd of the oracle itself sits 6e-6 .. 5e-4 from float64,
+and the kernel has to stay within a small factor (3x: CUDA powf is 4-ulp, glibc's < 1) of that noise."""
+import pytest
+import torch
+
+from oracle import colour, hybrid, quality
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dev():
+    assert torch.cuda.is_available()
+    return torch.device("cuda:0")
+
+
+def _rel(a, b):
+    return float((a.detach().double().cpu() - b.double()).abs().max() / b.double().abs().max().clamp_min(1e-30))
+
+
+def _oracle_grad(fn, x, y, dt):
+    xx = x.to(dt).clone().requires_grad_(True)
+    v = fn(xx, y.to(dt))
+    v.backward()
+    return v.detach(), xx.grad
+
+
+def _images(shape, seed, spread=0.1):
+    g = torch.Generator().manual_seed(seed)
+    tgt = torch.rand(shape, generator=g)
+    gen = tgt + spread * torch.randn(shape, generator=g)     # leaves [0,1]: exercises the clamp masks
+    return gen, tgt
+
+
+def _check_grad(mine, g32, g64, tol=1e-5):
+    e_mine, e_ref = _rel(mine, g64), _rel(g32, g64)
+    assert e_mine <= max(tol, 3.0 * e_ref), (e_mine, e_ref)
+    return e_mine, e_ref
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 37, 53), (1, 3, 128, 96), (3, 3, 8, 8)])
+def test_deltae_loss_value_and_grad(dev, shape):
+    from lowlight_image_enhancement_b200.NewBP_model.losses import DeltaE00Loss
+    gen, tgt = _images(shape, shape[2])
+    gen[0, :, :3, :3] = 0.5                                    # neutral grey pixels
+    gen[0, :, 3:5, :3] = tgt[0, :, 3:5, :3]                    # identical pixels
+    v32, g32 = _oracle_grad(colour.de00_loss, gen, tgt, torch.float32)
+    v64, g64 = _oracle_grad(colour.de00_loss, gen, tgt, torch.float64)
+    x = gen.to(dev).requires_grad_(True)
+    v = DeltaE00Loss()(x, tgt.to(dev))
+    assert v.dtype == torch.float32 and v.ndim == 0 and v.requires_grad
+    (3.0 * v).backward()
+    assert abs(float(v) - float(v64)) <= 1e-5 * float(v64)
+    _check_grad(x.grad / 3.0, g32, g64)
+    # pixels pushed outside [0,1] get exactly zero gradient on the clamped channels
+    outside = (gen < 0) | (gen > 1)
+    assert outside.any() and float(x.grad.cpu()[outside].abs().max()) == 0.0
+    # no-grad call takes the value-only kernel and agrees
+    with torch.no_grad():
+        v2 = DeltaE00Loss()(gen.to(dev), tgt.to(dev))
+    assert abs(float(v2) - float(v)) <= 1e-6 * float(v)
+
+
+def test_deltae_loss_contracts(dev):
+    """core_tests/test_losses_domain_norm.py:143-146: identical images give ~sqrt(eps), below 0.01."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import DeltaE00Loss
+    x = torch.rand(2, 3, 32, 32, device=dev)
+    v = DeltaE00Loss()(x, x.clone())
+    assert 0.0 < float(v) < 0.01 and abs(float(v) - 1e-3) < 1e-5
+    with pytest.raises(ValueError):
+        DeltaE00Loss()(x[:, :2], x[:, :2])
+    host = torch.rand(1, 3, 16, 16, requires_grad=True)       # host tensors: result and grad come back to the host
+    out = DeltaE00Loss()(host, torch.rand(1, 3, 16, 16))
+    out.backward()
+    assert out.device.type == "cpu" and host.grad is not None and host.grad.device.type == "cpu"
+    # black pixels sit on atan2's singular point (a = b = 0): ATen's backward returns 0 there, so the
+    # gradient stays finite and equal to the oracle's
+    blk = torch.zeros(1, 3, 4, 4)
+    tg = torch.rand(1, 3, 4, 4)
+    _, gref = _oracle_grad(colour.de00_loss, blk, tg, torch.float32)
+    xb = blk.to(dev).requires_grad_(True)
+    DeltaE00Loss()(xb, tg.to(dev)).backward()
+    assert torch.isfinite(gref).all() and torch.isfinite(xb.grad).all()
+    assert _rel(xb.grad, gref) < 1e-5
+
+
+@pytest.mark.parametrize("shape,ws", [((2, 3, 37, 53), 11), ((1, 3, 128, 96), 11), ((2, 1, 11, 11), 11),
+                                      ((1, 3, 33, 130), 7), ((1, 2, 70, 64), 3), ((1, 1, 16, 15), 15),
+                                      ((1, 3, 12, 200), 5)])
+def test_ssim_loss_value_and_grad(dev, shape, ws):
+    from lowlight_image_enhancement_b200.NewBP_model.losses import SSIMLoss
+
+    def f(a, b):
+        return quality.ssim_loss_kornia(a, b, ws, 1.0)
+
+    gen, tgt = _images(shape, shape[3] + ws)
+    v32, g32 = _oracle_grad(f, gen, tgt, torch.float32)
+    v64, g64 = _oracle_grad(f, gen, tgt, torch.float64)
+    x = gen.to(dev).requires_grad_(True)
+    v = SSIMLoss(window_size=ws)(x, tgt.to(dev))
+    (0.5 * v).backward()
+    assert abs(float(v) - float(v64)) <= 1e-5 * float(v64)
+    _check_grad(2.0 * x.grad, g32, g64)
+    outside = (gen < 0) | (gen > 1)
+    assert float(x.grad.cpu()[outside].abs().max()) == 0.0
+
+
+def test_ssim_loss_reductions_and_identity(dev):
+    from lowlight_image_enhancement_b200.NewBP_model.losses import SSIMLoss
+    gen, tgt = _images((2, 3, 40, 44), 5)
+    xg = gen.clamp(0, 1)
+    smap = torch.clamp((1 - quality.kornia_ssim_map(xg.double(), tgt.double())) / 2, 0, 1)
+    x = gen.to(dev).requires_grad_(True)
+    m = SSIMLoss(reduction="none")(x, tgt.to(dev))
+    assert m.shape == gen.shape and float((m.cpu().double() - smap).abs().max()) < 2e-6
+    wgt = torch.rand(gen.shape, generator=torch.Generator().manual_seed(1))
+    (m * wgt.to(dev)).sum().backward()
+    xr = gen.double().clone().requires_grad_(True)
+    (torch.clamp((1 - quality.kornia_ssim_map(xr.clamp(0, 1), tgt.double())) / 2, 0, 1) * wgt.double()).sum().backward()
+    assert _rel(x.grad, xr.grad) < 1e-5
+    s = SSIMLoss(reduction="sum")(gen.to(dev), tgt.to(dev))
+    assert abs(float(s) - float(smap.sum())) < 1e-5 * float(smap.sum())
+    ident = SSIMLoss()(tgt.to(dev), tgt.to(dev))
+    assert abs(float(ident)) < 1e-6
+    with pytest.raises(ValueError):
+        SSIMLoss(window_size=4)
+    with pytest.raises(RuntimeError):
+        SSIMLoss()(torch.rand(1, 3, 5, 40, device=dev), torch.rand(1, 3, 5, 40, device=dev))
+
+
+@pytest.mark.parametrize("mode", ["raw_kernel", "srgb_psf"])
+def test_hybrid_loss_plus_vs_oracle(dev, mode):
+    """losses.py:318-372 with the perceptual / LPIPS terms absent (out of scope): total, logs, gradient."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import HybridLossPlus
+    from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import CrosstalkPSF, build_psf_kernels
+    g = torch.Generator().manual_seed(31)
+    n = 2
+    B = torch.rand(n, 3, 48, 56, generator=g)
+    Bhat = (B + 0.08 * torch.randn(B.shape, generator=g))
+    rho = torch.tensor([100.0, 250.0]).view(n, 1, 1, 1)
+    A = (B / rho + 0.0005 * torch.randn(B.shape, generator=g)).clamp_min(0)
+    kern = build_psf_kernels("rgb", "B2")
+    kw = dict(w_l1=1.0, w_de=0.02, w_ssim=0.05, w_phys=0.05)
+    if mode == "raw_kernel":
+        ora_kw = dict(physics_kernel=kern)
+        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern)
+    else:
+        psf = CrosstalkPSF("rgb", kern)
+        ora_kw = dict(psf_kernel=psf.kernel.clone())
+        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_psf_module=psf)
+
+    def ora(dt):
+        x = Bhat.to(dt).clone().requires_grad_(True)
+        xs = x.clamp(0, 1)
+        kws = {k: v.to(dt) for k, v in ora_kw.items()}
+        tot, logs = hybrid.hybrid_loss(Bhat_raw=x, B_raw=B.to(dt), A_raw=A.to(dt), expo_ratio=rho.to(dt), Bhat_srgb01=xs,
+                                       B_srgb01=B.to(dt), A_srgb01=A.to(dt), **kw, **kws)
+        tot.backward()
+        return tot.detach(), logs, x.grad
+
+    t32, l32, g32 = ora(torch.float32)
+    t64, l64, g64 = ora(torch.float64)
+    x = Bhat.to(dev).requires_grad_(True)
+    xs = x.clamp(0, 1)                                             # irm:289-300: srgb tensor = clamp of the raw one
+    tot, logs = mod(Bhat_raw=x, B_raw=B.to(dev), A_raw=A.to(dev), expo_ratio=rho.to(dev), Bhat_srgb01=xs,
+                    B_srgb01=B.to(dev), A_srgb01=A.to(dev))
+    tot.backward()
+    assert set(logs) >= {"L1_raw", "Perc", "DeltaE", "SSIM", "Phys", "Total"}
+    for k in ("L1_raw", "DeltaE", "SSIM", "Phys", "Total"):
+        assert abs(float(logs[k]) - float(l64[k])) <= 1e-5 * abs(float(l64[k])), k
+        assert not logs[k].requires_grad
+    assert float(logs["Perc"]) == 0.0
+    assert abs(float(tot) - float(t64)) <= 1e-5 * float(t64)
+    _check_grad(x.grad, g32, g64)
+
+
+def test_hybrid_loss_plus_behaviour(dev):
+    from lowlight_image_enhancement_b200.NewBP_model.losses import HybridLossPlus
+    g = torch.Generator().manual_seed(3)
+    B = torch.rand(1, 3, 32, 32, generator=g).to(dev)
+    x = (B + 0.05).clone().requires_grad_(True)
+    rho = torch.tensor([100.0], device=dev)
+    kern = torch.tensor([[.01, .02, .01], [.02, .88, .02], [.01, .02, .01]]).view(1, 1, 3, 3)
+    args = dict(B_raw=B, A_raw=B / 100.0, expo_ratio=rho, B_srgb01=B)
+    # uncertainty weighting: val * exp(-2 s) + s, learnable log-sigmas receive gradients (losses.py:308-316)
+    mod = HybridLossPlus(device="cuda", use_uncertainty=True, physics_kernel=kern).to(dev)
+    tot, logs = mod(Bhat_raw=x, Bhat_srgb01=x.clamp(0, 1), **args)
+    tot.backward()
+    assert all(mod.log_sigma[k].grad is not None for k in ("l1", "de", "ssim", "phys"))
+    ref = sum(float(logs[k]) for k in ("L1_raw", "DeltaE", "SSIM", "Phys"))
+    assert abs(float(tot) - ref) < 1e-5 * ref                         # s = 0 -> plain sum
+    # switches
+    mod2 = HybridLossPlus(device="cuda", use_deltaE=False, use_ssim=False, use_phys=False)
+    tot2, logs2 = mod2(Bhat_raw=x, Bhat_srgb01=x, **args)
+    assert "DeltaE" not in logs2 and "SSIM" not in logs2 and "Phys" not in logs2
+    assert abs(float(tot2) - float(logs2["L1_raw"])) < 1e-7
+    # injected perceptual module is used and weighted
+    class Half(torch.nn.Module):
+        def forward(self, a, b):
+            return (a - b).pow(2).mean()
+    mod3 = HybridLossPlus(device="cuda", use_deltaE=False, use_ssim=False, use_phys=False, w_perc=0.5,
+                          perceptual_module=Half())
+    tot3, logs3 = mod3(Bhat_raw=x, Bhat_srgb01=x, **args)
+    assert abs(float(tot3) - (float(logs3["L1_raw"]) + 0.5 * float(logs3["Perc"]))) < 1e-7 and float(logs3["Perc"]) > 0
+    # non-finite term -> RuntimeError naming it (losses.py:298-306)
+    bad = x.detach().clone()
+    bad[0, 0, 0, 0] = float("nan")
+    with pytest.raises(RuntimeError, match="non-finite values in term 'L1_raw'"):
+        HybridLossPlus(device="cuda", physics_kernel=kern)(Bhat_raw=bad, Bhat_srgb01=bad, **args)
