@@ -27,7 +27,11 @@ import torch  # noqa: E402
 RHO = [100.0, 250.0, 300.0, 100.0, 250.0, 300.0, 100.0, 250.0]
 SHAPE = (8, 3, 512, 512)
 # dram bytes per launch from the committed `ncu --set full` capture of this workload (profiles/); None = not captured
-TRAFFIC = {}
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, `ncu --set full` of this command
+# (profiles/r1_bench_phys_c2_ncu_full.txt).  Reads equal the algorithmic 50.33 MB (no halo re-reads reach
+# DRAM); the 25.2 MB gradient written by the backward kernel is still held by the 126 MB L2 when the kernel
+# ends, so only ~1.3 MB of its write-back is attributed to the launch.
+TRAFFIC = {"phys_fwd_ring": 50.40e6, "phys_bwd_ring": 51.78e6}
 POOL = 8  # rotating buffer sets: 8 x (pred+obs+grad = 75.5 MB) = 604 MB >> 126 MB L2
 
 

@@ -56,6 +56,8 @@ int llie_check_device(void);
 /* Diagnostic knobs for A/B measurements (process-wide, not thread-safe; defaults are the product). */
 #define LLIE_TUNE_PHYS_PATH 1 /* 0 TMA row ring (default) | 1 TMA tile ring | 2 generic only | 3 register prefetch */
 #define LLIE_TUNE_PHYS_ROWS 2 /* rows per warp chunk of the rolling path; 0 = heuristic */
+#define LLIE_TUNE_SSIM_PATH 3 /* 0 streaming column kernel (default) | 1 shared-memory tile kernel */
+#define LLIE_TUNE_SSIM_SEG_ROWS 4 /* output rows per CTA of the streaming SSIM kernel; 0 = heuristic */
 int llie_tune(int key, int value);
 
 /* ------------------------------------------------------------------------

@@ -209,6 +209,8 @@ static int grid_x_for(int n, int work_items) {
     return per_sample;
 }
 
+void ssim_tune(int key, int value);  // ssim.cu
+
 int g_phys_path = 0;  // 0 TMA row ring (default), 1 TMA tile ring, 2 generic only, 3 register prefetch (llie_tune)
 
 }  // namespace llie
@@ -219,6 +221,8 @@ extern "C" int llie_tune(int key, int value) {
     switch (key) {
         case LLIE_TUNE_PHYS_PATH: g_phys_path = value; return LLIE_OK;
         case LLIE_TUNE_PHYS_ROWS: phys_roll_set_rows(value); phys_ring_set_rows(value); return LLIE_OK;
+        case LLIE_TUNE_SSIM_PATH:
+        case LLIE_TUNE_SSIM_SEG_ROWS: ssim_tune(key, value); return LLIE_OK;
         default: break;
     }
     llie::set_error("llie_tune: unknown key %d", key);

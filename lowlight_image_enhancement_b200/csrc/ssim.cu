@@ -29,6 +29,7 @@ struct SsimArgs {
     int *pflag;    // [gridDim.x]
     unsigned *ticket;
     int tiles_x, tiles_y, co;
+    int seg_rows;  // streaming kernel: output rows per CTA
 };
 
 __device__ __forceinline__ float ssim_load(const SsimArgs &a, const float *base, long long plane_stride, int sy,
@@ -233,6 +234,217 @@ static int launch_ssim(const SsimArgs &a, int grid, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------------
+// Streaming variant (default for non-luma inputs): one thread per output column of a 128-column strip, rows
+// streamed top to bottom through a 4-row shared-memory ring filled by cp.async three rows ahead (no
+// registers held by loads in flight, one __syncthreads per row).  Per input row a thread runs the K-tap
+// horizontal pass of the five moment maps from shared memory and scatters the five values into K rolling
+// vertical accumulators per map held in registers (slot = output row mod K, static after unrolling by K).
+// Shared memory per CTA is 4.4 KB instead of the tile kernel's 80 KB, so occupancy is bound by registers only.
+constexpr int SW = 128;
+constexpr int SD = 4;  // ring depth (rows)
+
+__device__ __forceinline__ void cp_async4(unsigned dst, const float *src, unsigned src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <int K>
+__global__ void __launch_bounds__(SW) ssim_stream_kernel(const SsimArgs a) {
+    constexpr int P = K / 2;
+    constexpr int RW = SW + 2 * P;
+    __shared__ float sX[SD][RW], sY[SD][RW];
+    __shared__ double red[32];
+    const llie_ssim_desc &d = a.d;
+    const int H = d.h, W = d.w, tid = threadIdx.x;
+    const int tpp = a.tiles_x * a.tiles_y;  // strips x row segments per plane
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int seg = trem / a.tiles_x, strip = trem - seg * a.tiles_x;
+    const int x0 = strip * SW, y0 = seg * a.seg_rows;
+    const int rows_out = min(a.seg_rows, H - y0);
+    const int nrows_in = rows_out + 2 * P;
+    const long long plane_elems = (long long)H * W;
+    const float *xb = a.x + (long long)plane * plane_elems;  // no luma here: plane == n * c + ch
+    const float *yb = a.y + (long long)plane * plane_elems;
+
+    float g[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
+
+    // padded source columns of this thread's ring slots (tid, and SW + tid for the right halo); columns no
+    // in-image output needs read as zero
+    const int gin0 = x0 - P + tid, gin1 = x0 - P + SW + tid;
+    const int cmain = gin0 <= W - 1 + P ? pad_index(gin0, W, d.pad_mode) : -1;
+    const bool has_ext = tid < 2 * P;
+    const int cext = (has_ext && gin1 <= W - 1 + P) ? pad_index(gin1, W, d.pad_mode) : -1;
+    const float *pxm = xb + max(cmain, 0), *pym = yb + max(cmain, 0);
+    const float *pxe = xb + max(cext, 0), *pye = yb + max(cext, 0);
+    const unsigned bm = cmain >= 0 ? 4u : 0u, be = cext >= 0 ? 4u : 0u;
+    const unsigned sxa = (unsigned)__cvta_generic_to_shared(&sX[0][tid]);
+    const unsigned sya = (unsigned)__cvta_generic_to_shared(&sY[0][tid]);
+
+    auto issue_row = [&](int i) {  // i is uniform over the CTA; one commit group per call
+        if (i < nrows_in) {
+            const int sy = pad_index(y0 - P + i, H, d.pad_mode);
+            const long long ro = (long long)max(sy, 0) * W;
+            const unsigned so = (unsigned)((i & (SD - 1)) * RW * 4);
+            const unsigned ok = sy >= 0 ? 4u : 0u;
+            cp_async4(sxa + so, pxm + ro, min(bm, ok));
+            cp_async4(sya + so, pym + ro, min(bm, ok));
+            if (has_ext) {
+                cp_async4(sxa + so + SW * 4, pxe + ro, min(be, ok));
+                cp_async4(sya + so + SW * 4, pye + ro, min(be, ok));
+            }
+        }
+        cp_async_commit();
+    };
+
+    const int gx = x0 + tid;
+    const int lo_y = d.interior ? P : 0, hi_y = d.interior ? H - P : H;
+    const bool col_in = gx < W;
+    const bool col_ok = col_in && (!d.interior || (gx >= P && gx < W - P));
+    const long long cstride = (long long)d.n * a.co * plane_elems;
+    long long off = ((long long)plane * H + y0) * W + gx;  // output element of the next completed row
+    float acc[5][K];
+#pragma unroll
+    for (int q = 0; q < 5; ++q)
+#pragma unroll
+        for (int j = 0; j < K; ++j) acc[q][j] = 0.f;
+    float facc = 0.f, chk_x = 0.f, chk_y = 0.f;
+
+#pragma unroll
+    for (int i = 0; i < SD - 1; ++i) issue_row(i);
+    for (int base = 0; base < nrows_in; base += K) {
+#pragma unroll
+        for (int ii = 0; ii < K; ++ii) {
+            const int i = base + ii;
+            if (i >= nrows_in) break;  // uniform
+            float *rx = sX[i & (SD - 1)], *ry = sY[i & (SD - 1)];
+            cp_async_wait<SD - 2>();  // this thread's copies of row i have landed
+            {
+                // own elements: finite check and the optional clamp, before they become visible to the CTA
+                float vx = rx[tid], vy = ry[tid];
+                chk_x = fmaf(vx, 0.f, chk_x);
+                chk_y = fmaf(vy, 0.f, chk_y);
+                if (d.clamp_in) {
+                    rx[tid] = fminf(fmaxf(vx, 0.f), 1.f);
+                    ry[tid] = fminf(fmaxf(vy, 0.f), 1.f);
+                }
+                if (has_ext) {
+                    vx = rx[SW + tid];
+                    vy = ry[SW + tid];
+                    chk_x = fmaf(vx, 0.f, chk_x);
+                    chk_y = fmaf(vy, 0.f, chk_y);
+                    if (d.clamp_in) {
+                        rx[SW + tid] = fminf(fmaxf(vx, 0.f), 1.f);
+                        ry[SW + tid] = fminf(fmaxf(vy, 0.f), 1.f);
+                    }
+                }
+            }
+            __syncthreads();          // row i visible to all; everyone is done with row i - 1
+            issue_row(i + SD - 1);    // refills the slot row i - 1 occupied
+            float h[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+                const float xv = rx[tid + j], yv = ry[tid + j];
+                h[0] = fmaf(g[j], xv, h[0]);
+                h[1] = fmaf(g[j], yv, h[1]);
+                h[2] = fmaf(g[j], xv * xv, h[2]);
+                h[3] = fmaf(g[j], yv * yv, h[3]);
+                h[4] = fmaf(g[j], xv * yv, h[4]);
+            }
+            // input row i feeds output rows o = i - j with tap j; slot(o) = o mod K = (ii - j) mod K
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+                const int sl = (ii - j + K) % K;
+#pragma unroll
+                for (int q = 0; q < 5; ++q) acc[q][sl] = (j == 0) ? g[0] * h[q] : fmaf(g[j], h[q], acc[q][sl]);
+            }
+            if (i >= K - 1) {  // output row o = i - (K - 1) is complete
+                const int sl = (ii + 1) % K;
+                const int gy = y0 + i - (K - 1);
+                const float mx = acc[0][sl], my = acc[1][sl];
+                const float mx2 = mx * mx, my2 = my * my, mxy = mx * my;
+                float sx = acc[2][sl] - mx2, sy = acc[3][sl] - my2;
+                const float sxy = acc[4][sl] - mxy;
+                if (d.clamp_var) {
+                    sx = fmaxf(sx, 0.f);
+                    sy = fmaxf(sy, 0.f);
+                }
+                const float num = (2.f * mxy + d.c1) * (2.f * sxy + d.c2);
+                const float den = (mx2 + my2 + d.c1) * (sx + sy + d.c2) + d.eps;
+                float sv = num / den;
+                if (a.out_map != nullptr && col_in) a.out_map[off] = sv;
+                if (a.coef != nullptr && col_in) {
+                    const float l = (1.f - sv) * 0.5f;
+                    const float up =
+                        (!d.loss_map) ? a.coef_scale : ((l >= 0.f && l <= 1.f) ? -0.5f * a.coef_scale : 0.f);
+                    const float inv = 1.f / den;
+                    const float n1 = 2.f * mxy + d.c1, n2 = 2.f * sxy + d.c2, d1 = mx2 + my2 + d.c1,
+                                d2 = sx + sy + d.c2;
+                    const float a3 = 2.f * n1 * inv;
+                    const float a2 = -sv * d1 * inv;
+                    const float dmu = 2.f * (my * n2 - sv * mx * d2) * inv;
+                    const float a1 = dmu - 2.f * mx * a2 - my * a3;
+                    float *cp = a.coef + off;
+                    cp[0] = up * a1;
+                    cp[cstride] = up * a2;
+                    cp[2 * cstride] = up * a3;
+                }
+                off += W;
+                if (d.loss_map) sv = fminf(fmaxf((1.f - sv) * 0.5f, 0.f), 1.f);
+                if (col_ok && gy >= lo_y && gy < hi_y) facc += sv;
+            }
+        }
+    }
+    cp_async_wait<0>();
+    const double bs = block_sum<double>((double)facc, red);
+    int flag = 0;
+    if (!(chk_x == 0.f)) flag |= 1;
+    if (!(chk_y == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (tid == 0) {
+        a.part[blockIdx.x] = bs;
+        a.pflag[blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x)) return;
+    const int lane = tid & 31, wrp = tid >> 5;
+    const int planes = d.n * a.co;
+    for (int pl = wrp; pl < planes; pl += SW / 32) {
+        const double *p = a.part + (size_t)pl * tpp;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int b = lane;
+        for (; b + 96 < tpp; b += 128) {
+            s0 += __ldcg(p + b);
+            s1 += __ldcg(p + b + 32);
+            s2 += __ldcg(p + b + 64);
+            s3 += __ldcg(p + b + 96);
+        }
+        for (; b < tpp; b += 32) s0 += __ldcg(p + b);
+        const double sm_ = warp_sum((s0 + s1) + (s2 + s3));
+        if (lane == 0) a.out_sum[pl] = sm_;
+    }
+    int fl = 0;
+    for (int b = tid; b < (int)gridDim.x; b += SW) fl |= __ldcg(a.pflag + b);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (tid == 0) *a.out_flags = ff;
+}
+
+template <int K>
+static int launch_ssim_stream(const SsimArgs &a, int grid, cudaStream_t st) {
+    ssim_stream_kernel<K><<<grid, SW, 0, st>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+int g_ssim_path = 0;      // 0 streaming (default) | 1 tile kernel
+int g_ssim_seg_rows = 0;  // 0 = heuristic
+
+// ---------------------------------------------------------------------------------------------------
 // Backward of the (D)SSIM sum w.r.t. x (kornia policy: reflect border, "same" size):
 //   dL/dx(q) = mask(q) * g_up * [ (G^T c1)(q) + 2 x(q) (G^T c2)(q) + y(q) (G^T c3)(q) ]
 // where c1..c3 are the coefficient maps the forward kernel stored and G^T is the adjoint of
@@ -426,16 +638,43 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
     a.out_sum = out_sum; a.out_map = out_map; a.out_flags = out_flags;
     a.coef = coef; a.coef_scale = coef_scale;
     a.co = d.luma ? 1 : d.c;
-    a.tiles_x = div_up(d.w, STW);
-    a.tiles_y = div_up(d.h, STH);
-    const long long grid = (long long)d.n * a.co * a.tiles_x * a.tiles_y;
     Workspace ws(workspace);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    long long grid;
+    const bool stream_ok = g_ssim_path == 0 && !d.luma;
+    if (stream_ok) {
+        // strips of 128 columns x row segments sized for ~3 resident waves (148 SMs x 5 CTAs), >= 48 rows each
+        a.tiles_x = div_up(d.w, SW);
+        const long long cols = (long long)d.n * a.co * a.tiles_x;
+        int segs = (int)((148LL * 5 * 3 + cols - 1) / cols);
+        int rows = g_ssim_seg_rows > 0 ? g_ssim_seg_rows : (d.h + segs - 1) / segs;
+        if (g_ssim_seg_rows <= 0 && rows < 48) rows = 48;
+        if (rows > d.h) rows = d.h;
+        a.seg_rows = rows;
+        a.tiles_y = div_up(d.h, rows);
+        grid = cols * a.tiles_y;
+    } else {
+        a.tiles_x = div_up(d.w, STW);
+        a.tiles_y = div_up(d.h, STH);
+        grid = (long long)d.n * a.co * a.tiles_x * a.tiles_y;
+    }
     LLIE_REQUIRE(grid <= 0x7fffffffLL && (size_t)grid * (sizeof(double) + sizeof(int)) <= ws.scratch_bytes,
                  "ssim_stats: workspace too small for %lld tiles", grid);
     a.part = reinterpret_cast<double *>(ws.scratch);
     a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)grid * sizeof(double));
     a.ticket = ws.tickets;
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (stream_ok) {
+        switch (d.ksize) {
+            case 1: return launch_ssim_stream<1>(a, (int)grid, st);
+            case 3: return launch_ssim_stream<3>(a, (int)grid, st);
+            case 5: return launch_ssim_stream<5>(a, (int)grid, st);
+            case 7: return launch_ssim_stream<7>(a, (int)grid, st);
+            case 9: return launch_ssim_stream<9>(a, (int)grid, st);
+            case 11: return launch_ssim_stream<11>(a, (int)grid, st);
+            case 13: return launch_ssim_stream<13>(a, (int)grid, st);
+            default: return launch_ssim_stream<15>(a, (int)grid, st);
+        }
+    }
     switch (d.ksize) {
         case 1: return launch_ssim<1>(a, (int)grid, st);
         case 3: return launch_ssim<3>(a, (int)grid, st);
@@ -447,6 +686,13 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
         default: return launch_ssim<15>(a, (int)grid, st);
     }
 }
+
+namespace llie {
+void ssim_tune(int key, int value) {
+    if (key == LLIE_TUNE_SSIM_PATH) g_ssim_path = value;
+    if (key == LLIE_TUNE_SSIM_SEG_ROWS) g_ssim_seg_rows = value;
+}
+}  // namespace llie
 
 extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
                                double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream) {

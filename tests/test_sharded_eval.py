@@ -1,0 +1,126 @@
+"""Sharded validation driver (lowlight_image_enhancement_b200/eval.py).
+
+CPU part: world_size-2 gloo run of the host logic (image -> rank rule of irm:359-361, per-rank float64
+sums, ONE all-reduce, means as irm:459-464) with an injected host metric function.
+GPU part: the device metric scalars equal the adapters' floats and the driver's means equal the
+serial loop over adapters."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from lowlight_image_enhancement_b200.eval import ShardedMeans, evaluate_pairs, shard_indices
+
+NAMES = ["a", "b", "c"]
+
+
+def _fake_metric(pred, target, names, flags, **_):
+    # deterministic per-image values that depend on the pair only
+    s = float(pred.sum()) - float(target.sum())
+    if not torch.isfinite(pred).all():
+        flags += 1
+    return torch.tensor([s, s * s, 1.0 + pred.numel()], dtype=torch.float64)
+
+
+def _pairs(n):
+    g = torch.Generator().manual_seed(5)
+    return [(torch.rand(3, 4 + i % 3, 5, generator=g), torch.rand(3, 4 + i % 3, 5, generator=g)) for i in range(n)]
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n, shard, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        touched = []
+        pairs = _pairs(n)
+
+        def getter(i):
+            touched.append(i)
+            return pairs[i]
+
+        res = evaluate_pairs(getter, NAMES, n_items=n, device="cpu", shard=shard, metric_fn=_fake_metric)
+        out.put((rank, res, touched))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,shard", [(7, "interleave"), (8, "block"), (1, "interleave")])
+def test_two_rank_gloo_matches_serial(n, shard):
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, shard, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    serial = evaluate_pairs(_pairs(n), NAMES, device="cpu", metric_fn=_fake_metric, rank=0, world_size=1)
+    seen = []
+    for rank, res, touched in got:
+        assert touched == shard_indices(n, rank, world, shard)       # a rank reads only its own images
+        seen += touched
+        assert res["count"] == n and res["nonfinite_inputs"] == 0
+        for k in NAMES:
+            assert res[k] == pytest.approx(serial[k], rel=1e-12)
+    assert sorted(seen) == list(range(n))                            # every image exactly once
+
+
+def test_shard_rules_and_accumulator():
+    assert shard_indices(10, 1, 4) == [1, 5, 9]                       # i % world == rank
+    assert [shard_indices(10, r, 4, "block") for r in range(4)] == [[0, 1, 2], [3, 4, 5], [6, 7], [8, 9]]
+    assert shard_indices(2, 3, 4) == []
+    with pytest.raises(ValueError):
+        shard_indices(4, 4, 4)
+    acc = ShardedMeans(["x", "y"], "cpu")
+    acc.add(torch.tensor([1.0, 10.0]))
+    acc.add(torch.tensor([3.0, float("inf")]), flags=torch.tensor([2], dtype=torch.int32))
+    out = acc.reduce()
+    assert out["x"] == 2.0 and out["y"] == float("inf") and out["count"] == 2 and out["nonfinite_inputs"] == 1
+    empty = ShardedMeans(["x"], "cpu").reduce()
+    assert empty["count"] == 0 and empty["x"] != empty["x"]
+    with pytest.raises(ValueError):
+        acc.add(torch.tensor([1.0]))
+
+
+@pytest.mark.gpu
+def test_device_metrics_equal_adapters():
+    from lowlight_image_enhancement_b200 import lowlight_metrics as lm
+    from lowlight_image_enhancement_b200.eval import METRIC_FUNCTIONS, image_metrics
+    dev = torch.device("cuda:0")
+    names = sorted(METRIC_FUNCTIONS)
+    g = torch.Generator().manual_seed(12)
+    pairs = []
+    for i in range(5):
+        gt = torch.rand(1, 3, 40 + 8 * i, 72, generator=g)
+        gt = torch.round(255 * torch.nn.functional.avg_pool2d(gt, 5, 1, 2)) / 255
+        pred = (gt + 0.04 * torch.randn(gt.shape, generator=g))
+        pairs.append((pred.to(dev), gt.to(dev)))
+    serial = {k: 0.0 for k in names}
+    for pred, gt in pairs:
+        vals = image_metrics(pred, gt, names)
+        assert vals.dtype == torch.float64 and vals.is_cuda
+        for k, v in zip(names, vals.tolist()):
+            ref = getattr(lm, k)(pred, gt)
+            assert v == pytest.approx(ref, rel=1e-6, abs=1e-9), k
+            serial[k] += ref / len(pairs)
+    res = evaluate_pairs(pairs, names, device=dev)
+    assert res["count"] == 5 and res["nonfinite_inputs"] == 0
+    for k in names:
+        assert res[k] == pytest.approx(serial[k], rel=1e-6)
+    bad = pairs[0][0].clone()
+    bad[0, 0, 0, 0] = float("nan")
+    assert evaluate_pairs([(bad, pairs[0][1])], ["linear_psnr", "deltae2000_mean"], device=dev)["nonfinite_inputs"] == 1
+    with pytest.raises(KeyError):
+        image_metrics(pairs[0][0], pairs[0][1], ["nope"])
