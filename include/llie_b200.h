@@ -226,6 +226,10 @@ int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, do
 int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const float *y, float grad_scale,
                           double *out_sum, float *out_grad, int32_t *out_flags, void *workspace, void *stream);
 
+/* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the
+ * < 1 ulp claim can be checked against a float64 pow from the test-suite. */
+int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream);
+
 /* Sobel magnitude sqrt(gx^2 + gy^2 + 1e-12) of [planes, h, w], zero padding (color_error.py:23-30, 296-301) */
 int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w, void *stream);
 

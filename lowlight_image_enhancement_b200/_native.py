@@ -85,6 +85,7 @@ _SIGNATURES = {
     "llie_ssim_loss_forward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, C.c_float, _VP, _VP, _VP, _VP, _VP,
                                          _VP]),
     "llie_ssim_loss_backward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, C.c_int32, _VP, _VP]),
+    "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),
     "llie_select_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "llie_select_quantiles": (C.c_int, [C.POINTER(SelectDesc), _VP, _VP, _VP, C.POINTER(C.c_double), _VP, _VP, _VP,

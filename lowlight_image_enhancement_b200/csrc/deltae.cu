@@ -6,9 +6,11 @@
 //                                      mod 2pi, boolean-mask wraps, sin(dtheta), + eps under the sqrt)
 //   * kornia 0.6.12 rgb_to_lab (color_error.py:79-85, losses.py:140-141) restated, see oracle/colour.py
 // plus the Sobel magnitude of the L plane (color_error.py:296-301) for the edge mask.
-// Precise transcendentals (powf / atan2f / sinf / cosf / expf, no fast-math): the tolerance is 1e-4
-// absolute on dE00.  This kernel is bound by the FP32/SFU pipes (~600 instructions per pixel against
-// 24 bytes), not by HBM.
+// Precise transcendentals (no fast-math): the tolerance is 1e-4 absolute on dE00.  The kernel is bound by
+// instruction issue (FP32 + SFU), not by HBM, so the three expensive groups of libm calls are replaced by
+// cheaper forms of at least the same accuracy: x^2.4 by a Newton-refined fifth root (pow24, < 1 ulp),
+// t^(1/3) by cbrtf (1 ulp; powf is 4), and the four cosines of T by one sincosf plus multiple-angle
+// identities.
 #include <math.h>
 
 #include "common.cuh"
@@ -17,11 +19,44 @@ namespace llie {
 
 constexpr float kPi = 3.14159265358979323846f;
 
+// b^2.4 for b in [0.09, 1] as (b * b^(1/5))^2.  The fifth root starts from the SFU estimate
+// exp2(0.2 log2 b) (~1e-6 relative) and takes one Newton step whose residual b - y^5 is evaluated with
+// FMA error terms; the correction is kept as a separate term through the final square, so the result is
+// rounded once: < 1 ulp against double pow (tests/test_gpu_ssim_colour.py::test_srgb_to_linear_ulp).
+__device__ __forceinline__ float pow24(float b) {
+    const float y = exp2f(0.2f * __log2f(b));
+    const float y2 = y * y, e2 = fmaf(y, y, -y2);          // y^2 = y2 + e2 exactly
+    const float y4 = y2 * y2;
+    const float e4 = fmaf(y2, y2, -y4) + 2.0f * y2 * e2;   // y^4 = y4 + e4 (+ O(e2^2))
+    const float r = fmaf(-y4, y, b) - e4 * y;              // b - y^5
+    const float dy = __fdividef(r, 5.0f * y4);             // Newton correction, |dy| ~ 1e-6 y
+    const float p = b * y, ep = fmaf(b, y, -p);            // b y = p + ep exactly
+    const float lo = fmaf(b, dy, ep);                      // b (y + dy) = p + lo
+    return fmaf(p, p, 2.0f * p * lo);
+}
 __device__ __forceinline__ float srgb_to_linear(float c) {
-    return c > 0.04045f ? powf((c + 0.055f) / 1.055f, 2.4f) : c / 12.92f;
+    return c > 0.04045f ? pow24((c + 0.055f) / 1.055f) : c / 12.92f;
 }
 __device__ __forceinline__ float lab_f(float t) {
-    return t > 0.008856f ? powf(fmaxf(t, 0.008856f), 1.0f / 3.0f) : 7.787f * t + 4.0f / 29.0f;
+    return t > 0.008856f ? cbrtf(t) : 7.787f * t + 4.0f / 29.0f;
+}
+
+// T = 1 - 0.17 cos(h - 30deg) + 0.24 cos 2h + 0.32 cos(3h + 6deg) - 0.20 cos(4h - 63deg) and dT/dh from one
+// sincosf and multiple-angle identities
+__device__ __forceinline__ float t_weight(float hb, float *dt) {
+    float s1, c1;
+    sincosf(hb, &s1, &c1);
+    const float c2 = fmaf(2.0f * c1, c1, -1.0f), s2 = 2.0f * s1 * c1;
+    const float c3 = c1 * fmaf(4.0f * c1, c1, -3.0f), s3 = s1 * fmaf(4.0f * c1, c1, -1.0f);
+    const float c4 = fmaf(2.0f * c2, c2, -1.0f), s4 = 2.0f * s2 * c2;
+    constexpr float C30 = 0.86602540378443865f, S30 = 0.5f;
+    constexpr float C6 = 0.99452189536827334f, S6 = 0.10452846326765347f;
+    constexpr float C63 = 0.45399049973954675f, S63 = 0.89100652418836786f;
+    const float ca = c1 * C30 + s1 * S30, sa = s1 * C30 - c1 * S30;  // h - 30
+    const float cb = c3 * C6 - s3 * S6, sb = s3 * C6 + c3 * S6;      // 3h + 6
+    const float cc = c4 * C63 + s4 * S63, sc = s4 * C63 - c4 * S63;  // 4h - 63
+    if (dt) *dt = 0.17f * sa - 0.48f * s2 - 0.96f * sb + 0.80f * sc;
+    return 1.0f - 0.17f * ca + 0.24f * c2 + 0.32f * cb - 0.20f * cc;
 }
 // kornia 0.6.12 rgb_to_lab
 __device__ __forceinline__ void rgb_to_lab(float r, float g, float b, float &L, float &A, float &B) {
@@ -73,8 +108,7 @@ __device__ float de00_metric(float L1, float a1, float b1, float L2, float a2, f
         hb = 0.5f * (hs + 2.0f * kPi);
     else
         hb = 0.5f * (hs - 2.0f * kPi);
-    const float t = 1.0f - 0.17f * cosf(hb - deg2rad(30.0f)) + 0.24f * cosf(2.0f * hb) +
-                    0.32f * cosf(3.0f * hb + deg2rad(6.0f)) - 0.20f * cosf(4.0f * hb - deg2rad(63.0f));
+    const float t = t_weight(hb, nullptr);
     const float q = ((hb * 180.0f / kPi) - 275.0f) / 25.0f;
     const float dth = deg2rad(30.0f) * expf(-(q * q));
     const float Cb7 = pow7(Cb);
@@ -112,8 +146,7 @@ __device__ float de00_loss(float L1, float a1, float b1, float L2, float a2, flo
     const float Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
     const float hs = h1 + h2;
     const float hb = hs / 2.0f - (fabsf(h1 - h2) > kPi ? kPi : 0.0f) + (hs < 0.0f ? 2.0f * kPi : 0.0f);
-    const float t = 1.0f - 0.17f * cosf(hb - deg2rad(30.0f)) + 0.24f * cosf(2.0f * hb) +
-                    0.32f * cosf(3.0f * hb + deg2rad(6.0f)) - 0.20f * cosf(4.0f * hb - deg2rad(63.0f));
+    const float t = t_weight(hb, nullptr);
     const float q = ((hb * (180.0f / kPi)) - 275.0f) / 25.0f;
     const float dro = 30.0f * expf(-(q * q));
     const float Cb7 = pow7(Cb);
@@ -232,11 +265,6 @@ __device__ __forceinline__ D3 dsin(D3 a) {
     sincosf(a.v, &s, &c);
     return dchain(s, c, a);
 }
-__device__ __forceinline__ D3 dcos(D3 a) {
-    float s, c;
-    sincosf(a.v, &s, &c);
-    return dchain(c, -s, a);
-}
 __device__ __forceinline__ D3 dexp(D3 a) {
     const float e = expf(a.v);
     return dchain(e, e, a);
@@ -274,8 +302,9 @@ __device__ D3 de00_loss_dual(float L1f, float a1f, float b1f, float L2, float a2
     const D3 hs = h1 + h2;
     D3 hb = 0.5f * hs;
     hb.v = hs.v / 2.0f - (fabsf(h1.v - h2.v) > kPi ? kPi : 0.0f) + (hs.v < 0.0f ? 2.0f * kPi : 0.0f);
-    const D3 t = (1.0f - 0.17f * dcos(hb - deg2rad(30.0f))) + 0.24f * dcos(2.0f * hb) +
-                 0.32f * dcos(3.0f * hb + deg2rad(6.0f)) - 0.20f * dcos(4.0f * hb - deg2rad(63.0f));
+    float dtdh;
+    const float tv = t_weight(hb.v, &dtdh);
+    const D3 t = dchain(tv, dtdh, hb);
     const D3 q = (1.0f / 25.0f) * ((180.0f / kPi) * hb - 275.0f);
     const D3 dro = 30.0f * dexp(-(q * q));
     const D3 Cb7 = dpow7(Cb);
@@ -292,7 +321,7 @@ __device__ D3 de00_loss_dual(float L1f, float a1f, float b1f, float L2, float a2
 // sRGB channel -> linear with derivative (autograd of where(c > .04045, pow(.., 2.4), c / 12.92))
 __device__ __forceinline__ float srgb_to_linear_d(float c, float &dc) {
     if (c > 0.04045f) {
-        const float base = (c + 0.055f) / 1.055f, v = powf(base, 2.4f);
+        const float base = (c + 0.055f) / 1.055f, v = pow24(base);
         dc = (2.4f / 1.055f) * (v / base);  // 2.4 base^1.4 / 1.055
         return v;
     }
@@ -301,8 +330,8 @@ __device__ __forceinline__ float srgb_to_linear_d(float c, float &dc) {
 }
 __device__ __forceinline__ float lab_f_d(float t, float &dt) {
     if (t > 0.008856f) {
-        const float v = powf(t, 1.0f / 3.0f);  // the reference's exponent is float(1/3), not an exact cube root
-        dt = (1.0f / 3.0f) * (v / t);          // t^(-2/3) / 3
+        const float v = cbrtf(t);
+        dt = (1.0f / 3.0f) * (v / t);  // t^(-2/3) / 3
         return v;
     }
     dt = 7.787f;
@@ -479,6 +508,22 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
     deltae_loss_grad_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+namespace llie {
+__global__ void srgb_to_linear_kernel(const float *in, float *out, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+        out[i] = srgb_to_linear(in[i]);
+}
+}  // namespace llie
+
+extern "C" int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream) {
+    LLIE_REQUIRE(in && out && n > 0, "selftest_srgb_to_linear: bad arguments");
+    long long blocks = (n + 255) / 256;
+    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
+    srgb_to_linear_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(in, out, n);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

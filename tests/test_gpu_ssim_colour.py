@@ -172,6 +172,23 @@ def test_colour_contracts(dev):
     assert e["mean"] == 0.0 and e["p95"] == 0.0
 
 
+def test_srgb_to_linear_ulp(dev):
+    """The kernels' x^2.4 (Newton-refined fifth root, csrc/deltae.cu pow24) against float64 pow on a dense
+    sweep of [0, 1] plus every 8-bit and 10-bit code value: < 1 ulp everywhere."""
+    from lowlight_image_enhancement_b200 import _native as nat
+    x = torch.cat([torch.linspace(0, 1, 2_000_003), torch.arange(256) / 255.0, torch.arange(1024) / 1023.0]).float()
+    xd = x.to(dev).contiguous()
+    out = torch.empty_like(xd)
+    nat.check(nat.lib().llie_selftest_srgb_to_linear(nat.ptr(xd), nat.ptr(out), xd.numel(), nat.stream_ptr(dev)), "selftest")
+    x64 = x.double()
+    base = ((x + 0.055) / 1.055).double()          # the fp32 quotient the kernel feeds to the power
+    ref = torch.where(x > 0.04045, base ** 2.4, x64 / 12.92)
+    got = out.cpu().double()
+    ulp = torch.abs(got - ref) / (2.0 ** (torch.floor(torch.log2(ref.clamp_min(1e-30))) - 23))
+    assert float(ulp[x > 0.04045].max()) < 1.0, float(ulp.max())
+    assert float(ulp.max()) < 1.0
+
+
 # ------------------------------------------------------------------ Sobel / quantile / edge mask
 def test_sobel_quantile_count_bit_exact(golden, dev):
     """g is the IEEE-754 value sqrt(fl(gx^2 + gy^2 + 1e-12)) (what the reference computes on a CUDA device).
