@@ -303,6 +303,129 @@ def run_ours(args, rank, world, dev):
     return line
 
 
+# ------------------------------------------------------------------------------------------------
+# secondary workloads (reported inside the same JSON line): BASELINE configs[3] eval and configs[2] hybrid loss
+# ------------------------------------------------------------------------------------------------
+EVAL_SHAPE = (1, 3, 2848, 4256)
+EVAL_METRICS = ["linear_psnr", "linear_ssim", "deltae2000_mean", "edge_deltae2000_mean"]
+
+
+def synth_eval_pair(seed, dev, shape=EVAL_SHAPE):
+    """gt = 8-bit noise low-passed by a 5x5 box and re-quantised, pred = clamp(gt + 0.03 N)."""
+    g = torch.Generator(device=dev).manual_seed(seed)
+    gt = torch.round(255 * torch.rand(shape, device=dev, generator=g)) / 255
+    gt = torch.round(255 * torch.nn.functional.avg_pool2d(gt, 5, 1, 2)) / 255
+    pred = (gt + 0.03 * torch.randn(shape, device=dev, generator=g)).clamp(0, 1)
+    return pred.contiguous(), gt.contiguous()
+
+
+def stressed_kernels(stress, dev):
+    """SURVEY.md §8d C3 (bench-defined; the reference names the family but gives no numbers):
+    K_c = delta + s * alpha_c * P2_offcentre, alpha = (1.3, 1.0, 0.7), renormalised to sum 1."""
+    p2 = torch.tensor([[.01, .02, .01], [.02, 0.0, .02], [.01, .02, .01]])
+    ks = []
+    for alpha in (1.3, 1.0, 0.7):
+        k = stress * alpha * p2
+        k[1, 1] = 1.0
+        ks.append(k / k.sum())
+    return torch.stack(ks).view(3, 1, 3, 3).to(dev)
+
+
+def run_extra(args, rank, world, dev):
+    """-> dict with 'eval_c4' (sharded eval, one all-reduce) and 'hybrid_c3' (HybridLossPlus fwd+bwd)."""
+    import torch.distributed as dist
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    from lowlight_image_enhancement_b200.eval import evaluate_pairs, image_metrics
+    from lowlight_image_enhancement_b200.metrics.ssim import torchmetrics_ssim_scores
+    from lowlight_image_enhancement_b200.NewBP_model.losses import HybridLossPlus
+    out = {}
+    peak, _ = peaks()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t)
+        return ms
+
+    # ---- eval: images sharded by index over the ranks, per-image metrics accumulated on the device,
+    # ONE all-reduce + ONE host sync at the end (lowlight_image_enhancement_b200/eval.py)
+    pool = [synth_eval_pair(4000 + 17 * rank + i, dev) for i in range(3)]   # 3 x 291 MB > L2
+    per_rank = max(6, min(48, args.steps))
+    n_img = per_rank * world
+    px = EVAL_SHAPE[2] * EVAL_SHAPE[3]
+    getter = lambda i: pool[(i // world) % 3]
+    evaluate_pairs(getter, EVAL_METRICS, n_items=3 * world, device=dev)    # warm-up (also NCCL)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize(dev)
+    t0 = time.perf_counter()
+    s_ev, e_ev = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s_ev.record()
+    res = evaluate_pairs(getter, EVAL_METRICS, n_items=n_img, device=dev)
+    e_ev.record()
+    torch.cuda.synchronize(dev)
+    wall = (time.perf_counter() - t0) * 1e3
+    ms = max_over_ranks(s_ev.elapsed_time(e_ev))
+    pr, gt = pool[0]
+    t_ssim = timed(lambda i: torchmetrics_ssim_scores(pool[i % 3][0], pool[i % 3][1], data_range=1.0, sigma=1.5,
+                                                      k1=0.01, k2=0.03), 6, dev) / 6
+    t_de = timed(lambda i: Fn.deltae(pool[i % 3][0], pool[i % 3][1], variant=0, clamp_in=True), 6, dev) / 6
+    t_ps = timed(lambda i: Fn.psnr_stats(pool[i % 3][1], pool[i % 3][0], 1, 1, 3 * px, cast_first=True, clamp_hi=None,
+                                         data_range=1.0, eps=1e-12), 6, dev) / 6
+    t_all = timed(lambda i: image_metrics(pool[i % 3][0], pool[i % 3][1], EVAL_METRICS), 6, dev) / 6
+
+    def kern(name, t, bpp, bound):
+        return {"kernel": name, "ms": round(t, 4), "Mpix/s": round(px / t / 1e3, 1),
+                "algorithmic_bytes": bpp * px, "achieved_gbs": round(bpp * px / t / 1e6, 1),
+                "frac_hbm": round(bpp * px / t / 1e6 / peak, 4), "bound": bound}
+    out["eval_c4"] = {
+        "workload": "PSNR + SSIM(torchmetrics policy) + dE00 mean + edge dE00 on 1x3x2848x4256 sRGB pairs (BASELINE configs[3]), "
+                    f"{per_rank} images per GPU sharded by index, device-side accumulation, one all-reduce, one host sync",
+        "value": round(n_img * px / 1e6 / (ms / 1e3), 1), "unit": "Mpix/s", "images": n_img, "n_gpus": world,
+        "ms_per_image_per_gpu": round(ms / per_rank, 4), "wall_ms": round(wall, 2),
+        "means": {k: (round(v, 6) if isinstance(v, float) else v) for k, v in res.items()},
+        "kernels": [kern("psnr_stats_kernel", t_ps, 24, "hbm"),
+                    kern("ssim_stream_kernel<11>", t_ssim, 24, "fp32 fma pipe (110 FMA per element)"),
+                    kern("deltae_kernel", t_de, 24, "instruction issue (fp32 + sfu)"),
+                    kern("all 4 metrics of one image (12 launches)", t_all, 36, "mixed")],
+    }
+    del pool, pr, gt
+    torch.cuda.empty_cache()
+
+    # ---- hybrid loss, C3: L1 + 0.05 DSSIM + 0.02 dE00 + 0.05 phys (stressed rgb kernel, RAW convention)
+    n = 16
+    g = torch.Generator(device=dev).manual_seed(103 + rank)
+    B = torch.rand(n, 3, 512, 512, device=dev, generator=g)
+    kern3 = stressed_kernels(2.0, dev)
+    A = (torch.nn.functional.conv2d(torch.nn.functional.pad(B, (1, 1, 1, 1), mode="replicate"), kern3, groups=3)
+         + 0.02 * torch.randn(B.shape, device=dev, generator=g)).clamp(0, 1)
+    xs = [(B + 0.05 * torch.randn(B.shape, device=dev, generator=g)).clamp(0, 1) for _ in range(4)]   # 4 x 50 MB + grads
+    rho = torch.ones(n, 1, 1, 1, device=dev)
+    hyb = HybridLossPlus(device=dev, w_l1_raw=1.0, w_perc=0.0, w_deltaE=0.02, w_ssim=0.05, w_phys=0.05,
+                         physics_kernel=kern3, check_finite=False)
+
+    def hstep(i):
+        x = xs[i % 4].detach().requires_grad_(True)
+        tot, _ = hyb(Bhat_raw=x, B_raw=B, A_raw=A, expo_ratio=rho, Bhat_srgb01=x, B_srgb01=B)
+        tot.backward()
+        return tot
+
+    for i in range(3):
+        hstep(i)
+    kh = max(6, min(50, args.steps))
+    ms_h = max_over_ranks(timed(hstep, kh, dev)) / kh
+    pxl = n * 512 * 512
+    out["hybrid_c3"] = {
+        "workload": "HybridLossPlus L1 + 0.05 DSSIM + 0.02 dE00 + 0.05 phys (stressed rgb PSF s=2) fwd+bwd, 16x3x512x512 fp32 "
+                    "(BASELINE configs[2]), per GPU",
+        "value": round(world * pxl / 1e6 / (ms_h / 1e3), 1), "unit": "Mpix/s", "ms_per_step": round(ms_h, 4),
+        "algorithmic_bytes_per_step": (36 + 48) * pxl,
+        "achieved_gbs": round((36 + 48) * pxl / ms_h / 1e6, 1), "n_gpus": world,
+    }
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -312,6 +435,7 @@ def main():
     ap.add_argument("--workload", default="phys_c2")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: 1 untimed-quality e2e step only")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: no cpu_baseline leg")
+    ap.add_argument("--skip-extra", action="store_true", help="profiling runs: no eval_c4 / hybrid_c3 sections")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
@@ -328,6 +452,10 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     line = run_ours(args, rank, world, dev)
+    if not args.skip_extra:
+        extra = run_extra(args, rank, world, dev)
+        if line is not None:
+            line.update(extra)
     if line is not None:
         print(json.dumps(line), flush=True)
     if world > 1:
