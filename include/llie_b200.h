@@ -196,13 +196,14 @@ int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, 
  * sensitivities of S to (mu_x, E[x^2], E[xy]); backward folds them through the adjoint of reflect-pad o
  * separable correlation:  out_grad = mask_[0,1](x) * g * (G^T c1 + 2 x G^T c2 + y G^T c3).
  * `grad_out` is a DEVICE pointer: one float (gradient of the reduced loss) or, with grad_out_is_map, a
- * [n,c,h,w] map (reduction 'none').  replaces kornia.losses.SSIMLoss autograd (losses.py:146-155). */
+ * [n,c,h,w] map (reduction 'none'); with `accumulate` the result is added to out_grad (fused hybrid loss).
+ * replaces kornia.losses.SSIMLoss autograd (losses.py:146-155). */
 int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
                            float grad_scale, double *out_sum, float *out_map, float *out_coef, int32_t *out_flags,
                            void *workspace, void *stream);
 int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                            const float *coef, const float *grad_out, int32_t grad_out_is_map, float *out_grad,
-                            void *stream);
+                            const float *coef, const float *grad_out, int32_t grad_out_is_map, int32_t accumulate,
+                            float *out_grad, void *stream);
 
 /* ------------------------------------------------------------------------
  * sRGB -> Lab(D65/2deg) -> CIEDE2000, per-image float64 sums (+ optional map / L plane of x).
@@ -225,6 +226,12 @@ int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, do
  * of `dE.mean()` when grad_scale = 1 / (n h w).  replaces losses.py:138-143 + its autograd graph. */
 int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const float *y, float grad_scale,
                           double *out_sum, float *out_grad, int32_t *out_flags, void *workspace, void *stream);
+
+/* nn.L1Loss value + gradient in one pass: out_sum[1] = sum |x - y| (float64); out_grad (NULL = value only) =
+ * grad_scale * sign(x - y), added to its previous content when `accumulate`.  n = element count.
+ * replaces NewBP_model/losses.py:249,332 (nn.L1Loss on the RAW tensors) and its autograd. */
+int llie_l1_grad(const float *x, const float *y, int64_t n, float grad_scale, int32_t accumulate, double *out_sum,
+                 float *out_grad, int32_t *out_flags, void *workspace, void *stream);
 
 /* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the
  * < 1 ulp claim can be checked against a float64 pow from the test-suite. */

@@ -206,15 +206,11 @@ class SSIMLoss(nn.Module):
 
 
 class _L1Mean(nn.Module):
-    """nn.L1Loss() (global mean) with its sign/numel gradient: the physics projector with a 1x1 identity
-    stencil, i.e. one read of each tensor forward and one backward (losses.py:249, 332)."""
+    """nn.L1Loss() (global mean) with its sign/numel gradient from one streaming pass (losses.py:249, 332)."""
 
     def forward(self, a: Tensor, b: Tensor) -> Tensor:
         x, y, home, dev = _pair_on_device(a, b)
-        n, c = x.shape[:2]
-        psf = Fn.PreparedPSF(torch.ones(c, 1, 1, 1, dtype=torch.float32, device=dev), Fn.PSF_DEPTHWISE, 1, 1, False)
-        cfg = Fn.PhysCfg(nat.PAD["zeros"], False, False, 1e-12, 1, False, False)
-        out = Fn.PhysProjector.apply(x, y, psf, None, 1.0, (0, 0, 0, 0), cfg)[n]
+        out = Fn.L1MeanFn.apply(x, y)
         return out if home == dev else out.to(home)
 
 
@@ -226,14 +222,19 @@ class HybridLossPlus(nn.Module):
 
     The reference checks every term for finiteness as it goes (5-7 host syncs per step); here the terms are
     checked together after the last one (a single sync), raising the same RuntimeError that names the first
-    offending term.  `check_finite=False` removes that sync (CUDA-graph capture)."""
+    offending term.  `check_finite=False` removes that sync (CUDA-graph capture).
+
+    With fixed weights the four kernel terms run as ONE autograd node (`Fn.HybridFusedFn`): every gradient kernel
+    runs in forward with its weight folded in and accumulates into one buffer per input, so backward is a scaling.
+    `fused=False`, `use_uncertainty=True` or a physics module that is not a plain `CrosstalkPSF` select the
+    per-term modules (same values, more launches)."""
 
     def __init__(self, device: str = "cuda", w_l1_raw: float = 1.0, w_perc: float = 0.02, w_lpips: float = 0.0,
                  w_deltaE: float = 0.02, w_ssim: float = 0.05, w_phys: float = 0.10, use_deltaE: bool = True,
                  use_ssim: bool = True, use_lpips: bool = False, use_phys: bool = True, use_uncertainty: bool = False,
                  physics_kernel: Optional[Tensor] = None, physics_psf_module: Optional[nn.Module] = None, *,
                  perceptual_module: Optional[nn.Module] = None, lpips_module: Optional[nn.Module] = None,
-                 check_finite: bool = True):
+                 check_finite: bool = True, fused: bool = True):
         super().__init__()
         device = _resolve_device(device)
         self.register_buffer("_zero", torch.tensor(0.0), persistent=False)
@@ -251,6 +252,8 @@ class HybridLossPlus(nn.Module):
             self.phys_srgb = None
         self.use_uncertainty = use_uncertainty
         self.check_finite = check_finite
+        self.fused = fused          # one autograd node for the kernel terms (falls back to per-term modules when it cannot)
+        self._spec = None
         if use_uncertainty:
             self.log_sigma = nn.ParameterDict({k: nn.Parameter(torch.zeros(()))
                                                for k in ("l1", "perc", "lpips", "de", "ssim", "phys")})
@@ -277,8 +280,92 @@ class HybridLossPlus(nn.Module):
             return (val * torch.exp(-2 * s.to(val.device)) + s.to(val.device)), val.detach()
         return self.w[name] * val, val.detach()
 
+    def _fused_spec(self, dev, Bhat_raw, A_raw, expo_ratio, Bhat_srgb01, A_srgb01):
+        """Arguments of Fn.HybridFusedFn for this call, or None when the modular path has to run (learned
+        uncertainty weights, a non-CrosstalkPSF / hooked physics module, unexpected shapes)."""
+        if self.use_uncertainty or Bhat_raw.ndim != 4 or Bhat_srgb01.ndim != 4 or Bhat_srgb01.shape[1] != 3:
+            return None
+        if self._spec is None:
+            self._spec = dict(w={k: float(v) for k, v in self.w.items()}, use_de=self.deltaE is not None,
+                              de_eps=self.deltaE.eps if self.deltaE is not None else 1e-6,
+                              use_ssim=self.ssim is not None,
+                              ssim_window=self.ssim.window_size if self.ssim is not None else 11,
+                              ssim_max_val=self.ssim.max_val if self.ssim is not None else 1.0)
+        spec = self._spec
+        spec["phys"] = None
+        if self.phys is not None:
+            n, c = Bhat_raw.shape[:2]
+            rho_t, rho_s, rho_st = _as_rho(expo_ratio, n, dev)
+            cfg = Fn.PhysCfg(nat.PAD["replicate"], False, False, 1e-12, 1, False, bool(self.phys.clamp_align))
+            spec["phys"] = dict(srgb=False, a=nat.stage(A_raw.detach(), dev, torch.float32), psf=self.phys._psf(c, dev),
+                                rho_t=rho_t, rho_s=rho_s, rho_st=rho_st, cfg=cfg)
+        elif self.phys_srgb is not None and A_srgb01 is not None:
+            psf = self.phys_srgb._fused_psf(dev)
+            if psf is None:
+                return None
+            rho_t, rho_s, rho_st = _as_rho(expo_ratio, Bhat_srgb01.shape[0], dev)
+            cfg = Fn.PhysCfg(nat.PAD["zeros"], False, False, 1e-12, 1, False, True)
+            spec["phys"] = dict(srgb=True, a=nat.stage(A_srgb01.detach(), dev, torch.float32), psf=psf, rho_t=rho_t,
+                                rho_s=rho_s, rho_st=rho_st, cfg=cfg)
+        return spec
+
     def forward(self, *, Bhat_raw: Tensor, B_raw: Tensor, A_raw: Tensor, expo_ratio: Tensor, Bhat_srgb01: Tensor,
                 B_srgb01: Tensor, A_srgb01: Optional[Tensor] = None):
+        if self.fused:
+            dev = nat.cuda_device_for(Bhat_raw, Bhat_srgb01)
+            spec = self._fused_spec(dev, Bhat_raw, A_raw, expo_ratio, Bhat_srgb01, A_srgb01)
+            if spec is not None:
+                return self._forward_fused(dev, spec, Bhat_raw, B_raw, Bhat_srgb01, B_srgb01)
+        return self._forward_modular(Bhat_raw=Bhat_raw, B_raw=B_raw, A_raw=A_raw, expo_ratio=expo_ratio,
+                                     Bhat_srgb01=Bhat_srgb01, B_srgb01=B_srgb01, A_srgb01=A_srgb01)
+
+    def _forward_fused(self, dev, spec, Bhat_raw, B_raw, Bhat_srgb01, B_srgb01):
+        """One autograd node for L1 + dE00 + DSSIM + physics (weights folded into the gradient kernels), the
+        injected perceptual / LPIPS modules on top; same `(total, logs)` as the modular path."""
+        home = Bhat_raw.device
+        xr = nat.stage(Bhat_raw, dev, torch.float32)
+        xs = nat.stage(Bhat_srgb01, dev, torch.float32)
+        br = nat.stage(B_raw.detach(), dev, torch.float32)
+        bs = nat.stage(B_srgb01.detach(), dev, torch.float32)
+        if xr.shape != br.shape or xs.shape != bs.shape:
+            raise ValueError("HybridLossPlus: prediction and target shapes differ")
+        total, terms = Fn.HybridFusedFn.apply(xr, xs, br, bs, spec)
+        logs: Dict[str, Tensor] = {"L1_raw": terms[0]}
+        checks = [("L1_raw", terms[0])]
+        if self.perc is not None:
+            lp = self.perc(Bhat_srgb01, B_srgb01)
+            checks.append(("Perc", lp))
+            lw, logs["Perc"] = self._weighted("perc", lp)
+            total = total + lw.to(dev)
+        else:
+            logs["Perc"] = self._zero.clone().to(home)
+        if self.lpips is not None:
+            ll = self.lpips(Bhat_srgb01, B_srgb01).mean()
+            checks.append(("LPIPS", ll))
+            lw, logs["LPIPS"] = self._weighted("lpips", ll)
+            total = total + lw.to(dev)
+        if spec["use_de"]:
+            logs["DeltaE"] = terms[1]
+            checks.append(("DeltaE", terms[1]))
+        if spec["use_ssim"]:
+            logs["SSIM"] = terms[2]
+            checks.append(("SSIM", terms[2]))
+        if spec["phys"] is not None:
+            logs["Phys"] = terms[3]
+            checks.append(("Phys_srgb" if spec["phys"]["srgb"] else "Phys_raw", terms[3]))
+        if self.check_finite:
+            vals = torch.stack([v.detach().reshape(()).float().to(dev) for _, v in checks])
+            if not bool(torch.isfinite(vals).all()):                      # the one host sync of the step
+                for name, v in checks:
+                    self._ensure_finite(name, v.detach())
+        if home != dev:
+            total = total.to(home)
+            logs = {k: v.to(home) for k, v in logs.items()}
+        logs["Total"] = total.detach()
+        return total, logs
+
+    def _forward_modular(self, *, Bhat_raw: Tensor, B_raw: Tensor, A_raw: Tensor, expo_ratio: Tensor,
+                         Bhat_srgb01: Tensor, B_srgb01: Tensor, A_srgb01: Optional[Tensor] = None):
         logs: Dict[str, Tensor] = {}
         terms = []          # (check name, value) in the reference's order
         total = 0.0

@@ -526,7 +526,158 @@ class SSIMLossFn(torch.autograd.Function):
         out = torch.empty_like(x)
         with torch.cuda.device(dev):
             rc = nat.lib().llie_ssim_loss_backward(ctx.desc, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(coef),
-                                                   nat.ptr(g), int(is_map), nat.ptr(out), nat.stream_ptr(dev))
+                                                   nat.ptr(g), int(is_map), 0, nat.ptr(out), nat.stream_ptr(dev))
         nat.check(rc, "llie_ssim_loss_backward")
         nat.count_launch()
         return out, None, None, None, None
+
+
+class L1MeanFn(torch.autograd.Function):
+    """nn.L1Loss() (global mean): value and sign/numel gradient from one streaming pass (llie_l1_grad)."""
+
+    @staticmethod
+    def forward(ctx, x: Tensor, y: Tensor):
+        a = x.detach().contiguous()
+        b = y.detach().contiguous()
+        dev = a.device
+        sums = torch.empty(1, dtype=torch.float64, device=dev)
+        flags = torch.empty(1, dtype=torch.int32, device=dev)
+        grad = torch.empty_like(a) if ctx.needs_input_grad[0] else None
+        with torch.cuda.device(dev):
+            rc = nat.lib().llie_l1_grad(nat.ptr(a), nat.ptr(b), a.numel(), 1.0 / a.numel(), 0, nat.ptr(sums),
+                                        nat.ptr(grad), nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+        nat.check(rc, "llie_l1_grad")
+        nat.count_launch()
+        if grad is not None:
+            ctx.save_for_backward(grad)
+        return (sums[0] / float(a.numel())).to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, gout):
+        (grad,) = ctx.saved_tensors
+        return grad * gout, None
+
+
+_ones: dict = {}
+
+
+def _one(dev: torch.device) -> Tensor:
+    t = _ones.get(dev)
+    if t is None:
+        t = torch.ones(1, dtype=torch.float32, device=dev)
+        _ones[dev] = t
+    return t
+
+
+class HybridFusedFn(torch.autograd.Function):
+    """The four kernel terms of HybridLossPlus with FIXED weights in one autograd node.
+
+    total = w_l1 L1(x_raw, b_raw) + w_de dE00(x_srgb, b_srgb) + w_ssim DSSIM(x_srgb, b_srgb) + w_phys Phys.
+    Every gradient kernel runs in forward with its weight folded into its scale and accumulates into one
+    buffer per input (x_raw: phys backward writes, L1 adds; x_srgb: dE00 writes, DSSIM backward adds), so
+    backward is two scalings.  Returns (total, term values [L1, dE, SSIM, Phys] as a non-differentiable
+    float32 vector; absent terms are NaN)."""
+
+    @staticmethod
+    def forward(ctx, x_raw, x_srgb, b_raw, b_srgb, spec):
+        w = spec["w"]
+        dev = x_raw.device
+        xr = x_raw.detach().contiguous()
+        xs = x_srgb.detach().contiguous()
+        br = b_raw.detach().contiguous()
+        bs = b_srgb.detach().contiguous()
+        need_raw, need_srgb = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        lib = nat.lib()
+        ws = nat.ptr(nat.workspace(dev))
+        flags = torch.empty(1, dtype=torch.int32, device=dev)
+        nan = torch.full((), float("nan"), dtype=torch.float32, device=dev)
+        vals = [nan, nan, nan, nan]
+        g_raw = g_srgb = None
+        launches = 0
+        with torch.cuda.device(dev):
+            st = nat.stream_ptr(dev)
+            # ---- RAW side: physics (writes the buffer) then L1 (adds)
+            ph = spec.get("phys")
+            if ph is not None and not ph["srgb"]:
+                n = xr.shape[0]
+                vec, _, _ = phys_forward(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"], False)
+                vals[3] = vec[n]
+                if need_raw:
+                    g_raw = phys_backward(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
+                                          _one(dev), w["phys"] / float(ph["a"].numel()))
+            l1s = torch.empty(1, dtype=torch.float64, device=dev)
+            acc = 1 if g_raw is not None else 0
+            if need_raw and g_raw is None:
+                g_raw = torch.empty_like(xr)
+            nat.check(lib.llie_l1_grad(nat.ptr(xr), nat.ptr(br), xr.numel(), w["l1"] / xr.numel(), acc, nat.ptr(l1s),
+                                       nat.ptr(g_raw), nat.ptr(flags), ws, st), "llie_l1_grad")
+            launches += 1
+            vals[0] = (l1s[0] / float(xr.numel())).to(torch.float32)
+            # ---- sRGB side: dE00 (writes) then DSSIM backward (adds), then the sRGB physics term if any
+            n, c, h, wd = xs.shape
+            if spec["use_de"]:
+                des = torch.empty(n, dtype=torch.float64, device=dev)
+                dd = nat.DeltaEDesc(n, h, wd, 1, 0, 1, 1.0, 1.0, 1.0, float(spec["de_eps"]))
+                if need_srgb:
+                    g_srgb = torch.empty_like(xs)
+                    nat.check(lib.llie_deltae_loss_grad(dd, nat.ptr(xs), nat.ptr(bs), w["de"] / float(n * h * wd),
+                                                        nat.ptr(des), nat.ptr(g_srgb), nat.ptr(flags), ws, st),
+                              "llie_deltae_loss_grad")
+                else:
+                    nat.check(lib.llie_deltae(dd, nat.ptr(xs), nat.ptr(bs), nat.ptr(des), None, None, nat.ptr(flags),
+                                              ws, st), "llie_deltae")
+                launches += 1
+                vals[1] = (des.sum() / float(n * h * wd)).to(torch.float32)
+            if spec["use_ssim"]:
+                k = int(spec["ssim_window"])
+                mv = float(spec["ssim_max_val"])
+                win = window_1d("kornia", k, 1.5, dev)
+                sd = nat.SsimDesc(n, c, h, wd, k, nat.PAD["reflect"], 0, 1, 0, 0, 1, (0.01 * mv) ** 2, (0.03 * mv) ** 2,
+                                  1e-12)
+                sss = torch.empty((n, c), dtype=torch.float64, device=dev)
+                if need_srgb:
+                    coef = torch.empty((3, n, c, h, wd), dtype=torch.float32, device=dev)
+                    nat.check(lib.llie_ssim_loss_forward(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win),
+                                                         w["ssim"] / float(xs.numel()), nat.ptr(sss), None,
+                                                         nat.ptr(coef), nat.ptr(flags), ws, st), "llie_ssim_loss_forward")
+                    acc = 1 if g_srgb is not None else 0
+                    if g_srgb is None:
+                        g_srgb = torch.empty_like(xs)
+                    nat.check(lib.llie_ssim_loss_backward(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), nat.ptr(coef),
+                                                          nat.ptr(_one(dev)), 0, acc, nat.ptr(g_srgb), st),
+                              "llie_ssim_loss_backward")
+                    launches += 2
+                else:
+                    nat.check(lib.llie_ssim_stats(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), nat.ptr(sss), None,
+                                                  nat.ptr(flags), ws, st), "llie_ssim_stats")
+                    launches += 1
+                vals[2] = (sss.sum() / float(xs.numel())).to(torch.float32)
+            if ph is not None and ph["srgb"]:
+                vec, _, _ = phys_forward(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"], False)
+                vals[3] = vec[n]
+                if need_srgb:
+                    gp = phys_backward(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
+                                       _one(dev), w["phys"] / float(ph["a"].numel()))
+                    g_srgb = gp if g_srgb is None else g_srgb.add_(gp)
+        nat.count_launch(launches)
+        terms = torch.stack(vals)
+        present = [0] + ([1] if spec["use_de"] else []) + ([2] if spec["use_ssim"] else []) + ([3] if ph is not None else [])
+        key = ("_wvec", dev.index)
+        if key not in spec:  # weights are fixed for the lifetime of the module: upload once
+            names = ("l1", "de", "ssim", "phys")
+            spec[key] = (torch.tensor(present, device=dev),
+                         torch.tensor([w[names[i]] for i in present], dtype=torch.float32, device=dev))
+        idx, wvec = spec[key]
+        total = (terms.index_select(0, idx) * wvec).sum()
+        ctx.save_for_backward(*[t for t in (g_raw, g_srgb) if t is not None])
+        ctx.have = (g_raw is not None, g_srgb is not None)
+        ctx.mark_non_differentiable(terms)
+        return total, terms
+
+    @staticmethod
+    def backward(ctx, gtot, _gterms):
+        saved = list(ctx.saved_tensors)
+        g_raw = saved.pop(0) if ctx.have[0] else None
+        g_srgb = saved.pop(0) if ctx.have[1] else None
+        return (g_raw * gtot if g_raw is not None else None, g_srgb * gtot if g_srgb is not None else None,
+                None, None, None)

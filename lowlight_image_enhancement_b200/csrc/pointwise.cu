@@ -258,3 +258,122 @@ extern "C" int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const 
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// nn.L1Loss (global mean) value + gradient in one streaming pass (NewBP_model/losses.py:249, 332):
+//   out_sum = sum |x - y| (float64),  grad = scale * sign(x - y)  [ + grad when accumulate ]
+// 8 B/element read (+ 4 read when accumulating), 4 written; sign(0) = 0 as in ATen.
+namespace llie {
+
+struct L1Args {
+    const float *x, *y;
+    float *grad;
+    double *out_sum;
+    int *out_flags;
+    double *part;
+    int *pflag;
+    unsigned *ticket;
+    long long n;
+    float scale;
+    int accumulate, vec_ok;
+};
+
+__device__ __forceinline__ float l1_term(float xv, float yv, float scale, float &acc, float &chk_x, float &chk_y) {
+    chk_x = fmaf(xv, 0.f, chk_x);
+    chk_y = fmaf(yv, 0.f, chk_y);
+    const float dlt = xv - yv;
+    acc += fabsf(dlt);
+    return dlt > 0.f ? scale : (dlt < 0.f ? -scale : 0.f);
+}
+
+__global__ void __launch_bounds__(256) l1_grad_kernel(const L1Args a) {
+    __shared__ double red[32];
+    float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    double dacc = 0.0;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+    if (a.vec_ok) {
+        const long long nv = a.n >> 2;
+        float4 *g4 = reinterpret_cast<float4 *>(a.grad);
+        int it = 0;
+        for (long long i = tid; i < nv; i += nth) {
+            const float4 xv = ldg_stream4(a.x + 4 * i), yv = ldg_stream4(a.y + 4 * i);
+            float4 g;
+            g.x = l1_term(xv.x, yv.x, a.scale, acc, chk_x, chk_y);
+            g.y = l1_term(xv.y, yv.y, a.scale, acc, chk_x, chk_y);
+            g.z = l1_term(xv.z, yv.z, a.scale, acc, chk_x, chk_y);
+            g.w = l1_term(xv.w, yv.w, a.scale, acc, chk_x, chk_y);
+            if (g4) {
+                if (a.accumulate) {
+                    const float4 o = g4[i];
+                    g.x += o.x; g.y += o.y; g.z += o.z; g.w += o.w;
+                }
+                g4[i] = g;
+            }
+            if (++it == 64) {  // bound the float32 run length: 256 terms per flush
+                dacc += (double)acc;
+                acc = 0.f;
+                it = 0;
+            }
+        }
+    } else {
+        int it = 0;
+        for (long long i = tid; i < a.n; i += nth) {
+            float g = l1_term(__ldg(a.x + i), __ldg(a.y + i), a.scale, acc, chk_x, chk_y);
+            if (a.grad) {
+                if (a.accumulate) g += a.grad[i];
+                a.grad[i] = g;
+            }
+            if (++it == 256) {
+                dacc += (double)acc;
+                acc = 0.f;
+                it = 0;
+            }
+        }
+    }
+    dacc += (double)acc;
+    const double bs = block_sum<double>(dacc, red);
+    int flag = 0;
+    if (!(chk_x == 0.f)) flag |= 1;
+    if (!(chk_y == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        a.part[blockIdx.x] = bs;
+        a.pflag[blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x)) return;
+    double s0 = 0.0;
+    int fl = 0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
+        s0 += __ldcg(a.part + b);
+        fl |= __ldcg(a.pflag + b);
+    }
+    const double t = block_sum<double>(s0, red);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        *a.out_sum = t;
+        *a.out_flags = ff;
+    }
+}
+
+}  // namespace llie
+
+extern "C" int llie_l1_grad(const float *x, const float *y, int64_t n, float grad_scale, int32_t accumulate,
+                            double *out_sum, float *out_grad, int32_t *out_flags, void *workspace, void *stream) {
+    LLIE_REQUIRE(x && y && out_sum && out_flags && workspace && n > 0, "l1_grad: bad arguments");
+    llie::L1Args a{};
+    a.x = x; a.y = y; a.grad = out_grad; a.out_sum = out_sum; a.out_flags = out_flags;
+    a.n = n; a.scale = grad_scale; a.accumulate = accumulate;
+    a.vec_ok = llie::aligned16(x) && llie::aligned16(y) && (!out_grad || llie::aligned16(out_grad)) && (n % 4 == 0);
+    long long blocks = (n / 4 + 255) / 256;
+    const long long cap = llie::kNumSM * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    llie::Workspace ws(workspace);
+    a.part = reinterpret_cast<double *>(ws.scratch);
+    a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)blocks * sizeof(double));
+    a.ticket = ws.tickets;
+    llie::l1_grad_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}

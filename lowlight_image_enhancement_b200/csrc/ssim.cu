@@ -453,7 +453,7 @@ int g_ssim_seg_rows = 0;  // 0 = heuristic
 // Same tiling as the forward kernel: (A) coefficient tile with halo (zeros outside the image) -> smem,
 // (B) horizontal pass + column folds, (C) vertical pass + row folds, combine with x, y (8 B/elem read).
 struct SsimBwdArgs {
-    int n, c, h, w, clamp_in, gout_is_map;
+    int n, c, h, w, clamp_in, gout_is_map, accumulate;
     const float *x, *y, *win, *coef;
     const float *gout;  // device scalar (upstream gradient of the reduced loss) or a [n,c,h,w] map
     float *out_grad;
@@ -602,7 +602,8 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
             yv = fminf(fmaxf(yv, 0.f), 1.f);
         }
         const float gr = g1 + 2.f * xv * g2 + yv * g3;
-        ob[off] = pass ? gr : 0.f;
+        const float res = pass ? gr : 0.f;
+        ob[off] = a.accumulate ? ob[off] + res : res;
     }
 }
 
@@ -711,7 +712,7 @@ extern "C" int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x
 
 extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
                                        const float *coef, const float *grad_out, int32_t grad_out_is_map,
-                                       float *out_grad, void *stream) {
+                                       int32_t accumulate, float *out_grad, void *stream) {
     LLIE_REQUIRE(desc && x && y && win1d && coef && grad_out && out_grad, "ssim_loss_backward: null pointer");
     const llie_ssim_desc &d = *desc;
     LLIE_REQUIRE(d.n > 0 && d.c > 0 && d.h > 0 && d.w > 0, "ssim_loss_backward: empty tensor");
@@ -721,7 +722,7 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
     LLIE_REQUIRE(d.ksize / 2 < d.h && d.ksize / 2 < d.w && d.ksize <= d.h && d.ksize <= d.w,
                  "ssim_loss_backward: window larger than the image");
     SsimBwdArgs a{};
-    a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map;
+    a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map; a.accumulate = accumulate;
     a.x = x; a.y = y; a.win = win1d; a.coef = coef; a.gout = grad_out; a.out_grad = out_grad;
     a.tiles_x = div_up(d.w, STW);
     a.tiles_y = div_up(d.h, STH);

@@ -135,8 +135,9 @@ def test_ssim_loss_reductions_and_identity(dev):
         SSIMLoss()(torch.rand(1, 3, 5, 40, device=dev), torch.rand(1, 3, 5, 40, device=dev))
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("mode", ["raw_kernel", "srgb_psf"])
-def test_hybrid_loss_plus_vs_oracle(dev, mode):
+def test_hybrid_loss_plus_vs_oracle(dev, mode, fused):
     """losses.py:318-372 with the perceptual / LPIPS terms absent (out of scope): total, logs, gradient."""
     from lowlight_image_enhancement_b200.NewBP_model.losses import HybridLossPlus
     from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import CrosstalkPSF, build_psf_kernels
@@ -150,11 +151,11 @@ def test_hybrid_loss_plus_vs_oracle(dev, mode):
     kw = dict(w_l1=1.0, w_de=0.02, w_ssim=0.05, w_phys=0.05)
     if mode == "raw_kernel":
         ora_kw = dict(physics_kernel=kern)
-        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern)
+        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, fused=fused)
     else:
         psf = CrosstalkPSF("rgb", kern)
         ora_kw = dict(psf_kernel=psf.kernel.clone())
-        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_psf_module=psf)
+        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_psf_module=psf, fused=fused)
 
     def ora(dt):
         x = Bhat.to(dt).clone().requires_grad_(True)
