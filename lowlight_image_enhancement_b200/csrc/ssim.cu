@@ -607,6 +607,158 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
     }
 }
 
+// Streaming backward (default when the upstream gradient is a scalar): same structure as ssim_stream_kernel —
+// one thread per column of a 128-column strip, coefficient rows (zero outside the image) streamed through a
+// cp.async ring, K-tap horizontal pass from shared memory, K rolling vertical accumulators per map in registers.
+// The mirror folds of the reflect adjoint are folded into the WEIGHTS: a border column adds the taps of its
+// mirrored partner to its own per-thread horizontal taps (computed once), and the vertical scatter weight of (input row p, output row y) gains
+// g[p + y + P] at the top (1 <= y <= P, p + y <= P) and g[p - (2H - 2 - y) + P] at the bottom; those tests are
+// uniform over the CTA and only compiled into the path taken by segments that touch the top / bottom rows.
+template <int K>
+__global__ void __launch_bounds__(SW) ssim_bwd_stream_kernel(const SsimBwdArgs a, int seg_rows) {
+    constexpr int P = K / 2;
+    constexpr int RW = SW + 2 * P;
+    __shared__ float sC[3][SD][RW];
+    __shared__ float sg[K];
+    const int H = a.h, W = a.w, tid = threadIdx.x;
+    const int tpp = a.tiles_x * a.tiles_y;
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int seg = trem / a.tiles_x, strip = trem - seg * a.tiles_x;
+    const int x0 = strip * SW, y0 = seg * seg_rows;
+    const int rows_out = min(seg_rows, H - y0);
+    const int nrows_in = rows_out + 2 * P;
+    const long long plane_elems = (long long)H * W;
+    const long long cstride = (long long)a.n * a.c * plane_elems;
+    const float *cb = a.coef + (long long)plane * plane_elems;
+    const float gs = __ldg(a.gout);
+
+    float g[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
+    if (tid < K) sg[tid] = __ldg(a.win + tid);
+
+    const int gin0 = x0 - P + tid, gin1 = x0 - P + SW + tid;
+    const bool has_ext = tid < 2 * P;
+    const unsigned bm = (gin0 >= 0 && gin0 < W) ? 4u : 0u;
+    const unsigned be = (has_ext && gin1 >= 0 && gin1 < W) ? 4u : 0u;
+    const float *pm = cb + min(max(gin0, 0), W - 1), *pe = cb + min(max(gin1, 0), W - 1);
+    const unsigned sca = (unsigned)__cvta_generic_to_shared(&sC[0][0][tid]);
+
+    auto issue_row = [&](int i) {
+        if (i < nrows_in) {
+            const int sy = y0 - P + i;
+            const unsigned ok = (sy >= 0 && sy < H) ? 4u : 0u;
+            const long long ro = (long long)min(max(sy, 0), H - 1) * W;
+            const unsigned so = (unsigned)((i & (SD - 1)) * RW * 4);
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                cp_async4(sca + m * SD * RW * 4 + so, pm + m * cstride + ro, min(bm, ok));
+                if (has_ext) cp_async4(sca + m * SD * RW * 4 + so + SW * 4, pe + m * cstride + ro, min(be, ok));
+            }
+        }
+        cp_async_commit();
+    };
+
+    const int gx = x0 + tid;
+    const bool col_in = gx < W;
+    const bool seg_fold = (y0 <= P) || (y0 + rows_out > H - 1 - P);
+    const float *xb = a.x + (long long)plane * plane_elems + gx, *yb = a.y + (long long)plane * plane_elems + gx;
+    float *ob = a.out_grad + (long long)plane * plane_elems + gx;
+    float acc[3][K];
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+        for (int j = 0; j < K; ++j) acc[m][j] = 0.f;
+
+#pragma unroll
+    for (int i = 0; i < SD - 1; ++i) issue_row(i);
+    __syncthreads();  // sg visible
+    // horizontal taps of THIS column with the mirror folds added: tap j reads image column x = gx - P + j; a left
+    // border column q in [1, P] also collects t(-q), i.e. + g[j + 2q]; a right border column + g[j + 2q - 2W + 2]
+    float gh[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+        float wj = g[j];
+        const int x = gx - P + j;
+        if (col_in && gx >= 1 && gx <= P && x >= 0 && j + 2 * gx <= 2 * P) wj += sg[j + 2 * gx];
+        if (col_in && gx >= W - 1 - P && gx <= W - 2 && x <= W - 1 && j + 2 * gx - 2 * W + 2 >= 0)
+            wj += sg[j + 2 * gx - 2 * W + 2];
+        gh[j] = wj;
+    }
+    for (int base = 0; base < nrows_in; base += K) {
+#pragma unroll
+        for (int ii = 0; ii < K; ++ii) {
+            const int i = base + ii;
+            if (i >= nrows_in) break;  // uniform
+            const int slot = i & (SD - 1);
+            cp_async_wait<SD - 2>();
+            __syncthreads();
+            issue_row(i + SD - 1);
+            const int p = y0 - P + i;
+            const bool vfold = seg_fold && (p < P || p >= H - P);  // uniform; only <= 2P rows of the image
+            // x, y of the output row this iteration completes (latency overlaps the arithmetic below)
+            const int oy = y0 + i - (K - 1);
+            float xr = 0.f, yr = 0.f;
+            if (i >= K - 1 && col_in) {
+                xr = __ldg(xb + (long long)oy * W);
+                yr = __ldg(yb + (long long)oy * W);
+            }
+            float h[3];
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                const float *row = &sC[m][slot][0];
+                float v = 0.f;
+#pragma unroll
+                for (int j = 0; j < K; ++j) v = fmaf(gh[j], row[tid + j], v);
+                h[m] = v;
+            }
+            if (!vfold) {
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    const int sl = (ii - j + K) % K;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) acc[m][sl] = (j == 0) ? g[0] * h[m] : fmaf(g[j], h[m], acc[m][sl]);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    const int sl = (ii - j + K) % K;
+                    const int y = y0 + i - j;
+                    float wj = g[j];
+                    if (y >= 1 && y <= P && p >= 0 && p + y <= P) wj += sg[p + y + P];
+                    if (y >= H - 1 - P && y <= H - 2 && p <= H - 1 && p >= 2 * H - 2 - y - P)
+                        wj += sg[p - (2 * H - 2 - y) + P];
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) acc[m][sl] = (j == 0) ? wj * h[m] : fmaf(wj, h[m], acc[m][sl]);
+                }
+            }
+            if (i >= K - 1 && col_in) {
+                const int sl = (ii + 1) % K;
+                float xv = xr, yv = yr;
+                bool pass = true;
+                if (a.clamp_in) {
+                    pass = (xr >= 0.f && xr <= 1.f);
+                    xv = fminf(fmaxf(xv, 0.f), 1.f);
+                    yv = fminf(fmaxf(yv, 0.f), 1.f);
+                }
+                const float gr = gs * (acc[0][sl] + 2.f * xv * acc[1][sl] + yv * acc[2][sl]);
+                const float res = pass ? gr : 0.f;
+                float *o = ob + (long long)oy * W;
+                *o = a.accumulate ? *o + res : res;
+            }
+        }
+    }
+    cp_async_wait<0>();
+}
+
+template <int K>
+static int launch_ssim_bwd_stream(const SsimBwdArgs &a, int grid, int seg_rows, cudaStream_t st) {
+    ssim_bwd_stream_kernel<K><<<grid, SW, 0, st>>>(a, seg_rows);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
 template <int K>
 static int launch_ssim_bwd(const SsimBwdArgs &a, int grid, cudaStream_t st) {
     constexpr int P = K / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
@@ -724,11 +876,32 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
     SsimBwdArgs a{};
     a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map; a.accumulate = accumulate;
     a.x = x; a.y = y; a.win = win1d; a.coef = coef; a.gout = grad_out; a.out_grad = out_grad;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (g_ssim_path == 0 && !grad_out_is_map) {
+        a.tiles_x = div_up(d.w, SW);
+        const long long cols = (long long)d.n * d.c * a.tiles_x;
+        int segs = (int)((148LL * 5 * 3 + cols - 1) / cols);
+        int rows = g_ssim_seg_rows > 0 ? g_ssim_seg_rows : (d.h + segs - 1) / segs;
+        if (g_ssim_seg_rows <= 0 && rows < 48) rows = 48;
+        if (rows > d.h) rows = d.h;
+        a.tiles_y = div_up(d.h, rows);
+        const long long grid = cols * a.tiles_y;
+        LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
+        switch (d.ksize) {
+            case 1: return launch_ssim_bwd_stream<1>(a, (int)grid, rows, st);
+            case 3: return launch_ssim_bwd_stream<3>(a, (int)grid, rows, st);
+            case 5: return launch_ssim_bwd_stream<5>(a, (int)grid, rows, st);
+            case 7: return launch_ssim_bwd_stream<7>(a, (int)grid, rows, st);
+            case 9: return launch_ssim_bwd_stream<9>(a, (int)grid, rows, st);
+            case 11: return launch_ssim_bwd_stream<11>(a, (int)grid, rows, st);
+            case 13: return launch_ssim_bwd_stream<13>(a, (int)grid, rows, st);
+            default: return launch_ssim_bwd_stream<15>(a, (int)grid, rows, st);
+        }
+    }
     a.tiles_x = div_up(d.w, STW);
     a.tiles_y = div_up(d.h, STH);
     const long long grid = (long long)d.n * d.c * a.tiles_x * a.tiles_y;
     LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
-    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     switch (d.ksize) {
         case 1: return launch_ssim_bwd<1>(a, (int)grid, st);
         case 3: return launch_ssim_bwd<3>(a, (int)grid, st);
