@@ -146,12 +146,15 @@ def tm_gaussian_1d(k, sigma, dtype):
     return (g / g.sum()).unsqueeze(0)
 
 
-def ssim_torchmetrics(preds, target, *, data_range=1.0, sigma=1.5, kernel_size=11, k1=0.01, k2=0.03):
+def ssim_torchmetrics(preds, target, *, data_range=1.0, sigma=1.5, kernel_size=11, k1=0.01, k2=0.03,
+                      compute_dtype=torch.float32):
     """Per-image scores, as StructuralSimilarityIndexMeasure(gaussian_kernel=True, reduction='none').
-    The Gaussian support is derived from sigma (2*int(3.5*sigma+0.5)+1), NOT from kernel_size."""
+    The Gaussian support is derived from sigma (2*int(3.5*sigma+0.5)+1), NOT from kernel_size.
+    `compute_dtype=torch.float64` evaluates the same formula in double (separates "we differ"
+    from "fp32 eager is itself noisy" — E[x^2] - mu^2 cancels badly on smooth 8-bit images)."""
     if preds.ndim == 3:
         preds, target = preds[None], target[None]
-    preds, target = preds.to(torch.float32), target.to(torch.float32)
+    preds, target = preds.to(compute_dtype), target.to(compute_dtype)
     c = preds.shape[1]
     gk = int(3.5 * sigma + 0.5) * 2 + 1
     pad = (gk - 1) // 2
