@@ -31,7 +31,7 @@ def rgb_to_lab(img: torch.Tensor) -> torch.Tensor:
     y = 0.212671 * r + 0.715160 * g + 0.072169 * b
     z = 0.019334 * r + 0.119193 * g + 0.950227 * b
     xyz = torch.stack([x, y, z], dim=-3)
-    white = torch.tensor([0.95047, 1.0, 1.08883], dtype=xyz.dtype)[..., :, None, None]
+    white = torch.tensor([0.95047, 1.0, 1.08883], dtype=xyz.dtype, device=xyz.device)[..., :, None, None]
     t = torch.div(xyz, white)
     thr = 0.008856
     f = torch.where(t > thr, torch.pow(t.clamp(min=thr), 1 / 3.0), 7.787 * t + 4.0 / 29.0)
@@ -136,7 +136,7 @@ def de00_summary(pred, target, percentiles=(50.0, 95.0), **kw):
     m = de00_map(pred, target, **kw)
     flat = m.reshape(m.shape[0], -1)
     out = {"mean": float(flat.mean(dim=1).mean())}
-    qs = torch.tensor([float(p) / 100.0 for p in percentiles], dtype=flat.dtype)
+    qs = torch.tensor([float(p) / 100.0 for p in percentiles], dtype=flat.dtype, device=flat.device)
     qv = torch.quantile(flat.reshape(-1), qs)
     for i, p in enumerate(percentiles):
         out[f"p{int(p)}"] = float(qv[i])
@@ -149,8 +149,8 @@ SOBEL_Y = torch.tensor([[-1.0, -2.0, -1.0], [0.0, 0.0, 0.0], [1.0, 2.0, 1.0]]).v
 
 def sobel_magnitude(l_plane):
     """color_error.py:296-301 on [N,1,H,W]."""
-    gx = F.conv2d(l_plane, SOBEL_X.to(l_plane.dtype), padding=1)
-    gy = F.conv2d(l_plane, SOBEL_Y.to(l_plane.dtype), padding=1)
+    gx = F.conv2d(l_plane, SOBEL_X.to(l_plane), padding=1)
+    gy = F.conv2d(l_plane, SOBEL_Y.to(l_plane), padding=1)
     return torch.sqrt(gx * gx + gy * gy + 1e-12)
 
 

@@ -97,7 +97,7 @@ def prepare_dense_psf(psf, c_in, c_out, dtype, normalize, nonneg, eps):
 
 def expand_rho(rho, ref):
     """phys_consistency.py:160-190,230-232."""
-    r = rho.to(dtype=ref.dtype) if torch.is_tensor(rho) else torch.tensor(float(rho), dtype=ref.dtype)
+    r = rho.to(dtype=ref.dtype) if torch.is_tensor(rho) else torch.tensor(float(rho), dtype=ref.dtype, device=ref.device)
     n, c = ref.shape[:2]
     if r.ndim == 0:
         r = r.view(1, 1, 1, 1).expand(n, 1, 1, 1)
@@ -174,7 +174,7 @@ def phys_loss_raw(bhat, a, rho, kernel, clamp_align=True):
 def align_exposure(a, rho):
     """losses.py:195-203."""
     if not torch.is_tensor(rho):
-        rho = torch.tensor(rho, dtype=a.dtype)
+        rho = torch.tensor(rho, dtype=a.dtype, device=a.device)
     if rho.dim() == 0:
         rho = rho.view(1)
     if rho.dim() == 1:

@@ -100,7 +100,7 @@ def ssim_linear(pred, target, *, data_range=1.0, kernel_size=11, sigma=1.5, k1=0
     if pred.ndim == 3:
         pred, target = pred[None], target[None]
     n, c, h, w = pred.shape
-    win = window2d_linear(kernel_size, sigma, gaussian, pred.dtype).repeat(c, 1, 1, 1)
+    win = window2d_linear(kernel_size, sigma, gaussian, pred.dtype).repeat(c, 1, 1, 1).to(pred.device)
     p = kernel_size // 2
 
     def padf(t):
@@ -161,7 +161,7 @@ def ssim_torchmetrics(preds, target, *, data_range=1.0, sigma=1.5, kernel_size=1
     c1 = (k1 * data_range) ** 2
     c2 = (k2 * data_range) ** 2
     g = tm_gaussian_1d(gk, sigma, preds.dtype)
-    win = torch.matmul(g.t(), g).expand(c, 1, gk, gk)
+    win = torch.matmul(g.t(), g).expand(c, 1, gk, gk).to(preds.device)
     xp = F.pad(preds, (pad, pad, pad, pad), mode="reflect")
     yp = F.pad(target, (pad, pad, pad, pad), mode="reflect")
     stack = torch.cat((xp, yp, xp * xp, yp * yp, xp * yp))
@@ -201,7 +201,7 @@ def kornia_gaussian_1d(k, sigma, dtype=torch.float32):
 def kornia_ssim_map(x, y, window_size=11, max_val=1.0, eps=1e-12):
     c = x.shape[1]
     g = kornia_gaussian_1d(window_size, 1.5, x.dtype)
-    win = torch.matmul(g.unsqueeze(-1), g.unsqueeze(-1).t()).expand(c, 1, window_size, window_size)
+    win = torch.matmul(g.unsqueeze(-1), g.unsqueeze(-1).t()).expand(c, 1, window_size, window_size).to(x.device)
     p = window_size // 2
 
     def filt(t):
