@@ -258,6 +258,7 @@ size_t llie_select_workspace_bytes(int32_t images, int32_t reserved);
  *   out_q      [segments, nq] floats (segments = joint ? 1 : images); NaN for an empty population
  *   out_count  [images] int64: participating elements per image (the edge-mask pixel count)
  *   out_sum    NULL or [segments] doubles: sum of the participating values */
+/* nq == 0 (q, out_q may be NULL): one pass that only yields the gated counts and sum (masked mean). */
 int llie_select_quantiles(const llie_select_desc *desc, const float *values, const float *gate,
                           const float *gate_thr, const double *q, float *out_q, int64_t *out_count,
                           double *out_sum, void *select_ws, void *stream);

@@ -416,25 +416,25 @@ def select_quantiles(values: Tensor, qs, *, joint: bool, gate: Optional[Tensor] 
     """torch.quantile(values[i].flatten(), q, interpolation='linear') per image (joint=False) or over all
     images together (joint=True), optionally only over elements with gate >= gate_thr[image].
     values / gate: contiguous fp32 CUDA [images, ...].  Returns (quantiles f32 [segments, nq],
-    counts int64 [images], sums f64 [segments] or None)."""
+    counts int64 [images], sums f64 [segments] or None).  `qs=[]`: one pass, counts and sum only."""
     import ctypes as C
     dev = values.device
     images = values.shape[0]
     per = values.numel() // images
     nq = len(qs)
     segs = 1 if joint else images
-    out_q = torch.empty((segs, nq), dtype=torch.float32, device=dev)
+    out_q = torch.empty((segs, nq), dtype=torch.float32, device=dev) if nq else None
     cnt = torch.empty(images, dtype=torch.int64, device=dev)
     sums = torch.empty(segs, dtype=torch.float64, device=dev) if want_sum else None
     d = nat.SelectDesc(images, per, nq, int(joint))
-    qarr = (C.c_double * nq)(*[float(q) for q in qs])
+    qarr = (C.c_double * max(nq, 1))(*[float(q) for q in qs])
     ws = _select_ws(dev, images)
     with torch.cuda.device(dev):
         rc = nat.lib().llie_select_quantiles(d, nat.ptr(values), nat.ptr(gate), nat.ptr(gate_thr), qarr,
                                              nat.ptr(out_q), nat.ptr(cnt), nat.ptr(sums), nat.ptr(ws),
                                              nat.stream_ptr(dev))
     nat.check(rc, "llie_select_quantiles")
-    nat.count_launch(6)
+    nat.count_launch(6 if nq else 2)
     return out_q, cnt, sums
 
 

@@ -422,35 +422,62 @@ __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs 
 
 // Sobel magnitude of a [planes, H, W] stack, zero padding (color_error.py:23-30, 296-301).  Products and
 // sums are kept un-contracted (no FMA) so that the result is the IEEE value torch computes.
-__global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, int H, int W, long long planes) {
-    const long long plane = (long long)H * W, total = plane * planes;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        const long long pl = i / plane;
-        const int rem = (int)(i - pl * plane);
-        const int y = rem / W, x = rem - y * W;
-        const float *p = L + pl * plane;
-        auto at = [&](int yy, int xx) -> float {
-            return (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(p + (long long)yy * W + xx) : 0.f;
-        };
-        const float v00 = at(y - 1, x - 1), v01 = at(y - 1, x), v02 = at(y - 1, x + 1);
-        const float v10 = at(y, x - 1), v12 = at(y, x + 1);
-        const float v20 = at(y + 1, x - 1), v21 = at(y + 1, x), v22 = at(y + 1, x + 1);
-        // gx = sum_k Kx[k] * v[k] in row-major tap order, gy likewise (zero taps contribute exactly 0)
-        float gx = __fmul_rn(-1.f, v00);
-        gx = __fadd_rn(gx, v02);
-        gx = __fadd_rn(gx, __fmul_rn(-2.f, v10));
-        gx = __fadd_rn(gx, __fmul_rn(2.f, v12));
-        gx = __fadd_rn(gx, __fmul_rn(-1.f, v20));
-        gx = __fadd_rn(gx, v22);
-        float gy = __fmul_rn(-1.f, v00);
-        gy = __fadd_rn(gy, __fmul_rn(-2.f, v01));
-        gy = __fadd_rn(gy, __fmul_rn(-1.f, v02));
-        gy = __fadd_rn(gy, v20);
-        gy = __fadd_rn(gy, __fmul_rn(2.f, v21));
-        gy = __fadd_rn(gy, v22);
-        const float s = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), 1e-12f);
-        g[i] = __fsqrt_rn(s);
+// One thread per column of a 32-row band: the three rows of the window roll through registers and the left /
+// right neighbours come from warp shuffles (the two edge lanes of a warp load theirs), so each value is read
+// from memory ~1.1 times instead of 9 and the kernel is bound by HBM, not by address arithmetic.
+constexpr int kSobelRows = 32;
+
+__device__ __forceinline__ float sobel_mag(float v00, float v01, float v02, float v10, float v12, float v20, float v21,
+                                           float v22) {
+    // gx = sum_k Kx[k] * v[k] in row-major tap order, gy likewise (zero taps contribute exactly 0)
+    float gx = __fmul_rn(-1.f, v00);
+    gx = __fadd_rn(gx, v02);
+    gx = __fadd_rn(gx, __fmul_rn(-2.f, v10));
+    gx = __fadd_rn(gx, __fmul_rn(2.f, v12));
+    gx = __fadd_rn(gx, __fmul_rn(-1.f, v20));
+    gx = __fadd_rn(gx, v22);
+    float gy = __fmul_rn(-1.f, v00);
+    gy = __fadd_rn(gy, __fmul_rn(-2.f, v01));
+    gy = __fadd_rn(gy, __fmul_rn(-1.f, v02));
+    gy = __fadd_rn(gy, v20);
+    gy = __fadd_rn(gy, __fmul_rn(2.f, v21));
+    gy = __fadd_rn(gy, v22);
+    const float s = __fadd_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy)), 1e-12f);
+    return __fsqrt_rn(s);
+}
+
+// grid (ceil(W / 256), ceil(H / kSobelRows), planes), 256 threads
+__global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, int H, int W) {
+    const int x = blockIdx.x * 256 + threadIdx.x;
+    const int y0 = blockIdx.y * kSobelRows, y1 = min(y0 + kSobelRows, H);
+    const long long plane = (long long)H * W;
+    const float *p = L + (long long)blockIdx.z * plane;
+    float *o = g + (long long)blockIdx.z * plane;
+    const int lane = threadIdx.x & 31;
+    const bool in = x < W;
+    auto row3 = [&](int yy, float &l, float &c, float &r) {
+        // (l, c, r) = L[yy][x-1 .. x+1] with zeros outside the image
+        c = 0.f;
+        float el = 0.f, er = 0.f;
+        if (yy >= 0 && yy < H) {
+            const float *rp = p + (long long)yy * W;
+            if (in) c = __ldg(rp + x);
+            if (lane == 0 && x >= 1 && x - 1 < W) el = __ldg(rp + x - 1);
+            if (lane == 31 && x + 1 < W) er = __ldg(rp + x + 1);
+        }
+        l = __shfl_up_sync(0xffffffffu, c, 1);
+        r = __shfl_down_sync(0xffffffffu, c, 1);
+        if (lane == 0) l = el;
+        if (lane == 31) r = er;
+    };
+    float a0, a1, a2, b0, b1, b2, c0, c1, c2;
+    row3(y0 - 1, a0, a1, a2);
+    row3(y0, b0, b1, b2);
+    for (int y = y0; y < y1; ++y) {
+        row3(y + 1, c0, c1, c2);
+        if (in) o[(long long)y * W + x] = sobel_mag(a0, a1, a2, b0, b2, c0, c1, c2);
+        a0 = b0; a1 = b1; a2 = b2;
+        b0 = c0; b1 = c1; b2 = c2;
     }
 }
 
@@ -531,10 +558,9 @@ extern "C" int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t
 extern "C" int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w,
                                     void *stream) {
     LLIE_REQUIRE(l_planes && out_g && planes > 0 && h > 0 && w > 0, "sobel: bad arguments");
-    const long long total = (long long)planes * h * w;
-    long long blocks = (total + 255) / 256;
-    if (blocks > kNumSM * 16) blocks = kNumSM * 16;
-    sobel_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w, planes);
+    LLIE_REQUIRE(planes <= 65535 && (h + kSobelRows - 1) / kSobelRows <= 65535, "sobel: grid too large");
+    dim3 grid((w + 255) / 256, (h + kSobelRows - 1) / kSobelRows, (unsigned)planes);
+    sobel_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

@@ -84,7 +84,7 @@ __global__ void __launch_bounds__(256) select_hist_kernel(const SelArgs a) {
         const unsigned digit = (key >> shift) & (bins - 1u);
         const unsigned hi = key & himask;
         // ranks that share a prefix share a histogram row (the common case: lo and hi are adjacent ranks)
-        if (hi == pre[0]) atomicAdd(&sh[digit], 1u);
+        if (nr >= 1 && hi == pre[0]) atomicAdd(&sh[digit], 1u);
         if (nr >= 2 && !same01 && hi == pre[1]) atomicAdd(&sh[bins + digit], 1u);
         if (nr >= 4 && hi == pre[2]) atomicAdd(&sh[2 * bins + digit], 1u);
         if (nr >= 4 && !same23 && hi == pre[3]) atomicAdd(&sh[3 * bins + digit], 1u);
@@ -190,7 +190,7 @@ __global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int i
     __syncthreads();
     // clear the histogram rows for the next pass / next call
     for (unsigned i = threadIdx.x; i < (unsigned)kMaxR * kBins; i += blockDim.x) gh[i] = 0ull;
-    if (a.pass == 2 && threadIdx.x == 0) {
+    if ((a.pass == 2 || d.nq == 0) && threadIdx.x == 0) {
         for (int qi = 0; qi < d.nq; ++qi) {
             float res = __int_as_float(0x7fc00000);  // empty population -> NaN (color_error.py:340-341)
             if (st.count) {
@@ -221,10 +221,11 @@ extern "C" size_t llie_select_workspace_bytes(int32_t images, int32_t blocks_hin
 extern "C" int llie_select_quantiles(const llie_select_desc *desc, const float *values, const float *gate,
                                      const float *gate_thr, const double *q, float *out_q, int64_t *out_count,
                                      double *out_sum, void *select_ws, void *stream) {
-    LLIE_REQUIRE(desc && values && q && out_q && out_count && select_ws, "select: null pointer");
+    LLIE_REQUIRE(desc && values && out_count && select_ws, "select: null pointer");
+    LLIE_REQUIRE(desc->nq == 0 || (q && out_q), "select: q / out_q missing");
     const llie_select_desc &d = *desc;
     LLIE_REQUIRE(d.images > 0 && d.images <= 65535 && d.per_image > 0, "select: bad population");
-    LLIE_REQUIRE(d.nq >= 1 && d.nq <= kMaxQ, "select: 1..%d quantiles per call", kMaxQ);
+    LLIE_REQUIRE(d.nq >= 0 && d.nq <= kMaxQ, "select: 0..%d quantiles per call", kMaxQ);
     LLIE_REQUIRE((gate == nullptr) == (gate_thr == nullptr), "select: gate and gate_thr go together");
     for (int i = 0; i < d.nq; ++i) LLIE_REQUIRE(q[i] >= 0.0 && q[i] <= 1.0, "select: q must be in [0,1]");
     SelArgs a{};
@@ -247,7 +248,8 @@ extern "C" int llie_select_quantiles(const llie_select_desc *desc, const float *
     a.psum = reinterpret_cast<double *>(((uintptr_t)w + 7) & ~(uintptr_t)7);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const size_t smem = (size_t)2 * d.nq * kBins * sizeof(unsigned);
-    for (int pass = 0; pass < 3; ++pass) {
+    const int passes = d.nq == 0 ? 1 : 3;  // nq == 0: gated count + sum only, one pass
+    for (int pass = 0; pass < passes; ++pass) {
         a.pass = pass;
         select_hist_kernel<<<dim3(bx, d.images), 256, smem, st>>>(a);
         select_scan_kernel<<<segs, 256, 0, st>>>(a, d.images, bx);

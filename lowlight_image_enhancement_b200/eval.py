@@ -88,7 +88,7 @@ def _edge_mean(pred, target, flags, *, q: float = 0.85, shared: Optional[_Colour
     per = cp.hw
     grad = Fn.sobel_magnitude(cp.lpl)
     thr, _, _ = Fn.select_quantiles(grad.view(cp.n, per), [q], joint=False)
-    _, counts, msum = Fn.select_quantiles(cp.dmap.view(cp.n, per), [0.95], joint=True, gate=grad.view(cp.n, per),
+    _, counts, msum = Fn.select_quantiles(cp.dmap.view(cp.n, per), [], joint=True, gate=grad.view(cp.n, per),
                                           gate_thr=thr.view(cp.n).contiguous(), want_sum=True)
     return msum.view(-1)[0] / counts.sum().double()
 

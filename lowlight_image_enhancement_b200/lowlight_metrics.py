@@ -11,7 +11,7 @@ from typing import Literal
 
 import torch
 
-from .metrics.color_error import deltaE2000_summary, edge_deltaE2000
+from .metrics.color_error import deltaE2000_summary, edge_deltaE2000_stats
 from .metrics.psnr import calculate_psnr
 from .metrics.ssim import calculate_ssim
 
@@ -39,4 +39,5 @@ def deltae2000_p95(pred: torch.Tensor, target: torch.Tensor, *,
 
 def edge_deltae2000_mean(pred: torch.Tensor, target: torch.Tensor, *,
                          whitepoint: Literal["D65-2", "D50-2"] = "D65-2", q: float = 0.85) -> float:
-    return edge_deltaE2000(pred, target, whitepoint=whitepoint, q=q, clamp01=True)["mean"]
+    # the reference also computes (and discards) the masked p95 through a second full sort
+    return edge_deltaE2000_stats(pred, target, whitepoint=whitepoint, q=q, clamp01=True, want_p95=False)["mean"]

@@ -118,7 +118,7 @@ def deltaE2000_summary(pred_srgb: Tensor, target_srgb: Tensor, *, percentiles: T
     return summary
 
 
-def _edge_core(pred_srgb, target_srgb, q, kwargs):
+def _edge_core(pred_srgb, target_srgb, q, kwargs, want_p95=True):
     kw = dict(kL=1.0, kC=1.0, kH=1.0, whitepoint="D65-2", eps=1e-12, clamp01=False)
     unknown = set(kwargs) - set(kw)
     if unknown:
@@ -130,27 +130,28 @@ def _edge_core(pred_srgb, target_srgb, q, kwargs):
     grad = Fn.sobel_magnitude(lpl)                                                   # [N,H,W]
     thr, _, _ = Fn.select_quantiles(grad.view(n, per), [q], joint=False)             # per-image quantile
     thr = thr.view(n).contiguous()
-    p95, counts, msum = Fn.select_quantiles(dmap.view(n, per), [0.95], joint=True, gate=grad.view(n, per),
-                                            gate_thr=thr, want_sum=True)
-    return flags, thr, p95.view(-1), counts, msum
+    p95, counts, msum = Fn.select_quantiles(dmap.view(n, per), [0.95] if want_p95 else [], joint=True,
+                                            gate=grad.view(n, per), gate_thr=thr, want_sum=True)
+    return flags, thr, (p95.view(-1) if want_p95 else None), counts, msum
 
 
 @torch.no_grad()
 def edge_deltaE2000_stats(pred_srgb: Tensor, target_srgb: Tensor, *, method: str = "sobel", q: float = 0.85,
-                          **kwargs) -> Dict[str, object]:
-    """edge_deltaE2000 plus the integers behind it: {'mean','p95','count','count_per_image','thresholds'}."""
+                          want_p95: bool = True, **kwargs) -> Dict[str, object]:
+    """edge_deltaE2000 plus the integers behind it: {'mean','p95','count','count_per_image','thresholds'}.
+    `want_p95=False` skips the masked 95th percentile (two histogram passes) and reports it as NaN."""
     if method != "sobel":
         raise ValueError(f"Unsupported edge detection method '{method}'. Currently only 'sobel' is available.")
     if not 0.0 < q < 1.0:
         raise ValueError(f"q must lie within (0,1); received {q}.")
-    flags, thr, p95, counts, msum = _edge_core(pred_srgb, target_srgb, q, kwargs)
+    flags, thr, p95, counts, msum = _edge_core(pred_srgb, target_srgb, q, kwargs, want_p95)
     _raise_nonfinite(flags)
     cnt = counts.cpu()
     total = int(cnt.sum())
     if total == 0:
         return {"mean": float("nan"), "p95": float("nan"), "count": 0, "count_per_image": cnt, "thresholds": thr.cpu()}
-    return {"mean": float(msum.item()) / total, "p95": float(p95.item()), "count": total, "count_per_image": cnt,
-            "thresholds": thr.cpu()}
+    return {"mean": float(msum.item()) / total, "p95": float(p95.item()) if want_p95 else float("nan"),
+            "count": total, "count_per_image": cnt, "thresholds": thr.cpu()}
 
 
 @torch.no_grad()
