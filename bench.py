@@ -28,10 +28,10 @@ RHO = [100.0, 250.0, 300.0, 100.0, 250.0, 300.0, 100.0, 250.0]
 SHAPE = (8, 3, 512, 512)
 # dram bytes per launch from the committed `ncu --set full` capture of this workload (profiles/); None = not captured
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, `ncu --set full` of this command
-# (profiles/r1_bench_phys_c2_ncu_full.txt).  Reads equal the algorithmic 50.33 MB (no halo re-reads reach
+# (profiles/r1_bench_phys_c2_ncu_full.txt, r1_bench_phys_c2_fused_ncu_full.txt).  Reads equal the algorithmic 50.33 MB (no halo re-reads reach
 # DRAM); the 25.2 MB gradient written by the backward kernel is still held by the 126 MB L2 when the kernel
 # ends, so only ~1.3 MB of its write-back is attributed to the launch.
-TRAFFIC = {"phys_fwd_ring": 50.40e6, "phys_bwd_ring": 51.78e6}
+TRAFFIC = {"phys_fwd_ring": 50.40e6, "phys_bwd_ring": 51.78e6, "phys_fused_ring": 51.96e6}
 POOL = 8  # rotating buffer sets: 8 x (pred+obs+grad = 75.5 MB) = 604 MB >> 126 MB L2
 
 
@@ -216,24 +216,36 @@ def run_ours(args, rank, world, dev):
         p, o, r = sets[i % POOL]
         return Fn.phys_backward(p, o, psf, r, 0.0, st, cfg, gout, gscale, out=grads[i % POOL])
 
-    def step(i):
+    def fused(i):
+        p, o, r = sets[i % POOL]
+        return Fn.phys_value_and_grad(p, o, psf, r, 0.0, st, cfg, gout, gscale, out=grads[i % POOL])
+
+    def step2(i):
         fwd(i)
         bwd(i)
 
+    # a step = loss value (per-sample means, batch mean, flags) AND d loss / d pred.  One fused launch
+    # (llie_phys_value_and_grad) yields both from a single pass over pred / obs; --two-pass times the separate
+    # forward + backward kernels instead (same outputs, 20 instead of 12 bytes per element).
+    step = step2 if args.two_pass else fused
     K, W = args.steps, max(3, args.warmup)
     g_step, g_f, g_b = GraphLoop(step, K, dev), GraphLoop(fwd, K, dev), GraphLoop(bwd, K, dev)
+    g_2 = GraphLoop(step2, K, dev)
+    g_u = GraphLoop(fused, K, dev)
     for _ in range(max(1, W * g_step.replays // K)):
         g_step.run()
     # per-kernel timings (live, CUDA events on the launching stream): K launches of each kernel alone
     t_f = min(g_f.run() for _ in range(3)) / K
     t_b = min(g_b.run() for _ in range(3)) / K
+    t_u = min(g_u.run() for _ in range(3)) / K
+    t_2 = min(g_2.run() for _ in range(3)) / K
     if world > 1:
         dist.barrier()
     l0 = nat.launches
     with ClockSampler(dev.index) as clk:
         ms = g_step.run()
         time.sleep(0.25)  # let the sampler see the clocks right after the (sub-ms .. ms) timed region
-    launches = 2 * K  # one forward + one backward kernel per step, replayed from the captured graph
+    launches = (2 if args.two_pass else 1) * K  # kernels per step, replayed from the captured graph
     del l0
     if world > 1:
         t = torch.tensor([ms], device=dev)
@@ -274,23 +286,32 @@ def run_ours(args, rank, world, dev):
     bytes_f, bytes_b = 8 * elems, 12 * elems
     ach_b = bytes_b / (t_b * 1e-3) / 1e9
     ach_f = bytes_f / (t_f * 1e-3) / 1e9
+    ach_u = bytes_b / (t_u * 1e-3) / 1e9   # the fused pass moves the backward's 12 B/element
+    roof = ({"kernel": "phys_bwd_ring", "achieved": ach_b, "us": t_b} if args.two_pass else
+            {"kernel": "phys_bwd_ring<FUSED> (value + gradient)", "achieved": ach_u, "us": t_u})
     line = {
         "metric": "Mpix/s phys-cons fwd+bwd", "value": round(value, 1), "unit": "Mpix/s", "n_gpus": world,
         "steps": K, "warmup": W, "ms_per_step": round(ms / K, 5), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "phys_cons_raw rgb B2 depthwise PSF, per-image rho, 8x3x512x512 fp32, fwd+bwd (BASELINE configs[1])",
+                   "step": ("forward kernel + backward kernel" if args.two_pass else
+                            "loss value + gradient from one fused launch (llie_phys_value_and_grad); "
+                            f"two-pass forward + backward = {round(t_2 * 1e3, 2)} us per step"),
                    "l2": f"inputs rotate over {POOL} resident buffer sets (604 MB per GPU) > 126 MB L2",
                    "launch": f"steps captured in CUDA graphs of {K // g_step.replays} steps, replayed {g_step.replays}x",
                    "per_gpu_batch": list(SHAPE)},
-        "roofline": {"bound": "hbm", "kernel": "phys_bwd_ring", "achieved": round(ach_b, 1), "peak": peak,
-                     "unit": "GB/s", "frac": round(ach_b / peak, 4), "traffic": TRAFFIC.get("phys_bwd_ring"),
+        "roofline": {"bound": "hbm", "kernel": roof["kernel"], "achieved": round(roof["achieved"], 1), "peak": peak,
+                     "unit": "GB/s", "frac": round(roof["achieved"] / peak, 4),
+                     "traffic": TRAFFIC.get("phys_bwd_ring" if args.two_pass else "phys_fused_ring"),
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_b,
-                     "us_per_launch": round(t_b * 1e3, 2)},
+                     "us_per_launch": round(roof["us"] * 1e3, 2)},
         "kernels": [
             {"kernel": "phys_fwd_ring", "us": round(t_f * 1e3, 2), "algorithmic_bytes": bytes_f,
              "achieved_gbs": round(ach_f, 1), "frac": round(ach_f / peak, 4), "traffic": TRAFFIC.get("phys_fwd_ring")},
             {"kernel": "phys_bwd_ring", "us": round(t_b * 1e3, 2), "algorithmic_bytes": bytes_b,
-             "achieved_gbs": round(ach_b, 1), "frac": round(ach_b / peak, 4), "traffic": TRAFFIC.get("phys_bwd_ring")}],
+             "achieved_gbs": round(ach_b, 1), "frac": round(ach_b / peak, 4), "traffic": TRAFFIC.get("phys_bwd_ring")},
+            {"kernel": "phys_bwd_ring<FUSED>", "us": round(t_u * 1e3, 2), "algorithmic_bytes": bytes_b,
+             "achieved_gbs": round(ach_u, 1), "frac": round(ach_u / peak, 4), "traffic": TRAFFIC.get("phys_fused_ring")}],
         "e2e": {"value": round(e2e_val, 1), "unit": "Mpix/s", "h2d_bytes_per_step": 2 * 4 * elems,
                 "d2h_bytes_per_step": 4, "steps": Ke, "api": "metrics.phys_consistency.phys_cons_raw(differentiable=True)+backward"},
         "gpu_launches": launches,
@@ -436,6 +457,7 @@ def main():
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs: 1 untimed-quality e2e step only")
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: no cpu_baseline leg")
     ap.add_argument("--skip-extra", action="store_true", help="profiling runs: no eval_c4 / hybrid_c3 sections")
+    ap.add_argument("--two-pass", action="store_true", help="time separate forward + backward kernels per step")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":

@@ -197,6 +197,29 @@ def phys_backward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_scalar
     return grad
 
 
+def phys_value_and_grad(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_scalar, rho_strides, cfg: PhysCfg,
+                        gout: Tensor, gscale: float, out: Optional[Tensor] = None):
+    """Loss vector and gradient from one pass (llie_phys_value_and_grad).  Returns (vec[N+2], flags, grad)."""
+    dev = pred.device
+    n, c_in, h, w = pred.shape
+    c_out = obs.shape[1]
+    buf = torch.empty(n + 3, dtype=torch.float32, device=dev)
+    flags = buf[n + 2:].view(torch.int32)
+    grad = torch.empty_like(pred) if out is None else out
+    d = _desc(cfg, pred, c_out, psf, rho_scalar, rho_strides)
+    needs_scratch = bool(nat.lib().llie_phys_backward_needs_scratch(d, nat.ptr(pred), nat.ptr(obs), nat.ptr(rho_t),
+                                                                    nat.ptr(grad)))
+    scratch = torch.empty((n, c_out, h, w), dtype=torch.float32, device=dev) if needs_scratch else None
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_phys_value_and_grad(d, nat.ptr(pred), nat.ptr(obs), nat.ptr(psf.weights), nat.ptr(rho_t),
+                                                nat.ptr(gout), 1 if gout.numel() > 1 else 0, gscale, nat.ptr(buf),
+                                                None, nat.ptr(flags), nat.ptr(grad), nat.ptr(scratch),
+                                                nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+    nat.check(rc, "llie_phys_value_and_grad")
+    nat.count_launch(3 if needs_scratch else 1)
+    return buf[: n + 2], flags, grad
+
+
 class PhysProjector(torch.autograd.Function):
     """vec[N+2] = (per-sample means, batch mean, batch sum) of the loss map; differentiable in pred."""
 
@@ -600,11 +623,13 @@ class HybridFusedFn(torch.autograd.Function):
             ph = spec.get("phys")
             if ph is not None and not ph["srgb"]:
                 n = xr.shape[0]
-                vec, _, _ = phys_forward(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"], False)
+                if need_raw:  # value and gradient from one pass
+                    vec, _, g_raw = phys_value_and_grad(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"],
+                                                        ph["cfg"], _one(dev), w["phys"] / float(ph["a"].numel()))
+                else:
+                    vec, _, _ = phys_forward(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
+                                             False)
                 vals[3] = vec[n]
-                if need_raw:
-                    g_raw = phys_backward(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
-                                          _one(dev), w["phys"] / float(ph["a"].numel()))
             l1s = torch.empty(1, dtype=torch.float64, device=dev)
             acc = 1 if g_raw is not None else 0
             if need_raw and g_raw is None:
@@ -653,12 +678,14 @@ class HybridFusedFn(torch.autograd.Function):
                     launches += 1
                 vals[2] = (sss.sum() / float(xs.numel())).to(torch.float32)
             if ph is not None and ph["srgb"]:
-                vec, _, _ = phys_forward(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"], False)
-                vals[3] = vec[n]
                 if need_srgb:
-                    gp = phys_backward(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
-                                       _one(dev), w["phys"] / float(ph["a"].numel()))
+                    vec, _, gp = phys_value_and_grad(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"],
+                                                     ph["cfg"], _one(dev), w["phys"] / float(ph["a"].numel()))
                     g_srgb = gp if g_srgb is None else g_srgb.add_(gp)
+                else:
+                    vec, _, _ = phys_forward(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
+                                             False)
+                vals[3] = vec[n]
         nat.count_launch(launches)
         terms = torch.stack(vals)
         present = [0] + ([1] if spec["use_de"] else []) + ([2] if spec["use_ssim"] else []) + ([3] if ph is not None else [])

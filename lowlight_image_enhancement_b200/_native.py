@@ -75,6 +75,8 @@ _SIGNATURES = {
     "llie_phys_forward": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_phys_backward": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, C.c_int64, C.c_float,
                                      _VP, _VP, _VP]),
+    "llie_phys_value_and_grad": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP, _VP, C.c_int64, C.c_float, _VP, _VP,
+                                          _VP, _VP, _VP, _VP, _VP]),
     "llie_phys_backward_needs_scratch": (C.c_int, [C.POINTER(PhysDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_forward": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_adjoint": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),

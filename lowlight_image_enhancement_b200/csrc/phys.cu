@@ -300,3 +300,25 @@ extern "C" int llie_phys_backward(const llie_phys_desc *desc, const float *pred,
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
+
+extern "C" int llie_phys_value_and_grad(const llie_phys_desc *desc, const float *pred, const float *obs,
+                                        const float *psf, const float *rho, const float *gout, int64_t gout_stride,
+                                        float gscale, float *out_mean, double *out_sum, int32_t *out_flags,
+                                        float *grad_pred, float *scratch, void *workspace, void *stream) {
+    if (int rc = validate(desc)) return rc;
+    LLIE_REQUIRE(pred && obs && psf && gout && grad_pred && out_mean && out_flags && workspace,
+                 "phys_value_and_grad: null pointer");
+    PhysArgs a{};
+    a.d = *desc;
+    a.pred = pred; a.obs = obs; a.psf = psf; a.rho = rho;
+    a.gout = gout; a.gout_stride = gout_stride; a.gscale = gscale;
+    a.grad = grad_pred; a.scratch = scratch;
+    a.out_mean = out_mean; a.out_sum = out_sum; a.out_map = nullptr; a.out_flags = out_flags;
+    fill_domain(a);
+    if (g_phys_path == 0 && phys_ring_eligible(a) && aligned16(grad_pred))
+        return launch_phys_fused_ring(a, workspace, reinterpret_cast<cudaStream_t>(stream));
+    // shapes the fused kernel does not take: the two single-purpose passes, same results
+    if (int rc = llie_phys_forward(desc, pred, obs, psf, rho, out_mean, out_sum, nullptr, out_flags, workspace, stream))
+        return rc;
+    return llie_phys_backward(desc, pred, obs, psf, rho, gout, gout_stride, gscale, grad_pred, scratch, stream);
+}

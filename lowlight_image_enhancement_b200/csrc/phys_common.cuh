@@ -84,6 +84,7 @@ __device__ __forceinline__ int preimages(int i, int n, int p, int mode, int out[
 bool phys_ring_eligible(const PhysArgs &a);
 int launch_phys_fwd_ring(PhysArgs &a, void *workspace, cudaStream_t st);
 int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st);
+int launch_phys_fused_ring(PhysArgs &a, void *workspace, cudaStream_t st);
 void phys_ring_set_rows(int r);
 
 // register-rolling path (phys_roll.cu)

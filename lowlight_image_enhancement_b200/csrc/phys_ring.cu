@@ -422,12 +422,19 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
 // row j+1, completes conv / q row j+1 and grad row j.  The first two entries only warm up the conv
 // partial sums (q forced to 0 by the row mask), the next two the grad partial sums.
 // ------------------------------------------------------------------------------------------------
-template <bool ROBUST, bool CLIPY, bool CLIPA>
+template <bool ROBUST, bool CLIPY, bool CLIPA, bool FUSED = false>
 __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const PhysArgs a, const RingGeom g) {
     extern __shared__ __align__(128) unsigned char smraw[];
     float *ring = reinterpret_cast<float *>(smraw);
     const float *zrow = ring + kSlots * kSlotF;
     __shared__ uint64_t full[kSlots], empty[kSlots];
+    // FUSED (value + gradient in one pass): the loss of the residual rows an item OWNS (qr in [ya, yb), centre
+    // four columns of each lane) is reduced exactly like in phys_fwd_ring
+    __shared__ int red_i[FUSED ? 32 : 1];
+    __shared__ double red_d[FUSED ? 32 : 1];
+    __shared__ double red_w[FUSED ? 8 : 1];
+    int iter = 0;
+    float chk_p = 0.f, chk_o = 0.f;
     const llie_phys_desc &d = a.d;
     const int H = d.h, W = d.w, mode = d.pad_mode;
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
@@ -460,10 +467,10 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                 }
             }
         }
-        return;
+        if (!FUSED) return;
     }
 
-    for (int item = blockIdx.x; item < g.items; item += gridDim.x) {
+    for (int item = blockIdx.x; wrp < kCons / 32 && item < g.items; item += gridDim.x) {
         const Item it = decode_item(item, g, d.c_out, H);
         const int xr = it.x0 + tid * 4;
         const bool active = xr < W;
@@ -489,6 +496,10 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
 #pragma unroll
         for (int i = 0; i < 6; ++i)
             qm[i] = (active && (xr - 1 + i >= a.x_lo) && (xr - 1 + i < a.x_lo + a.wo)) ? gs : 0.f;
+        float dm[4];  // FUSED: 1 where centre column x+i is inside the compared domain (independent of gs)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dm[i] = (active && (xr + i >= a.x_lo) && (xr + i < a.x_lo + a.wo)) ? 1.f : 0.f;
+        float lacc = 0.f;
         // edge-fold weights (image-edge lanes): column -1 gets K[.][0] q(., 0), column W gets K[.][2] q(., W-1)
         const float k0 = is_left ? w[0] : w[2], k1 = is_left ? w[3] : w[5], k2 = is_left ? w[6] : w[8];
         const int tgt = is_left ? (mode == LLIE_PAD_REFLECT ? 1 : 0) : (mode == LLIE_PAD_REFLECT ? 2 : 3);
@@ -526,16 +537,23 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                 float cv[6];
                 roll3<6>(r8, w, cA, cB, cv);  // conv row qr over columns x-1 .. x+4
                 float qc[6];
+                float lrow = 0.f;
 #pragma unroll
                 for (int i = 0; i < 6; ++i) {
                     float yv = cv[i], t = av[i] * ra;
                     float m = GENERAL ? qm[i] * rowm : qm[i];
                     if (CLIPY) {
+                        if (FUSED && i >= 1 && i <= 4) chk_p = fmaf(yv, 0.f, chk_p);
                         m = (yv >= 0.f && yv <= 1.f) ? m : 0.f;  // torch.clamp backward passes lo <= y <= hi
                         yv = clamp01(yv);
                     }
-                    if (CLIPA) t = clamp01(t);
+                    if (CLIPA) {
+                        if (FUSED && i >= 1 && i <= 4) chk_o = fmaf(t, 0.f, chk_o);
+                        t = clamp01(t);
+                    }
                     const float r = yv - t;
+                    if (FUSED && i >= 1 && i <= 4)
+                        lrow = fmaf(ROBUST ? sqrtf(fmaf(r, r, eps2)) : fabsf(r), dm[i - 1], lrow);
                     if (ROBUST) {
                         qc[i] = (m != 0.f) ? m * (r / sqrtf(fmaf(r, r, eps2))) : 0.f;
                     } else {
@@ -543,6 +561,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                         qc[i] = (r != 0.f) ? copysignf(m, r) : 0.f;
                     }
                 }
+                if (FUSED)  // rows outside [ya, yb) are recomputed halo rows owned by the neighbouring item
+                    lacc = fmaf(lrow, (rowm != 0.f && qr >= it.ya && qr < it.yb) ? 1.f : 0.f, lacc);
                 // ---- grad (virtual) row j: q row j+1 completes it (flipped kernel, rolling form)
                 float gr[4];
                 roll3<4>(qc, wf, gA, gB, gr);
@@ -602,6 +622,22 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
             if (lane == 0) mbar_arrive(&empty[rs.slot]);
             rs.advance();
         }
+        if (FUSED) {
+            const double ws = warp_sum((double)lacc);
+            double *rw = red_w + (iter & 1) * 4;
+            if (lane == 0) rw[wrp] = ws;
+            asm volatile("bar.sync 1, %0;" ::"n"(kCons) : "memory");
+            if (tid == 0) g.part[item] = (rw[0] + rw[1]) + (rw[2] + rw[3]);
+            ++iter;
+        }
+    }
+    if (FUSED) {
+        int flag = 0;
+        if (!(chk_p == 0.f)) flag |= 1;
+        if (!(chk_o == 0.f)) flag |= 2;
+        const int f = block_or(flag, red_i);
+        if (tid == 0) g.pflag[blockIdx.x] = f;
+        if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i, red_d);
     }
 }
 
@@ -682,6 +718,35 @@ int launch_phys_fwd_ring(PhysArgs &a, void *workspace, cudaStream_t st) {
     g.pflag = reinterpret_cast<int *>(g.samp + a.d.n);
     a.ticket = ws.tickets;
     LLIE_RING_DISPATCH(phys_fwd_ring, a.d, grid, st, a, g);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+#define LLIE_RING_DISPATCH_FUSED(d, GRID, ST, ...)                                                            \
+    do {                                                                                                      \
+        const int key = ((d).robust ? 4 : 0) | ((d).clip_y ? 2 : 0) | ((d).clip_a ? 1 : 0);                   \
+        switch (key) {                                                                                        \
+            case 0: LLIE_RING_ONE((phys_bwd_ring<false, false, false, true>), GRID, ST, __VA_ARGS__); break;  \
+            case 1: LLIE_RING_ONE((phys_bwd_ring<false, false, true, true>), GRID, ST, __VA_ARGS__); break;   \
+            case 2: LLIE_RING_ONE((phys_bwd_ring<false, true, false, true>), GRID, ST, __VA_ARGS__); break;   \
+            case 3: LLIE_RING_ONE((phys_bwd_ring<false, true, true, true>), GRID, ST, __VA_ARGS__); break;    \
+            case 4: LLIE_RING_ONE((phys_bwd_ring<true, false, false, true>), GRID, ST, __VA_ARGS__); break;   \
+            case 5: LLIE_RING_ONE((phys_bwd_ring<true, false, true, true>), GRID, ST, __VA_ARGS__); break;    \
+            case 6: LLIE_RING_ONE((phys_bwd_ring<true, true, false, true>), GRID, ST, __VA_ARGS__); break;    \
+            default: LLIE_RING_ONE((phys_bwd_ring<true, true, true, true>), GRID, ST, __VA_ARGS__); break;    \
+        }                                                                                                     \
+    } while (0)
+
+// loss value (per-sample means / batch mean / sum, flags) AND gradient from one pass over pred / obs
+int launch_phys_fused_ring(PhysArgs &a, void *workspace, cudaStream_t st) {
+    int grid;
+    RingGeom g = make_geom(a.d, grid);
+    Workspace ws(workspace);
+    g.part = reinterpret_cast<double *>(ws.scratch);
+    g.samp = g.part + (size_t)g.items;
+    g.pflag = reinterpret_cast<int *>(g.samp + a.d.n);
+    a.ticket = ws.tickets;
+    LLIE_RING_DISPATCH_FUSED(a.d, grid, st, a, g);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

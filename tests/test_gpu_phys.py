@@ -250,3 +250,29 @@ def test_full_size_properties(dev):
     # deterministic: bitwise identical on repeat
     a2 = phys_cons_raw(pred / 300, zero, k, rho, reduction="none", crop="same", padding="zeros")
     assert torch.equal(a, a2)
+
+
+@pytest.mark.parametrize("padding", ["reflect", "replicate", "zeros"])
+@pytest.mark.parametrize("crop", ["valid", "same"])
+@pytest.mark.parametrize("robust,clip", [(False, (False, False)), (True, (True, False)), (False, (False, True))])
+@pytest.mark.parametrize("shape", [(2, 3, 64, 128), (1, 3, 70, 252), (3, 3, 33, 8), (8, 3, 512, 512), (2, 3, 37, 50)])
+def test_phys_value_and_grad_equals_two_passes(dev, padding, crop, robust, clip, shape):
+    """llie_phys_value_and_grad (one fused pass) returns exactly what llie_phys_forward + llie_phys_backward do:
+    the loss vector to 1e-6 relative (different but fixed reduction grouping), the gradient bit for bit."""
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    from lowlight_image_enhancement_b200 import _native as nat
+    g = torch.Generator().manual_seed(sum(shape))
+    n = shape[0]
+    pred = torch.rand(shape, generator=g).to(dev)
+    obs = (pred * 0.9 + 0.05 * torch.randn(shape, generator=g).to(dev)).clamp(0, 1.1).contiguous()
+    k = depthwise_from_spec("B2").to(dev)
+    psf = Fn.PreparedPSF(k.contiguous(), Fn.PSF_DEPTHWISE, 3, 3, False)
+    rho = torch.tensor([0.9, 1.1, 1.3, 1.0, 0.8, 1.2, 0.7, 1.05][:n], device=dev)
+    cfg = Fn.PhysCfg(nat.PAD[padding], crop == "valid", robust, 1e-3, 0 if clip[0] else 1, clip[0], clip[1])
+    gout = torch.rand(n, generator=g).to(dev)
+    vec, flags, _ = Fn.phys_forward(pred, obs, psf, rho, 0.0, (1, 0, 0, 0), cfg, False)
+    grad = Fn.phys_backward(pred, obs, psf, rho, 0.0, (1, 0, 0, 0), cfg, gout, 0.37)
+    vec2, flags2, grad2 = Fn.phys_value_and_grad(pred, obs, psf, rho, 0.0, (1, 0, 0, 0), cfg, gout, 0.37)
+    assert torch.equal(grad, grad2)
+    assert torch.allclose(vec, vec2, rtol=1e-6, atol=0)
+    assert int(flags) == int(flags2)
