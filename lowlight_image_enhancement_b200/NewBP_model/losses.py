@@ -214,6 +214,30 @@ class _L1Mean(nn.Module):
         return out if home == dev else out.to(home)
 
 
+class HybridLoss(nn.Module):
+    """Legacy L1 + perceptual loss (losses.py:72-89): `forward(generated, target) -> (total, l1, perceptual)`.
+    The L1 term runs on the one-pass value + gradient kernel; the VGG19 perceptual network is out of scope
+     and is injected as `perceptual_module` (None -> the term is 0)."""
+
+    def __init__(self, lambda_l1: float = 1.0, lambda_perceptual: float = 0.1, device: str = "cuda", *,
+                 perceptual_module: Optional[nn.Module] = None):
+        super().__init__()
+        self.device = _resolve_device(device)
+        self.lambda_l1 = lambda_l1
+        self.lambda_perceptual = lambda_perceptual
+        self.l1_loss = _L1Mean()
+        self.perceptual_loss = perceptual_module
+
+    def forward(self, generated_img: Tensor, target_img: Tensor):
+        l1_val = self.l1_loss(generated_img, target_img)
+        if self.perceptual_loss is not None:
+            perceptual_val = self.perceptual_loss(generated_img, target_img)
+        else:
+            perceptual_val = torch.zeros((), dtype=l1_val.dtype, device=l1_val.device)
+        total = self.lambda_l1 * l1_val + self.lambda_perceptual * perceptual_val
+        return total, l1_val, perceptual_val
+
+
 class HybridLossPlus(nn.Module):
     """Pluggable hybrid loss, same constructor / kwargs-only forward / `(total, logs)` contract as
     losses.py:223-372.  L1, DeltaE00, DSSIM and the physics term run on the sm_100a kernels; the VGG

@@ -215,3 +215,25 @@ def test_hybrid_loss_plus_behaviour(dev):
     bad[0, 0, 0, 0] = float("nan")
     with pytest.raises(RuntimeError, match="non-finite values in term 'L1_raw'"):
         HybridLossPlus(device="cuda", physics_kernel=kern)(Bhat_raw=bad, Bhat_srgb01=bad, **args)
+
+
+def test_legacy_hybrid_loss(dev):
+    """losses.py:72-89: (total, l1, perceptual) with an injected perceptual module; L1 gradient = sign / numel."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import HybridLoss
+    g = torch.Generator().manual_seed(2)
+    a, b = torch.rand(2, 3, 33, 47, generator=g), torch.rand(2, 3, 33, 47, generator=g)
+
+    class Perc(torch.nn.Module):
+        def forward(self, x, y):
+            return (x - y).pow(2).mean()
+
+    x = a.to(dev).requires_grad_(True)
+    tot, l1, pv = HybridLoss(1.0, 0.1, "cuda", perceptual_module=Perc())(x, b.to(dev))
+    tot.backward()
+    xr = a.clone().requires_grad_(True)
+    ref = torch.nn.functional.l1_loss(xr, b) + 0.1 * (xr - b).pow(2).mean()
+    ref.backward()
+    assert abs(float(tot) - float(ref)) < 1e-6 and abs(float(l1) - float(torch.nn.functional.l1_loss(a, b))) < 1e-7
+    assert _rel(x.grad, xr.grad) < 1e-6
+    tot2, _, p2 = HybridLoss(device="cuda")(x.detach(), b.to(dev))
+    assert float(p2) == 0.0 and abs(float(tot2) - float(l1)) < 1e-7
