@@ -72,22 +72,56 @@ __global__ void __launch_bounds__(256) select_hist_kernel(const SelArgs a) {
     const float *gt = a.gate ? a.gate + (long long)img * d.per_image : nullptr;
     unsigned long long cnt = 0;
     double sum = 0.0;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < d.per_image;
-         i += (long long)gridDim.x * blockDim.x) {
-        if (gt && !(__ldg(gt + i) >= thr)) continue;
-        const float val = __ldg(v + i);
-        const unsigned key = fkey(val);
-        if (a.pass == 0) {
-            ++cnt;
-            sum += (double)val;
+    // Fast path (the common case): at most one histogram row (one quantile whose two ranks still share their
+    // prefix, or the count/sum-only call) and 16-byte aligned rows -> 128-bit streaming loads, ~10 instructions
+    // per element instead of ~65.
+    const bool one_row = nr == 0 || nr == 1 || (nr == 2 && same01);
+    const bool vec_ok = (d.per_image & 3) == 0 && (reinterpret_cast<uintptr_t>(v) & 15u) == 0 &&
+                        (gt == nullptr || (reinterpret_cast<uintptr_t>(gt) & 15u) == 0);
+    if (one_row && vec_ok) {
+        const long long nv = d.per_image >> 2;
+        const unsigned pre0 = pre[0], bmask = bins - 1u;
+        const bool want_hist = nr >= 1, pass0 = a.pass == 0, want_sum = pass0 && a.out_sum != nullptr;
+        unsigned c32 = 0;
+        auto elem = [&](float val, bool keep) {
+            if (!keep) return;
+            const unsigned key = fkey(val);
+            ++c32;
+            if (want_sum) sum += (double)val;
+            if (want_hist && (key & himask) == pre0) atomicAdd(&sh[(key >> shift) & bmask], 1u);
+        };
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
+             i += (long long)gridDim.x * blockDim.x) {
+            const float4 x = ldg_stream4(v + 4 * i);
+            bool k0 = true, k1 = true, k2 = true, k3 = true;
+            if (gt) {
+                const float4 gg = ldg_stream4(gt + 4 * i);
+                k0 = gg.x >= thr; k1 = gg.y >= thr; k2 = gg.z >= thr; k3 = gg.w >= thr;
+            }
+            elem(x.x, k0);
+            elem(x.y, k1);
+            elem(x.z, k2);
+            elem(x.w, k3);
         }
-        const unsigned digit = (key >> shift) & (bins - 1u);
-        const unsigned hi = key & himask;
-        // ranks that share a prefix share a histogram row (the common case: lo and hi are adjacent ranks)
-        if (nr >= 1 && hi == pre[0]) atomicAdd(&sh[digit], 1u);
-        if (nr >= 2 && !same01 && hi == pre[1]) atomicAdd(&sh[bins + digit], 1u);
-        if (nr >= 4 && hi == pre[2]) atomicAdd(&sh[2 * bins + digit], 1u);
-        if (nr >= 4 && !same23 && hi == pre[3]) atomicAdd(&sh[3 * bins + digit], 1u);
+        cnt = pass0 ? c32 : 0ull;
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < d.per_image;
+             i += (long long)gridDim.x * blockDim.x) {
+            if (gt && !(__ldg(gt + i) >= thr)) continue;
+            const float val = __ldg(v + i);
+            const unsigned key = fkey(val);
+            if (a.pass == 0) {
+                ++cnt;
+                sum += (double)val;
+            }
+            const unsigned digit = (key >> shift) & (bins - 1u);
+            const unsigned hi = key & himask;
+            // ranks that share a prefix share a histogram row (the common case: lo and hi are adjacent ranks)
+            if (nr >= 1 && hi == pre[0]) atomicAdd(&sh[digit], 1u);
+            if (nr >= 2 && !same01 && hi == pre[1]) atomicAdd(&sh[bins + digit], 1u);
+            if (nr >= 4 && hi == pre[2]) atomicAdd(&sh[2 * bins + digit], 1u);
+            if (nr >= 4 && !same23 && hi == pre[3]) atomicAdd(&sh[3 * bins + digit], 1u);
+        }
     }
     __syncthreads();
     unsigned long long *gh = a.hist + (size_t)seg * kMaxR * kBins;
@@ -154,19 +188,40 @@ __global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int i
         const bool shared_row = (r & 1) && st.prefix[r] == st.prefix[r - 1] && a.pass >= 0;
         const unsigned long long *row = gh + (size_t)(shared_row ? r - 1 : r) * kBins;
         const unsigned long long k = st.k[r];
-        // 256 threads x (bins / 256) bins: chunk sums, then thread 0 walks chunks, then bins
+        // 256 threads x (bins / 256) bins each: block-wide exclusive scan of the chunk sums, then the one thread
+        // whose chunk holds rank k walks its own <= 8 bins (registers)
         const int per = bins / 256;
-        unsigned long long cs = 0;
-        for (int j = 0; j < per; ++j) cs += row[threadIdx.x * per + j];
-        chunk[threadIdx.x] = cs;
+        unsigned long long bv[8], cs = 0;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            bv[j] = j < per ? row[threadIdx.x * per + j] : 0ull;
+            cs += bv[j];
+        }
+        const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+        unsigned long long incl = cs;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) chunk[wid] = incl;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            unsigned long long cum = 0;
-            int c = 0;
-            while (c < 255 && cum + chunk[c] <= k) cum += chunk[c++];
-            int b = c * per;
-            while (b < c * per + per - 1 && cum + row[b] <= k) cum += row[b++];
-            chunk[0] = (unsigned long long)b;
+        unsigned long long base = 0;
+        for (int w2 = 0; w2 < wid; ++w2) base += chunk[w2];
+        const unsigned long long excl = base + incl - cs;
+        bool sel = excl <= k && k < excl + cs;
+        const int any = __syncthreads_or(sel ? 1 : 0);   // also orders the chunk[] reads before the writes below
+        if (!any && threadIdx.x == 255) sel = true;       // rank beyond the population (empty set): last chunk
+        if (sel) {
+            unsigned long long cum = excl;
+            int jb = 0;
+#pragma unroll
+            for (int j = 0; j < 7; ++j)
+                if (jb == j && j < per - 1 && cum + bv[j] <= k) {
+                    cum += bv[j];
+                    jb = j + 1;
+                }
+            chunk[0] = (unsigned long long)(threadIdx.x * per + jb);
             chunk[1] = k - cum;
         }
         __syncthreads();
