@@ -230,6 +230,12 @@ typedef struct llie_deltae_desc {
 int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum, float *out_map,
                 float *out_l, int32_t *out_flags, void *workspace, void *stream);
 
+/* llie_deltae plus out_sqerr[n] = sum over the image of (x - y)^2 in float64 on the RAW (unclamped) inputs, so
+ * that the whole-image PSNR (metrics/psnr.py:39-88) rides on the colour pass instead of re-reading both images. */
+int llie_deltae_sqerr(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                      double *out_sqerr, float *out_map, float *out_l, int32_t *out_flags, void *workspace,
+                      void *stream);
+
 /* DeltaE00Loss forward + analytic backward in ONE pass (variant 1, sRGB inputs): per-image sums of dE00 and
  * out_grad[n,3,h,w] = grad_scale * d dE00(pixel) / d x (clamp pass-through mask included), i.e. the gradient
  * of `dE.mean()` when grad_scale = 1 / (n h w).  replaces losses.py:138-143 + its autograd graph. */

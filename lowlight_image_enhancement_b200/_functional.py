@@ -387,8 +387,9 @@ def ssim_stats(x: Tensor, y: Tensor, win: Tensor, *, pad_mode: int, c1: float, c
 # ------------------------------------------------------------------------------------------------
 def deltae(x: Tensor, y: Tensor, *, variant: int, kL: float = 1.0, kC: float = 1.0, kH: float = 1.0,
            eps: float = 1e-12, input_lab: bool = False, clamp_in: bool = False, want_map: bool = False,
-           want_l: bool = False):
-    """Launch llie_deltae on contiguous fp32 CUDA [N,3,H,W].  Returns (sums f64[N], flags, map|None, L|None)."""
+           want_l: bool = False, sqerr_out: Optional[list] = None):
+    """Launch llie_deltae on contiguous fp32 CUDA [N,3,H,W].  Returns (sums f64[N], flags, map|None, L|None).
+    `sqerr_out=[]`: the pass also sums (x - y)^2 in float64 per image (llie_deltae_sqerr), appended to the list."""
     dev = x.device
     n, _, h, w = x.shape
     sums = torch.empty(n, dtype=torch.float64, device=dev)
@@ -397,8 +398,15 @@ def deltae(x: Tensor, y: Tensor, *, variant: int, kL: float = 1.0, kC: float = 1
     lpl = torch.empty((n, h, w), dtype=torch.float32, device=dev) if want_l else None
     d = nat.DeltaEDesc(n, h, w, variant, int(input_lab), int(clamp_in), float(kL), float(kC), float(kH), float(eps))
     with torch.cuda.device(dev):
-        rc = nat.lib().llie_deltae(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(dmap), nat.ptr(lpl),
-                                   nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+        if sqerr_out is not None:
+            sq = torch.empty(n, dtype=torch.float64, device=dev)
+            sqerr_out.append(sq)
+            rc = nat.lib().llie_deltae_sqerr(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(sq), nat.ptr(dmap),
+                                             nat.ptr(lpl), nat.ptr(flags), nat.ptr(nat.workspace(dev)),
+                                             nat.stream_ptr(dev))
+        else:
+            rc = nat.lib().llie_deltae(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(dmap), nat.ptr(lpl),
+                                       nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
     nat.check(rc, "llie_deltae")
     nat.count_launch()
     return sums, flags, dmap, lpl

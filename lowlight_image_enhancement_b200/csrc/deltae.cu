@@ -169,6 +169,8 @@ struct DeArgs {
     double *part;  // [n][G]
     int *pflag;    // [n][G]
     unsigned *ticket;
+    double *out_sq;   // NULL or [n]: sum over the 3 channels of (x - y)^2 in float64 (PSNR rides on this pass)
+    double *part_sq;  // [n][G]
 };
 
 __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
@@ -178,12 +180,18 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
     const long long plane = (long long)d.h * d.w;
     const float *x0 = a.x + (long long)n * 3 * plane, *y0 = a.y + (long long)n * 3 * plane;
     float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    double sq = 0.0;
+    const bool want_sq = a.out_sq != nullptr;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
          i += (long long)G * blockDim.x) {
         float p0 = __ldcs(x0 + i), p1 = __ldcs(x0 + plane + i), p2 = __ldcs(x0 + 2 * plane + i);
         float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
         chk_x = fmaf(p0, 0.f, fmaf(p1, 0.f, fmaf(p2, 0.f, chk_x)));
         chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
+        if (want_sq) {  // metrics/psnr.py:39-88: both images promoted to float64 before the difference
+            const double d0 = (double)p0 - (double)t0, d1 = (double)p1 - (double)t1, d2 = (double)p2 - (double)t2;
+            sq = fma(d0, d0, fma(d1, d1, fma(d2, d2, sq)));
+        }
         float L1, A1, B1, L2, A2, B2;
         if (d.input_lab) {
             L1 = p0; A1 = p1; B1 = p2;
@@ -203,18 +211,22 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
         if (a.out_l) a.out_l[(long long)n * plane + i] = L1;
     }
     const double bs = block_sum<double>((double)acc, red);
+    double bq = 0.0;
+    if (want_sq) bq = block_sum<double>(sq, red);
     int flag = 0;
     if (!(chk_x == 0.f)) flag |= 1;
     if (!(chk_y == 0.f)) flag |= 2;
     const int f = block_or(flag, reinterpret_cast<int *>(red));
     if (threadIdx.x == 0) {
         a.part[(size_t)n * G + blockIdx.x] = bs;
+        if (want_sq) a.part_sq[(size_t)n * G + blockIdx.x] = bq;
         a.pflag[(size_t)n * G + blockIdx.x] = f;
     }
     if (!last_block_done(a.ticket, gridDim.x * gridDim.y)) return;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    for (int s = wrp; s < d.n; s += 8) {
-        const double *p = a.part + (size_t)s * G;
+    for (int s = wrp; s < d.n * (want_sq ? 2 : 1); s += 8) {
+        const int img = s % d.n;
+        const double *p = (s < d.n ? a.part : a.part_sq) + (size_t)img * G;
         double s0 = 0.0, s1 = 0.0;
         int b = lane;
         for (; b + 32 < G; b += 64) {
@@ -223,7 +235,7 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
         }
         for (; b < G; b += 32) s0 += __ldcg(p + b);
         const double t = warp_sum(s0 + s1);
-        if (lane == 0) a.out_sum[s] = t;
+        if (lane == 0) (s < d.n ? a.out_sum : a.out_sq)[img] = t;
     }
     int fl = 0;
     for (int b = threadIdx.x; b < G * d.n; b += blockDim.x) fl |= __ldcg(a.pflag + b);
@@ -485,8 +497,9 @@ __global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, in
 
 using namespace llie;
 
-extern "C" int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
-                           float *out_map, float *out_l, int32_t *out_flags, void *workspace, void *stream) {
+static int deltae_launch(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                         double *out_sq, float *out_map, float *out_l, int32_t *out_flags, void *workspace,
+                         void *stream) {
     LLIE_REQUIRE(desc && x && y && out_sum && out_flags && workspace, "deltae: null pointer");
     LLIE_REQUIRE(desc->n > 0 && desc->h > 0 && desc->w > 0, "deltae: empty tensor");
     LLIE_REQUIRE(desc->n <= 65535, "deltae: batch too large for grid.y");
@@ -501,14 +514,28 @@ extern "C" int llie_deltae(const llie_deltae_desc *desc, const float *x, const f
     if (G < 1) G = 1;
     Workspace ws(workspace);
     const size_t slots = (size_t)G * desc->n;
-    LLIE_REQUIRE(slots * (sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "deltae: workspace too small");
+    LLIE_REQUIRE(slots * (2 * sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "deltae: workspace too small");
     a.part = reinterpret_cast<double *>(ws.scratch);
-    a.pflag = reinterpret_cast<int *>(ws.scratch + slots * sizeof(double));
+    a.part_sq = a.part + slots;
+    a.pflag = reinterpret_cast<int *>(ws.scratch + 2 * slots * sizeof(double));
+    a.out_sq = out_sq;
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
     deltae_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
+}
+
+extern "C" int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                           float *out_map, float *out_l, int32_t *out_flags, void *workspace, void *stream) {
+    return deltae_launch(desc, x, y, out_sum, nullptr, out_map, out_l, out_flags, workspace, stream);
+}
+
+extern "C" int llie_deltae_sqerr(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                                 double *out_sqerr, float *out_map, float *out_l, int32_t *out_flags,
+                                 void *workspace, void *stream) {
+    LLIE_REQUIRE(out_sqerr, "deltae_sqerr: null pointer");
+    return deltae_launch(desc, x, y, out_sum, out_sqerr, out_map, out_l, out_flags, workspace, stream);
 }
 
 extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const float *y, float grad_scale,

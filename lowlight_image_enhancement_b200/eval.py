@@ -38,9 +38,14 @@ def _stage_pair(pred: Tensor, target: Tensor):
     return nat.stage(pred.detach(), dev, torch.float32), nat.stage(target.detach(), dev, torch.float32), dev
 
 
-def _psnr(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.0) -> Tensor:
-    """lowlight_metrics.py:211-214 -> metrics/psnr.py:39-88 (whole-tensor MSE in float64)."""
+def _psnr(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.0, shared=None) -> Tensor:
+    """lowlight_metrics.py:211-214 -> metrics/psnr.py:39-88 (whole-tensor MSE in float64).  When a colour pass
+    runs for the same pair the float64 sum of squared differences comes from it (no second read of the images)."""
     from . import _functional as Fn
+    if shared is not None and shared.sqerr is not None:
+        mse = shared.sqerr.sum() / float(pred.numel())
+        val = 10.0 * torch.log10(float(data_range) ** 2 / mse)
+        return torch.where(mse.abs() <= 1e-12, torch.full_like(val, float("inf")), val)   # isclose(mse, 0, atol=1e-12)
     table, fl, _ = Fn.psnr_stats(target, pred, 1, 1, pred.numel(), cast_first=True, clamp_hi=None,
                                  data_range=float(data_range), eps=1e-12)
     flags |= fl
@@ -58,10 +63,13 @@ class _ColourPass:
     """One dE00 pass per image pair shared by the colour metrics that were asked for: the per-image sums
     always, the dE map / L(pred) plane only when a percentile or the edge metric needs them."""
 
-    def __init__(self, pred: Tensor, target: Tensor, flags: Tensor, want_map: bool, want_l: bool):
+    def __init__(self, pred: Tensor, target: Tensor, flags: Tensor, want_map: bool, want_l: bool,
+                 want_sqerr: bool = False):
         from . import _functional as Fn
+        sq = [] if want_sqerr else None
         self.sums, fl, self.dmap, self.lpl = Fn.deltae(pred, target, variant=0, clamp_in=True, want_map=want_map,
-                                                       want_l=want_l)
+                                                       want_l=want_l, sqerr_out=sq)
+        self.sqerr = sq[0] if want_sqerr else None
         flags |= fl
         self.hw = pred.shape[-2] * pred.shape[-1]
         self.n = pred.shape[0]
@@ -117,12 +125,14 @@ def image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], flags: Opt
             raise KeyError(f"unknown metric '{name}'; available: {sorted(METRIC_FUNCTIONS)}")
     colour = [n for n in names if n in _COLOUR]
     shared = None
-    if len(colour) > 1:  # one Lab + dE00 pass for all colour metrics of this pair
-        shared = _ColourPass(p, t, flags, any(_COLOUR[n][0] for n in colour), any(_COLOUR[n][1] for n in colour))
+    ride_psnr = "linear_psnr" in names and len(colour) >= 1 and p.shape[1] == 3
+    if len(colour) > 1 or ride_psnr:  # one Lab + dE00 pass for all colour metrics (and the PSNR) of this pair
+        shared = _ColourPass(p, t, flags, any(_COLOUR[n][0] for n in colour), any(_COLOUR[n][1] for n in colour),
+                             want_sqerr=ride_psnr)
     vals = []
     for name in names:
         kw = dict(opts.get(name, {}))
-        if name in _COLOUR and shared is not None:
+        if (name in _COLOUR or name == "linear_psnr") and shared is not None:
             kw["shared"] = shared
         vals.append(METRIC_FUNCTIONS[name](p, t, flags, **kw).reshape(()))
     return torch.stack(vals)
