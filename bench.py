@@ -411,6 +411,20 @@ def run_extra(args, rank, world, dev):
                     kern("deltae_kernel", t_de, 24, "instruction issue (fp32 + sfu)"),
                     kern("all 4 metrics of one image (12 launches)", t_all, 36, "mixed")],
     }
+    if world == 1 and not args.skip_cpu:
+        # reference CPU path of the same four adapters on ONE full-resolution pair (bounded sample: ~15-30 s)
+        from oracle import colour, quality
+        torch.set_num_threads(os.cpu_count() or 1)
+        cp, cg = pool[0][0].cpu(), pool[0][1].cpu()
+        t0 = time.perf_counter()
+        quality.calculate_psnr(cg, cp, 1.0)
+        float(quality.ssim_torchmetrics(cp, cg).mean())
+        colour.de00_summary(cp, cg, percentiles=(95.0,))          # deltae2000_mean pays the p95 sort in the reference
+        colour.edge_stats(cp, cg, q=0.85)
+        dt = time.perf_counter() - t0
+        out["eval_c4"]["cpu_baseline"] = {"value": round(px / 1e6 / dt, 3), "unit": "Mpix/s", "cores": os.cpu_count(),
+                                          "kind": "port", "sample": f"1 full-resolution pair, the same 4 adapters, {dt:.1f} s"}
+        del cp, cg
     del pool, pr, gt
     torch.cuda.empty_cache()
 
@@ -444,6 +458,17 @@ def run_extra(args, rank, world, dev):
         "algorithmic_bytes_per_step": (36 + 48) * pxl,
         "achieved_gbs": round((36 + 48) * pxl / ms_h / 1e6, 1), "n_gpus": world,
     }
+    if world == 1 and not args.skip_cpu:
+        from oracle import hybrid as ohyb
+        cb, ca, ck = B.cpu(), A.cpu(), kern3.cpu()
+        cx = xs[0].cpu().requires_grad_(True)
+        t0 = time.perf_counter()
+        tot, _ = ohyb.hybrid_loss(Bhat_raw=cx, B_raw=cb, A_raw=ca, expo_ratio=rho.cpu(), Bhat_srgb01=cx, B_srgb01=cb,
+                                  w_l1=1.0, w_de=0.02, w_ssim=0.05, w_phys=0.05, physics_kernel=ck)
+        tot.backward()
+        dt = time.perf_counter() - t0
+        out["hybrid_c3"]["cpu_baseline"] = {"value": round(pxl / 1e6 / dt, 3), "unit": "Mpix/s", "cores": os.cpu_count(),
+                                            "kind": "port", "sample": f"1 step (no warm-up) of the oracle hybrid loss fwd+bwd, {dt:.1f} s"}
     return out
 
 
