@@ -248,6 +248,26 @@ int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const fl
 int llie_l1_grad(const float *x, const float *y, int64_t n, float grad_scale, int32_t accumulate, double *out_sum,
                  float *out_grad, int32_t *out_flags, void *workspace, void *stream);
 
+/* BasicSR pixel losses, value + gradient in one pass:
+ *   out_sum[1]  = sum_e w_e psi(x_e - y_e)                                  (float64)
+ *   out_grad    = grad_scale * sample_coef[n] * w_e * psi'(x_e - y_e)       (NULL = value only; += when accumulate)
+ * psi: LLIE_PIX_L1 |d|, LLIE_PIX_MSE d^2, LLIE_PIX_CHARBONNIER sqrt(d^2 + eps).  `weight` NULL or [n, c, plane]
+ * (weight_per_channel = 1) / [n, 1, plane] (0); `sample_coef` NULL or [n] device floats.  plane = H*W, % 4 == 0.
+ * replaces NAFNet_base/basicsr/models/losses/losses.py:18-31, 112-138 and loss_util.py:31-60 + autograd. */
+#define LLIE_PIX_L1 0
+#define LLIE_PIX_MSE 1
+#define LLIE_PIX_CHARBONNIER 2
+int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y, const float *weight, int32_t weight_per_channel,
+                         const float *sample_coef, int32_t n, int32_t c, int64_t plane, float eps, float grad_scale,
+                         int32_t accumulate, double *out_sum, float *out_grad, int32_t *out_flags, void *workspace,
+                         void *stream);
+
+/* Merge of overlapping validation tiles: out[1, c, h, w] = average over the tiles covering each pixel, summed in
+ * tile order (tiles [n_tiles, c, tile_h, tile_w], tile_ij [n_tiles][2] = top-left (row, col), int32, device).
+ * replaces NAFNet_base/basicsr/models/image_restoration_model.py:215-241 (grids_inverse, done on the host there). */
+int llie_tile_merge(const float *tiles, const int32_t *tile_ij, int32_t n_tiles, int32_t c, int32_t tile_h,
+                    int32_t tile_w, int32_t h, int32_t w, float *out, void *stream);
+
 /* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the
  * < 1 ulp claim can be checked against a float64 pow from the test-suite. */
 int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream);

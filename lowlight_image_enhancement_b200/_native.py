@@ -90,6 +90,9 @@ _SIGNATURES = {
     "llie_ssim_loss_backward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP,
                                           _VP]),
     "llie_l1_grad": (C.c_int, [_VP, _VP, C.c_int64, C.c_float, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
+    "llie_pixel_loss_grad": (C.c_int, [C.c_int32, _VP, _VP, _VP, C.c_int32, _VP, C.c_int32, C.c_int32, C.c_int64, C.c_float,
+                                       C.c_float, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
+    "llie_tile_merge": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _VP, _VP]),
     "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),
     "llie_select_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),

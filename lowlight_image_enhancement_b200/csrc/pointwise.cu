@@ -377,3 +377,180 @@ extern "C" int llie_l1_grad(const float *x, const float *y, int64_t n, float gra
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// Overlapping-tile merge of the validation driver (image_restoration_model.py:215-241 `grids_inverse`):
+//   out[c, y, x] = ( sum over tiles t covering (y, x), in tile order, of tiles[t, c, y - i_t, x - j_t] ) / count
+// The reference does this on the HOST (zeros + slice adds + divide, then one upload); here every output
+// pixel gathers its covering tiles on the device in the same order, so the fp32 result is identical.
+namespace llie {
+
+__global__ void __launch_bounds__(256) tile_merge_kernel(const float *tiles, const int *idx, int T, int C, int th,
+                                                         int tw, int H, int W, float *out) {
+    const long long total = (long long)C * H * W;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < total;
+         e += (long long)gridDim.x * blockDim.x) {
+        const int x = (int)(e % W);
+        const int y = (int)((e / W) % H);
+        const int c = (int)(e / ((long long)W * H));
+        float acc = 0.f, cnt = 0.f;
+        for (int t = 0; t < T; ++t) {
+            const int i = __ldg(idx + 2 * t), j = __ldg(idx + 2 * t + 1);
+            if (y >= i && y < i + th && x >= j && x < j + tw) {
+                acc += __ldg(tiles + (((long long)t * C + c) * th + (y - i)) * tw + (x - j));
+                cnt += 1.f;
+            }
+        }
+        out[e] = acc / cnt;  // an uncovered pixel is 0 / 0 = NaN, as in the reference
+    }
+}
+
+}  // namespace llie
+
+extern "C" int llie_tile_merge(const float *tiles, const int32_t *tile_ij, int32_t n_tiles, int32_t c, int32_t tile_h,
+                               int32_t tile_w, int32_t h, int32_t w, float *out, void *stream) {
+    LLIE_REQUIRE(tiles && tile_ij && out && n_tiles > 0 && c > 0 && tile_h > 0 && tile_w > 0 && h > 0 && w > 0,
+                 "tile_merge: bad arguments");
+    const long long total = (long long)c * h * w;
+    long long blocks = (total + 255) / 256;
+    if (blocks > llie::kNumSM * 16) blocks = llie::kNumSM * 16;
+    llie::tile_merge_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(tiles, tile_ij, n_tiles, c,
+                                                                                            tile_h, tile_w, h, w, out);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// BasicSR pixel losses (NAFNet_base/basicsr/models/losses/losses.py:18-31, loss_util.py:31-60): value and gradient
+// of  sum_e w_e psi(x_e - y_e)  in one streaming pass, psi = |d| (L1), d^2 (MSE) or sqrt(d^2 + eps) (Charbonnier;
+// eps is NOT squared there), optional element weights w [N, 1|C, H, W] and an optional per-sample device
+// coefficient (PSNRLoss backward).  grad = scale * coef[n] * w * psi'(d).
+namespace llie {
+
+struct PixArgs {
+    const float *x, *y, *w, *coef;
+    float *grad;
+    double *out_sum;
+    int *out_flags;
+    double *part;
+    int *pflag;
+    unsigned *ticket;
+    long long n_elem, plane, chw;
+    int mode, w_per_channel, accumulate;
+    float eps, scale;
+};
+
+__device__ __forceinline__ float pix_term(int mode, float eps, float d, float &dpsi) {
+    if (mode == LLIE_PIX_L1) {
+        dpsi = d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f);
+        return fabsf(d);
+    }
+    if (mode == LLIE_PIX_MSE) {
+        dpsi = 2.f * d;
+        return d * d;
+    }
+    const float r = sqrtf(fmaf(d, d, eps));
+    dpsi = d / r;
+    return r;
+}
+
+__global__ void __launch_bounds__(256) pixel_loss_kernel(const PixArgs a) {
+    __shared__ double red[32];
+    float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    double dacc = 0.0;
+    const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nth = (long long)gridDim.x * blockDim.x;
+    const long long nv = a.n_elem >> 2;  // launcher guarantees plane % 4 == 0 and 16-byte alignment
+    int it = 0;
+    for (long long i = tid; i < nv; i += nth) {
+        const long long e = 4 * i;
+        const float4 xv = ldg_stream4(a.x + e), yv = ldg_stream4(a.y + e);
+        float4 wv = make_float4(1.f, 1.f, 1.f, 1.f);
+        const long long n = e / a.chw;
+        if (a.w) {
+            const long long we = a.w_per_channel ? e : n * a.plane + (e % a.plane);
+            wv = ldg_stream4(a.w + we);
+        }
+        const float s = a.coef ? a.scale * __ldg(a.coef + n) : a.scale;
+        const float xs[4] = {xv.x, xv.y, xv.z, xv.w}, ys[4] = {yv.x, yv.y, yv.z, yv.w};
+        const float ws[4] = {wv.x, wv.y, wv.z, wv.w};
+        float g[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            chk_x = fmaf(xs[k], 0.f, chk_x);
+            chk_y = fmaf(ys[k], 0.f, chk_y);
+            float dpsi;
+            const float v = pix_term(a.mode, a.eps, xs[k] - ys[k], dpsi);
+            acc = fmaf(ws[k], v, acc);
+            g[k] = s * ws[k] * dpsi;
+        }
+        if (a.grad) {
+            float4 *gp = reinterpret_cast<float4 *>(a.grad + e);
+            float4 o = make_float4(g[0], g[1], g[2], g[3]);
+            if (a.accumulate) {
+                const float4 p = *gp;
+                o.x += p.x; o.y += p.y; o.z += p.z; o.w += p.w;
+            }
+            *gp = o;
+        }
+        if (++it == 64) {
+            dacc += (double)acc;
+            acc = 0.f;
+            it = 0;
+        }
+    }
+    dacc += (double)acc;
+    const double bs = block_sum<double>(dacc, red);
+    int flag = 0;
+    if (!(chk_x == 0.f)) flag |= 1;
+    if (!(chk_y == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        a.part[blockIdx.x] = bs;
+        a.pflag[blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x)) return;
+    double s0 = 0.0;
+    int fl = 0;
+    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) {
+        s0 += __ldcg(a.part + b);
+        fl |= __ldcg(a.pflag + b);
+    }
+    const double t = block_sum<double>(s0, red);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (threadIdx.x == 0) {
+        *a.out_sum = t;
+        *a.out_flags = ff;
+    }
+}
+
+}  // namespace llie
+
+extern "C" int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y, const float *weight,
+                                    int32_t weight_per_channel, const float *sample_coef, int32_t n, int32_t c,
+                                    int64_t plane, float eps, float grad_scale, int32_t accumulate, double *out_sum,
+                                    float *out_grad, int32_t *out_flags, void *workspace, void *stream) {
+    LLIE_REQUIRE(x && y && out_sum && out_flags && workspace && n > 0 && c > 0 && plane > 0, "pixel_loss: bad arguments");
+    LLIE_REQUIRE(mode >= LLIE_PIX_L1 && mode <= LLIE_PIX_CHARBONNIER, "pixel_loss: unknown mode %d", mode);
+    LLIE_REQUIRE(plane % 4 == 0 && llie::aligned16(x) && llie::aligned16(y) && (!weight || llie::aligned16(weight)) &&
+                     (!out_grad || llie::aligned16(out_grad)),
+                 "pixel_loss: H*W must be a multiple of 4 and the tensors 16-byte aligned");
+    llie::PixArgs a{};
+    a.x = x; a.y = y; a.w = weight; a.coef = sample_coef; a.grad = out_grad;
+    a.out_sum = out_sum; a.out_flags = out_flags;
+    a.plane = plane; a.chw = (long long)c * plane; a.n_elem = (long long)n * a.chw;
+    a.mode = mode; a.w_per_channel = weight_per_channel; a.accumulate = accumulate;
+    a.eps = eps; a.scale = grad_scale;
+    long long blocks = (a.n_elem / 4 + 255) / 256;
+    const long long cap = llie::kNumSM * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    llie::Workspace ws(workspace);
+    a.part = reinterpret_cast<double *>(ws.scratch);
+    a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)blocks * sizeof(double));
+    a.ticket = ws.tickets;
+    llie::pixel_loss_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}

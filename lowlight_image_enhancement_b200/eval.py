@@ -22,7 +22,7 @@ import torch
 import torch.distributed as dist
 from torch import Tensor
 
-__all__ = ["METRIC_FUNCTIONS", "ShardedMeans", "shard_indices", "image_metrics", "evaluate_pairs"]
+__all__ = ["METRIC_FUNCTIONS", "ShardedMeans", "TileGrid", "shard_indices", "image_metrics", "evaluate_pairs"]
 
 
 # ------------------------------------------------------------------------------------------------
@@ -215,3 +215,71 @@ def evaluate_pairs(pairs, names: Sequence[str], *, n_items: Optional[int] = None
         vals = fn(pred, target, names, flags, **opts)
         acc.add(vals, flags)
     return acc.reduce()
+
+
+# ------------------------------------------------------------------------------------------------
+# tiled inference of the validation driver (irm:167-241): split on the device, merge on the device
+# ------------------------------------------------------------------------------------------------
+class TileGrid:
+    """Overlapping crop grid of `ImageRestorationModel.grids` / `grids_inverse`.
+
+    Same placement rule as the reference (irm:179-208): `ceil(size / crop)` tiles per axis, the stride is the
+    smallest integer (a multiple of `scale`) that still reaches the far border, the last tile of a row / column is
+    pushed back inside.  `split` slices the low-quality image into the tile batch, `merge` averages the network
+    outputs of overlapping tiles with one kernel on the device — the reference builds the average on the host and
+    uploads it (irm:216-240)."""
+
+    def __init__(self, h: int, w: int, crop_h: int, crop_w: int, scale: int = 1):
+        import math
+        self.h, self.w, self.scale = int(h), int(w), int(scale)
+        self.crop_h = int(crop_h) // scale * scale
+        self.crop_w = int(crop_w) // scale * scale
+        if not (0 < self.crop_h <= h and 0 < self.crop_w <= w):
+            raise ValueError(f"crop {(crop_h, crop_w)} does not fit the image {(h, w)}")
+        rows = (h - 1) // self.crop_h + 1
+        cols = (w - 1) // self.crop_w + 1
+        step_i = self.crop_h if rows == 1 else math.ceil((h - self.crop_h) / (rows - 1) - 1e-8)
+        step_j = self.crop_w if cols == 1 else math.ceil((w - self.crop_w) / (cols - 1) - 1e-8)
+        step_i, step_j = step_i // scale * scale, step_j // scale * scale
+
+        def starts(size, crop, step):
+            out, pos = [], 0
+            while True:
+                if pos + crop >= size:
+                    out.append(size - crop)
+                    return out
+                out.append(pos)
+                pos += step
+                if step <= 0:  # degenerate stride (crop == size handled above): avoid an endless walk
+                    raise ValueError("tile stride collapsed to zero")
+
+        self.indices = [(i, j) for i in starts(h, self.crop_h, step_i) for j in starts(w, self.crop_w, step_j)]
+        self._idx_dev = {}
+
+    def split(self, lq: Tensor) -> Tensor:
+        """[1, C, h/scale, w/scale] -> [T, C, crop_h/scale, crop_w/scale] (tile order = `indices`)."""
+        if lq.shape[0] != 1:
+            raise ValueError("tiled validation runs one image at a time (irm:171)")
+        s = self.scale
+        return torch.cat([lq[:, :, i // s:(i + self.crop_h) // s, j // s:(j + self.crop_w) // s] for i, j in self.indices])
+
+    @torch.no_grad()
+    def merge(self, outs: Tensor) -> Tensor:
+        """[T, C, crop_h, crop_w] network outputs -> [1, C, h, w] average, on the tiles' device."""
+        from . import _native as nat
+        t, c, th, tw = outs.shape
+        if t != len(self.indices) or (th, tw) != (self.crop_h, self.crop_w):
+            raise ValueError(f"expected {len(self.indices)} tiles of {(self.crop_h, self.crop_w)}, got {tuple(outs.shape)}")
+        dev = nat.cuda_device_for(outs)
+        x = nat.stage(outs.detach(), dev, torch.float32)
+        idx = self._idx_dev.get(dev)
+        if idx is None:
+            idx = torch.tensor(self.indices, dtype=torch.int32, device=dev).contiguous()
+            self._idx_dev[dev] = idx
+        out = torch.empty((1, c, self.h, self.w), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = nat.lib().llie_tile_merge(nat.ptr(x), nat.ptr(idx), t, c, th, tw, self.h, self.w, nat.ptr(out),
+                                           nat.stream_ptr(dev))
+        nat.check(rc, "llie_tile_merge")
+        nat.count_launch()
+        return out

@@ -173,3 +173,29 @@ def l_plane_inputs():
     lp = torch.randint(0, 801, (3, 1, 37, 53), generator=g).to(torch.float32) / 8.0
     lp[2] = 42.0  # constant image: every pixel equals the threshold -> all selected except borders differ
     return lp
+
+
+# ------------------------------------------------------------------ BasicSR pixel-loss inputs
+PIXEL_LOSS_CASES = [
+    dict(name="l1_mean", loss="l1", reduction="mean", weight=None),
+    dict(name="l1_sum", loss="l1", reduction="sum", weight=None),
+    dict(name="l1_w1_mean", loss="l1", reduction="mean", weight=1),
+    dict(name="l1_wc_mean", loss="l1", reduction="mean", weight=3),
+    dict(name="mse_mean", loss="mse", reduction="mean", weight=None),
+    dict(name="mse_wc_sum", loss="mse", reduction="sum", weight=3),
+    dict(name="mse_w1_mean", loss="mse", reduction="mean", weight=1),
+    dict(name="charb_mean", loss="charbonnier", reduction="mean", weight=None),
+    dict(name="charb_eps_mean", loss="charbonnier", reduction="mean", weight=None, eps=1e-6),
+    dict(name="charb_w1_sum", loss="charbonnier", reduction="sum", weight=1),
+    dict(name="psnr", loss="psnr", toY=False),
+    dict(name="psnr_toY", loss="psnr", toY=True),
+]
+
+
+def pixel_loss_inputs(shape=(3, 3, 24, 20)):
+    g = _gen(71)
+    tgt = torch.rand(*shape, generator=g)
+    pred = (tgt + 0.1 * torch.randn(*shape, generator=g)).clamp(0, 1)
+    w1 = torch.rand(shape[0], 1, *shape[2:], generator=g)
+    wc = torch.rand(*shape, generator=g)
+    return pred, tgt, {None: None, 1: w1, 3: wc}

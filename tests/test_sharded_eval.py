@@ -124,3 +124,55 @@ def test_device_metrics_equal_adapters():
     assert evaluate_pairs([(bad, pairs[0][1])], ["linear_psnr", "deltae2000_mean"], device=dev)["nonfinite_inputs"] == 1
     with pytest.raises(KeyError):
         image_metrics(pairs[0][0], pairs[0][1], ["nope"])
+
+
+def _reference_grid(h, w, ch, cw, scale=1):
+    """image_restoration_model.py:167-208 index walk restated for the test."""
+    import math
+    ch, cw = ch // scale * scale, cw // scale * scale
+    nr, nc = (h - 1) // ch + 1, (w - 1) // cw + 1
+    sj = cw if nc == 1 else math.ceil((w - cw) / (nc - 1) - 1e-8)
+    si = ch if nr == 1 else math.ceil((h - ch) / (nr - 1) - 1e-8)
+    si, sj = si // scale * scale, sj // scale * scale
+    out, i, last_i = [], 0, False
+    while i < h and not last_i:
+        j = 0
+        if i + ch >= h:
+            i, last_i = h - ch, True
+        last_j = False
+        while j < w and not last_j:
+            if j + cw >= w:
+                j, last_j = w - cw, True
+            out.append((i, j))
+            j += sj
+        i += si
+    return out
+
+
+@pytest.mark.parametrize("h,w,ch,cw", [(100, 130, 64, 64), (64, 64, 64, 64), (257, 300, 128, 96), (90, 50, 40, 50)])
+def test_tile_grid_indices(h, w, ch, cw):
+    from lowlight_image_enhancement_b200.eval import TileGrid
+    g = TileGrid(h, w, ch, cw)
+    assert g.indices == _reference_grid(h, w, ch, cw)
+    lq = torch.arange(h * w, dtype=torch.float32).view(1, 1, h, w)
+    tiles = g.split(lq)
+    assert tiles.shape == (len(g.indices), 1, g.crop_h, g.crop_w)
+    for t, (i, j) in enumerate(g.indices):
+        assert torch.equal(tiles[t, 0], lq[0, 0, i:i + g.crop_h, j:j + g.crop_w])
+
+
+@pytest.mark.gpu
+def test_tile_merge_equals_host_average():
+    """grids_inverse (irm:215-241) on the device: identical fp32 result to the host accumulation."""
+    from lowlight_image_enhancement_b200.eval import TileGrid
+    dev = torch.device("cuda:0")
+    h, w = 257, 300
+    g = TileGrid(h, w, 128, 96)
+    outs = torch.rand(len(g.indices), 3, g.crop_h, g.crop_w, generator=torch.Generator().manual_seed(3))
+    preds, cnt = torch.zeros(1, 3, h, w), torch.zeros(1, 1, h, w)
+    for t, (i, j) in enumerate(g.indices):
+        preds[0, :, i:i + g.crop_h, j:j + g.crop_w] += outs[t]
+        cnt[0, 0, i:i + g.crop_h, j:j + g.crop_w] += 1.0
+    ref = preds / cnt
+    got = g.merge(outs.to(dev))
+    assert got.is_cuda and torch.equal(got.cpu(), ref)
