@@ -42,6 +42,10 @@ constexpr int kSlotF = kG * kPairF;
 constexpr int kCtasPerSM = 4;
 constexpr size_t kRingSmem = ((size_t)kSlots * kSlotF + kRowF) * sizeof(float);  // ring + zero row
 
+constexpr int kSlotInterior = 0, kSlotGeneral = 1, kSlotWarm = 2;  // consumer code paths per ring slot
+template <int K>
+using SlotKind = std::integral_constant<int, K>;
+
 struct RingGeom {
     int groups, chunks;  // column groups of 512 px, row chunks per plane (even split of H)
     int items, items_per_sample;
@@ -329,10 +333,13 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
             float sA[4] = {0.f, 0.f, 0.f, 0.f}, sB[4] = {0.f, 0.f, 0.f, 0.f};
             float acc = 0.f;
             const int E = it.yb - it.ya + 2;
-            // one slot = kG entries.  GENERAL handles partial slots, zero-padding rows, warm-up and
-            // cropped rows; the interior slots of an item (all rows real, in-domain) take the lean path.
-            auto do_slot = [&](auto general_tag, int e0, const float *sp) {
-                constexpr bool GENERAL = decltype(general_tag)::value;
+            // one slot = kG entries.  GENERAL handles partial slots, zero-padding rows and cropped rows; the
+            // interior slots of an item (all rows real, in-domain) take the lean path; WARM is the first slot
+            // of an item that does not touch the plane's top edge: its first two entries only feed the
+            // rolling conv sums (no residual), the other two are interior entries.
+            auto do_slot = [&](auto kind_tag, int e0, const float *sp) {
+                constexpr int KIND = decltype(kind_tag)::value;
+                constexpr bool GENERAL = KIND == kSlotGeneral, WARM = KIND == kSlotWarm;
 #pragma unroll
                 for (int u = 0; u < kG; ++u) {
                     const int e = e0 + u;
@@ -350,6 +357,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
                     const float4 ob = reinterpret_cast<const float4 *>(rowp + kRowF)[tid + 1];
                     float cv[4];
                     roll3<4>(r6, w, sA, sB, cv);
+                    if (WARM && u < 2) continue;  // compile-time after unrolling: cv and the obs row are dead
                     const float av[4] = {ob.x, ob.y, ob.z, ob.w};
                     float mv[4], racc = 0.f;
 #pragma unroll
@@ -385,13 +393,17 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
             int y_end = it.yb < a.y_lo + a.ho ? it.yb : a.y_lo + a.ho;
             if (y_end > H - 1) y_end = H - 1;                      // pred row y+1 must be a real row
             const int e_lo = y_first - it.ya + 2, e_hi = y_end - it.ya + 2;
+            // warm-up slot: pred rows ya-1 .. ya+2 real, output rows ya, ya+1 compared
+            const bool warm_ok = it.ya >= 1 && it.ya + 2 <= H - 1 && it.ya >= a.y_lo && it.ya + 1 < a.y_lo + a.ho;
             for (int e0 = 0; e0 < E; e0 += kG) {
                 const float *sp = ring + rs.slot * kSlotF;
                 mbar_wait(&full[rs.slot], rs.phase);
                 if (e0 >= e_lo && e0 + kG <= e_hi)
-                    do_slot(std::false_type{}, e0, sp);
+                    do_slot(SlotKind<kSlotInterior>{}, e0, sp);
+                else if (e0 == 0 && warm_ok)
+                    do_slot(SlotKind<kSlotWarm>{}, e0, sp);
                 else
-                    do_slot(std::true_type{}, e0, sp);
+                    do_slot(SlotKind<kSlotGeneral>{}, e0, sp);
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&empty[rs.slot]);
                 rs.advance();
@@ -515,8 +527,11 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
 
         // GENERAL slots: partial slots, zero-padding rows, warm-up entries, cropped q rows, virtual rows;
         // interior slots (all pred rows real, q row compared, grad row a plain image row) run lean.
-        auto do_slot = [&](auto general_tag, int kb, const float *sp) {
-            constexpr bool GENERAL = decltype(general_tag)::value;
+        // WARM: the first slot of an item away from the plane's top edge (entries 0..3 = exactly the warm-up):
+        // entries 0, 1 only feed the rolling conv sums, entries 2, 3 the rolling grad sums; nothing is stored.
+        auto do_slot = [&](auto kind_tag, int kb, const float *sp) {
+            constexpr int KIND = decltype(kind_tag)::value;
+            constexpr bool GENERAL = KIND == kSlotGeneral, WARM = KIND == kSlotWarm;
 #pragma unroll
             for (int u = 0; u < kG; ++u) {
                 const int k = kb + u;
@@ -536,6 +551,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                 const float av[6] = {so[4 * tid + 3], ob.x, ob.y, ob.z, ob.w, so[4 * tid + 8]};
                 float cv[6];
                 roll3<6>(r8, w, cA, cB, cv);  // conv row qr over columns x-1 .. x+4
+                if (WARM && u < 2) continue;  // compile-time after unrolling: cv and the obs row are dead
                 float qc[6];
                 float lrow = 0.f;
 #pragma unroll
@@ -552,7 +568,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                         t = clamp01(t);
                     }
                     const float r = yv - t;
-                    if (FUSED && i >= 1 && i <= 4)
+                    if (FUSED && !(WARM && u == 2) && i >= 1 && i <= 4)
                         lrow = fmaf(ROBUST ? sqrtf(fmaf(r, r, eps2)) : fabsf(r), dm[i - 1], lrow);
                     if (ROBUST) {
                         qc[i] = (m != 0.f) ? m * (r / sqrtf(fmaf(r, r, eps2))) : 0.f;
@@ -561,8 +577,13 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                         qc[i] = (r != 0.f) ? copysignf(m, r) : 0.f;
                     }
                 }
-                if (FUSED)  // rows outside [ya, yb) are recomputed halo rows owned by the neighbouring item
-                    lacc = fmaf(lrow, (rowm != 0.f && qr >= it.ya && qr < it.yb) ? 1.f : 0.f, lacc);
+                if (FUSED) {  // rows outside [ya, yb) are recomputed halo rows owned by the neighbouring item
+                    if (WARM) {
+                        if (u == 3) lacc += lrow;  // q row ya; entry 2 is row ya - 1 of the item above
+                    } else {
+                        lacc = fmaf(lrow, (rowm != 0.f && qr >= it.ya && qr < it.yb) ? 1.f : 0.f, lacc);
+                    }
+                }
                 // ---- grad (virtual) row j: q row j+1 completes it (flipped kernel, rolling form)
                 float gr[4];
                 roll3<4>(qc, wf, gA, gB, gr);
@@ -575,10 +596,10 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                     for (int i = 0; i < 4; ++i)
                         if (i == tgt) gr[i] += ecol;
                 }
-                if (!GENERAL) {
+                if (KIND == kSlotInterior) {
                     if (active)
                         *reinterpret_cast<float4 *>(gp + (long long)j * W) = make_float4(gr[0], gr[1], gr[2], gr[3]);
-                } else if (k >= 4) {  // CTA-uniform: entries 0..3 are warm-up
+                } else if (GENERAL && k >= 4) {  // CTA-uniform: entries 0..3 are warm-up
                     if (j == -1) {
 #pragma unroll
                         for (int i = 0; i < 4; ++i) carry[i] = gr[i];
@@ -611,13 +632,17 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         if (j_hi > a.y_lo + a.ho - 1) j_hi = a.y_lo + a.ho - 1;
         const int k_lo = (j_lo - ja + 4) > 4 ? (j_lo - ja + 4) : 4, k_hi = j_hi - ja + 4;
 
+        // warm-up slot: pred rows ja-2 .. ja+1 real (so ja == ya: not the folded first chunk), q rows ja-1, ja compared
+        const bool warm_ok = ja >= 2 && ja + 1 <= H - 1 && ja - 1 >= a.y_lo && ja < a.y_lo + a.ho;
         for (int kb = 0; kb < E; kb += kG) {
             const float *sp = ring + rs.slot * kSlotF;
             mbar_wait(&full[rs.slot], rs.phase);
             if (kb >= k_lo && kb + kG <= k_hi)
-                do_slot(std::false_type{}, kb, sp);
+                do_slot(SlotKind<kSlotInterior>{}, kb, sp);
+            else if (kb == 0 && warm_ok)
+                do_slot(SlotKind<kSlotWarm>{}, kb, sp);
             else
-                do_slot(std::true_type{}, kb, sp);
+                do_slot(SlotKind<kSlotGeneral>{}, kb, sp);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[rs.slot]);
             rs.advance();
