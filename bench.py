@@ -197,6 +197,8 @@ def run_ours(args, rank, world, dev):
     from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw
     from oracle import psf_ops  # kernel constants for input synthesis only
 
+    if args.no_pdl:
+        nat.check(nat.lib().llie_tune(5, 0), "llie_tune")  # LLIE_TUNE_PHYS_PDL
     sets = [synth_batch(1000 * rank + 102 + i, dev) for i in range(POOL)]
     grads = [torch.empty(SHAPE, device=dev) for _ in range(POOL)]
     kern = psf_ops.canonical_kernels("rgb").to(dev)
@@ -483,6 +485,7 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: no cpu_baseline leg")
     ap.add_argument("--skip-extra", action="store_true", help="profiling runs: no eval_c4 / hybrid_c3 sections")
     ap.add_argument("--two-pass", action="store_true", help="time separate forward + backward kernels per step")
+    ap.add_argument("--no-pdl", action="store_true", help="A/B: plain launches instead of programmatic dependent launch")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":

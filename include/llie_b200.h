@@ -58,6 +58,8 @@ int llie_check_device(void);
 #define LLIE_TUNE_PHYS_ROWS 2 /* rows per warp chunk of the rolling path; 0 = heuristic */
 #define LLIE_TUNE_SSIM_PATH 3 /* 0 streaming column kernel (default) | 1 shared-memory tile kernel */
 #define LLIE_TUNE_SSIM_SEG_ROWS 4 /* output rows per CTA of the streaming SSIM kernel; 0 = heuristic */
+#define LLIE_TUNE_PHYS_PDL 5 /* 1 (default): ring kernels are launched with programmatic stream serialization, so the
+                                prologue of a kernel overlaps the tail of the previous one | 0 plain launches */
 int llie_tune(int key, int value);
 
 /* ------------------------------------------------------------------------

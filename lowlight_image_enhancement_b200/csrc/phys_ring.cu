@@ -46,6 +46,19 @@ constexpr int kSlotInterior = 0, kSlotGeneral = 1, kSlotWarm = 2;  // consumer c
 template <int K>
 using SlotKind = std::integral_constant<int, K>;
 
+// Timeline tracing for tools/micro/ring_trace.cu (compile with -DLLIE_RING_TRACE; never in the product build)
+#ifdef LLIE_RING_TRACE
+__device__ unsigned long long g_ring_trace[1024 * 16];
+__device__ __forceinline__ void ring_stamp(int k) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if (blockIdx.x < 1024) g_ring_trace[blockIdx.x * 16 + k] = t;
+}
+#define RING_STAMP(cond, k) do { if (cond) ring_stamp(k); } while (0)
+#else
+#define RING_STAMP(cond, k) do { } while (0)
+#endif
+
 struct RingGeom {
     int groups, chunks;  // column groups of 512 px, row chunks per plane (even split of H)
     int items, items_per_sample;
@@ -97,27 +110,79 @@ __device__ __forceinline__ int src_row(int r, int H, int mode) {
     return -1;
 }
 
+// Packed fp32 pairs (sm_100 FFMA2 / FMUL2: one issue slot for two IEEE fp32 operations; a pair whose halves are the
+// same register is encoded as a scalar broadcast operand, so broadcast weights cost nothing).
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t pack2(float lo, float hi) {
+    f2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f2_t v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+#ifndef LLIE_ROLL3_SCALAR
+__device__ __forceinline__ f2_t fma2(f2_t a, f2_t b, f2_t c) {
+    f2_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f2_t mul2(f2_t a, f2_t b) {
+    f2_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+#else  // A/B build (tools/micro): the same chains as scalar FFMA / FMUL
+__device__ __forceinline__ f2_t fma2(f2_t a, f2_t b, f2_t c) {
+    float al, ah, bl, bh, cl, ch;
+    unpack2(a, al, ah); unpack2(b, bl, bh); unpack2(c, cl, ch);
+    return pack2(fmaf(al, bl, cl), fmaf(ah, bh, ch));
+}
+__device__ __forceinline__ f2_t mul2(f2_t a, f2_t b) {
+    float al, ah, bl, bh;
+    unpack2(a, al, ah); unpack2(b, bl, bh);
+    return pack2(al * bl, ah * bh);
+}
+#endif
+
 // Rolling ("scatter") form of the 9-tap chain over NC output columns; r has NC + 2 entries (one
 // neighbour on each side).  When input row rho arrives it completes output row rho-1 (kernel row
 // 2), extends output row rho (kernel row 1) and opens output row rho+1 (kernel row 0).  The
 // summation order per output is row-0 taps, row-1 taps, row-2 taps, left to right.
+// Adjacent columns 2p, 2p + 1 share one packed accumulator (A[p], B[p] hold the pair).  The outer taps (dx = 0, 2) read
+// the register-aligned data pairs (r[2p], r[2p+1]) / (r[2p+2], r[2p+3]) and are one FFMA2 each; the middle tap's pair
+// (r[2p+1], r[2p+2]) straddles two aligned pairs, so it stays two scalar FFMAs on the halves of the accumulator (no
+// repacking moves).  Same operation order as the scalar chain: bit-identical, 4 issue slots per 6 multiply-adds.
+__device__ __forceinline__ f2_t mid_tap(float wq, float ra, float rb, f2_t acc) {
+    float lo, hi;
+    unpack2(acc, lo, hi);
+    lo = fmaf(wq, ra, lo);
+    hi = fmaf(wq, rb, hi);
+    return pack2(lo, hi);
+}
 template <int NC>
-__device__ __forceinline__ void roll3(const float (&r)[NC + 2], const float (&w)[9], float (&A)[NC], float (&B)[NC],
-                                      float (&out)[NC]) {
+__device__ __forceinline__ void roll3(const float (&r)[NC + 2], const float (&w)[9], f2_t (&A)[NC / 2],
+                                      f2_t (&B)[NC / 2], float (&out)[NC]) {
+    static_assert(NC % 2 == 0, "roll3 pairs columns");
+    constexpr int HP = NC / 2;
+    f2_t ev[HP + 1];  // (r0,r1) (r2,r3) ...
 #pragma unroll
-    for (int i = 0; i < NC; ++i) {
-        float o = fmaf(w[6], r[i], A[i]);
-        o = fmaf(w[7], r[i + 1], o);
-        o = fmaf(w[8], r[i + 2], o);
-        out[i] = o;
-        float t = fmaf(w[3], r[i], B[i]);
-        t = fmaf(w[4], r[i + 1], t);
-        t = fmaf(w[5], r[i + 2], t);
-        A[i] = t;
-        float u = w[0] * r[i];
-        u = fmaf(w[1], r[i + 1], u);
-        u = fmaf(w[2], r[i + 2], u);
-        B[i] = u;
+    for (int p = 0; p <= HP; ++p) ev[p] = pack2(r[2 * p], r[2 * p + 1]);
+#pragma unroll
+    for (int p = 0; p < HP; ++p) {
+        const float ra = r[2 * p + 1], rb = r[2 * p + 2];
+        f2_t o = fma2(pack2(w[6], w[6]), ev[p], A[p]);
+        o = mid_tap(w[7], ra, rb, o);
+        o = fma2(pack2(w[8], w[8]), ev[p + 1], o);
+        unpack2(o, out[2 * p], out[2 * p + 1]);
+        f2_t t = fma2(pack2(w[3], w[3]), ev[p], B[p]);
+        t = mid_tap(w[4], ra, rb, t);
+        t = fma2(pack2(w[5], w[5]), ev[p + 1], t);
+        A[p] = t;
+        f2_t u = mul2(pack2(w[0], w[0]), ev[p]);
+        u = mid_tap(w[1], ra, rb, u);
+        u = fma2(pack2(w[2], w[2]), ev[p + 1], u);
+        B[p] = u;
     }
 }
 
@@ -135,12 +200,25 @@ struct RingState {
     }
 };
 
-// common prologue: zero the ring (stale words are read by masked lanes / rows and must be finite),
-// the zero row and the zero words; init the barriers
-__device__ __forceinline__ void ring_setup(float *ring, uint64_t *full, uint64_t *empty) {
+// common prologue: init the barriers and zero what the consumers may read without a TMA write: the zero row, the
+// zero words and the 4-column halos of every row segment (never written in the first / last strip of a plane).
+// Strips that the image only partly covers (W % kCols != 0) have idle lanes reading unwritten columns: those launches
+// zero the whole ring (stale words must be finite, they meet 0-weights).
+__device__ __forceinline__ void ring_setup(float *ring, uint64_t *full, uint64_t *empty, bool zero_all) {
     float4 *r4 = reinterpret_cast<float4 *>(ring);
-    const int n4 = (int)(kRingSmem / 16);
-    for (int i = threadIdx.x; i < n4; i += kRingThreads) r4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (zero_all) {
+        const int n4 = (int)(kRingSmem / 16);
+        for (int i = threadIdx.x; i < n4; i += kRingThreads) r4[i] = z;
+    } else {
+        constexpr int kSegs = kSlots * kG * 2, kRow4 = kRowF / 4;
+        for (int i = threadIdx.x; i < kSegs * 3; i += kRingThreads) {
+            const int seg = i / 3, part = i - seg * 3;
+            r4[seg * kRow4 + (part == 0 ? 0 : (part == 1 ? kRowD / 4 - 1 : kRowD / 4))] = z;
+        }
+        for (int i = threadIdx.x; i < kRow4; i += kRingThreads) r4[kSegs * kRow4 + i] = z;  // the zero row
+    }
+    RING_STAMP(threadIdx.x == 0, 8);
     if (threadIdx.x == 0) {
         for (int s = 0; s < kSlots; ++s) {
             mbar_init(&full[s], 1);
@@ -148,6 +226,7 @@ __device__ __forceinline__ void ring_setup(float *ring, uint64_t *full, uint64_t
         }
         mbar_fence_init();
     }
+    RING_STAMP(threadIdx.x == 0, 9);
     fence_proxy_async();  // generic-proxy zero fill before the async-proxy (TMA) writes
     __syncthreads();
 }
@@ -191,35 +270,58 @@ __device__ __forceinline__ bool ring_last_block(unsigned *ticket, unsigned total
     return s_last;
 }
 
-// last CTA: fixed-order per-sample sums of the per-item partials.  Many samples: one warp per sample
-// (samples in flight together); few samples: the whole CTA per sample with 8 loads in flight per
-// thread.  Either way the summation order only depends on the launch geometry.
-__device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, double *red_d) {
+// last CTA: fixed-order per-sample sums of the per-item partials.  The partials (and flags) are fetched with ALL
+// loads of a thread in flight together - one L2 round trip instead of one per 32 partials - and staged in the (now
+// idle) ring shared memory; the per-sample sums then read shared memory, one warp per sample.  The summation order
+// only depends on the launch geometry.
+constexpr int kStageMax = (int)(kRingSmem / sizeof(double));
+__device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, double *red_d, double *stage) {
     constexpr int kSmemSamples = 64;
     __shared__ double s_samp[kSmemSamples];
     const int N = a.d.n;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int NT = blockDim.x;
     const int per = g.items_per_sample;
     double *samp = N <= kSmemSamples ? s_samp : g.samp;
-    int fl = 0;  // flag loads go first so that they overlap the partial-sum loads
-    for (int b = threadIdx.x; b < (int)gridDim.x; b += blockDim.x) fl |= __ldcg(g.pflag + b);
-    if (N >= nw) {
+    int fl = 0;
+    {
+        int fv[4];
+        for (int b0 = threadIdx.x; b0 < (int)gridDim.x; b0 += 4 * NT) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) fv[k] = b0 + k * NT < (int)gridDim.x ? __ldcg(g.pflag + b0 + k * NT) : 0;
+            fl |= (fv[0] | fv[1]) | (fv[2] | fv[3]);
+        }
+    }
+    const bool staged = g.items <= kStageMax;
+    if (staged) {
+        for (int b0 = threadIdx.x; b0 < g.items; b0 += 8 * NT) {
+            double v[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = b0 + k * NT < g.items ? __ldcg(g.part + b0 + k * NT) : 0.0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (b0 + k * NT < g.items) stage[b0 + k * NT] = v[k];
+        }
+        __syncthreads();
+    }
+    RING_STAMP(threadIdx.x == 0, 10);
+    const double *src = staged ? stage : g.part;
+    if (staged || N >= nw) {
         for (int n = wrp; n < N; n += nw) {
-            const double *p = g.part + (size_t)n * per;
+            const double *p = src + (size_t)n * per;
             double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
             int b = lane;
             for (; b + 96 < per; b += 128) {
-                s0 += __ldcg(p + b);
-                s1 += __ldcg(p + b + 32);
-                s2 += __ldcg(p + b + 64);
-                s3 += __ldcg(p + b + 96);
+                s0 += p[b];
+                s1 += p[b + 32];
+                s2 += p[b + 64];
+                s3 += p[b + 96];
             }
-            for (; b < per; b += 32) s0 += __ldcg(p + b);
+            for (; b < per; b += 32) s0 += p[b];
             const double s = warp_sum((s0 + s1) + (s2 + s3));
             if (lane == 0) samp[n] = s;
         }
     } else {
-        const int NT = blockDim.x;
         for (int n = 0; n < N; ++n) {
             const double *p = g.part + (size_t)n * per;
             double acc[8];
@@ -237,6 +339,7 @@ __device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, 
         }
     }
     const int ff = block_or(fl, red_i);  // contains the __syncthreads that publishes samp[]
+    RING_STAMP(threadIdx.x == 0, 11);
     if (threadIdx.x == 0) {
         double batch = 0.0, total = 0.0;
         int f = ff;
@@ -281,7 +384,9 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
     const llie_phys_desc &d = a.d;
     const int H = d.h, W = d.w, mode = d.pad_mode;
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
-    ring_setup(ring, full, empty);
+    pdl_launch_dependents();  // the next kernel's CTAs may run their prologue while this grid drains
+    ring_setup(ring, full, empty, (W % kCols) != 0);
+    pdl_wait();  // nothing before this line reads or writes global memory
     int iter = 0;
 
     float chk_p = 0.f, chk_o = 0.f;  // x*0 accumulators: NaN iff a non-finite value went through a clip
@@ -330,7 +435,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
             for (int i = 0; i < 4; ++i) cm[i] = (active && xr + i >= a.x_lo && xr + i < a.x_lo + a.wo) ? 1.f : 0.f;
             const bool map_on = a.out_map != nullptr && active;
             const bool map_vec = (a.wo & 3) == 0 && a.x_lo == 0;
-            float sA[4] = {0.f, 0.f, 0.f, 0.f}, sB[4] = {0.f, 0.f, 0.f, 0.f};
+            f2_t sA[2] = {0ull, 0ull}, sB[2] = {0ull, 0ull};  // packed rolling sums (columns 0|1, 2|3)
             float acc = 0.f;
             const int E = it.yb - it.ya + 2;
             // one slot = kG entries.  GENERAL handles partial slots, zero-padding rows and cropped rows; the
@@ -354,7 +459,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
                     }
                     const float4 v = reinterpret_cast<const float4 *>(pz)[tid + 1];
                     const float r6[6] = {pz[lidx], v.x, v.y, v.z, v.w, pz[ridx]};
-                    const float4 ob = reinterpret_cast<const float4 *>(rowp + kRowF)[tid + 1];
+                    const float *so = (GENERAL && e < 2) ? zrow : rowp + kRowF;  // no obs row travels with warm-up entries
+                    const float4 ob = reinterpret_cast<const float4 *>(so)[tid + 1];
                     float cv[4];
                     roll3<4>(r6, w, sA, sB, cv);
                     if (WARM && u < 2) continue;  // compile-time after unrolling: cv and the obs row are dead
@@ -424,7 +530,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
     if (!(chk_o == 0.f)) flag |= 2;
     const int f = block_or(flag, red_i);
     if (tid == 0) g.pflag[blockIdx.x] = f;
-    if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i, red_d);
+    if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i, red_d, reinterpret_cast<double *>(smraw));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -453,7 +559,12 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
     const bool fold = mode != LLIE_PAD_ZEROS;
     const int fold_top = mode == LLIE_PAD_REFLECT ? 1 : 0;          // image row that padded row -1 reads
     const int fold_bot = mode == LLIE_PAD_REFLECT ? H - 2 : H - 1;  // image row that padded row H reads
-    ring_setup(ring, full, empty);
+    RING_STAMP(threadIdx.x == 0, 0);
+    pdl_launch_dependents();
+    ring_setup(ring, full, empty, (W % kCols) != 0);
+    RING_STAMP(threadIdx.x == 0, 1);
+    pdl_wait();  // nothing before this line reads or writes global memory
+    RING_STAMP(threadIdx.x == 0, 2);
     RingState rs{0, 0u};
 
     if (wrp == kCons / 32) {
@@ -517,10 +628,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         const int tgt = is_left ? (mode == LLIE_PAD_REFLECT ? 1 : 0) : (mode == LLIE_PAD_REFLECT ? 2 : 3);
         const bool edge_fold = fold && (is_left || is_right);
 
-        float cA[6], cB[6];
-#pragma unroll
-        for (int i = 0; i < 6; ++i) cA[i] = cB[i] = 0.f;
-        float gA[4] = {0.f, 0.f, 0.f, 0.f}, gB[4] = {0.f, 0.f, 0.f, 0.f};
+        f2_t cA[3] = {0ull, 0ull, 0ull}, cB[3] = {0ull, 0ull, 0ull};  // packed rolling sums (columns 0|1, 2|3, 4|5)
+        f2_t gA[2] = {0ull, 0ull}, gB[2] = {0ull, 0ull};
         float eA = 0.f, eB = 0.f;  // partial sums of the folded padded column (image-edge lanes only)
         float carry[4] = {0.f, 0.f, 0.f, 0.f};
         const int E = jb - ja + 4;
@@ -546,7 +655,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                 }
                 const float4 v = reinterpret_cast<const float4 *>(pz)[tid + 1];
                 const float r8[8] = {pz[4 * tid + 2], pz[lidx], v.x, v.y, v.z, v.w, pz[ridx], pz[4 * tid + 9]};
-                const float *so = rowp + kRowF;
+                const float *so = (GENERAL && rowm == 0.f) ? zrow : rowp + kRowF;  // obs travels with compared rows only
                 const float4 ob = reinterpret_cast<const float4 *>(so)[tid + 1];
                 const float av[6] = {so[4 * tid + 3], ob.x, ob.y, ob.z, ob.w, so[4 * tid + 8]};
                 float cv[6];
@@ -637,6 +746,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         for (int kb = 0; kb < E; kb += kG) {
             const float *sp = ring + rs.slot * kSlotF;
             mbar_wait(&full[rs.slot], rs.phase);
+            RING_STAMP(tid == 0 && kb == 0 && item == (int)blockIdx.x, 3);
             if (kb >= k_lo && kb + kG <= k_hi)
                 do_slot(SlotKind<kSlotInterior>{}, kb, sp);
             else if (kb == 0 && warm_ok)
@@ -647,6 +757,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
             if (lane == 0) mbar_arrive(&empty[rs.slot]);
             rs.advance();
         }
+        RING_STAMP(tid == 0, 4);
         if (FUSED) {
             const double ws = warp_sum((double)lacc);
             double *rw = red_w + (iter & 1) * 4;
@@ -662,7 +773,11 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         if (!(chk_o == 0.f)) flag |= 2;
         const int f = block_or(flag, red_i);
         if (tid == 0) g.pflag[blockIdx.x] = f;
-        if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i, red_d);
+        RING_STAMP(tid == 0, 5);
+        const bool last = ring_last_block(a.ticket, gridDim.x);
+        RING_STAMP(tid == 0, 6);
+        if (last) ring_finalize(a, g, red_i, red_d, reinterpret_cast<double *>(smraw));
+        RING_STAMP(tid == 0 && last, 7);
     }
 }
 
@@ -671,6 +786,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
 // ------------------------------------------------------------------------------------------------
 static int g_ring_rows = 0;  // 0 = heuristic; set through llie_tune(LLIE_TUNE_PHYS_ROWS, r)
 void phys_ring_set_rows(int r) { g_ring_rows = r; }
+static int g_ring_pdl = 1;   // programmatic dependent launch of the ring kernels (llie_tune(LLIE_TUNE_PHYS_PDL, 0|1))
+void phys_ring_set_pdl(int on) { g_ring_pdl = on ? 1 : 0; }
 
 static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     RingGeom g{};
@@ -717,7 +834,17 @@ bool phys_ring_eligible(const PhysArgs &a) {
     do {                                                                                                         \
         auto kern = K;                                                                                           \
         LLIE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRingSmem));   \
-        kern<<<GRID, kRingThreads, kRingSmem, ST>>>(__VA_ARGS__);                                                \
+        cudaLaunchConfig_t cfg = {};                                                                             \
+        cfg.gridDim = dim3(GRID);                                                                                \
+        cfg.blockDim = dim3(kRingThreads);                                                                       \
+        cfg.dynamicSmemBytes = kRingSmem;                                                                        \
+        cfg.stream = ST;                                                                                         \
+        cudaLaunchAttribute attr[1];                                                                             \
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                         \
+        attr[0].val.programmaticStreamSerializationAllowed = g_ring_pdl;                                         \
+        cfg.attrs = attr;                                                                                        \
+        cfg.numAttrs = 1;                                                                                        \
+        LLIE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, __VA_ARGS__));                                               \
     } while (0)
 #define LLIE_RING_DISPATCH(KERNEL, d, GRID, ST, ...)                                               \
     do {                                                                                           \
@@ -783,5 +910,11 @@ int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st) {
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
+
+#ifdef LLIE_RING_TRACE
+extern "C" int llie_debug_ring_trace(unsigned long long *host_dst) {
+    return (int)cudaMemcpyFromSymbol(host_dst, g_ring_trace, sizeof(unsigned long long) * 1024 * 16);
+}
+#endif
 
 }  // namespace llie

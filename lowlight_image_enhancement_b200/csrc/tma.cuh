@@ -83,6 +83,12 @@ __device__ __forceinline__ void tma_load_3d(void *smem_dst, const CUtensorMap *m
         "l"(map), "r"(smem_u32(bar)), "r"(x), "r"(y), "r"(z)
         : "memory");
 }
+// Programmatic dependent launch (PDL): `pdl_launch_dependents` lets the NEXT kernel in the stream start its CTAs
+// (prologue only) as this grid's CTAs retire; `pdl_wait` blocks until every prerequisite grid has completed and its
+// memory is visible.  Both are no-ops when the kernel was launched without the programmatic attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap *map) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
