@@ -231,6 +231,17 @@ def run_ours(args, rank, world, dev):
     # forward + backward kernels instead (same outputs, 20 instead of 12 bytes per element).
     step = step2 if args.two_pass else fused
     K, W = args.steps, max(3, args.warmup)
+    # serialised reference timing first (every launch waits for the previous grid before its first global access);
+    # the `early` flag is a kernel argument, so it is frozen into a graph at capture time
+    g_su = GraphLoop(fused, K, dev)
+    g_su.run()
+    t_u_serial = min(g_su.run() for _ in range(3)) / K
+    del g_su
+    overlap = not (args.no_overlap or args.no_pdl)
+    if overlap:
+        # the K steps read / write 8 rotating, disjoint buffer sets: exactly the stream-overlap contract of
+        # LLIE_TUNE_PHYS_OVERLAP (include/llie_b200.h) -- consecutive launches only share the workspace
+        Fn.phys_stream_overlap(True)
     g_step, g_f, g_b = GraphLoop(step, K, dev), GraphLoop(fwd, K, dev), GraphLoop(bwd, K, dev)
     g_2 = GraphLoop(step2, K, dev)
     g_u = GraphLoop(fused, K, dev)
@@ -248,6 +259,7 @@ def run_ours(args, rank, world, dev):
         ms = g_step.run()
         time.sleep(0.25)  # let the sampler see the clocks right after the (sub-ms .. ms) timed region
     launches = (2 if args.two_pass else 1) * K  # kernels per step, replayed from the captured graph
+    Fn.phys_stream_overlap(False)  # the e2e leg below runs under autograd: default (serialised) launches
     del l0
     if world > 1:
         t = torch.tensor([ms], device=dev)
@@ -300,13 +312,20 @@ def run_ours(args, rank, world, dev):
                             "loss value + gradient from one fused launch (llie_phys_value_and_grad); "
                             f"two-pass forward + backward = {round(t_2 * 1e3, 2)} us per step"),
                    "l2": f"inputs rotate over {POOL} resident buffer sets (604 MB per GPU) > 126 MB L2",
-                   "launch": f"steps captured in CUDA graphs of {K // g_step.replays} steps, replayed {g_step.replays}x",
+                   "launch": f"steps captured in CUDA graphs of {K // g_step.replays} steps, replayed {g_step.replays}x; "
+                             + ("programmatic dependent launch with the stream-overlap contract (LLIE_TUNE_PHYS_OVERLAP: "
+                                "consecutive steps touch disjoint buffer sets, so a launch waits for the previous grid "
+                                "only before it touches the shared workspace); "
+                                f"fully serialised launches: {round(t_u_serial * 1e3, 2)} us per fused launch"
+                                if overlap else "serialised launches"),
                    "per_gpu_batch": list(SHAPE)},
         "roofline": {"bound": "hbm", "kernel": roof["kernel"], "achieved": round(roof["achieved"], 1), "peak": peak,
                      "unit": "GB/s", "frac": round(roof["achieved"] / peak, 4),
                      "traffic": TRAFFIC.get("phys_bwd_ring" if args.two_pass else "phys_fused_ring"),
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_b,
-                     "us_per_launch": round(roof["us"] * 1e3, 2)},
+                     "us_per_launch": round(roof["us"] * 1e3, 2),
+                     "us_per_launch_serialised": round(t_u_serial * 1e3, 2),
+                     "frac_serialised": round(bytes_b / (t_u_serial * 1e-3) / 1e9 / peak, 4)},
         "kernels": [
             {"kernel": "phys_fwd_ring", "us": round(t_f * 1e3, 2), "algorithmic_bytes": bytes_f,
              "achieved_gbs": round(ach_f, 1), "frac": round(ach_f / peak, 4), "traffic": TRAFFIC.get("phys_fwd_ring")},
@@ -430,6 +449,51 @@ def run_extra(args, rank, world, dev):
     del pool, pr, gt
     torch.cuda.empty_cache()
 
+    # ---- decode / normalise step in front of the path: SID-sized 16-bit frames -> planar fp32,
+    # and the linear -> sRGB (+ LPIPS range) map of the evaluation helpers.  HBM-bound streaming kernels.
+    from lowlight_image_enhancement_b200.metrics.evaluation import srgb_and_lpips_inputs
+    h_, w_ = EVAL_SHAPE[2], EVAL_SHAPE[3]
+    gi = torch.Generator(device=dev).manual_seed(5000 + rank)
+    frames = [(torch.randint(0, 65536, (1, h_, w_, 3), generator=gi, dtype=torch.int32, device=dev) // 64).to(torch.uint16)
+              for _ in range(3)]                                                        # 3 x 72.7 MB in, 291 MB out each
+    lin = [torch.rand(EVAL_SHAPE, device=dev, generator=gi) for _ in range(3)]
+    el = 3 * px
+    for _ in range(2):  # warm-up (allocator + first launch)
+        Fn.decode_u16(frames[0], 100.0), Fn.decode_u16(frames[0], 1.0, want_aligned=False), srgb_and_lpips_inputs(lin[0])
+    t_dec = timed(lambda i: Fn.decode_u16(frames[i % 3], 100.0), 9, dev) / 9
+    t_dec1 = timed(lambda i: Fn.decode_u16(frames[i % 3], 1.0, want_aligned=False), 9, dev) / 9
+    t_srgb = timed(lambda i: srgb_and_lpips_inputs(lin[i % 3]), 9, dev) / 9
+
+    def kern_b(name, t, bpe):
+        return {"kernel": name, "ms": round(t, 4), "Mpix/s": round(px / t / 1e3, 1), "algorithmic_bytes": bpe * el,
+                "achieved_gbs": round(bpe * el / t / 1e6, 1), "frac_hbm": round(bpe * el / t / 1e6 / peak, 4),
+                "bound": "hbm"}
+    out["ingest_c4"] = {
+        "workload": "decode of one 2848x4256x3 uint16 frame to planar fp32 (raw + exposure-aligned / raw only) and "
+                    "linear -> sRGB + LPIPS-range map of one 1x3x2848x4256 image; outputs allocated per call",
+        "kernels": [kern_b("decode_u16_c3_kernel (raw + aligned)", t_dec, 10),
+                    kern_b("decode_u16_c3_kernel (raw)", t_dec1, 6),
+                    kern_b("linear_to_srgb_kernel (srgb + lpips)", t_srgb, 12)],
+    }
+    if world == 1 and not args.skip_cpu:
+        from oracle import ingest as oing
+        torch.set_num_threads(os.cpu_count() or 1)
+        f_np = frames[0][0].cpu().numpy()
+        x_cpu = lin[0].cpu()
+        t0 = time.perf_counter()
+        oing.decode_pair(f_np, f_np, 100.0)
+        dt_d = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        oing.norm_to_lpips_range(oing.linear_to_srgb(x_cpu))
+        dt_s = time.perf_counter() - t0
+        out["ingest_c4"]["cpu_baseline"] = {
+            "decode_pair_Mpix/s": round(2 * px / 1e6 / dt_d, 2), "linear_to_srgb_Mpix/s": round(px / 1e6 / dt_s, 2),
+            "unit": "Mpix/s", "cores": os.cpu_count(), "kind": "port",
+            "sample": f"one short + long frame decode ({dt_d:.2f} s, numpy is single-threaded) and one sRGB map ({dt_s:.2f} s)"}
+        del f_np, x_cpu
+    del frames, lin
+    torch.cuda.empty_cache()
+
     # ---- hybrid loss, C3: L1 + 0.05 DSSIM + 0.02 dE00 + 0.05 phys (stressed rgb kernel, RAW convention)
     n = 16
     g = torch.Generator(device=dev).manual_seed(103 + rank)
@@ -485,6 +549,7 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: no cpu_baseline leg")
     ap.add_argument("--skip-extra", action="store_true", help="profiling runs: no eval_c4 / hybrid_c3 sections")
     ap.add_argument("--two-pass", action="store_true", help="time separate forward + backward kernels per step")
+    ap.add_argument("--no-overlap", action="store_true", help="A/B: every launch waits for the previous grid at its top")
     ap.add_argument("--no-pdl", action="store_true", help="A/B: plain launches instead of programmatic dependent launch")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)

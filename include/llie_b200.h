@@ -60,6 +60,14 @@ int llie_check_device(void);
 #define LLIE_TUNE_SSIM_SEG_ROWS 4 /* output rows per CTA of the streaming SSIM kernel; 0 = heuristic */
 #define LLIE_TUNE_PHYS_PDL 5 /* 1 (default): ring kernels are launched with programmatic stream serialization, so the
                                 prologue of a kernel overlaps the tail of the previous one | 0 plain launches */
+#define LLIE_TUNE_PHYS_OVERLAP 6 /* 0 (default) | 1: stream-overlap CONTRACT for loops of phys calls over independent
+                                    batches (dataset evaluation, benchmarks): the caller guarantees that the kernel
+                                    launched right before a phys call on the same stream writes none of the call's
+                                    buffers pred, obs, psf, rho, gout, grad, map and reads none of grad / map (the small
+                                    outputs out_mean / out_sum / out_flags are written after the wait and may be shared).  The ring kernels then wait for
+                                    the previous grid only before they touch the shared workspace, so launch i + 1 streams
+                                    and computes on the SMs the early finishers of launch i have left.  Never set it under
+                                    autograd (gout comes from the previous kernel). */
 int llie_tune(int key, int value);
 
 /* ------------------------------------------------------------------------
@@ -269,6 +277,31 @@ int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y, const flo
  * replaces NAFNet_base/basicsr/models/image_restoration_model.py:215-241 (grids_inverse, done on the host there). */
 int llie_tile_merge(const float *tiles, const int32_t *tile_ij, int32_t n_tiles, int32_t c, int32_t tile_h,
                     int32_t tile_w, int32_t h, int32_t w, float *out, void *stream);
+
+/* ------------------------------------------------------------------------
+ * Input decode / normalise step in front of the path.
+ * src is the decoded 16-bit PNG, interleaved [n, h, w, c] uint16 on the device; outputs are planar float32
+ * [n, c, crop_h, crop_w] (either may be NULL):
+ *   out_raw     = float32(u) / 65535                      (one IEEE division)
+ *   out_aligned = clip(out_raw * rho, 0, 1)               (rho: [n] device floats, or rho_scalar when NULL)
+ * bit-exact with the host arithmetic it replaces: NAFNet_base/basicsr/data/sony_sid_lmdb_dataset.py:208-212
+ * (astype(float32) / MAX_16BIT_VALUE, np.clip(short_raw * expo_ratio, 0, 1)), :161-194 (crop window),
+ * :57 (cv2 BGR -> RGB, swap_rb = 1) and basicsr/utils/img_util.py:28-34 (HWC -> CHW float tensor).
+ * ------------------------------------------------------------------------ */
+typedef struct llie_decode_desc {
+    int32_t n, h, w, c;          /* source images */
+    int32_t top, left;           /* crop window origin inside the source */
+    int32_t crop_h, crop_w;      /* output size (== h, w for no crop) */
+    int32_t swap_rb;             /* 1: output channel k reads source channel 2 - k (c >= 3, first three channels) */
+} llie_decode_desc;
+int llie_decode_u16(const llie_decode_desc *desc, const uint16_t *src, const float *rho, float rho_scalar,
+                    float *out_raw, float *out_aligned, void *stream);
+
+/* linear RGB -> sRGB (IEC 61966-2-1) of the evaluation helpers, NaN-propagating like torch.clamp / torch.where:
+ *   s = where(x' <= 0.0031308, 12.92 x', 1.055 max(x', 0.0031308)^(1/2.4) - 0.055),  x' = clamp(x, 0, 1)
+ * out_srgb = s, out_lpips = 2 s - 1 (either may be NULL; both from one read of x).
+ * replaces metrics/evaluation.py:27-38 (_linear_to_srgb) and :50-52 (_norm_to_lpips_range). */
+int llie_linear_to_srgb(const float *x, int64_t n, float *out_srgb, float *out_lpips, void *stream);
 
 /* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the
  * < 1 ulp claim can be checked against a float64 pow from the test-suite. */

@@ -220,6 +220,12 @@ def phys_value_and_grad(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_
     return buf[: n + 2], flags, grad
 
 
+def phys_stream_overlap(enabled: bool) -> None:
+    """Process-wide stream-overlap contract of the phys ring kernels (LLIE_TUNE_PHYS_OVERLAP, include/llie_b200.h):
+    enable only around loops of phys calls over independent buffers, never under autograd."""
+    nat.check(nat.lib().llie_tune(6, 1 if enabled else 0), "llie_tune")
+
+
 class PhysProjector(torch.autograd.Function):
     """vec[N+2] = (per-sample means, batch mean, batch sum) of the loss map; differentiable in pred."""
 
@@ -423,6 +429,59 @@ def sobel_magnitude(l_planes: Tensor) -> Tensor:
     nat.check(rc, "llie_sobel_magnitude")
     nat.count_launch()
     return out
+
+
+def decode_u16(src: Tensor, rho, *, crop=None, swap_rb: bool = False, want_raw: bool = True,
+               want_aligned: bool = True) -> Tuple[Optional[Tensor], Optional[Tensor]]:
+    """[N, H, W, C] (or [H, W, C]) uint16 CUDA -> planar float32 ``(raw, aligned)`` of shape [N, C, h, w]:
+    raw = u / 65535, aligned = clip(raw * rho, 0, 1).  ``rho``: float or [N] tensor; ``crop`` = (top, left, h, w)."""
+    if src.dtype != torch.uint16:
+        raise TypeError(f"decode_u16 expects a uint16 tensor, got {src.dtype}")
+    if src.dim() == 3:
+        src = src.unsqueeze(0)
+    if src.dim() != 4:
+        raise ValueError(f"decode_u16 expects [N, H, W, C] or [H, W, C], got {tuple(src.shape)}")
+    dev = nat.cuda_device_for(src)
+    nat.ensure_device(dev)
+    src = nat.stage(src, dev)
+    n, h, w, c = src.shape
+    top, left, ch, cw = (0, 0, h, w) if crop is None else (int(v) for v in crop)
+    if ch < 1 or cw < 1 or top < 0 or left < 0 or top + ch > h or left + cw > w:
+        raise ValueError(f"crop window {(top, left, ch, cw)} outside the {h}x{w} source")
+    rho_t, rho_s = None, 1.0
+    if torch.is_tensor(rho):
+        rho_t = nat.stage(rho.reshape(-1), dev, torch.float32)
+        if rho_t.numel() == 1 and n != 1:
+            rho_t = rho_t.expand(n).contiguous()
+        if rho_t.numel() != n:
+            raise ValueError(f"rho has {rho_t.numel()} entries for {n} images")
+    else:
+        rho_s = float(rho)
+    raw = torch.empty((n, c, ch, cw), dtype=torch.float32, device=dev) if want_raw else None
+    ali = torch.empty((n, c, ch, cw), dtype=torch.float32, device=dev) if want_aligned else None
+    d = nat.DecodeDesc(n, h, w, c, top, left, ch, cw, 1 if swap_rb else 0)
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_decode_u16(d, nat.ptr(src), nat.ptr(rho_t), rho_s, nat.ptr(raw), nat.ptr(ali),
+                                       nat.stream_ptr(dev))
+    nat.check(rc, "llie_decode_u16")
+    nat.count_launch()
+    return raw, ali
+
+
+def linear_to_srgb(x: Tensor, *, want_srgb: bool = True, want_lpips: bool = False
+                   ) -> Tuple[Optional[Tensor], Optional[Tensor]]:
+    """fp32 CUDA tensor -> ``(srgb, 2 * srgb - 1)`` from one read of ``x`` (either output optional)."""
+    dev = nat.cuda_device_for(x)
+    nat.ensure_device(dev)
+    x = nat.stage(x, dev, torch.float32)
+    srgb = torch.empty_like(x) if want_srgb else None
+    lp = torch.empty_like(x) if want_lpips else None
+    if x.numel():
+        with torch.cuda.device(dev):
+            rc = nat.lib().llie_linear_to_srgb(nat.ptr(x), x.numel(), nat.ptr(srgb), nat.ptr(lp), nat.stream_ptr(dev))
+        nat.check(rc, "llie_linear_to_srgb")
+        nat.count_launch()
+    return srgb, lp
 
 
 _sel_ws: dict = {}

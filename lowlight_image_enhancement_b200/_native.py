@@ -59,6 +59,11 @@ class DeltaEDesc(C.Structure):
                [(k, C.c_float) for k in ("kL", "kC", "kH", "eps")]
 
 
+class DecodeDesc(C.Structure):
+    _fields_ = [("n", C.c_int32), ("h", C.c_int32), ("w", C.c_int32), ("c", C.c_int32), ("top", C.c_int32),
+                ("left", C.c_int32), ("crop_h", C.c_int32), ("crop_w", C.c_int32), ("swap_rb", C.c_int32)]
+
+
 class SelectDesc(C.Structure):
     _fields_ = [("images", C.c_int32), ("per_image", C.c_int64), ("nq", C.c_int32), ("joint", C.c_int32)]
 
@@ -93,6 +98,8 @@ _SIGNATURES = {
     "llie_pixel_loss_grad": (C.c_int, [C.c_int32, _VP, _VP, _VP, C.c_int32, _VP, C.c_int32, C.c_int32, C.c_int64, C.c_float,
                                        C.c_float, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
     "llie_tile_merge": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _VP, _VP]),
+    "llie_decode_u16": (C.c_int, [C.POINTER(DecodeDesc), _VP, _VP, C.c_float, _VP, _VP, _VP]),
+    "llie_linear_to_srgb": (C.c_int, [_VP, C.c_int64, _VP, _VP, _VP]),
     "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),
     "llie_select_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
@@ -158,16 +165,21 @@ _ws_cache: dict = {}
 _checked_devices: set = set()
 
 
+def ensure_device(dev: torch.device) -> None:
+    """Raise unless `dev` is a compute-capability 10.x device (checked once per device)."""
+    if dev.index not in _checked_devices:
+        with torch.cuda.device(dev):
+            check(lib().llie_check_device(), "llie_check_device")
+        _checked_devices.add(dev.index)
+
+
 def workspace(dev: torch.device) -> torch.Tensor:
     """Zero-initialised, self-resetting scratch buffer per (device, stream)."""
     stream = torch.cuda.current_stream(dev)
     key = (dev.index, stream.cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None:
-        if dev.index not in _checked_devices:
-            with torch.cuda.device(dev):
-                check(lib().llie_check_device(), "llie_check_device")
-            _checked_devices.add(dev.index)
+        ensure_device(dev)
         ws = torch.zeros(lib().llie_workspace_bytes(), dtype=torch.uint8, device=dev)
         _ws_cache[key] = ws
     return ws

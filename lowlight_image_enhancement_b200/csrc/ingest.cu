@@ -1,0 +1,191 @@
+// Input decode / normalise step in front of the loss and metric path.
+//
+//   decode_u16   16-bit PNG samples (interleaved [n, h, w, c], as the image decoder leaves them) ->
+//                planar float32 raw = u / 65535 and aligned = clip(raw * rho, 0, 1), optional crop window and
+//                B<->R swap.  HBM-bound: 2 B read + 4 (or 8) B written per element.
+//   linear_to_srgb   IEC 61966-2-1 OETF of the evaluation helpers, with the LPIPS range map 2 s - 1 as an optional
+//                second output of the same pass.
+//
+// Both follow the host arithmetic of the reference operation by operation (one IEEE rounding per numpy / ATen
+// operation, no FMA contraction), so decode_u16 is bit-exact and linear_to_srgb differs from ATen only by the
+// rounding of x^(1/2.4) (here cbrt(x) * sqrt(sqrt(cbrt(x))), < 3 ulp).
+#include "common.cuh"
+
+namespace llie {
+
+constexpr int kDecThreads = 256;
+
+struct DecArgs {
+    llie_decode_desc d;
+    const uint16_t *src;
+    const float *rho;
+    float rho_scalar;
+    float *raw, *aligned;
+};
+
+__device__ __forceinline__ float dec_raw(unsigned u) { return __fdiv_rn((float)u, 65535.0f); }
+__device__ __forceinline__ float dec_aligned(float raw, float rho) {
+    return fminf(fmaxf(__fmul_rn(raw, rho), 0.f), 1.f);
+}
+
+// C == 3, crop width % 4 == 0: one thread = 4 pixels of a row = 12 samples (24 B in, 3 x 16 B out per plane set).
+// VEC: the 24 B are three aligned 8-byte loads; otherwise twelve 2-byte loads (same sectors, L1-coalesced).
+template <bool VEC>
+__global__ void __launch_bounds__(kDecThreads) decode_u16_c3_kernel(const DecArgs a) {
+    const llie_decode_desc &d = a.d;
+    const int quads = d.crop_w >> 2;
+    const long long total = (long long)d.n * d.crop_h * quads;
+    const long long plane = (long long)d.crop_h * d.crop_w;
+    for (long long t = (long long)blockIdx.x * kDecThreads + threadIdx.x; t < total;
+         t += (long long)gridDim.x * kDecThreads) {
+        const int qx = (int)(t % quads);
+        const long long r = t / quads;
+        const int y = (int)(r % d.crop_h), n = (int)(r / d.crop_h);
+        const uint16_t *sp = a.src + (((long long)n * d.h + d.top + y) * d.w + d.left + 4 * qx) * 3;
+        unsigned s[12];
+        if (VEC) {
+            const uint2 *sv = reinterpret_cast<const uint2 *>(sp);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const uint2 v = __ldg(sv + k);
+                s[4 * k] = v.x & 0xffffu;
+                s[4 * k + 1] = v.x >> 16;
+                s[4 * k + 2] = v.y & 0xffffu;
+                s[4 * k + 3] = v.y >> 16;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < 12; ++k) s[k] = __ldg(sp + k);
+        }
+        const float rho = a.rho != nullptr ? __ldg(a.rho + n) : a.rho_scalar;
+        const long long o = ((long long)n * 3) * plane + (long long)y * d.crop_w + 4 * qx;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const int sc = d.swap_rb ? 2 - c : c;
+            float v[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) v[p] = dec_raw(s[3 * p + sc]);
+            if (a.raw != nullptr) __stcs(reinterpret_cast<float4 *>(a.raw + o + c * plane), make_float4(v[0], v[1], v[2], v[3]));
+            if (a.aligned != nullptr)
+                __stcs(reinterpret_cast<float4 *>(a.aligned + o + c * plane),
+                       make_float4(dec_aligned(v[0], rho), dec_aligned(v[1], rho), dec_aligned(v[2], rho),
+                                   dec_aligned(v[3], rho)));
+        }
+    }
+}
+
+// any channel count / width: one thread per output element (planar order, coalesced stores)
+__global__ void __launch_bounds__(kDecThreads) decode_u16_generic_kernel(const DecArgs a) {
+    const llie_decode_desc &d = a.d;
+    const long long plane = (long long)d.crop_h * d.crop_w;
+    const long long total = (long long)d.n * d.c * plane;
+    for (long long t = (long long)blockIdx.x * kDecThreads + threadIdx.x; t < total;
+         t += (long long)gridDim.x * kDecThreads) {
+        const int x = (int)(t % d.crop_w);
+        long long r = t / d.crop_w;
+        const int y = (int)(r % d.crop_h);
+        r /= d.crop_h;
+        const int c = (int)(r % d.c), n = (int)(r / d.c);
+        const int sc = (d.swap_rb && d.c >= 3 && c < 3) ? 2 - c : c;
+        const unsigned u = __ldg(a.src + (((long long)n * d.h + d.top + y) * d.w + d.left + x) * d.c + sc);
+        const float v = dec_raw(u);
+        if (a.raw != nullptr) a.raw[t] = v;
+        if (a.aligned != nullptr) a.aligned[t] = dec_aligned(v, a.rho != nullptr ? __ldg(a.rho + n) : a.rho_scalar);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// x -> where(x <= 0.0031308, 12.92 x, 1.055 * max(x, 0.0031308)^(1/2.4) - 0.055) after clamp(x, 0, 1);
+// NaN propagates as in torch.clamp / torch.where.
+__device__ __forceinline__ float srgb_oetf(float x) {
+    if (x != x) return x;
+    x = fminf(fmaxf(x, 0.f), 1.f);
+    const float xt = fmaxf(x, 0.0031308f);
+    const float t = cbrtf(xt);                     // x^(1/3)
+    const float p = __fmul_rn(t, sqrtf(sqrtf(t)));  // x^(1/3) * x^(1/12) = x^(5/12)
+    const float high = __fsub_rn(__fmul_rn(1.055f, p), 0.055f);
+    return x <= 0.0031308f ? __fmul_rn(12.92f, x) : high;
+}
+
+__global__ void __launch_bounds__(256) linear_to_srgb_kernel(const float *__restrict__ x, long long n,
+                                                             float *__restrict__ out_srgb,
+                                                             float *__restrict__ out_lpips, bool vec) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long t0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (vec) {
+        const long long n4 = n >> 2;
+        for (long long i = t0; i < n4; i += stride) {
+            const float4 v = ldg_stream4(x + 4 * i);
+            const float4 s = make_float4(srgb_oetf(v.x), srgb_oetf(v.y), srgb_oetf(v.z), srgb_oetf(v.w));
+            if (out_srgb != nullptr) __stcs(reinterpret_cast<float4 *>(out_srgb) + i, s);
+            if (out_lpips != nullptr)
+                __stcs(reinterpret_cast<float4 *>(out_lpips) + i,
+                       make_float4(__fsub_rn(__fmul_rn(s.x, 2.f), 1.f), __fsub_rn(__fmul_rn(s.y, 2.f), 1.f),
+                                   __fsub_rn(__fmul_rn(s.z, 2.f), 1.f), __fsub_rn(__fmul_rn(s.w, 2.f), 1.f)));
+        }
+        for (long long i = (n4 << 2) + t0; i < n; i += stride) {
+            const float s = srgb_oetf(__ldg(x + i));
+            if (out_srgb != nullptr) out_srgb[i] = s;
+            if (out_lpips != nullptr) out_lpips[i] = __fsub_rn(__fmul_rn(s, 2.f), 1.f);
+        }
+    } else {
+        for (long long i = t0; i < n; i += stride) {
+            const float s = srgb_oetf(__ldg(x + i));
+            if (out_srgb != nullptr) out_srgb[i] = s;
+            if (out_lpips != nullptr) out_lpips[i] = __fsub_rn(__fmul_rn(s, 2.f), 1.f);
+        }
+    }
+}
+
+static int grid_for(long long work_items, int threads, int per_sm) {
+    const long long blocks = (work_items + threads - 1) / threads;
+    const long long cap = (long long)kNumSM * per_sm;
+    return (int)(blocks < cap ? (blocks < 1 ? 1 : blocks) : cap);
+}
+
+}  // namespace llie
+
+using namespace llie;
+
+extern "C" int llie_decode_u16(const llie_decode_desc *desc, const uint16_t *src, const float *rho, float rho_scalar,
+                               float *out_raw, float *out_aligned, void *stream) {
+    LLIE_REQUIRE(desc != nullptr && src != nullptr, "llie_decode_u16: null descriptor / source");
+    const llie_decode_desc &d = *desc;
+    LLIE_REQUIRE(d.n >= 1 && d.h >= 1 && d.w >= 1 && d.c >= 1, "llie_decode_u16: empty source [%d,%d,%d,%d]", d.n, d.h,
+                 d.w, d.c);
+    LLIE_REQUIRE(d.crop_h >= 1 && d.crop_w >= 1 && d.top >= 0 && d.left >= 0 && d.top + d.crop_h <= d.h &&
+                     d.left + d.crop_w <= d.w,
+                 "llie_decode_u16: crop window (%d,%d)+(%d,%d) outside the %dx%d source", d.top, d.left, d.crop_h,
+                 d.crop_w, d.h, d.w);
+    LLIE_REQUIRE(out_raw != nullptr || out_aligned != nullptr, "llie_decode_u16: no output requested");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    DecArgs a{d, src, rho, rho_scalar, out_raw, out_aligned};
+    const bool out_ok = (out_raw == nullptr || aligned16(out_raw)) && (out_aligned == nullptr || aligned16(out_aligned));
+    if (d.c == 3 && (d.crop_w & 3) == 0 && out_ok) {
+        const long long items = (long long)d.n * d.crop_h * (d.crop_w >> 2);
+        const int grid = grid_for(items, kDecThreads, 8);
+        const bool vec = (reinterpret_cast<uintptr_t>(src) & 7u) == 0 && (d.w & 3) == 0 && (d.left & 3) == 0;
+        if (vec)
+            decode_u16_c3_kernel<true><<<grid, kDecThreads, 0, st>>>(a);
+        else
+            decode_u16_c3_kernel<false><<<grid, kDecThreads, 0, st>>>(a);
+    } else {
+        const long long items = (long long)d.n * d.c * d.crop_h * d.crop_w;
+        decode_u16_generic_kernel<<<grid_for(items, kDecThreads, 8), kDecThreads, 0, st>>>(a);
+    }
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+extern "C" int llie_linear_to_srgb(const float *x, int64_t n, float *out_srgb, float *out_lpips, void *stream) {
+    LLIE_REQUIRE(x != nullptr && n >= 0, "llie_linear_to_srgb: null input");
+    LLIE_REQUIRE(out_srgb != nullptr || out_lpips != nullptr, "llie_linear_to_srgb: no output requested");
+    if (n == 0) return LLIE_OK;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const bool vec = aligned16(x) && (out_srgb == nullptr || aligned16(out_srgb)) &&
+                     (out_lpips == nullptr || aligned16(out_lpips));
+    const long long items = vec ? (n + 3) / 4 : n;
+    linear_to_srgb_kernel<<<grid_for(items, 256, 8), 256, 0, st>>>(x, n, out_srgb, out_lpips, vec);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}

@@ -222,6 +222,7 @@ extern "C" int llie_tune(int key, int value) {
         case LLIE_TUNE_PHYS_PATH: g_phys_path = value; return LLIE_OK;
         case LLIE_TUNE_PHYS_ROWS: phys_roll_set_rows(value); phys_ring_set_rows(value); return LLIE_OK;
         case LLIE_TUNE_PHYS_PDL: phys_ring_set_pdl(value); return LLIE_OK;
+        case LLIE_TUNE_PHYS_OVERLAP: phys_ring_set_overlap(value); return LLIE_OK;
         case LLIE_TUNE_SSIM_PATH:
         case LLIE_TUNE_SSIM_SEG_ROWS: ssim_tune(key, value); return LLIE_OK;
         default: break;

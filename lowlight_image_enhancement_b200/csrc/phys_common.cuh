@@ -87,6 +87,7 @@ int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st);
 int launch_phys_fused_ring(PhysArgs &a, void *workspace, cudaStream_t st);
 void phys_ring_set_rows(int r);
 void phys_ring_set_pdl(int on);
+void phys_ring_set_overlap(int on);
 
 // register-rolling path (phys_roll.cu)
 bool phys_roll_eligible(const PhysArgs &a);

@@ -65,6 +65,7 @@ struct RingGeom {
     double *part;  // [items] per-item partial sums
     double *samp;  // [n] per-sample sums (finalize scratch)
     int *pflag;    // [gridDim.x]
+    int early;     // stream-overlap contract (LLIE_TUNE_PHYS_OVERLAP): only the workspace depends on the previous kernel
 };
 
 struct Item {
@@ -386,7 +387,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
     pdl_launch_dependents();  // the next kernel's CTAs may run their prologue while this grid drains
     ring_setup(ring, full, empty, (W % kCols) != 0);
-    pdl_wait();  // nothing before this line reads or writes global memory
+    if (!g.early) pdl_wait();  // nothing before this line reads or writes global memory
     int iter = 0;
 
     float chk_p = 0.f, chk_o = 0.f;  // x*0 accumulators: NaN iff a non-finite value went through a clip
@@ -520,7 +521,10 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
             double *rw = red_w + (iter & 1) * 4;
             if (lane == 0) rw[wrp] = ws;
             asm volatile("bar.sync 1, %0;" ::"n"(kCons) : "memory");
-            if (tid == 0) g.part[item] = (rw[0] + rw[1]) + (rw[2] + rw[3]);
+            if (tid == 0) {
+                if (g.early && iter == 0) pdl_wait();  // the workspace is shared with the previous launch
+                g.part[item] = (rw[0] + rw[1]) + (rw[2] + rw[3]);
+            }
             ++iter;
         }
     }
@@ -563,7 +567,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
     pdl_launch_dependents();
     ring_setup(ring, full, empty, (W % kCols) != 0);
     RING_STAMP(threadIdx.x == 0, 1);
-    pdl_wait();  // nothing before this line reads or writes global memory
+    if (!g.early) pdl_wait();  // nothing before this line reads or writes global memory
     RING_STAMP(threadIdx.x == 0, 2);
     RingState rs{0, 0u};
 
@@ -763,10 +767,15 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
             double *rw = red_w + (iter & 1) * 4;
             if (lane == 0) rw[wrp] = ws;
             asm volatile("bar.sync 1, %0;" ::"n"(kCons) : "memory");
-            if (tid == 0) g.part[item] = (rw[0] + rw[1]) + (rw[2] + rw[3]);
+            if (tid == 0) {
+                if (g.early && iter == 0) pdl_wait();  // the workspace is shared with the previous launch
+                g.part[item] = (rw[0] + rw[1]) + (rw[2] + rw[3]);
+            }
             ++iter;
         }
     }
+    // gradient-only launches touch no workspace; the wait keeps grid completion transitively ordered
+    if (!FUSED && g.early && tid == 0) pdl_wait();
     if (FUSED) {
         int flag = 0;
         if (!(chk_p == 0.f)) flag |= 1;
@@ -788,6 +797,12 @@ static int g_ring_rows = 0;  // 0 = heuristic; set through llie_tune(LLIE_TUNE_P
 void phys_ring_set_rows(int r) { g_ring_rows = r; }
 static int g_ring_pdl = 1;   // programmatic dependent launch of the ring kernels (llie_tune(LLIE_TUNE_PHYS_PDL, 0|1))
 void phys_ring_set_pdl(int on) { g_ring_pdl = on ? 1 : 0; }
+// stream-overlap contract (llie_tune(LLIE_TUNE_PHYS_OVERLAP, 1)): the caller guarantees that no buffer of a ring launch
+// except the workspace is read or written by the kernel launched right before it on the same stream.  The kernels then
+// wait for the previous grid only where they touch the workspace, so the CTAs of launch i + 1 stream and compute on
+// the SMs that the early finishers of launch i have left (and under its last-CTA finalize).
+static int g_ring_overlap = 0;
+void phys_ring_set_overlap(int on) { g_ring_overlap = on ? 1 : 0; }
 
 static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     RingGeom g{};
@@ -813,6 +828,7 @@ static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     const long long items = (long long)d.n * g.items_per_sample;
     g.items = (int)items;
     grid = items < slots ? (int)items : slots;
+    g.early = (g_ring_pdl && g_ring_overlap) ? 1 : 0;
     return g;
 }
 

@@ -28,4 +28,9 @@ Pinning status (DESIGN.md §Oracle has the table):
   the 18 Lab pairs of ``standard_tests/data/ciede2000_pairs.json`` and seeded
   tensors; kornia ``rgb_to_lab`` is restated → sRGB-input entry points are
   **parity unpinned** at the Lab conversion (loose cross-check: cv2 Lab).
+* ``oracle.pixel_losses`` — PINNED against the reference's BasicSR loss classes
+  (``tests/golden/make_golden_basicsr.py``).
+* ``oracle.ingest``   — PINNED: the reference dataset's ``__getitem__`` arithmetic
+  (bit-compared) and the ``metrics/evaluation.py`` tensor helpers
+  (``tests/golden/make_golden_ingest.py``).
 """

@@ -199,3 +199,34 @@ def pixel_loss_inputs(shape=(3, 3, 24, 20)):
     w1 = torch.rand(shape[0], 1, *shape[2:], generator=g)
     wc = torch.rand(*shape, generator=g)
     return pred, tgt, {None: None, 1: w1, 3: wc}
+
+
+# ------------------------------------------------------------------ decode / normalise step
+INGEST_CASES = [
+    dict(name="full", h=24, w=40, ratio=100.0, crop=None, seed=301),
+    dict(name="crop_aligned", h=40, w=64, ratio=250.0, crop=(8, 12, 32, 32), seed=302),  # vector loads
+    dict(name="crop_shifted", h=37, w=50, ratio=100.0, crop=(5, 6, 16, 16), seed=305),   # 2-byte loads, vector stores
+    dict(name="crop_odd", h=37, w=50, ratio=300.0, crop=(3, 7, 21, 21), seed=303),       # width % 4 != 0: generic kernel
+    dict(name="dark", h=16, w=16, ratio=1.0, crop=None, seed=304),
+]
+
+
+def ingest_inputs(case):
+    """Two [H, W, 3] uint16 arrays (numpy): a short exposure concentrated near black (so that ratio x value straddles
+    the clip at 1) with the extremes 0 and 65535 present, and a long exposure over the full range."""
+    import numpy as np
+    g = _gen(case["seed"])
+    h, w = case["h"], case["w"]
+    short = (torch.rand(h, w, 3, generator=g) ** 3 * (65535.0 * 4.0 / case["ratio"])).clamp(0, 65535).to(torch.int32)
+    long = torch.randint(0, 65536, (h, w, 3), generator=g, dtype=torch.int32)
+    short[0, 0, 0], short[0, 1, 1], long[0, 0, 2], long[1, 0, 0] = 0, 65535, 65535, 0
+    return short.numpy().astype(np.uint16), long.numpy().astype(np.uint16)
+
+
+def srgb_inputs():
+    """[2, 3, 33, 47] linear values: uniform in [-0.1, 1.1] with the OETF knee, 0, 1 and tiny values planted."""
+    g = _gen(311)
+    x = torch.rand(2, 3, 33, 47, generator=g) * 1.2 - 0.1
+    x[0, 0, 0, :8] = torch.tensor([0.0, 1.0, 0.0031308, 0.0031307, 0.0031309, 1e-8, 0.5, 0.18])
+    x[1, 1, 1, :8] = torch.logspace(-6, 0, 8)
+    return x
