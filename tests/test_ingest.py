@@ -118,7 +118,9 @@ def test_decode_full_size_round_trip_and_clip():
     raw, ali = Fn.decode_u16(u, 100.0)
     back = torch.round(raw * 65535.0).to(torch.int32).permute(0, 2, 3, 1)
     assert torch.equal(back, u.to(torch.int32))
-    assert torch.equal(raw, u.to(torch.float32).permute(0, 3, 1, 2) / 65535.0)
+    # tensor / tensor: ATen's CUDA "divide by a scalar" multiplies by the reciprocal, which is not numpy's division
+    planes = u.to(torch.float32).permute(0, 3, 1, 2)
+    assert torch.equal(raw, planes / torch.full_like(planes, 65535.0))
     assert torch.equal(ali, (raw * 100.0).clamp(0.0, 1.0))
 
 
