@@ -428,7 +428,7 @@ def run_extra(args, rank, world, dev):
         "ms_per_image_per_gpu": round(ms / per_rank, 4), "wall_ms": round(wall, 2),
         "means": {k: (round(v, 6) if isinstance(v, float) else v) for k, v in res.items()},
         "kernels": [kern("psnr_stats_kernel", t_ps, 24, "hbm"),
-                    kern("ssim_stream_kernel<11>", t_ssim, 24, "fp32 fma pipe (110 FMA per element)"),
+                    kern("ssim_stream2_kernel<11, 4 maps>", t_ssim, 24, "instruction issue (88 FMA + ~85 other instructions per element)"),
                     kern("deltae_kernel", t_de, 24, "instruction issue (fp32 + sfu)"),
                     kern("all 4 metrics of one image (12 launches)", t_all, 36, "mixed")],
     }

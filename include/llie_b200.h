@@ -56,7 +56,8 @@ int llie_check_device(void);
 /* Diagnostic knobs for A/B measurements (process-wide, not thread-safe; defaults are the product). */
 #define LLIE_TUNE_PHYS_PATH 1 /* 0 TMA row ring (default) | 1 TMA tile ring | 2 generic only | 3 register prefetch */
 #define LLIE_TUNE_PHYS_ROWS 2 /* rows per warp chunk of the rolling path; 0 = heuristic */
-#define LLIE_TUNE_SSIM_PATH 3 /* 0 streaming column kernel (default) | 1 shared-memory tile kernel */
+#define LLIE_TUNE_SSIM_PATH 3 /* 0 auto (two-column streaming kernel for statistics-only 11-tap calls, else the
+                                 one-column streaming kernel) | 1 shared-memory tile kernel | 2 one-column streaming */
 #define LLIE_TUNE_SSIM_SEG_ROWS 4 /* output rows per CTA of the streaming SSIM kernel; 0 = heuristic */
 #define LLIE_TUNE_PHYS_PDL 5 /* 1 (default): ring kernels are launched with programmatic stream serialization, so the
                                 prologue of a kernel overlaps the tail of the previous one | 0 plain launches */

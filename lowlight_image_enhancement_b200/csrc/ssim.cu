@@ -441,7 +441,232 @@ static int launch_ssim_stream(const SsimArgs &a, int grid, cudaStream_t st) {
     return LLIE_OK;
 }
 
-int g_ssim_path = 0;      // 0 streaming (default) | 1 tile kernel
+// ---------------------------------------------------------------------------------------------------
+// Streaming variant 2 (statistics only: no SSIM map, no loss coefficients; the eval / metric path): the same row
+// ring and rolling vertical accumulators, but
+//   * one thread owns TWO adjacent output columns of a 256-column strip: the K + 1 input values it needs per row and
+//     array come from (K + 1) / 2 conflict-free LDS.64, the x^2 / y^2 / xy products of a position are formed once and
+//     feed both columns, and the per-row bookkeeping (ring refill, barrier, address arithmetic) is paid per two
+//     elements;
+//   * without the per-image variance clamp (torchmetrics / kornia policies) sigma_x^2 and sigma_y^2 only enter SSIM
+//     through their sum, so FOUR moment maps are filtered (x, y, x^2 + y^2, xy) instead of five: 88 instead of 110
+//     multiply-adds per element.  MAPS5 keeps the five maps for `clamp_var` (ssim_linear), bit-identical to
+//     ssim_stream_kernel.
+// 312 -> ~170 instructions per element at K = 11.
+constexpr int S2W = 256;
+constexpr int S2T = 128;
+
+template <int K, bool MAPS5>
+__global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) {
+    constexpr int P = K / 2;
+    constexpr int RW = S2W + 2 * P;  // even: row starts stay 8-byte aligned
+    constexpr int M = MAPS5 ? 5 : 4;
+    static_assert(2 * P <= S2T && (RW % 2) == 0, "halo slots are loaded by the first 2P threads");
+    __shared__ __align__(16) float sX[SD][RW], sY[SD][RW];
+    __shared__ double red[32];
+    const llie_ssim_desc &d = a.d;
+    const int H = d.h, W = d.w, tid = threadIdx.x;
+    const int tpp = a.tiles_x * a.tiles_y;
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int seg = trem / a.tiles_x, strip = trem - seg * a.tiles_x;
+    const int x0 = strip * S2W, y0 = seg * a.seg_rows;
+    const int rows_out = min(a.seg_rows, H - y0);
+    const int nrows_in = rows_out + 2 * P;
+    const long long plane_elems = (long long)H * W;
+    const float *xb = a.x + (long long)plane * plane_elems;
+    const float *yb = a.y + (long long)plane * plane_elems;
+
+    float g[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
+
+    // ring slots of this thread: tid, S2T + tid, and 2 * S2T + tid for the right halo (tid < 2P)
+    const bool has_ext = tid < 2 * P;
+    int csrc[3];
+    unsigned cbytes[3];
+    const float *px[3], *py[3];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int gin = x0 - P + s * S2T + tid;
+        const int c = ((s < 2 || has_ext) && gin <= W - 1 + P) ? pad_index(gin, W, d.pad_mode) : -1;
+        csrc[s] = c;
+        cbytes[s] = c >= 0 ? 4u : 0u;
+        px[s] = xb + max(c, 0);
+        py[s] = yb + max(c, 0);
+    }
+    const unsigned sxa = (unsigned)__cvta_generic_to_shared(&sX[0][tid]);
+    const unsigned sya = (unsigned)__cvta_generic_to_shared(&sY[0][tid]);
+
+    auto issue_row = [&](int i) {  // i is uniform over the CTA; one commit group per call
+        if (i < nrows_in) {
+            const int sy = pad_index(y0 - P + i, H, d.pad_mode);
+            const long long ro = (long long)max(sy, 0) * W;
+            const unsigned so = (unsigned)((i & (SD - 1)) * RW * 4);
+            const unsigned ok = sy >= 0 ? 4u : 0u;
+#pragma unroll
+            for (int s = 0; s < 2; ++s) {
+                cp_async4(sxa + so + s * S2T * 4, px[s] + ro, min(cbytes[s], ok));
+                cp_async4(sya + so + s * S2T * 4, py[s] + ro, min(cbytes[s], ok));
+            }
+            if (has_ext) {
+                cp_async4(sxa + so + 2 * S2T * 4, px[2] + ro, min(cbytes[2], ok));
+                cp_async4(sya + so + 2 * S2T * 4, py[2] + ro, min(cbytes[2], ok));
+            }
+        }
+        cp_async_commit();
+    };
+
+    const int gx = x0 + 2 * tid;  // first of the two output columns
+    const int lo_y = d.interior ? P : 0, hi_y = d.interior ? H - P : H;
+    bool col_ok[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) col_ok[c] = gx + c < W && (!d.interior || (gx + c >= P && gx + c < W - P));
+    float acc[M][2][K];
+#pragma unroll
+    for (int q = 0; q < M; ++q)
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int j = 0; j < K; ++j) acc[q][c][j] = 0.f;
+    float facc = 0.f, chk_x = 0.f, chk_y = 0.f;
+
+#pragma unroll
+    for (int i = 0; i < SD - 1; ++i) issue_row(i);
+    for (int base = 0; base < nrows_in; base += K) {
+#pragma unroll
+        for (int ii = 0; ii < K; ++ii) {
+            const int i = base + ii;
+            if (i >= nrows_in) break;  // uniform
+            float *rx = sX[i & (SD - 1)], *ry = sY[i & (SD - 1)];
+            cp_async_wait<SD - 2>();  // this thread's copies of row i have landed
+#pragma unroll
+            for (int s = 0; s < 3; ++s) {
+                if (s == 2 && !has_ext) break;
+                const float vx = rx[s * S2T + tid], vy = ry[s * S2T + tid];
+                chk_x = fmaf(vx, 0.f, chk_x);
+                chk_y = fmaf(vy, 0.f, chk_y);
+                if (d.clamp_in) {
+                    rx[s * S2T + tid] = fminf(fmaxf(vx, 0.f), 1.f);
+                    ry[s * S2T + tid] = fminf(fmaxf(vy, 0.f), 1.f);
+                }
+            }
+            __syncthreads();        // row i visible to all; everyone is done with row i - 1
+            issue_row(i + SD - 1);  // refills the slot row i - 1 occupied
+            float h[M][2];
+#pragma unroll
+            for (int q = 0; q < M; ++q) h[q][0] = h[q][1] = 0.f;
+            const float2 *rx2 = reinterpret_cast<const float2 *>(rx) + tid;
+            const float2 *ry2 = reinterpret_cast<const float2 *>(ry) + tid;
+#pragma unroll
+            for (int k = 0; k < (K + 1) / 2; ++k) {
+                const float2 xv = rx2[k], yv = ry2[k];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int p = 2 * k + e;  // position p feeds column 0 with tap p and column 1 with tap p - 1
+                    const float xe = e ? xv.y : xv.x, ye = e ? yv.y : yv.x;
+                    float m[M];
+                    m[0] = xe;
+                    m[1] = ye;
+                    if (MAPS5) {
+                        m[2] = xe * xe;
+                        m[3] = ye * ye;
+                        m[4] = xe * ye;
+                    } else {
+                        m[2] = fmaf(xe, xe, ye * ye);
+                        m[3] = xe * ye;
+                    }
+#pragma unroll
+                    for (int q = 0; q < M; ++q) {
+                        if (p <= K - 1) h[q][0] = fmaf(g[p <= K - 1 ? p : 0], m[q], h[q][0]);
+                        if (p >= 1) h[q][1] = fmaf(g[p >= 1 ? p - 1 : 0], m[q], h[q][1]);
+                    }
+                }
+            }
+            // input row i feeds output rows o = i - j with tap j; slot(o) = o mod K = (ii - j) mod K
+#pragma unroll
+            for (int j = 0; j < K; ++j) {
+                const int sl = (ii - j + K) % K;
+#pragma unroll
+                for (int q = 0; q < M; ++q)
+#pragma unroll
+                    for (int c = 0; c < 2; ++c)
+                        acc[q][c][sl] = (j == 0) ? g[0] * h[q][c] : fmaf(g[j], h[q][c], acc[q][c][sl]);
+            }
+            if (i >= K - 1) {  // output row o = i - (K - 1) is complete
+                const int sl = (ii + 1) % K;
+                const int gy = y0 + i - (K - 1);
+                const bool row_ok = gy >= lo_y && gy < hi_y;
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const float mx = acc[0][c][sl], my = acc[1][c][sl];
+                    const float mx2 = mx * mx, my2 = my * my, mxy = mx * my;
+                    float vsum, sxy;
+                    if (MAPS5) {
+                        float sx = acc[2][c][sl] - mx2, sy = acc[3][c][sl] - my2;
+                        if (d.clamp_var) {
+                            sx = fmaxf(sx, 0.f);
+                            sy = fmaxf(sy, 0.f);
+                        }
+                        vsum = sx + sy;
+                        sxy = acc[4][c][sl] - mxy;
+                    } else {
+                        vsum = (acc[2][c][sl] - mx2) - my2;
+                        sxy = acc[3][c][sl] - mxy;
+                    }
+                    const float num = (2.f * mxy + d.c1) * (2.f * sxy + d.c2);
+                    const float den = (mx2 + my2 + d.c1) * (vsum + d.c2) + d.eps;
+                    float sv = num / den;
+                    if (d.loss_map) sv = fminf(fmaxf((1.f - sv) * 0.5f, 0.f), 1.f);
+                    if (col_ok[c] && row_ok) facc += sv;
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+    const double bs = block_sum<double>((double)facc, red);
+    int flag = 0;
+    if (!(chk_x == 0.f)) flag |= 1;
+    if (!(chk_y == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (tid == 0) {
+        a.part[blockIdx.x] = bs;
+        a.pflag[blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x)) return;
+    const int lane = tid & 31, wrp = tid >> 5;
+    const int planes = d.n * a.co;
+    for (int pl = wrp; pl < planes; pl += S2T / 32) {
+        const double *p = a.part + (size_t)pl * tpp;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int b = lane;
+        for (; b + 96 < tpp; b += 128) {
+            s0 += __ldcg(p + b);
+            s1 += __ldcg(p + b + 32);
+            s2 += __ldcg(p + b + 64);
+            s3 += __ldcg(p + b + 96);
+        }
+        for (; b < tpp; b += 32) s0 += __ldcg(p + b);
+        const double sm_ = warp_sum((s0 + s1) + (s2 + s3));
+        if (lane == 0) a.out_sum[pl] = sm_;
+    }
+    int fl = 0;
+    for (int b = tid; b < (int)gridDim.x; b += S2T) fl |= __ldcg(a.pflag + b);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (tid == 0) *a.out_flags = ff;
+}
+
+template <int K>
+static int launch_ssim_stream2(const SsimArgs &a, int grid, cudaStream_t st) {
+    if (a.d.clamp_var)
+        ssim_stream2_kernel<K, true><<<grid, S2T, 0, st>>>(a);
+    else
+        ssim_stream2_kernel<K, false><<<grid, S2T, 0, st>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+int g_ssim_path = 0;      // 0 auto: two-column streaming kernel where eligible, else streaming | 1 tile kernel | 2 one-column streaming
 int g_ssim_seg_rows = 0;  // 0 = heuristic
 
 // ---------------------------------------------------------------------------------------------------
@@ -773,6 +998,30 @@ static int launch_ssim_bwd(const SsimBwdArgs &a, int grid, cudaStream_t st) {
 
 using namespace llie;
 
+// Output rows per CTA of the streaming kernels.  Every column strip is cut into the same number of row segments; the
+// grid then runs in waves of `slots` resident CTAs, and a wave that is only partly filled costs a full segment time
+// (e.g. 918 CTAs on 888 slots = 3 waves for 2.07 waves of work).  Pick, among 1..4 waves, the segment count whose
+// (slot fill) x (useful rows / rows incl. the `halo` warm-up rows) is best, with at least `min_rows` rows per segment.
+static int pick_seg_rows(long long cols, int h, int slots, int min_rows, int halo) {
+    int best_rows = h;
+    double best = -1.0;
+    for (int waves = 1; waves <= 4; ++waves) {
+        long long segs = (long long)waves * slots / cols;
+        if (segs < 1) segs = 1;
+        int rows = (int)((h + segs - 1) / segs);
+        if (rows < min_rows) rows = min_rows < h ? min_rows : h;
+        const long long tiles_y = (h + rows - 1) / rows;
+        const long long grid = cols * tiles_y;
+        const long long used_waves = (grid + slots - 1) / slots;
+        const double eff = (double)grid / (double)(used_waves * slots) * rows / (rows + halo);
+        if (eff > best + 1e-9) {
+            best = eff;
+            best_rows = rows;
+        }
+    }
+    return best_rows;
+}
+
 static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d, double *out_sum,
                         float *out_map, float *coef, float coef_scale, int32_t *out_flags, void *workspace,
                         void *stream) {
@@ -794,15 +1043,24 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
     Workspace ws(workspace);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     long long grid;
-    const bool stream_ok = g_ssim_path == 0 && !d.luma;
-    if (stream_ok) {
+    const bool stream_ok = g_ssim_path != 1 && !d.luma;
+    // statistics only (no map / coefficient planes), the 11-tap window of all three reference policies
+    const bool stream2_ok = stream_ok && g_ssim_path == 0 && d.ksize == 11 && out_map == nullptr && coef == nullptr;
+    if (stream2_ok) {
+        // strips of 256 columns x row segments sized for ~2 resident waves (148 SMs x 3 CTAs), >= 64 rows each
+        a.tiles_x = div_up(d.w, S2W);
+        const long long cols = (long long)d.n * a.co * a.tiles_x;
+        const int rows = g_ssim_seg_rows > 0 ? (g_ssim_seg_rows < d.h ? g_ssim_seg_rows : d.h)
+                                             : pick_seg_rows(cols, d.h, kNumSM * 3, 64, d.ksize - 1);
+        a.seg_rows = rows;
+        a.tiles_y = div_up(d.h, rows);
+        grid = cols * a.tiles_y;
+    } else if (stream_ok) {
         // strips of 128 columns x row segments sized for ~3 resident waves (148 SMs x 5 CTAs), >= 48 rows each
         a.tiles_x = div_up(d.w, SW);
         const long long cols = (long long)d.n * a.co * a.tiles_x;
-        int segs = (int)((148LL * 5 * 3 + cols - 1) / cols);
-        int rows = g_ssim_seg_rows > 0 ? g_ssim_seg_rows : (d.h + segs - 1) / segs;
-        if (g_ssim_seg_rows <= 0 && rows < 48) rows = 48;
-        if (rows > d.h) rows = d.h;
+        const int rows = g_ssim_seg_rows > 0 ? (g_ssim_seg_rows < d.h ? g_ssim_seg_rows : d.h)
+                                             : pick_seg_rows(cols, d.h, kNumSM * 4, 48, d.ksize - 1);
         a.seg_rows = rows;
         a.tiles_y = div_up(d.h, rows);
         grid = cols * a.tiles_y;
@@ -816,6 +1074,7 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
     a.part = reinterpret_cast<double *>(ws.scratch);
     a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)grid * sizeof(double));
     a.ticket = ws.tickets;
+    if (stream2_ok) return launch_ssim_stream2<11>(a, (int)grid, st);
     if (stream_ok) {
         switch (d.ksize) {
             case 1: return launch_ssim_stream<1>(a, (int)grid, st);

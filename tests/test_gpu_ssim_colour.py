@@ -277,3 +277,48 @@ def test_adapters(dev):
     assert abs(lm.deltae2000_p95(p, t) - rs["p95"]) < 1e-4
     re_ = colour.edge_stats(pred.clamp(0, 1), gt.clamp(0, 1), q=0.85)
     assert abs(lm.edge_deltae2000_mean(p, t) - re_["mean"]) < 5e-3   # mask ties may differ on random floats
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 64, 300), (1, 3, 257, 513), (1, 1, 40, 11), (1, 3, 700, 1030)])
+@pytest.mark.parametrize("pad", ["reflect", "replicate", "circular", "zeros"])
+@pytest.mark.parametrize("policy", ["linear", "torchmetrics", "kornia_loss"])
+def test_two_column_ssim_kernel_vs_one_column(shape, pad, policy):
+    """The statistics-only two-column kernel (default for 11-tap calls without a map) against the one-column
+    streaming kernel (LLIE_TUNE_SSIM_PATH = 2): both the five-map (clamp_var) and the four-map instantiation (x^2 + y^2
+    filtered as one map) within 1e-6 relative of it, and the latter within 1e-5 of a float64 oracle."""
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    from lowlight_image_enhancement_b200 import _native as nat
+    from oracle import quality
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(sum(shape) + len(pad))
+    x = torch.rand(shape, generator=g)
+    y = (x + 0.1 * torch.randn(shape, generator=g)).clamp(-0.05, 1.05)
+    xd, yd = x.to(dev), y.to(dev)
+    win = Fn.window_1d("torchmetrics", 11, 1.5, dev)
+    kw = dict(pad_mode=nat.PAD[pad], c1=0.01 ** 2, c2=0.03 ** 2, eps=0.0)
+    if policy == "linear":
+        kw.update(clamp_var=True, eps=1e-12)
+    elif policy == "torchmetrics":
+        kw.update(interior=True)
+    else:
+        kw.update(clamp_in=False, loss_map=True, eps=1e-12)
+    try:
+        nat.check(nat.lib().llie_tune(3, 2), "llie_tune")
+        ref, fref, _ = Fn.ssim_stats(xd, yd, win, **kw)
+        nat.check(nat.lib().llie_tune(3, 0), "llie_tune")
+        got, fgot, _ = Fn.ssim_stats(xd, yd, win, **kw)
+    finally:
+        nat.check(nat.lib().llie_tune(3, 0), "llie_tune")
+    assert int(fref) == int(fgot) == 0
+    # (five-map instantiation: the same per-pixel values; the float32 per-thread partial sums group differently)
+    assert torch.allclose(ref, got, rtol=1e-6, atol=0), (ref, got)
+    if policy == "torchmetrics" and pad == "reflect":
+        h, w = shape[2] - 10, shape[3] - 10
+        want = quality.ssim_torchmetrics(x, y, compute_dtype=torch.float64)
+        mine = (got.sum(dim=1) / (shape[1] * h * w)).cpu()
+        assert torch.allclose(mine, want.double().view(-1), rtol=1e-5, atol=0), (mine, want)
+    # non-finite input raises the same flag bit
+    xd2 = xd.clone()
+    xd2[0, 0, 3, 7] = float("nan")
+    _, fl, _ = Fn.ssim_stats(xd2, yd, win, **kw)
+    assert int(fl) & 1
