@@ -254,11 +254,15 @@ __device__ __forceinline__ void produce_slot(float *slot, uint64_t *full, const 
     }
 }
 
-// Thread 0 publishes the CTA's results; returns true in ALL threads of the last CTA to arrive.
-__device__ __forceinline__ bool ring_last_block(unsigned *ticket, unsigned total_blocks) {
+// CTA epilogue: OR of the per-thread flags (one barrier), thread 0 publishes the CTA's flag word and takes a ticket;
+// returns true in ALL threads of the last CTA to arrive.  `early`: thread 0 first waits for the previous grid (the
+// workspace is shared with it; a no-op when it already waited for this CTA's per-item partial).
+__device__ __forceinline__ bool ring_publish(int flag, int *pflag, unsigned *ticket, unsigned total_blocks, bool early) {
     __shared__ bool s_last;
-    __syncthreads();
+    const int f = __syncthreads_or(flag);  // also orders thread 0's partial stores of the item loop before the fence
     if (threadIdx.x == 0) {
+        if (early) pdl_wait();
+        pflag[blockIdx.x] = f;
         __threadfence();
         const unsigned t = atomicAdd(ticket, 1u);
         s_last = (t == total_blocks - 1);
@@ -532,9 +536,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
     int flag = 0;
     if (!(chk_p == 0.f)) flag |= 1;
     if (!(chk_o == 0.f)) flag |= 2;
-    const int f = block_or(flag, red_i);
-    if (tid == 0) g.pflag[blockIdx.x] = f;
-    if (ring_last_block(a.ticket, gridDim.x)) ring_finalize(a, g, red_i, red_d, reinterpret_cast<double *>(smraw));
+    if (ring_publish(flag, g.pflag, a.ticket, gridDim.x, g.early != 0))
+        ring_finalize(a, g, red_i, red_d, reinterpret_cast<double *>(smraw));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -780,10 +783,8 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         int flag = 0;
         if (!(chk_p == 0.f)) flag |= 1;
         if (!(chk_o == 0.f)) flag |= 2;
-        const int f = block_or(flag, red_i);
-        if (tid == 0) g.pflag[blockIdx.x] = f;
         RING_STAMP(tid == 0, 5);
-        const bool last = ring_last_block(a.ticket, gridDim.x);
+        const bool last = ring_publish(flag, g.pflag, a.ticket, gridDim.x, g.early != 0);
         RING_STAMP(tid == 0, 6);
         if (last) ring_finalize(a, g, red_i, red_d, reinterpret_cast<double *>(smraw));
         RING_STAMP(tid == 0 && last, 7);
