@@ -199,6 +199,8 @@ def run_ours(args, rank, world, dev):
 
     if args.no_pdl:
         nat.check(nat.lib().llie_tune(5, 0), "llie_tune")  # LLIE_TUNE_PHYS_PDL
+    if args.ring_rows:
+        nat.check(nat.lib().llie_tune(2, args.ring_rows), "llie_tune")  # LLIE_TUNE_PHYS_ROWS (A/B)
     sets = [synth_batch(1000 * rank + 102 + i, dev) for i in range(POOL)]
     grads = [torch.empty(SHAPE, device=dev) for _ in range(POOL)]
     kern = psf_ops.canonical_kernels("rgb").to(dev)
@@ -549,6 +551,7 @@ def main():
     ap.add_argument("--skip-cpu", action="store_true", help="profiling runs: no cpu_baseline leg")
     ap.add_argument("--skip-extra", action="store_true", help="profiling runs: no eval_c4 / hybrid_c3 sections")
     ap.add_argument("--two-pass", action="store_true", help="time separate forward + backward kernels per step")
+    ap.add_argument("--ring-rows", type=int, default=0, help="A/B: rows per work item of the phys ring kernels")
     ap.add_argument("--no-overlap", action="store_true", help="A/B: every launch waits for the previous grid at its top")
     ap.add_argument("--no-pdl", action="store_true", help="A/B: plain launches instead of programmatic dependent launch")
     args = ap.parse_args()

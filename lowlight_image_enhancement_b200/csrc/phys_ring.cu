@@ -811,8 +811,16 @@ static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     const long long cols = (long long)d.n * d.c_out * g.groups;  // independent column strips
     const int slots = kNumSM * kCtasPerSM;
     int chunks;
+    const bool overlap = g_ring_pdl && g_ring_overlap;
     if (g_ring_rows > 0) {
         chunks = d.h / g_ring_rows;
+    } else if (overlap) {
+        // stream-overlap loops: several launches are resident at once (launch i + 1 starts as soon as every CTA of
+        // launch i has started), so the machine is filled ACROSS launches and a CTA should live long: ~128-row items
+        // halve the warm-up rows and amortise the per-CTA ramp (setup, first TMA round trip, epilogue ~ 5 us) that a
+        // one-item CTA of ~21 rows pays once per 13 us of work (C2 sweep: 17.7 us per fused launch at 21 rows,
+        // 13.5 at 64, 12.9 at 128..256, 13.9 at 512)
+        chunks = (d.h + 64) / 128;
     } else {
         // items = k * (resident CTA slots): every persistent CTA gets the same number of items (no
         // tail wave) and the rows of a plane are split evenly; k aims at ~48-row chunks (warm-up rows
@@ -829,7 +837,7 @@ static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     const long long items = (long long)d.n * g.items_per_sample;
     g.items = (int)items;
     grid = items < slots ? (int)items : slots;
-    g.early = (g_ring_pdl && g_ring_overlap) ? 1 : 0;
+    g.early = overlap ? 1 : 0;
     return g;
 }
 

@@ -280,9 +280,11 @@ def test_phys_value_and_grad_equals_two_passes(dev, padding, crop, robust, clip,
 
 @pytest.mark.parametrize("shape", [(8, 3, 512, 512), (2, 3, 96, 640), (4, 3, 130, 252)])
 def test_phys_stream_overlap_is_bit_identical(dev, shape):
-    """LLIE_TUNE_PHYS_OVERLAP (launch i + 1 waits for launch i only before it touches the shared workspace): a mixed
-    back-to-back sequence of fused / forward / backward launches over rotating, disjoint buffer sets must return
-    bit for bit what fully serialised launches return, on a stream and replayed from a CUDA graph."""
+    """LLIE_TUNE_PHYS_OVERLAP (launch i + 1 waits for launch i only before it touches the shared workspace, and work
+    items grow to ~128 rows): a mixed back-to-back sequence of fused / forward / backward launches over rotating,
+    disjoint buffer sets must return what fully serialised launches return -- gradients bit for bit, loss vectors to
+    1e-6 relative (the item partition, hence the grouping of the float32 partial sums, differs between the modes) --
+    on a stream and replayed from a CUDA graph."""
     from lowlight_image_enhancement_b200 import _functional as Fn
     from lowlight_image_enhancement_b200 import _native as nat
     g = torch.Generator().manual_seed(7 + sum(shape))
@@ -313,6 +315,9 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
                 outs.append((gr.clone(),))
         return outs
 
+    def same(a, b):  # loss vectors are 1-D [n + 2], gradients 4-D
+        return torch.equal(a, b) if a.dim() == 4 else torch.allclose(a, b, rtol=1e-6, atol=0)
+
     ref = sequence(2)
     torch.cuda.synchronize(dev)
     try:
@@ -322,7 +327,7 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
         got = sequence(2)
         torch.cuda.synchronize(dev)
         for r, o in zip(ref, got):
-            assert all(torch.equal(a, b) for a, b in zip(r, o))
+            assert all(same(a, b) for a, b in zip(r, o))
         # back-to-back phys launches only (the overlap proper): stream, then graph replay
         def burst():
             for i in range(4 * pool):
@@ -340,8 +345,9 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
             want[i] = (v.clone(), gr.clone())
         torch.cuda.synchronize(dev)
         Fn.phys_stream_overlap(True)
+        first = [v.clone() for v in keep]
         for i, v in enumerate(keep):
-            assert torch.equal(v, want[i % pool][0]), i
+            assert same(v, want[i % pool][0]), i
         for b in range(pool):
             assert torch.equal(grads[b], want[b][1]), b
         side = torch.cuda.Stream(dev)
@@ -360,7 +366,7 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
                 graph.replay()
         side.synchronize()
         for i, v in enumerate(keep):
-            assert torch.equal(v, want[i % pool][0]), i
+            assert torch.equal(v, first[i]), i  # overlapped launches are reproducible bit for bit
         for b in range(pool):
             assert torch.equal(grads[b], want[b][1]), b
     finally:
