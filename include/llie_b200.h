@@ -304,6 +304,33 @@ int llie_decode_u16(const llie_decode_desc *desc, const uint16_t *src, const flo
  * replaces metrics/evaluation.py:27-38 (_linear_to_srgb) and :50-52 (_norm_to_lpips_range). */
 int llie_linear_to_srgb(const float *x, int64_t n, float *out_srgb, float *out_lpips, void *stream);
 
+/* ------------------------------------------------------------------------
+ * Per-pair epilogue of the sharded evaluation driver: adapter values from the raw device sums, added to the rank's
+ * running vector acc = [k metric sums, pair count, pairs with non-finite input] (float64), one launch, no host sync.
+ * replaces the host arithmetic of NAFNet_base/basicsr/metrics/lowlight_metrics.py:211-272 (the five adapters) and
+ * the `metric_results[name] += value` accumulation of image_restoration_model.py:420-428.
+ *   sqerr        [n] float64 sums of (pred - target)^2 per image            (llie_deltae_sqerr)   -> linear_psnr
+ *   ssim_sums    [n, ssim_c] float64 SSIM-map sums over ssim_count elements (llie_ssim_stats)     -> linear_ssim
+ *   de_sums      [n] float64 dE00 sums over hw pixels                       (llie_deltae)         -> deltae2000_mean
+ *   de_p95       [1] float                                                  (llie_select_quantiles) -> deltae2000_p95
+ *   edge_sum     [1] float64, edge_counts [n] int64                         (gated select)        -> edge_deltae2000_mean
+ *   flags0..3    NULL or the out_flags words of the kernels above
+ * A slot of -1 skips that metric (its inputs may be NULL).
+ * ------------------------------------------------------------------------ */
+typedef struct llie_eval_desc {
+    int32_t n, c;            /* images in this pair batch, channels */
+    int64_t hw;              /* pixels per image */
+    int32_t ssim_c;          /* columns of ssim_sums */
+    int64_t ssim_count;      /* elements per image the SSIM sums cover */
+    double data_range;       /* PSNR peak */
+    int32_t k;               /* metric slots in acc */
+    int32_t slot_psnr, slot_ssim, slot_de_mean, slot_de_p95, slot_edge;
+} llie_eval_desc;
+int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const double *ssim_sums,
+                         const double *de_sums, const float *de_p95, const double *edge_sum,
+                         const int64_t *edge_counts, const int32_t *flags0, const int32_t *flags1,
+                         const int32_t *flags2, const int32_t *flags3, double *acc, void *stream);
+
 /* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the
  * < 1 ulp claim can be checked against a float64 pow from the test-suite. */
 int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream);

@@ -64,6 +64,13 @@ class DecodeDesc(C.Structure):
                 ("left", C.c_int32), ("crop_h", C.c_int32), ("crop_w", C.c_int32), ("swap_rb", C.c_int32)]
 
 
+class EvalDesc(C.Structure):
+    _fields_ = [("n", C.c_int32), ("c", C.c_int32), ("hw", C.c_int64), ("ssim_c", C.c_int32),
+                ("ssim_count", C.c_int64), ("data_range", C.c_double), ("k", C.c_int32), ("slot_psnr", C.c_int32),
+                ("slot_ssim", C.c_int32), ("slot_de_mean", C.c_int32), ("slot_de_p95", C.c_int32),
+                ("slot_edge", C.c_int32)]
+
+
 class SelectDesc(C.Structure):
     _fields_ = [("images", C.c_int32), ("per_image", C.c_int64), ("nq", C.c_int32), ("joint", C.c_int32)]
 
@@ -100,6 +107,7 @@ _SIGNATURES = {
     "llie_tile_merge": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _VP, _VP]),
     "llie_decode_u16": (C.c_int, [C.POINTER(DecodeDesc), _VP, _VP, C.c_float, _VP, _VP, _VP]),
     "llie_linear_to_srgb": (C.c_int, [_VP, C.c_int64, _VP, _VP, _VP]),
+    "llie_eval_accumulate": (C.c_int, [C.POINTER(EvalDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),
     "llie_select_workspace_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),

@@ -22,7 +22,8 @@ import torch
 import torch.distributed as dist
 from torch import Tensor
 
-__all__ = ["METRIC_FUNCTIONS", "ShardedMeans", "TileGrid", "shard_indices", "image_metrics", "evaluate_pairs"]
+__all__ = ["METRIC_FUNCTIONS", "ShardedMeans", "TileGrid", "shard_indices", "image_metrics", "accumulate_image_metrics",
+           "evaluate_pairs"]
 
 
 # ------------------------------------------------------------------------------------------------
@@ -54,9 +55,10 @@ def _psnr(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.
 
 def _ssim(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.0) -> Tensor:
     """lowlight_metrics.py:217-220 -> SSIMEvaluator (torchmetrics policy), mean over the batch's images."""
-    from .metrics.ssim import torchmetrics_ssim_scores
-    return torchmetrics_ssim_scores(pred, target, data_range=float(data_range), sigma=1.5, k1=0.01, k2=0.03) \
-        .double().mean()
+    from .metrics.ssim import ssim_sums_torchmetrics
+    sums, count, fl = ssim_sums_torchmetrics(pred, target, data_range=float(data_range), sigma=1.5, k1=0.01, k2=0.03)
+    flags |= fl
+    return (sums.sum(dim=1) / float(count)).to(torch.float32).double().mean()
 
 
 class _ColourPass:
@@ -138,6 +140,71 @@ def image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], flags: Opt
     return torch.stack(vals)
 
 
+_FAST = ("linear_psnr", "linear_ssim", "deltae2000_mean", "deltae2000_p95", "edge_deltae2000_mean")
+
+
+@torch.no_grad()
+def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], acc: "ShardedMeans", **opts) -> bool:
+    """`acc.add(image_metrics(pred, target, names, flags), flags)` with the whole epilogue in ONE launch
+    (`llie_eval_accumulate`): the metric kernels leave their raw sums on the device and a single-thread kernel forms
+    the adapter values and adds them to `acc.vec`.  Returns False (nothing launched) when the request is outside what
+    that kernel covers -- an unknown metric, a PSNR that cannot ride on a colour pass, a CPU accumulator -- and the
+    caller falls back to `image_metrics`."""
+    from . import _functional as Fn
+    from . import _native as nat
+    from .metrics.ssim import ssim_sums_torchmetrics
+    names = list(names)
+    if any(n not in _FAST for n in names) or len(set(names)) != len(names) or names != acc.names:
+        return False
+    p, t, dev = _stage_pair(pred, target)
+    if acc.vec.device != dev or p.shape[1] != 3 and ("linear_psnr" in names or any(n in _COLOUR for n in names)):
+        return False
+    colour = [n for n in names if n in _COLOUR]
+    if "linear_psnr" in names and not colour:
+        return False
+    n, c, h, w = p.shape
+    slot = {nm: i for i, nm in enumerate(names)}
+    fl: List[Optional[Tensor]] = []
+    sq = sums = dmap = lpl = None
+    if colour:
+        want_map = any(_COLOUR[nm][0] for nm in colour)
+        want_l = any(_COLOUR[nm][1] for nm in colour)
+        sql = [] if "linear_psnr" in names else None
+        sums, f, dmap, lpl = Fn.deltae(p, t, variant=0, clamp_in=True, want_map=want_map, want_l=want_l, sqerr_out=sql)
+        sq = sql[0] if sql is not None else None
+        fl.append(f)
+    ssim_sums, ssim_count, ssim_c = None, 1, 1
+    if "linear_ssim" in names:
+        kw = opts.get("linear_ssim", {})
+        ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)), sigma=1.5,
+                                                          k1=0.01, k2=0.03)
+        ssim_c = ssim_sums.shape[1]
+        fl.append(f)
+    p95 = None
+    if "deltae2000_p95" in names:
+        p95, _, _ = Fn.select_quantiles(dmap.view(n, -1), [0.95], joint=True)
+    esum = ecnt = None
+    if "edge_deltae2000_mean" in names:
+        q = float(opts.get("edge_deltae2000_mean", {}).get("q", 0.85))
+        grad = Fn.sobel_magnitude(lpl)
+        thr, _, _ = Fn.select_quantiles(grad.view(n, h * w), [q], joint=False)
+        _, ecnt, esum = Fn.select_quantiles(dmap.view(n, h * w), [], joint=True, gate=grad.view(n, h * w),
+                                            gate_thr=thr.view(n).contiguous(), want_sum=True)
+    while len(fl) < 4:
+        fl.append(None)
+    d = nat.EvalDesc(n, c, h * w, ssim_c, ssim_count, float(opts.get("linear_psnr", {}).get("data_range", 1.0)),
+                     len(names), slot.get("linear_psnr", -1), slot.get("linear_ssim", -1),
+                     slot.get("deltae2000_mean", -1), slot.get("deltae2000_p95", -1),
+                     slot.get("edge_deltae2000_mean", -1))
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_eval_accumulate(d, nat.ptr(sq), nat.ptr(ssim_sums), nat.ptr(sums), nat.ptr(p95),
+                                            nat.ptr(esum), nat.ptr(ecnt), nat.ptr(fl[0]), nat.ptr(fl[1]),
+                                            nat.ptr(fl[2]), nat.ptr(fl[3]), nat.ptr(acc.vec), nat.stream_ptr(dev))
+    nat.check(rc, "llie_eval_accumulate")
+    nat.count_launch()
+    return True
+
+
 # ------------------------------------------------------------------------------------------------
 # sharding + the one collective
 # ------------------------------------------------------------------------------------------------
@@ -211,6 +278,8 @@ def evaluate_pairs(pairs, names: Sequence[str], *, n_items: Optional[int] = None
     flags = torch.zeros(1, dtype=torch.int32, device=acc.device)
     for i in shard_indices(total, rank, world_size, shard):
         pred, target = getter(i)
+        if metric_fn is None and acc.device.type == "cuda" and accumulate_image_metrics(pred, target, names, acc, **opts):
+            continue  # raw sums -> adapter values -> acc.vec in one launch
         flags.zero_()
         vals = fn(pred, target, names, flags, **opts)
         acc.add(vals, flags)

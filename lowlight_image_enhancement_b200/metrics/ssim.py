@@ -105,11 +105,25 @@ def torchmetrics_ssim_scores(pred: Tensor, target: Tensor, *, data_range: float,
         raise NotImplementedError("the CUDA SSIM kernel supports Gaussian supports up to 15 taps (sigma <= 2.07)")
     if h <= 2 * pad or w <= 2 * pad:
         raise ValueError(f"Images of size {(h, w)} are too small for a {gk}x{gk} SSIM window.")
+    sums, count, _ = ssim_sums_torchmetrics(pred, target, data_range=data_range, sigma=sigma, k1=k1, k2=k2, luma=luma)
+    return (sums.sum(dim=1) / float(count)).to(torch.float32)
+
+
+def ssim_sums_torchmetrics(pred: Tensor, target: Tensor, *, data_range: float, sigma: float, k1: float, k2: float,
+                           luma: bool = False):
+    """The raw form of `torchmetrics_ssim_scores`: (float64 sums [N, Co] of the interior SSIM map, elements per image
+    those sums cover, kernel flags) -- score_n = float32(sums[n].sum() / count)."""
+    n, c, h, w = pred.shape
+    gk = int(3.5 * sigma + 0.5) * 2 + 1
+    pad = (gk - 1) // 2
+    if gk > 15:
+        raise NotImplementedError("the CUDA SSIM kernel supports Gaussian supports up to 15 taps (sigma <= 2.07)")
+    if h <= 2 * pad or w <= 2 * pad:
+        raise ValueError(f"Images of size {(h, w)} are too small for a {gk}x{gk} SSIM window.")
     win = Fn.window_1d("torchmetrics", gk, float(sigma), pred.device)
-    sums, _, _ = Fn.ssim_stats(pred, target, win, pad_mode=nat.PAD["reflect"], c1=(k1 * data_range) ** 2,
-                               c2=(k2 * data_range) ** 2, eps=0.0, luma=luma, interior=True)
-    co = sums.shape[1]
-    return (sums.sum(dim=1) / float(co * (h - 2 * pad) * (w - 2 * pad))).to(torch.float32)
+    sums, flags, _ = Fn.ssim_stats(pred, target, win, pad_mode=nat.PAD["reflect"], c1=(k1 * data_range) ** 2,
+                                   c2=(k2 * data_range) ** 2, eps=0.0, luma=luma, interior=True)
+    return sums, sums.shape[1] * (h - 2 * pad) * (w - 2 * pad), flags
 
 
 class SSIMEvaluator:

@@ -88,3 +88,51 @@ def test_psnr_full_size_properties(dev):
     b = float(psnr_linear(pred * 255, gt * 255, data_range=255.0))
     assert abs(a - b) < 1e-5 * abs(a)
     assert abs(float(cpsnr_rgb(pred, gt)) - a) < 1e-5
+
+
+@pytest.mark.parametrize("names", [
+    ["linear_psnr", "linear_ssim", "deltae2000_mean", "edge_deltae2000_mean"],
+    ["deltae2000_p95", "linear_ssim"],
+    ["edge_deltae2000_mean", "deltae2000_mean", "deltae2000_p95", "linear_psnr", "linear_ssim"],
+    ["linear_ssim"],
+])
+@pytest.mark.parametrize("batch", [1, 2])
+def test_one_launch_eval_epilogue_matches_torch_glue(names, batch):
+    """`accumulate_image_metrics` (raw device sums -> adapter values -> running vector in ONE launch,
+    llie_eval_accumulate) against `image_metrics` + `ShardedMeans.add` (the same arithmetic as torch glue): identical
+    float64 sums, counts and non-finite flags; requests it does not cover report False and launch nothing."""
+    from lowlight_image_enhancement_b200.eval import ShardedMeans, accumulate_image_metrics, evaluate_pairs, image_metrics
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(41 + batch)
+    pairs = []
+    for i in range(3):
+        gt = torch.round(255 * torch.nn.functional.avg_pool2d(torch.rand(batch, 3, 72, 100, generator=g), 5, 1, 2)) / 255
+        pr = (gt + 0.04 * torch.randn(gt.shape, generator=g)).clamp(0, 1)
+        pairs.append((pr.to(dev), gt.to(dev)))
+    pairs[1][0][0, 1, 5, 5] = float("nan")  # one pair with a non-finite input
+    fast, slow = ShardedMeans(names, dev), ShardedMeans(names, dev)
+    flags = torch.zeros(1, dtype=torch.int32, device=dev)
+    for pr, gt in pairs:
+        assert accumulate_image_metrics(pr, gt, names, fast)
+        flags.zero_()
+        slow.add(image_metrics(pr, gt, names, flags), flags)
+    a, b = fast.vec.cpu(), slow.vec.cpu()
+    k = len(names)
+    assert a[k] == b[k] == 3 and a[k + 1] == b[k + 1] == 1
+    ok = ~torch.isnan(b[:k])
+    assert torch.equal(torch.isnan(a[:k]), torch.isnan(b[:k]))
+    assert torch.allclose(a[:k][ok], b[:k][ok], rtol=1e-12, atol=0), (a, b)
+    # the driver takes the fast path and reports the same means
+    clean = [pairs[0], pairs[2]]
+    res = evaluate_pairs(clean, names, device=dev, rank=0, world_size=1)
+    ref = ShardedMeans(names, dev)
+    for pr, gt in clean:
+        flags.zero_()
+        ref.add(image_metrics(pr, gt, names, flags), flags)
+    want = ref.reduce()
+    for nm in names:
+        assert res[nm] == pytest.approx(want[nm], rel=1e-12), nm
+    assert res["count"] == 2 and res["nonfinite_inputs"] == 0
+    # not covered: PSNR without a colour pass, unknown names, a vector on another device
+    assert not accumulate_image_metrics(pairs[0][0], pairs[0][1], ["linear_psnr"], ShardedMeans(["linear_psnr"], dev))
+    assert not accumulate_image_metrics(pairs[0][0], pairs[0][1], names, ShardedMeans(names, "cpu"))
