@@ -143,8 +143,19 @@ def image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], flags: Opt
 _FAST = ("linear_psnr", "linear_ssim", "deltae2000_mean", "deltae2000_p95", "edge_deltae2000_mean")
 
 
+_side: Dict[int, "torch.cuda.Stream"] = {}
+
+
+def _side_stream(dev: torch.device) -> "torch.cuda.Stream":
+    st = _side.get(dev.index)
+    if st is None:
+        st = _side[dev.index] = torch.cuda.Stream(dev)
+    return st
+
+
 @torch.no_grad()
-def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], acc: "ShardedMeans", **opts) -> bool:
+def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], acc: "ShardedMeans", *,
+                             concurrent: bool = True, **opts) -> bool:
     """`acc.add(image_metrics(pred, target, names, flags), flags)` with the whole epilogue in ONE launch
     (`llie_eval_accumulate`): the metric kernels leave their raw sums on the device and a single-thread kernel forms
     the adapter values and adds them to `acc.vec`.  Returns False (nothing launched) when the request is outside what
@@ -166,19 +177,35 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
     slot = {nm: i for i, nm in enumerate(names)}
     fl: List[Optional[Tensor]] = []
     sq = sums = dmap = lpl = None
+    ssim_sums, ssim_count, ssim_c = None, 1, 1
+    main = torch.cuda.current_stream(dev)
+    joined = None
+    if "linear_ssim" in names:
+        kw = opts.get("linear_ssim", {})
+        # SSIM shares nothing with the colour / edge chain but the inputs: on a side stream (own workspace) its CTAs
+        # fill the SMs that the chain's one-block scans, small Sobel / histogram grids and kernel tails leave idle
+        side = _side_stream(dev) if colour and concurrent else None
+        if side is not None:
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
+                                                                  sigma=1.5, k1=0.01, k2=0.03)
+            for x_ in (ssim_sums, f):
+                x_.record_stream(main)
+            for x_ in (p, t):
+                x_.record_stream(side)
+            joined = side
+        else:
+            ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
+                                                              sigma=1.5, k1=0.01, k2=0.03)
+        ssim_c = ssim_sums.shape[1]
+        fl.append(f)
     if colour:
         want_map = any(_COLOUR[nm][0] for nm in colour)
         want_l = any(_COLOUR[nm][1] for nm in colour)
         sql = [] if "linear_psnr" in names else None
         sums, f, dmap, lpl = Fn.deltae(p, t, variant=0, clamp_in=True, want_map=want_map, want_l=want_l, sqerr_out=sql)
         sq = sql[0] if sql is not None else None
-        fl.append(f)
-    ssim_sums, ssim_count, ssim_c = None, 1, 1
-    if "linear_ssim" in names:
-        kw = opts.get("linear_ssim", {})
-        ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)), sigma=1.5,
-                                                          k1=0.01, k2=0.03)
-        ssim_c = ssim_sums.shape[1]
         fl.append(f)
     p95 = None
     if "deltae2000_p95" in names:
@@ -192,6 +219,8 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
                                             gate_thr=thr.view(n).contiguous(), want_sum=True)
     while len(fl) < 4:
         fl.append(None)
+    if joined is not None:
+        main.wait_stream(joined)
     d = nat.EvalDesc(n, c, h * w, ssim_c, ssim_count, float(opts.get("linear_psnr", {}).get("data_range", 1.0)),
                      len(names), slot.get("linear_psnr", -1), slot.get("linear_ssim", -1),
                      slot.get("deltae2000_mean", -1), slot.get("deltae2000_p95", -1),
