@@ -263,6 +263,7 @@ class HybridLossPlus(nn.Module):
         device = _resolve_device(device)
         self.register_buffer("_zero", torch.tensor(0.0), persistent=False)
         self._zero: Tensor
+        self._zero_cache: Dict[torch.device, Tensor] = {}
         self.l1_raw = _L1Mean()
         self.perc = perceptual_module
         self.deltaE = DeltaE00Loss() if use_deltaE else None
@@ -283,6 +284,14 @@ class HybridLossPlus(nn.Module):
                                                for k in ("l1", "perc", "lpips", "de", "ssim", "phys")})
         else:
             self.w = dict(l1=w_l1_raw, perc=w_perc, lpips=w_lpips, de=w_deltaE, ssim=w_ssim, phys=w_phys)
+
+    def _zero_on(self, dev: torch.device) -> Tensor:
+        """A fresh 0-d zero on `dev` without a host -> device copy per step: the buffer lives wherever the module
+        was left (CPU unless `.to()` was called), and a pageable H2D copy is a full stream synchronisation."""
+        z = self._zero_cache.get(dev)
+        if z is None:
+            z = self._zero_cache[dev] = torch.zeros((), dtype=self._zero.dtype, device=dev)
+        return z.clone()
 
     @staticmethod
     def _ensure_finite(name: str, value: Tensor):
@@ -362,7 +371,7 @@ class HybridLossPlus(nn.Module):
             lw, logs["Perc"] = self._weighted("perc", lp)
             total = total + lw.to(dev)
         else:
-            logs["Perc"] = self._zero.clone().to(home)
+            logs["Perc"] = self._zero_on(home)
         if self.lpips is not None:
             ll = self.lpips(Bhat_srgb01, B_srgb01).mean()
             checks.append(("LPIPS", ll))
@@ -404,7 +413,7 @@ class HybridLossPlus(nn.Module):
         if self.perc is not None:
             add("Perc", "perc", "Perc", self.perc(Bhat_srgb01, B_srgb01))
         else:
-            logs["Perc"] = self._zero.clone().to(Bhat_raw.device)
+            logs["Perc"] = self._zero_on(Bhat_raw.device)
         if self.lpips is not None:
             add("LPIPS", "lpips", "LPIPS", self.lpips(Bhat_srgb01, B_srgb01).mean())
         if self.deltaE is not None:

@@ -442,7 +442,7 @@ static int launch_ssim_stream(const SsimArgs &a, int grid, cudaStream_t st) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-// Streaming variant 2 (statistics only: no SSIM map, no loss coefficients; the eval / metric path): the same row
+// Streaming variant 2 (no SSIM map; statistics, optionally the loss-coefficient planes): the same row
 // ring and rolling vertical accumulators, but
 //   * one thread owns TWO adjacent output columns of a 256-column strip: the K + 1 input values it needs per row and
 //     array come from (K + 1) / 2 conflict-free LDS.64, the x^2 / y^2 / xy products of a position are formed once and
@@ -456,7 +456,7 @@ static int launch_ssim_stream(const SsimArgs &a, int grid, cudaStream_t st) {
 constexpr int S2W = 256;
 constexpr int S2T = 128;
 
-template <int K, bool MAPS5>
+template <int K, bool MAPS5, bool COEF = false>
 __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) {
     constexpr int P = K / 2;
     constexpr int RW = S2W + 2 * P;  // even: row starts stay 8-byte aligned
@@ -530,6 +530,9 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
 #pragma unroll
             for (int j = 0; j < K; ++j) acc[q][c][j] = 0.f;
     float facc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    const long long cstride = (long long)d.n * a.co * plane_elems;
+    long long off = ((long long)plane * H + y0) * W + gx;  // COEF: first element of the next completed row
+    const bool vec2 = (W & 1) == 0;                         // even rows keep the column pair 8-byte aligned
 
 #pragma unroll
     for (int i = 0; i < SD - 1; ++i) issue_row(i);
@@ -597,6 +600,7 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
                 const int sl = (ii + 1) % K;
                 const int gy = y0 + i - (K - 1);
                 const bool row_ok = gy >= lo_y && gy < hi_y;
+                float cf[3][2];
 #pragma unroll
                 for (int c = 0; c < 2; ++c) {
                     const float mx = acc[0][c][sl], my = acc[1][c][sl];
@@ -617,8 +621,36 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
                     const float num = (2.f * mxy + d.c1) * (2.f * sxy + d.c2);
                     const float den = (mx2 + my2 + d.c1) * (vsum + d.c2) + d.eps;
                     float sv = num / den;
+                    if (COEF) {  // dLoss/dS times the sensitivities of S to mu_x, E[x^2], E[xy] (ssim_stream_kernel)
+                        const float l = (1.f - sv) * 0.5f;
+                        const float up =
+                            (!d.loss_map) ? a.coef_scale : ((l >= 0.f && l <= 1.f) ? -0.5f * a.coef_scale : 0.f);
+                        const float inv = 1.f / den;
+                        const float n1 = 2.f * mxy + d.c1, n2 = 2.f * sxy + d.c2, d1 = mx2 + my2 + d.c1,
+                                    d2 = vsum + d.c2;
+                        const float a3 = 2.f * n1 * inv;
+                        const float a2 = -sv * d1 * inv;
+                        const float dmu = 2.f * (my * n2 - sv * mx * d2) * inv;
+                        const float a1 = dmu - 2.f * mx * a2 - my * a3;
+                        cf[0][c] = up * a1;
+                        cf[1][c] = up * a2;
+                        cf[2][c] = up * a3;
+                    }
                     if (d.loss_map) sv = fminf(fmaxf((1.f - sv) * 0.5f, 0.f), 1.f);
                     if (col_ok[c] && row_ok) facc += sv;
+                }
+                if (COEF) {
+                    float *cp = a.coef + off;
+#pragma unroll
+                    for (int q = 0; q < 3; ++q) {
+                        if (vec2 && gx + 1 < W) {
+                            *reinterpret_cast<float2 *>(cp + q * cstride) = make_float2(cf[q][0], cf[q][1]);
+                        } else {
+                            if (gx < W) cp[q * cstride] = cf[q][0];
+                            if (gx + 1 < W) cp[q * cstride + 1] = cf[q][1];
+                        }
+                    }
+                    off += W;
                 }
             }
         }
@@ -658,7 +690,9 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
 
 template <int K>
 static int launch_ssim_stream2(const SsimArgs &a, int grid, cudaStream_t st) {
-    if (a.d.clamp_var)
+    if (a.coef != nullptr)
+        ssim_stream2_kernel<K, false, true><<<grid, S2T, 0, st>>>(a);
+    else if (a.d.clamp_var)
         ssim_stream2_kernel<K, true><<<grid, S2T, 0, st>>>(a);
     else
         ssim_stream2_kernel<K, false><<<grid, S2T, 0, st>>>(a);
@@ -1045,7 +1079,9 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
     long long grid;
     const bool stream_ok = g_ssim_path != 1 && !d.luma;
     // statistics only (no map / coefficient planes), the 11-tap window of all three reference policies
-    const bool stream2_ok = stream_ok && g_ssim_path == 0 && d.ksize == 11 && out_map == nullptr && coef == nullptr;
+    // (the loss-coefficient planes are written by the four-map instantiation: no variance clamp on that path)
+    const bool stream2_ok = stream_ok && g_ssim_path == 0 && d.ksize == 11 && out_map == nullptr &&
+                            (coef == nullptr || !d.clamp_var);
     if (stream2_ok) {
         // strips of 256 columns x row segments sized for ~2 resident waves (148 SMs x 3 CTAs), >= 64 rows each
         a.tiles_x = div_up(d.w, S2W);
