@@ -273,6 +273,11 @@ int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y, const flo
                          int32_t accumulate, double *out_sum, float *out_grad, int32_t *out_flags, void *workspace,
                          void *stream);
 
+/* g[0..n) *= *scale (device scalar), a no-op launch when *scale == 1: applies autograd's upstream scalar to a gradient
+ * that a value + gradient kernel already produced in the forward pass.  replaces the `grad * grad_output` multiply of
+ * the autograd graph behind NewBP_model/losses.py:92-372. */
+int llie_scale_inplace(float *g, int64_t n, const float *scale, void *stream);
+
 /* Merge of overlapping validation tiles: out[1, c, h, w] = average over the tiles covering each pixel, summed in
  * tile order (tiles [n_tiles, c, tile_h, tile_w], tile_ij [n_tiles][2] = top-left (row, col), int32, device).
  * replaces NAFNet_base/basicsr/models/image_restoration_model.py:215-241 (grids_inverse, done on the host there). */

@@ -531,6 +531,25 @@ def select_quantiles(values: Tensor, qs, *, joint: bool, gate: Optional[Tensor] 
 # ------------------------------------------------------------------------------------------------
 # Differentiable loss terms (NewBP_model/losses.py:92-155)
 # ------------------------------------------------------------------------------------------------
+def apply_upstream(ctx, grad: Tensor, gout: Tensor) -> Tensor:
+    """`grad * gout` for a gradient buffer this node produced in its forward pass and a 0-d upstream gradient: scaled
+    IN PLACE by a kernel that exits at once when the scalar is 1 (`loss.backward()`), so the common case costs a
+    launch instead of a read + write of the buffer.  The buffer is private to the node; a second backward through a
+    retained graph (or anything but a 0-d float upstream) takes the plain out-of-place multiply."""
+    if getattr(ctx, "_llie_scaled", False) or gout.dim() != 0 or not gout.is_cuda or gout.device != grad.device \
+            or torch.is_grad_enabled() and gout.requires_grad:
+        prev = getattr(ctx, "_llie_prev", None)
+        return grad * (gout if prev is None else gout / prev)
+    g = gout.detach().to(torch.float32)
+    dev = grad.device
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_scale_inplace(nat.ptr(grad), grad.numel(), nat.ptr(g), nat.stream_ptr(dev))
+    nat.check(rc, "llie_scale_inplace")
+    nat.count_launch()
+    ctx._llie_scaled, ctx._llie_prev = True, g
+    return grad
+
+
 class DeltaE00LossFn(torch.autograd.Function):
     """mean dE00 (loss variant) of clamp(gen,0,1) vs clamp(tgt,0,1); the gradient w.r.t. `gen` is produced by
     the same kernel pass as the value (llie_deltae_loss_grad) and only scaled in backward."""
@@ -564,7 +583,7 @@ class DeltaE00LossFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gout):
         (grad,) = ctx.saved_tensors
-        return grad * gout, None, None
+        return apply_upstream(ctx, grad, gout), None, None
 
 
 class SSIMLossFn(torch.autograd.Function):
@@ -645,7 +664,7 @@ class L1MeanFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, gout):
         (grad,) = ctx.saved_tensors
-        return grad * gout, None
+        return apply_upstream(ctx, grad, gout), None
 
 
 _ones: dict = {}
@@ -773,5 +792,13 @@ class HybridFusedFn(torch.autograd.Function):
         saved = list(ctx.saved_tensors)
         g_raw = saved.pop(0) if ctx.have[0] else None
         g_srgb = saved.pop(0) if ctx.have[1] else None
-        return (g_raw * gtot if g_raw is not None else None, g_srgb * gtot if g_srgb is not None else None,
-                None, None, None)
+        if g_raw is not None and g_srgb is not None:
+            # two buffers, one upstream scalar: the "already scaled" bookkeeping is per node, so scale both now
+            again = getattr(ctx, "_llie_scaled", False)
+            g_raw = apply_upstream(ctx, g_raw, gtot)
+            if not again:
+                ctx._llie_scaled = False
+            g_srgb = apply_upstream(ctx, g_srgb, gtot)
+            return g_raw, g_srgb, None, None, None
+        return (apply_upstream(ctx, g_raw, gtot) if g_raw is not None else None,
+                apply_upstream(ctx, g_srgb, gtot) if g_srgb is not None else None, None, None, None)
