@@ -237,3 +237,38 @@ def test_legacy_hybrid_loss(dev):
     assert _rel(x.grad, xr.grad) < 1e-6
     tot2, _, p2 = HybridLoss(device="cuda")(x.detach(), b.to(dev))
     assert float(p2) == 0.0 and abs(float(tot2) - float(l1)) < 1e-7
+
+
+def test_upstream_scalar_is_applied_in_place_and_survives_retained_graphs(dev):
+    """The gradient buffers the value + gradient kernels fill in forward are scaled by autograd's upstream scalar in
+    place (a no-op launch for 1.0): any scalar, and repeated backward passes through a retained graph, must give
+    scale x the unit gradient -- for the single-term losses and for the fused HybridLossPlus node (two buffers)."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import DeltaE00Loss, HybridLossPlus
+    g = torch.Generator().manual_seed(91)
+    b = torch.rand(2, 3, 40, 48, generator=g).to(dev)
+    x0 = (b + 0.05 * torch.randn(b.shape, generator=g).to(dev)).clamp(0, 1)
+
+    def unit_and_scaled(make_loss, scales):
+        x = x0.clone().requires_grad_(True)
+        make_loss(x).backward()
+        unit = x.grad.clone()
+        x = x0.clone().requires_grad_(True)
+        loss = make_loss(x)
+        got = []
+        for i, s in enumerate(scales):
+            x.grad = None
+            (loss * s).backward(retain_graph=i + 1 < len(scales))
+            got.append(x.grad.clone())
+        return unit, got
+
+    de = DeltaE00Loss()
+    kern = torch.tensor([[.01, .02, .01], [.02, .88, .02], [.01, .02, .01]], device=dev).view(1, 1, 3, 3)
+    hyb = HybridLossPlus(device=dev, w_phys=0.05, physics_kernel=kern, check_finite=False)
+    rho = torch.ones(2, 1, 1, 1, device=dev)
+    for make in (lambda x: de(x, b),
+                 lambda x: hyb(Bhat_raw=x, B_raw=b, A_raw=b * 0.9, expo_ratio=rho, Bhat_srgb01=x, B_srgb01=b)[0]):
+        scales = [1.0, 2.5, -0.75, 1.0]
+        unit, got = unit_and_scaled(make, scales)
+        assert float(unit.abs().max()) > 0
+        for s, gr in zip(scales, got):
+            assert torch.allclose(gr, unit * s, rtol=2e-6, atol=1e-12), s
