@@ -1018,6 +1018,217 @@ static int launch_ssim_bwd_stream(const SsimBwdArgs &a, int grid, int seg_rows, 
     return LLIE_OK;
 }
 
+// Two-column streaming backward (default for the 11-tap window): the structure of ssim_bwd_stream_kernel with the
+// column pairing of ssim_stream2_kernel -- 256-column strips, one thread = two adjacent gradient columns, the K + 1
+// coefficient values per row and plane from (K + 1) / 2 LDS.64, per-row bookkeeping paid per two elements.  Each of the
+// two columns carries its own horizontal taps (mirror folds added), the vertical fold weights are shared.
+template <int K>
+__global__ void __launch_bounds__(S2T, 3) ssim_bwd_stream2_kernel(const SsimBwdArgs a, int seg_rows) {
+    constexpr int P = K / 2;
+    constexpr int RW = S2W + 2 * P;
+    static_assert(2 * P <= S2T && (RW % 2) == 0, "halo slots are loaded by the first 2P threads");
+    __shared__ __align__(16) float sC[3][SD][RW];
+    __shared__ __align__(16) float sIO[3][SD][S2W];  // x, y and (accumulate) the old gradient of the row a ring entry completes
+    __shared__ float sg[K];
+    const int H = a.h, W = a.w, tid = threadIdx.x;
+    const int tpp = a.tiles_x * a.tiles_y;
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int seg = trem / a.tiles_x, strip = trem - seg * a.tiles_x;
+    const int x0 = strip * S2W, y0 = seg * seg_rows;
+    const int rows_out = min(seg_rows, H - y0);
+    const int nrows_in = rows_out + 2 * P;
+    const long long plane_elems = (long long)H * W;
+    const long long cstride = (long long)a.n * a.c * plane_elems;
+    const float *cb = a.coef + (long long)plane * plane_elems;
+    const float gs = __ldg(a.gout);
+
+    float g[K];
+#pragma unroll
+    for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
+    if (tid < K) sg[tid] = __ldg(a.win + tid);
+
+    // ring slots of this thread: tid, S2T + tid, 2 * S2T + tid (right halo, tid < 2P); zero outside the image
+    const bool has_ext = tid < 2 * P;
+    unsigned cbytes[3];
+    const float *pc[3];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int gin = x0 - P + s * S2T + tid;
+        cbytes[s] = ((s < 2 || has_ext) && gin >= 0 && gin < W) ? 4u : 0u;
+        pc[s] = cb + min(max(gin, 0), W - 1);
+    }
+    const unsigned sca = (unsigned)__cvta_generic_to_shared(&sC[0][0][tid]);
+    const unsigned sio = (unsigned)__cvta_generic_to_shared(&sIO[0][0][2 * tid]);
+    const int gx = x0 + 2 * tid;
+    const bool in0 = gx < W, in1 = gx + 1 < W;
+    const bool vec2 = (W & 1) == 0;  // even rows keep the column pair 8-byte aligned
+    const float *xb = a.x + (long long)plane * plane_elems + gx, *yb = a.y + (long long)plane * plane_elems + gx;
+    float *ob = a.out_grad + (long long)plane * plane_elems + gx;
+    const float *iosrc[3] = {xb, yb, ob};
+    const int nio = a.accumulate ? 3 : 2;
+
+    auto issue_row = [&](int i) {
+        if (i < nrows_in) {
+            if (i >= K - 1) {
+                // x / y / old gradient of output row oy = y0 + i - (K - 1), which ring entry i completes: they travel
+                // with the coefficient row (three rows ahead) instead of stalling the row on global loads
+                const long long oo = (long long)(y0 + i - (K - 1)) * W;
+                const unsigned so2 = (unsigned)((i & (SD - 1)) * S2W * 4);
+                for (int m = 0; m < nio; ++m) {
+                    const unsigned dst = sio + m * SD * S2W * 4 + so2;
+                    if (vec2) {
+                        asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;" ::"r"(dst),
+                                     "l"(in0 ? iosrc[m] + oo : a.x), "r"(in0 ? 8u : 0u)
+                                     : "memory");
+                    } else {
+                        cp_async4(dst, in0 ? iosrc[m] + oo : a.x, in0 ? 4u : 0u);
+                        cp_async4(dst + 4, in1 ? iosrc[m] + oo + 1 : a.x, in1 ? 4u : 0u);
+                    }
+                }
+            }
+            const int sy = y0 - P + i;
+            const unsigned ok = (sy >= 0 && sy < H) ? 4u : 0u;
+            const long long ro = (long long)min(max(sy, 0), H - 1) * W;
+            const unsigned so = (unsigned)((i & (SD - 1)) * RW * 4);
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+#pragma unroll
+                for (int s = 0; s < 2; ++s)
+                    cp_async4(sca + m * SD * RW * 4 + so + s * S2T * 4, pc[s] + m * cstride + ro, min(cbytes[s], ok));
+                if (has_ext)
+                    cp_async4(sca + m * SD * RW * 4 + so + 2 * S2T * 4, pc[2] + m * cstride + ro, min(cbytes[2], ok));
+            }
+        }
+        cp_async_commit();
+    };
+
+    const bool seg_fold = (y0 <= P) || (y0 + rows_out > H - 1 - P);
+    float acc[3][2][K];
+#pragma unroll
+    for (int m = 0; m < 3; ++m)
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+#pragma unroll
+            for (int j = 0; j < K; ++j) acc[m][c][j] = 0.f;
+
+#pragma unroll
+    for (int i = 0; i < SD - 1; ++i) issue_row(i);
+    __syncthreads();  // sg visible
+    // horizontal taps of the two columns with the mirror folds added (see ssim_bwd_stream_kernel)
+    float gh[2][K];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        const int gc = gx + c;
+        const bool cin = gc < W;
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+            float wj = g[j];
+            const int x = gc - P + j;
+            if (cin && gc >= 1 && gc <= P && x >= 0 && j + 2 * gc <= 2 * P) wj += sg[j + 2 * gc];
+            if (cin && gc >= W - 1 - P && gc <= W - 2 && x <= W - 1 && j + 2 * gc - 2 * W + 2 >= 0)
+                wj += sg[j + 2 * gc - 2 * W + 2];
+            gh[c][j] = wj;
+        }
+    }
+    for (int base = 0; base < nrows_in; base += K) {
+#pragma unroll
+        for (int ii = 0; ii < K; ++ii) {
+            const int i = base + ii;
+            if (i >= nrows_in) break;  // uniform
+            const int slot = i & (SD - 1);
+            cp_async_wait<SD - 2>();
+            __syncthreads();
+            issue_row(i + SD - 1);
+            const int p = y0 - P + i;
+            const bool vfold = seg_fold && (p < P || p >= H - P);  // uniform; only <= 2P rows of the image
+            const int oy = y0 + i - (K - 1);
+            // x, y (and the old gradient) of the output row this iteration completes: this thread's own ring words
+            const float2 xq = *reinterpret_cast<const float2 *>(&sIO[0][slot][2 * tid]);
+            const float2 yq = *reinterpret_cast<const float2 *>(&sIO[1][slot][2 * tid]);
+            const float2 oq = a.accumulate ? *reinterpret_cast<const float2 *>(&sIO[2][slot][2 * tid])
+                                           : make_float2(0.f, 0.f);
+            const float xr[2] = {xq.x, xq.y}, yr[2] = {yq.x, yq.y};
+            float h[3][2];
+#pragma unroll
+            for (int m = 0; m < 3; ++m) {
+                const float2 *row2 = reinterpret_cast<const float2 *>(&sC[m][slot][0]) + tid;
+                float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+                for (int k = 0; k < (K + 1) / 2; ++k) {
+                    const float2 cv = row2[k];
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int q = 2 * k + e;  // position q: tap q of column 0, tap q - 1 of column 1
+                        const float ce = e ? cv.y : cv.x;
+                        if (q <= K - 1) v0 = fmaf(gh[0][q <= K - 1 ? q : 0], ce, v0);
+                        if (q >= 1) v1 = fmaf(gh[1][q >= 1 ? q - 1 : 0], ce, v1);
+                    }
+                }
+                h[m][0] = v0;
+                h[m][1] = v1;
+            }
+            if (!vfold) {
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    const int sl = (ii - j + K) % K;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m)
+#pragma unroll
+                        for (int c = 0; c < 2; ++c)
+                            acc[m][c][sl] = (j == 0) ? g[0] * h[m][c] : fmaf(g[j], h[m][c], acc[m][c][sl]);
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < K; ++j) {
+                    const int sl = (ii - j + K) % K;
+                    const int y = y0 + i - j;
+                    float wj = g[j];
+                    if (y >= 1 && y <= P && p >= 0 && p + y <= P) wj += sg[p + y + P];
+                    if (y >= H - 1 - P && y <= H - 2 && p <= H - 1 && p >= 2 * H - 2 - y - P)
+                        wj += sg[p - (2 * H - 2 - y) + P];
+#pragma unroll
+                    for (int m = 0; m < 3; ++m)
+#pragma unroll
+                        for (int c = 0; c < 2; ++c)
+                            acc[m][c][sl] = (j == 0) ? wj * h[m][c] : fmaf(wj, h[m][c], acc[m][c][sl]);
+                }
+            }
+            if (i >= K - 1 && in0) {
+                const int sl = (ii + 1) % K;
+                float res[2];
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    float xv = xr[c], yv = yr[c];
+                    bool pass = true;
+                    if (a.clamp_in) {
+                        pass = (xr[c] >= 0.f && xr[c] <= 1.f);
+                        xv = fminf(fmaxf(xv, 0.f), 1.f);
+                        yv = fminf(fmaxf(yv, 0.f), 1.f);
+                    }
+                    const float gr = gs * (acc[0][c][sl] + 2.f * xv * acc[1][c][sl] + yv * acc[2][c][sl]);
+                    res[c] = pass ? gr : 0.f;
+                }
+                float *o = ob + (long long)oy * W;
+                if (vec2) {
+                    *reinterpret_cast<float2 *>(o) = make_float2(oq.x + res[0], oq.y + res[1]);
+                } else {
+                    o[0] = oq.x + res[0];
+                    if (in1) o[1] = oq.y + res[1];
+                }
+            }
+        }
+    }
+    cp_async_wait<0>();
+}
+
+template <int K>
+static int launch_ssim_bwd_stream2(const SsimBwdArgs &a, int grid, int seg_rows, cudaStream_t st) {
+    ssim_bwd_stream2_kernel<K><<<grid, S2T, 0, st>>>(a, seg_rows);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
 template <int K>
 static int launch_ssim_bwd(const SsimBwdArgs &a, int grid, cudaStream_t st) {
     constexpr int P = K / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
@@ -1172,7 +1383,17 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
     a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map; a.accumulate = accumulate;
     a.x = x; a.y = y; a.win = win1d; a.coef = coef; a.gout = grad_out; a.out_grad = out_grad;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (g_ssim_path == 0 && !grad_out_is_map) {
+    if (g_ssim_path == 0 && !grad_out_is_map && d.ksize == 11) {
+        a.tiles_x = div_up(d.w, S2W);
+        const long long cols = (long long)d.n * d.c * a.tiles_x;
+        const int rows = g_ssim_seg_rows > 0 ? (g_ssim_seg_rows < d.h ? g_ssim_seg_rows : d.h)
+                                             : pick_seg_rows(cols, d.h, kNumSM * 3, 64, d.ksize - 1);
+        a.tiles_y = div_up(d.h, rows);
+        const long long grid = cols * a.tiles_y;
+        LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
+        return launch_ssim_bwd_stream2<11>(a, (int)grid, rows, st);
+    }
+    if (g_ssim_path != 1 && !grad_out_is_map) {
         a.tiles_x = div_up(d.w, SW);
         const long long cols = (long long)d.n * d.c * a.tiles_x;
         int segs = (int)((148LL * 5 * 3 + cols - 1) / cols);
