@@ -340,6 +340,11 @@ int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const 
  * < 1 ulp claim can be checked against a float64 pow from the test-suite. */
 int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream);
 
+/* Accuracy self-test hook: the kernels divide by their compile-time constants (which: 0 1.055, 1 12.92, 2 0.95047,
+ * 3 1.08883, 4 25, 5 pi) with a three-instruction FMA sequence that must equal the IEEE division; *out_mismatch (device)
+ * = number of operands among the float bit patterns first_bits .. first_bits + count - 1 where it does not. */
+int llie_selftest_div_const(int32_t which, uint32_t first_bits, uint64_t count, uint64_t *out_mismatch, void *stream);
+
 /* Sobel magnitude sqrt(gx^2 + gy^2 + 1e-12) of [planes, h, w], zero padding (color_error.py:23-30, 296-301) */
 int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w, void *stream);
 

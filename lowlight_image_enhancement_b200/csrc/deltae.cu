@@ -19,6 +19,19 @@ namespace llie {
 
 constexpr float kPi = 3.14159265358979323846f;
 
+// x / C for a compile-time constant C, correctly rounded, in three instructions (Markstein): with y = RN(1 / C) folded
+// at compile time, q = RN(x y) is within an ulp of the quotient, r = x - C q is exact in one FMA and RN(q + r y) is the
+// IEEE quotient -- for every finite x whose quotient is a normal number and every C whose significand is not all ones
+// (llie_selftest_div_const + tests/test_gpu_ssim_colour.py compare it with the division instruction over hundreds of
+// millions of operands).  The division instruction costs ~12 issue slots with its FCHK / slow-path branch; this
+// kernel divides by constants 18 times per pixel.
+__device__ __forceinline__ float div_const(float x, float c, float rc) {
+    const float q = x * rc;
+    const float r = fmaf(-c, q, x);
+    return fmaf(r, rc, q);
+}
+#define DIVC(x, C) div_const((x), (C), 1.0f / (C))
+
 // b^2.4 for b in [0.09, 1] as (b * b^(1/5))^2.  The fifth root starts from the SFU estimate
 // exp2(0.2 log2 b) (~1e-6 relative) and takes one Newton step whose residual b - y^5 is evaluated with
 // FMA error terms; the correction is kept as a separate term through the final square, so the result is
@@ -35,7 +48,7 @@ __device__ __forceinline__ float pow24(float b) {
     return fmaf(p, p, 2.0f * p * lo);
 }
 __device__ __forceinline__ float srgb_to_linear(float c) {
-    return c > 0.04045f ? pow24((c + 0.055f) / 1.055f) : c / 12.92f;
+    return c > 0.04045f ? pow24(DIVC(c + 0.055f, 1.055f)) : DIVC(c, 12.92f);
 }
 __device__ __forceinline__ float lab_f(float t) {
     return t > 0.008856f ? cbrtf(t) : 7.787f * t + 4.0f / 29.0f;
@@ -66,7 +79,7 @@ __device__ __forceinline__ void rgb_to_lab(float r, float g, float b, float &L, 
     const float x = 0.412453f * r + 0.357580f * g + 0.180423f * b;
     const float y = 0.212671f * r + 0.715160f * g + 0.072169f * b;
     const float z = 0.019334f * r + 0.119193f * g + 0.950227f * b;
-    const float fx = lab_f(x / 0.95047f), fy = lab_f(y / 1.0f), fz = lab_f(z / 1.08883f);
+    const float fx = lab_f(DIVC(x, 0.95047f)), fy = lab_f(y), fz = lab_f(DIVC(z, 1.08883f));
     L = 116.0f * fy - 16.0f;
     A = 500.0f * (fx - fy);
     B = 200.0f * (fy - fz);
@@ -109,7 +122,7 @@ __device__ float de00_metric(float L1, float a1, float b1, float L2, float a2, f
     else
         hb = 0.5f * (hs - 2.0f * kPi);
     const float t = t_weight(hb, nullptr);
-    const float q = ((hb * 180.0f / kPi) - 275.0f) / 25.0f;
+    const float q = DIVC(DIVC(hb * 180.0f, kPi) - 275.0f, 25.0f);
     const float dth = deg2rad(30.0f) * expf(-(q * q));
     const float Cb7 = pow7(Cb);
     const float rc = 2.0f * sqrtf(Cb7 / (Cb7 + k25 + eps));
@@ -147,7 +160,7 @@ __device__ float de00_loss(float L1, float a1, float b1, float L2, float a2, flo
     const float hs = h1 + h2;
     const float hb = hs / 2.0f - (fabsf(h1 - h2) > kPi ? kPi : 0.0f) + (hs < 0.0f ? 2.0f * kPi : 0.0f);
     const float t = t_weight(hb, nullptr);
-    const float q = ((hb * (180.0f / kPi)) - 275.0f) / 25.0f;
+    const float q = DIVC((hb * (180.0f / kPi)) - 275.0f, 25.0f);
     const float dro = 30.0f * expf(-(q * q));
     const float Cb7 = pow7(Cb);
     const float rc = 2.0f * sqrtf(Cb7 / (Cb7 + k25 + eps));
@@ -333,12 +346,12 @@ __device__ D3 de00_loss_dual(float L1f, float a1f, float b1f, float L2, float a2
 // sRGB channel -> linear with derivative (autograd of where(c > .04045, pow(.., 2.4), c / 12.92))
 __device__ __forceinline__ float srgb_to_linear_d(float c, float &dc) {
     if (c > 0.04045f) {
-        const float base = (c + 0.055f) / 1.055f, v = pow24(base);
+        const float base = DIVC(c + 0.055f, 1.055f), v = pow24(base);
         dc = (2.4f / 1.055f) * (v / base);  // 2.4 base^1.4 / 1.055
         return v;
     }
     dc = 1.0f / 12.92f;
-    return c / 12.92f;
+    return DIVC(c, 12.92f);
 }
 __device__ __forceinline__ float lab_f_d(float t, float &dt) {
     if (t > 0.008856f) {
@@ -391,7 +404,7 @@ __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs 
         const float Y = 0.212671f * l0 + 0.715160f * l1 + 0.072169f * l2;
         const float Z = 0.019334f * l0 + 0.119193f * l1 + 0.950227f * l2;
         float dfx, dfy, dfz;
-        const float fx = lab_f_d(X / 0.95047f, dfx), fy = lab_f_d(Y / 1.0f, dfy), fz = lab_f_d(Z / 1.08883f, dfz);
+        const float fx = lab_f_d(DIVC(X, 0.95047f), dfx), fy = lab_f_d(Y, dfy), fz = lab_f_d(DIVC(Z, 1.08883f), dfz);
         const float L1 = 116.0f * fy - 16.0f, A1 = 500.0f * (fx - fy), B1 = 200.0f * (fy - fz);
         float L2, A2, B2;
         rgb_to_lab(t0, t1, t2, L2, A2, B2);
@@ -399,7 +412,7 @@ __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs 
         acc += de.v;
         // reverse through Lab -> f -> XYZ -> linear -> sRGB
         const float gfx = 500.0f * de.y, gfy = 116.0f * de.x - 500.0f * de.y + 200.0f * de.z, gfz = -200.0f * de.z;
-        const float gX = gfx * dfx / 0.95047f, gY = gfy * dfy, gZ = gfz * dfz / 1.08883f;
+        const float gX = DIVC(gfx * dfx, 0.95047f), gY = gfy * dfy, gZ = DIVC(gfz * dfz, 1.08883f);
         const float gl0 = 0.412453f * gX + 0.212671f * gY + 0.019334f * gZ;
         const float gl1 = 0.357580f * gX + 0.715160f * gY + 0.119193f * gZ;
         const float gl2 = 0.180423f * gX + 0.072169f * gY + 0.950227f * gZ;
@@ -572,6 +585,53 @@ __global__ void srgb_to_linear_kernel(const float *in, float *out, long long n) 
         out[i] = srgb_to_linear(in[i]);
 }
 }  // namespace llie
+
+// self-test of div_const: operands are ALL float bit patterns first_bits .. first_bits + count - 1; out_mismatch counts
+// the operands whose three-instruction quotient differs from the division instruction (NaN results compare equal)
+namespace llie {
+template <int WHICH>
+__device__ __forceinline__ bool divc_differs(float x) {
+    float a, b;
+    if (WHICH == 0) { a = DIVC(x, 1.055f); b = __fdiv_rn(x, 1.055f); }
+    else if (WHICH == 1) { a = DIVC(x, 12.92f); b = __fdiv_rn(x, 12.92f); }
+    else if (WHICH == 2) { a = DIVC(x, 0.95047f); b = __fdiv_rn(x, 0.95047f); }
+    else if (WHICH == 3) { a = DIVC(x, 1.08883f); b = __fdiv_rn(x, 1.08883f); }
+    else if (WHICH == 4) { a = DIVC(x, 25.0f); b = __fdiv_rn(x, 25.0f); }
+    else { a = DIVC(x, kPi); b = __fdiv_rn(x, kPi); }
+    return __float_as_uint(a) != __float_as_uint(b) && !(a != a && b != b);
+}
+__global__ void div_const_selftest_kernel(int which, unsigned first_bits, unsigned long long count,
+                                          unsigned long long *out_mismatch) {
+    unsigned long long bad = 0;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < count;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        const float x = __uint_as_float(first_bits + (unsigned)i);
+        bool d;
+        switch (which) {
+            case 0: d = divc_differs<0>(x); break;
+            case 1: d = divc_differs<1>(x); break;
+            case 2: d = divc_differs<2>(x); break;
+            case 3: d = divc_differs<3>(x); break;
+            case 4: d = divc_differs<4>(x); break;
+            default: d = divc_differs<5>(x); break;
+        }
+        bad += d ? 1ull : 0ull;
+    }
+    bad = warp_sum(bad);
+    if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out_mismatch, bad);
+}
+}  // namespace llie
+
+extern "C" int llie_selftest_div_const(int32_t which, uint32_t first_bits, uint64_t count, uint64_t *out_mismatch,
+                                       void *stream) {
+    LLIE_REQUIRE(out_mismatch && which >= 0 && which <= 5 && count > 0, "selftest_div_const: bad arguments");
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    LLIE_CUDA_OK(cudaMemsetAsync(out_mismatch, 0, sizeof(uint64_t), st));
+    div_const_selftest_kernel<<<kNumSM * 16, 256, 0, st>>>(which, first_bits, count,
+                                                           reinterpret_cast<unsigned long long *>(out_mismatch));
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
 
 extern "C" int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream) {
     LLIE_REQUIRE(in && out && n > 0, "selftest_srgb_to_linear: bad arguments");
