@@ -472,9 +472,9 @@ __device__ __forceinline__ float sobel_mag(float v00, float v01, float v02, floa
 }
 
 // grid (ceil(W / 256), ceil(H / kSobelRows), planes), 256 threads
-__global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, int H, int W) {
+__global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, int H, int W, int rows) {
     const int x = blockIdx.x * 256 + threadIdx.x;
-    const int y0 = blockIdx.y * kSobelRows, y1 = min(y0 + kSobelRows, H);
+    const int y0 = blockIdx.y * rows, y1 = min(y0 + rows, H);
     const long long plane = (long long)H * W;
     const float *p = L + (long long)blockIdx.z * plane;
     float *o = g + (long long)blockIdx.z * plane;
@@ -495,14 +495,21 @@ __global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, in
         if (lane == 0) l = el;
         if (lane == 31) r = er;
     };
-    float a0, a1, a2, b0, b1, b2, c0, c1, c2;
+    float a0, a1, a2, b0, b1, b2;
     row3(y0 - 1, a0, a1, a2);
     row3(y0, b0, b1, b2);
-    for (int y = y0; y < y1; ++y) {
-        row3(y + 1, c0, c1, c2);
-        if (in) o[(long long)y * W + x] = sobel_mag(a0, a1, a2, b0, b2, c0, c1, c2);
-        a0 = b0; a1 = b1; a2 = b2;
-        b0 = c0; b1 = c1; b2 = c2;
+    // four rows per step: their loads are independent and issue back to back (one 4-byte load in flight per thread
+    // left the kernel latency-bound at 2.2 TB/s); the arithmetic per output is unchanged
+    for (int y = y0; y < y1; y += 4) {
+        float n0[4], n1[4], n2[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) row3(y + 1 + u, n0[u], n1[u], n2[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (in && y + u < y1) o[(long long)(y + u) * W + x] = sobel_mag(a0, a1, a2, b0, b2, n0[u], n1[u], n2[u]);
+            a0 = b0; a1 = b1; a2 = b2;
+            b0 = n0[u]; b1 = n1[u]; b2 = n2[u];
+        }
     }
 }
 
@@ -645,9 +652,10 @@ extern "C" int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t
 extern "C" int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w,
                                     void *stream) {
     LLIE_REQUIRE(l_planes && out_g && planes > 0 && h > 0 && w > 0, "sobel: bad arguments");
-    LLIE_REQUIRE(planes <= 65535 && (h + kSobelRows - 1) / kSobelRows <= 65535, "sobel: grid too large");
-    dim3 grid((w + 255) / 256, (h + kSobelRows - 1) / kSobelRows, (unsigned)planes);
-    sobel_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w);
+    const int rows = kSobelRows;  // (a one-wave grid of 44-row blocks was slower: 59 vs 45 us at 2848 x 4256)
+    LLIE_REQUIRE(planes <= 65535 && (h + rows - 1) / rows <= 65535, "sobel: grid too large");
+    dim3 grid((w + 255) / 256, (h + rows - 1) / rows, (unsigned)planes);
+    sobel_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w, rows);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

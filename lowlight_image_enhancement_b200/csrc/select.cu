@@ -90,8 +90,31 @@ __global__ void __launch_bounds__(256) select_hist_kernel(const SelArgs a) {
             if (want_sum) sum += (double)val;
             if (want_hist && (key & himask) == pre0) atomicAdd(&sh[(key >> shift) & bmask], 1u);
         };
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv;
-             i += (long long)gridDim.x * blockDim.x) {
+        // four independent 128-bit loads per tensor in flight per thread: with one, 2048 resident threads per SM
+        // keep 4.8 MB in flight chip-wide and the pass ran at 2.1 TB/s (latency-bound)
+        const long long stride = (long long)gridDim.x * blockDim.x;
+        long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+        for (; i + 3 * stride < nv; i += 4 * stride) {
+            float4 x[4], gg[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) x[u] = ldg_stream4(v + 4 * (i + u * stride));
+            if (gt) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) gg[u] = ldg_stream4(gt + 4 * (i + u * stride));
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                bool k0 = true, k1 = true, k2 = true, k3 = true;
+                if (gt) {
+                    k0 = gg[u].x >= thr; k1 = gg[u].y >= thr; k2 = gg[u].z >= thr; k3 = gg[u].w >= thr;
+                }
+                elem(x[u].x, k0);
+                elem(x[u].y, k1);
+                elem(x[u].z, k2);
+                elem(x[u].w, k3);
+            }
+        }
+        for (; i < nv; i += stride) {
             const float4 x = ldg_stream4(v + 4 * i);
             bool k0 = true, k1 = true, k2 = true, k3 = true;
             if (gt) {
