@@ -6,7 +6,7 @@ PSNR table.  rgb_ssim: per-channel `ssim_linear` scores (channelwise.py:262-295)
 """
 from __future__ import annotations
 
-from typing import Dict, Literal, Tuple, Union
+from typing import Dict, Literal, Tuple, TypedDict, Union
 
 import torch
 from torch import Tensor
@@ -14,7 +14,34 @@ from torch import Tensor
 from .. import _functional as Fn
 from .. import _native as nat
 
-__all__ = ["rgb_psnr", "cpsnr_rgb", "rgb_ssim"]
+__all__ = ["rgb_psnr", "cpsnr_rgb", "rgb_ssim", "MetricMeta", "PSNRResult", "CPSNRResult", "SSIMResult"]
+
+
+class MetricMeta(TypedDict):
+    """channelwise.py:32-34."""
+    domain: Literal["linear", "srgb"]
+    data_range: float
+
+
+class PSNRResult(TypedDict):
+    R: Tensor
+    G: Tensor
+    B: Tensor
+    mean: Tensor
+    meta: MetricMeta
+
+
+class CPSNRResult(TypedDict):
+    cpsnr: Tensor
+    meta: MetricMeta
+
+
+class SSIMResult(TypedDict):
+    R: Tensor
+    G: Tensor
+    B: Tensor
+    mean: Tensor
+    meta: MetricMeta
 
 _Reduction = Literal["mean", "sum", "none"]
 

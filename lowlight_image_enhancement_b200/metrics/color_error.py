@@ -9,6 +9,7 @@ sort of up to 12 M values per image in the reference) is an exact 3-pass radix s
 """
 from __future__ import annotations
 
+import math
 import warnings
 from typing import Dict, Iterable, Tuple
 
@@ -176,3 +177,53 @@ def edge_mask_from_l(l_plane: Tensor, q: float = 0.85):
     thr = thr.view(n).contiguous()
     _, counts, _ = Fn.select_quantiles(flat, [0.5], joint=False, gate=flat, gate_thr=thr)
     return g, thr, counts
+
+
+# ------------------------------------------------------------------------------------------------
+# the private helpers the reference's own tests import (standard_tests/test_color_error.py:31-36)
+# ------------------------------------------------------------------------------------------------
+def _deg2rad(deg: float) -> float:
+    """color_error.py:101-102."""
+    return deg * math.pi / 180.0
+
+
+@torch.no_grad()
+def _deltaE00_lab_map(lab1: Tensor, lab2: Tensor, *, kL: float, kC: float, kH: float, eps: float) -> Tensor:
+    """CIEDE2000 (metric variant) on Lab tensors [N, 3, H, W] -> [N, H, W] (color_error.py:105-210): the same kernel
+    as `deltaE2000_map` with the sRGB -> Lab stage switched off."""
+    if lab1.shape != lab2.shape or lab1.ndim != 4 or lab1.shape[1] != 3:
+        raise ValueError(f"expected two [N, 3, H, W] Lab tensors, got {tuple(lab1.shape)} / {tuple(lab2.shape)}")
+    dev = nat.cuda_device_for(lab1, lab2)
+    a = nat.stage(lab1.detach(), dev, torch.float32)
+    b = nat.stage(lab2.detach(), dev, torch.float32)
+    _, _, dmap, _ = Fn.deltae(a, b, variant=0, kL=kL, kC=kC, kH=kH, eps=eps, input_lab=True, want_map=True)
+    return dmap
+
+
+def _compute_percentiles(values: Tensor, percentiles: Iterable[float]) -> Dict[str, float]:
+    """color_error.py:213-231 with the sort replaced by the exact radix select (same `torch.quantile` values)."""
+    percentiles = list(percentiles)
+    flat = values.reshape(-1)
+    if flat.numel() == 0:
+        return {f"p{int(p)}": float("nan") for p in percentiles}
+    qs = []
+    for p in percentiles:
+        q = float(p)
+        if not 0.0 <= q <= 100.0:
+            raise ValueError(f"Percentile values must lie within [0, 100]; received {q}.")
+        qs.append(q / 100.0)
+    dev = nat.cuda_device_for(flat)
+    v = nat.stage(flat.detach(), dev, torch.float32).view(1, -1)
+    stats: Dict[str, float] = {}
+    for i in range(0, len(qs), 2):  # the select kernel takes one or two quantiles per call
+        qv, _, _ = Fn.select_quantiles(v, qs[i:i + 2], joint=True)
+        for j, val in enumerate(qv.view(-1).tolist()):
+            stats[f"p{int(percentiles[i + j])}"] = float(val)
+    return stats
+
+
+@torch.no_grad()
+def _sobel_magnitude(l_channel: Tensor) -> Tensor:
+    """sqrt(gx^2 + gy^2 + 1e-12) of the L channel [N, 1, H, W], zero padding (color_error.py:296-301)."""
+    dev = nat.cuda_device_for(l_channel)
+    return Fn.sobel_magnitude(nat.stage(l_channel.detach(), dev, torch.float32))

@@ -345,3 +345,34 @@ def test_constant_division_equals_ieee_division():
             rc = nat.lib().llie_selftest_div_const(which, first | 0x80000000, count, nat.ptr(bad), nat.stream_ptr(dev))
         nat.check(rc, "llie_selftest_div_const")
         assert int(bad.item()) == 0, (which, int(bad.item()))
+
+
+def test_private_helpers_the_reference_tests_import(golden, dev):
+    """`_deltaE00_lab_map`, `_compute_percentiles`, `_sobel_magnitude` (standard_tests/test_color_error.py imports the
+    first): the Lab-input map against the reference-formula goldens of the 18 Sharma pairs + 110 seeded pairs, the
+    percentiles against torch.quantile, the Sobel magnitude against the oracle."""
+    from lowlight_image_enhancement_b200.metrics.color_error import (_compute_percentiles, _deg2rad,
+                                                                       _deltaE00_lab_map, _sobel_magnitude)
+    lab1, lab2 = lab_inputs()
+    keep = np.ones(128, bool)
+    keep[LAB_UNSTABLE] = False
+    m = _deltaE00_lab_map(lab1.to(dev), lab2.to(dev), kL=1.0, kC=1.0, kH=1.0, eps=1e-12)
+    assert m.shape == (lab1.shape[0],) + tuple(lab1.shape[2:])
+    assert np.abs(_np(m).reshape(-1) - golden["de_metric"].reshape(-1))[keep].max() < 1e-4
+    mk = _deltaE00_lab_map(lab1.to(dev), lab2.to(dev), kL=2.0, kC=1.5, kH=0.7, eps=1e-12)
+    assert np.abs(_np(mk).reshape(-1) - golden["de_metric_k"].reshape(-1))[keep].max() < 1e-4
+    same = _deltaE00_lab_map(lab1.to(dev), lab1.to(dev), kL=1.0, kC=1.0, kH=1.0, eps=1e-12)
+    assert float(same.abs().max()) <= 1e-5                       # identity (test_color_error.py:84-100)
+    with pytest.raises(ValueError):
+        _deltaE00_lab_map(lab1[:, :2].to(dev), lab2[:, :2].to(dev), kL=1.0, kC=1.0, kH=1.0, eps=1e-12)
+    g = torch.Generator().manual_seed(77)
+    vals = torch.rand(3, 41, 53, generator=g) * 20
+    got = _compute_percentiles(vals.to(dev), (50.0, 95.0, 1.0))
+    want = torch.quantile(vals.reshape(-1), torch.tensor([0.5, 0.95, 0.01]))
+    assert [got["p50"], got["p95"], got["p1"]] == [float(v) for v in want]   # exact order statistics + ATen's lerp
+    assert all(np.isnan(v) for v in _compute_percentiles(torch.empty(0, device=dev), (50.0,)).values())
+    with pytest.raises(ValueError):
+        _compute_percentiles(vals.to(dev), (101.0,))
+    lch = torch.rand(2, 1, 33, 48, generator=g) * 100
+    assert float((_sobel_magnitude(lch.to(dev)).cpu() - colour.sobel_magnitude(lch)).abs().max()) <= 1e-4
+    assert _deg2rad(180.0) == pytest.approx(np.pi)
