@@ -341,7 +341,7 @@ int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const 
 int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t n, void *stream);
 
 /* Accuracy self-test hook: the kernels divide by their compile-time constants (which: 0 1.055, 1 12.92, 2 0.95047,
- * 3 1.08883, 4 25, 5 pi) with a three-instruction FMA sequence that must equal the IEEE division; *out_mismatch (device)
+ * 3 1.08883, 4 25, 5 pi, 6 65535 of the uint16 decode) with a three-instruction FMA sequence that must equal the IEEE division; *out_mismatch (device)
  * = number of operands among the float bit patterns first_bits .. first_bits + count - 1 where it does not. */
 int llie_selftest_div_const(int32_t which, uint32_t first_bits, uint64_t count, uint64_t *out_mismatch, void *stream);
 

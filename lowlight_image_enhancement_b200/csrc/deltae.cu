@@ -659,7 +659,8 @@ __device__ __forceinline__ bool divc_differs(float x) {
     else if (WHICH == 2) { a = DIVC(x, 0.95047f); b = __fdiv_rn(x, 0.95047f); }
     else if (WHICH == 3) { a = DIVC(x, 1.08883f); b = __fdiv_rn(x, 1.08883f); }
     else if (WHICH == 4) { a = DIVC(x, 25.0f); b = __fdiv_rn(x, 25.0f); }
-    else { a = DIVC(x, kPi); b = __fdiv_rn(x, kPi); }
+    else if (WHICH == 5) { a = DIVC(x, kPi); b = __fdiv_rn(x, kPi); }
+    else { a = DIVC(x, 65535.0f); b = __fdiv_rn(x, 65535.0f); }  // the uint16 decode of ingest.cu
     return __float_as_uint(a) != __float_as_uint(b) && !(a != a && b != b);
 }
 __global__ void div_const_selftest_kernel(int which, unsigned first_bits, unsigned long long count,
@@ -675,7 +676,8 @@ __global__ void div_const_selftest_kernel(int which, unsigned first_bits, unsign
             case 2: d = divc_differs<2>(x); break;
             case 3: d = divc_differs<3>(x); break;
             case 4: d = divc_differs<4>(x); break;
-            default: d = divc_differs<5>(x); break;
+            case 5: d = divc_differs<5>(x); break;
+            default: d = divc_differs<6>(x); break;
         }
         bad += d ? 1ull : 0ull;
     }
@@ -686,7 +688,7 @@ __global__ void div_const_selftest_kernel(int which, unsigned first_bits, unsign
 
 extern "C" int llie_selftest_div_const(int32_t which, uint32_t first_bits, uint64_t count, uint64_t *out_mismatch,
                                        void *stream) {
-    LLIE_REQUIRE(out_mismatch && which >= 0 && which <= 5 && count > 0, "selftest_div_const: bad arguments");
+    LLIE_REQUIRE(out_mismatch && which >= 0 && which <= 6 && count > 0, "selftest_div_const: bad arguments");
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     LLIE_CUDA_OK(cudaMemsetAsync(out_mismatch, 0, sizeof(uint64_t), st));
     div_const_selftest_kernel<<<kNumSM * 16, 256, 0, st>>>(which, first_bits, count,

@@ -23,54 +23,96 @@ struct DecArgs {
     float *raw, *aligned;
 };
 
-__device__ __forceinline__ float dec_raw(unsigned u) { return __fdiv_rn((float)u, 65535.0f); }
+// u / 65535 as q = u * rc, r = fma(-65535, q, u), q' = fma(r, rc, q): the correctly rounded quotient (same bits as
+// the division instruction; llie_selftest_div_const(6) checks every float in [2^-100, 2^100]) in 3 instructions.
+__device__ __forceinline__ float dec_raw(unsigned u) {
+    const float x = (float)u, rc = 1.0f / 65535.0f;
+    const float q = __fmul_rn(x, rc);
+    return __fmaf_rn(__fmaf_rn(-65535.0f, q, x), rc, q);
+}
 __device__ __forceinline__ float dec_aligned(float raw, float rho) {
     return fminf(fmaxf(__fmul_rn(raw, rho), 0.f), 1.f);
 }
 
 // C == 3, crop width % 4 == 0: one thread = 4 pixels of a row = 12 samples (24 B in, 3 x 16 B out per plane set).
 // VEC: the 24 B are three aligned 8-byte loads; otherwise twelve 2-byte loads (same sectors, L1-coalesced).
+// The flat item index is split into (row, quad) once per thread and then advanced by the grid stride with adds and
+// compares only (step_rows / step_quads come from the host); two items are in flight per thread.
 template <bool VEC>
-__global__ void __launch_bounds__(kDecThreads) decode_u16_c3_kernel(const DecArgs a) {
+__device__ __forceinline__ void dec_load12(const uint16_t *sp, unsigned (&s)[12]) {
+    if (VEC) {
+        const uint2 *sv = reinterpret_cast<const uint2 *>(sp);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const uint2 v = __ldg(sv + k);
+            s[4 * k] = v.x & 0xffffu;
+            s[4 * k + 1] = v.x >> 16;
+            s[4 * k + 2] = v.y & 0xffffu;
+            s[4 * k + 3] = v.y >> 16;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 12; ++k) s[k] = __ldg(sp + k);
+    }
+}
+
+__device__ __forceinline__ void dec_store12(const DecArgs &a, const unsigned (&s)[12], float rho, long long o,
+                                            long long plane) {
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {  // c = source channel; it lands in plane c, or 2 - c under the B<->R swap
+        const long long oc = o + (a.d.swap_rb ? 2 - c : c) * plane;
+        float v[4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p) v[p] = dec_raw(s[3 * p + c]);
+        if (a.raw != nullptr) __stcs(reinterpret_cast<float4 *>(a.raw + oc), make_float4(v[0], v[1], v[2], v[3]));
+        if (a.aligned != nullptr)
+            __stcs(reinterpret_cast<float4 *>(a.aligned + oc),
+                   make_float4(dec_aligned(v[0], rho), dec_aligned(v[1], rho), dec_aligned(v[2], rho),
+                               dec_aligned(v[3], rho)));
+    }
+}
+
+struct DecPos {
+    int row, qx;  // row = n * crop_h + y
+    __device__ __forceinline__ void advance(int step_rows, int step_quads, int quads) {
+        row += step_rows;
+        qx += step_quads;
+        if (qx >= quads) {
+            qx -= quads;
+            ++row;
+        }
+    }
+};
+
+template <bool VEC>
+__global__ void __launch_bounds__(kDecThreads) decode_u16_c3_kernel(const DecArgs a, int step_rows, int step_quads) {
     const llie_decode_desc &d = a.d;
     const int quads = d.crop_w >> 2;
-    const long long total = (long long)d.n * d.crop_h * quads;
+    const int rows = d.n * d.crop_h;
     const long long plane = (long long)d.crop_h * d.crop_w;
-    for (long long t = (long long)blockIdx.x * kDecThreads + threadIdx.x; t < total;
-         t += (long long)gridDim.x * kDecThreads) {
-        const int qx = (int)(t % quads);
-        const long long r = t / quads;
-        const int y = (int)(r % d.crop_h), n = (int)(r / d.crop_h);
-        const uint16_t *sp = a.src + (((long long)n * d.h + d.top + y) * d.w + d.left + 4 * qx) * 3;
-        unsigned s[12];
-        if (VEC) {
-            const uint2 *sv = reinterpret_cast<const uint2 *>(sp);
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const uint2 v = __ldg(sv + k);
-                s[4 * k] = v.x & 0xffffu;
-                s[4 * k + 1] = v.x >> 16;
-                s[4 * k + 2] = v.y & 0xffffu;
-                s[4 * k + 3] = v.y >> 16;
-            }
-        } else {
-#pragma unroll
-            for (int k = 0; k < 12; ++k) s[k] = __ldg(sp + k);
+    const unsigned t0 = blockIdx.x * kDecThreads + threadIdx.x;
+    DecPos p{(int)(t0 / (unsigned)quads), (int)(t0 % (unsigned)quads)};
+    auto src_of = [&](const DecPos &q, int &n, int &y) {
+        n = d.n == 1 ? 0 : q.row / d.crop_h;
+        y = q.row - n * d.crop_h;
+        return a.src + (((long long)n * d.h + d.top + y) * d.w + d.left + 4 * q.qx) * 3;
+    };
+    while (p.row < rows) {
+        DecPos p2 = p;
+        p2.advance(step_rows, step_quads, quads);
+        const bool two = p2.row < rows;
+        int n0, y0, n1 = 0, y1 = 0;
+        unsigned s0[12], s1[12];
+        dec_load12<VEC>(src_of(p, n0, y0), s0);
+        if (two) dec_load12<VEC>(src_of(p2, n1, y1), s1);
+        const float rho0 = a.rho != nullptr ? __ldg(a.rho + n0) : a.rho_scalar;
+        dec_store12(a, s0, rho0, ((long long)n0 * 3) * plane + (long long)y0 * d.crop_w + 4 * p.qx, plane);
+        if (two) {
+            const float rho1 = a.rho != nullptr ? __ldg(a.rho + n1) : a.rho_scalar;
+            dec_store12(a, s1, rho1, ((long long)n1 * 3) * plane + (long long)y1 * d.crop_w + 4 * p2.qx, plane);
         }
-        const float rho = a.rho != nullptr ? __ldg(a.rho + n) : a.rho_scalar;
-        const long long o = ((long long)n * 3) * plane + (long long)y * d.crop_w + 4 * qx;
-#pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            const int sc = d.swap_rb ? 2 - c : c;
-            float v[4];
-#pragma unroll
-            for (int p = 0; p < 4; ++p) v[p] = dec_raw(s[3 * p + sc]);
-            if (a.raw != nullptr) __stcs(reinterpret_cast<float4 *>(a.raw + o + c * plane), make_float4(v[0], v[1], v[2], v[3]));
-            if (a.aligned != nullptr)
-                __stcs(reinterpret_cast<float4 *>(a.aligned + o + c * plane),
-                       make_float4(dec_aligned(v[0], rho), dec_aligned(v[1], rho), dec_aligned(v[2], rho),
-                                   dec_aligned(v[3], rho)));
-        }
+        p = p2;
+        p.advance(step_rows, step_quads, quads);
     }
 }
 
@@ -163,12 +205,17 @@ extern "C" int llie_decode_u16(const llie_decode_desc *desc, const uint16_t *src
     const bool out_ok = (out_raw == nullptr || aligned16(out_raw)) && (out_aligned == nullptr || aligned16(out_aligned));
     if (d.c == 3 && (d.crop_w & 3) == 0 && out_ok) {
         const long long items = (long long)d.n * d.crop_h * (d.crop_w >> 2);
+        LLIE_REQUIRE(items < (1ll << 31) && (long long)d.n * d.crop_h < (1ll << 30),
+                     "llie_decode_u16: %lld four-pixel items exceed the 32-bit item index", items);
         const int grid = grid_for(items, kDecThreads, 8);
+        const int quads = d.crop_w >> 2;
+        const long long stride = (long long)grid * kDecThreads;
+        const int step_rows = (int)(stride / quads), step_quads = (int)(stride % quads);
         const bool vec = (reinterpret_cast<uintptr_t>(src) & 7u) == 0 && (d.w & 3) == 0 && (d.left & 3) == 0;
         if (vec)
-            decode_u16_c3_kernel<true><<<grid, kDecThreads, 0, st>>>(a);
+            decode_u16_c3_kernel<true><<<grid, kDecThreads, 0, st>>>(a, step_rows, step_quads);
         else
-            decode_u16_c3_kernel<false><<<grid, kDecThreads, 0, st>>>(a);
+            decode_u16_c3_kernel<false><<<grid, kDecThreads, 0, st>>>(a, step_rows, step_quads);
     } else {
         const long long items = (long long)d.n * d.c * d.crop_h * d.crop_w;
         decode_u16_generic_kernel<<<grid_for(items, kDecThreads, 8), kDecThreads, 0, st>>>(a);

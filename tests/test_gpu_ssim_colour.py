@@ -327,14 +327,14 @@ def test_two_column_ssim_kernel_vs_one_column(shape, pad, policy):
 def test_constant_division_equals_ieee_division():
     """`div_const` (x * RN(1/C), one FMA for the exact remainder, one FMA for the correction) must be the IEEE quotient:
     every float bit pattern from 2^-100 up to 2^100 (1.68e9 operands, both the positive range the colour path sees and
-    far beyond it) for each of the six constants the kernels divide by."""
+    far beyond it) for each of the seven constants the kernels divide by (the last is the 65535 of the uint16 decode)."""
     from lowlight_image_enhancement_b200 import _native as nat
     dev = torch.device("cuda:0")
     nat.ensure_device(dev)
     bad = torch.zeros(1, dtype=torch.int64, device=dev)
     first = (127 - 100) << 23          # 2^-100
     count = ((127 + 100) << 23) - first
-    for which in range(6):
+    for which in range(7):
         with torch.cuda.device(dev):
             rc = nat.lib().llie_selftest_div_const(which, first, count, nat.ptr(bad), nat.stream_ptr(dev))
         nat.check(rc, "llie_selftest_div_const")
