@@ -237,7 +237,17 @@ extern "C" int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const 
     const size_t esz = desc->dtype ? 8 : 4;
     a.vec_ok = aligned16(x) && aligned16(y) && ((desc->plane * esz) % 16 == 0);
     long long per_block = 256LL * vn * 4;
-    int G = div_up(kNumSM * 8, nc);
+    // exactly one wave of resident blocks (the register count, not the 2048-thread limit, decides how many fit)
+    static int occ[2] = {0, 0};
+    if (occ[desc->dtype] == 0) {
+        int o = 0;
+        if (desc->dtype == 0)
+            LLIE_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, psnr_stats_kernel<float>, 256, 0));
+        else
+            LLIE_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, psnr_stats_kernel<double>, 256, 0));
+        occ[desc->dtype] = o < 1 ? 1 : o;
+    }
+    int G = (kNumSM * occ[desc->dtype]) / nc;
     long long maxg = (desc->plane + per_block - 1) / per_block;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;
