@@ -10,6 +10,16 @@ namespace llie {
 
 constexpr int kNumSM = 148;  // B200: 2 dies x 74 SMs (grids are sized in multiples of this)
 
+// Blocks of `kernel` that fit on one SM at `threads` threads (registers and shared memory included): grid-stride
+// kernels size their grid to ONE wave of kNumSM * resident_blocks(...) so that no partly filled second wave trails
+// (8 blocks of 256 threads only fit below 33 registers).  Call sites cache the value in a function-local static.
+template <typename K>
+inline int resident_blocks(K kernel, int threads, size_t smem = 0) {
+    int o = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, threads, smem) != cudaSuccess || o < 1) o = 1;
+    return o;
+}
+
 // ---------------------------------------------------------------- error plumbing
 void set_error(const char *fmt, ...);
 int cuda_fail(cudaError_t e, const char *what);

@@ -15,6 +15,11 @@
 
 #include "common.cuh"
 
+// grid = LLIE_DE_WAVES waves of resident blocks: one wave leaves the slowest SM's blocks as the tail (402 us per 12 Mpx
+// pair), 1.6 waves as before 383, four waves let the block scheduler even it out (366); 8 is no better
+#ifndef LLIE_DE_WAVES
+#define LLIE_DE_WAVES 4
+#endif
 namespace llie {
 
 constexpr float kPi = 3.14159265358979323846f;
@@ -583,7 +588,8 @@ static int deltae_launch(const llie_deltae_desc *desc, const float *x, const flo
     a.d = *desc;
     a.x = x; a.y = y; a.out_sum = out_sum; a.out_map = out_map; a.out_l = out_l; a.out_flags = out_flags;
     const long long plane = (long long)desc->h * desc->w;
-    int G = div_up(kNumSM * 8, desc->n);
+    static const int occ = resident_blocks(deltae_kernel, 256);
+    int G = kNumSM * occ * LLIE_DE_WAVES / desc->n;
     const long long maxg = (plane + 255) / 256;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;
@@ -625,7 +631,8 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
     a.eps = desc->eps; a.scale = grad_scale;
     a.x = x; a.y = y; a.out_sum = out_sum; a.out_grad = out_grad; a.out_flags = out_flags;
     const long long plane = (long long)desc->h * desc->w;
-    int G = div_up(kNumSM * 8, desc->n);
+    static const int occ = resident_blocks(deltae_loss_grad_kernel, 256);
+    int G = kNumSM * occ / desc->n;  // one wave: the training-size batches gain nothing from more, the hybrid step loses
     const long long maxg = (plane + 255) / 256;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;

@@ -6,6 +6,9 @@
 
 #include "common.cuh"
 
+#ifndef LLIE_PSNR_WAVES
+#define LLIE_PSNR_WAVES 1
+#endif
 namespace llie {
 
 struct PsnrArgs {
@@ -247,7 +250,7 @@ extern "C" int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const 
             LLIE_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, psnr_stats_kernel<double>, 256, 0));
         occ[desc->dtype] = o < 1 ? 1 : o;
     }
-    int G = (kNumSM * occ[desc->dtype]) / nc;
+    int G = (kNumSM * occ[desc->dtype] * LLIE_PSNR_WAVES) / nc;
     long long maxg = (desc->plane + per_block - 1) / per_block;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;
@@ -376,7 +379,8 @@ extern "C" int llie_l1_grad(const float *x, const float *y, int64_t n, float gra
     a.n = n; a.scale = grad_scale; a.accumulate = accumulate;
     a.vec_ok = llie::aligned16(x) && llie::aligned16(y) && (!out_grad || llie::aligned16(out_grad)) && (n % 4 == 0);
     long long blocks = (n / 4 + 255) / 256;
-    const long long cap = llie::kNumSM * 8;
+    static const int occ = llie::resident_blocks(llie::l1_grad_kernel, 256);
+    const long long cap = llie::kNumSM * occ;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     llie::Workspace ws(workspace);
@@ -553,7 +557,8 @@ extern "C" int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y
     a.mode = mode; a.w_per_channel = weight_per_channel; a.accumulate = accumulate;
     a.eps = eps; a.scale = grad_scale;
     long long blocks = (a.n_elem / 4 + 255) / 256;
-    const long long cap = llie::kNumSM * 8;
+    static const int occ = llie::resident_blocks(llie::pixel_loss_kernel, 256);
+    const long long cap = llie::kNumSM * occ;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     llie::Workspace ws(workspace);

@@ -312,7 +312,12 @@ extern "C" int llie_select_quantiles(const llie_select_desc *desc, const float *
     for (int i = 0; i < d.nq; ++i) a.q[i] = (float)q[i];
     a.out_q = out_q; a.out_count = reinterpret_cast<long long *>(out_count); a.out_sum = out_sum;
     const int segs = d.joint ? 1 : d.images;
-    int bx = div_up(kNumSM * 8, d.images);
+    static int occ_nq[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // resident blocks per SM by nq (dynamic shared memory grows with it)
+    const int oi = d.nq < 7 ? d.nq : 7;
+    if (occ_nq[oi] == 0 || oi == 7)
+        occ_nq[oi] = resident_blocks(select_hist_kernel, 256, (size_t)2 * d.nq * kBins * sizeof(unsigned));
+    const int per_sm = occ_nq[oi] < 8 ? occ_nq[oi] : 8;  // the partial-sum workspace holds kNumSM * 8 slots per segment
+    int bx = kNumSM * per_sm / d.images;
     const long long maxb = (d.per_image + 1023) / 1024;
     if (bx > maxb) bx = (int)maxb;
     if (bx < 1) bx = 1;
