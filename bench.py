@@ -424,7 +424,7 @@ def run_extra(args, rank, world, dev):
                                                       k1=0.01, k2=0.03), 6, dev) / 6
     t_de = timed_warm(lambda i: Fn.deltae(pool[i % 3][0], pool[i % 3][1], variant=0, clamp_in=True), 6, dev) / 6
     t_ps = timed_warm(lambda i: Fn.psnr_stats(pool[i % 3][1], pool[i % 3][0], 1, 1, 3 * px, cast_first=True, clamp_hi=None,
-                                         data_range=1.0, eps=1e-12), 6, dev) / 6
+                                         data_range=1.0, eps=1e-12), 24, dev) / 24
     t_all = timed_warm(lambda i: image_metrics(pool[i % 3][0], pool[i % 3][1], EVAL_METRICS), 6, dev) / 6
     acc_k = ShardedMeans(EVAL_METRICS, dev)
     t_fast = timed_warm(lambda i: accumulate_image_metrics(pool[i % 3][0], pool[i % 3][1], EVAL_METRICS, acc_k), 6,
@@ -476,9 +476,9 @@ def run_extra(args, rank, world, dev):
     el = 3 * px
     for _ in range(2):  # warm-up (allocator + first launch)
         Fn.decode_u16(frames[0], 100.0), Fn.decode_u16(frames[0], 1.0, want_aligned=False), srgb_and_lpips_inputs(lin[0])
-    t_dec = timed_warm(lambda i: Fn.decode_u16(frames[i % 3], 100.0), 9, dev) / 9
-    t_dec1 = timed_warm(lambda i: Fn.decode_u16(frames[i % 3], 1.0, want_aligned=False), 9, dev) / 9
-    t_srgb = timed_warm(lambda i: srgb_and_lpips_inputs(lin[i % 3]), 9, dev) / 9
+    t_dec = timed_warm(lambda i: Fn.decode_u16(frames[i % 3], 100.0), 27, dev) / 27
+    t_dec1 = timed_warm(lambda i: Fn.decode_u16(frames[i % 3], 1.0, want_aligned=False), 27, dev) / 27
+    t_srgb = timed_warm(lambda i: srgb_and_lpips_inputs(lin[i % 3]), 27, dev) / 27
 
     def kern_b(name, t, bpe):
         return {"kernel": name, "ms": round(t, 4), "Mpix/s": round(px / t / 1e3, 1), "algorithmic_bytes": bpe * el,

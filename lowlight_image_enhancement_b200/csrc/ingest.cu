@@ -11,6 +11,9 @@
 // rounding of x^(1/2.4) (here cbrt(x) * sqrt(sqrt(cbrt(x))), < 3 ulp).
 #include "common.cuh"
 
+#ifndef LLIE_INGEST_WAVES
+#define LLIE_INGEST_WAVES 12
+#endif
 namespace llie {
 
 constexpr int kDecThreads = 256;
@@ -207,11 +210,16 @@ extern "C" int llie_decode_u16(const llie_decode_desc *desc, const uint16_t *src
         const long long items = (long long)d.n * d.crop_h * (d.crop_w >> 2);
         LLIE_REQUIRE(items < (1ll << 31) && (long long)d.n * d.crop_h < (1ll << 30),
                      "llie_decode_u16: %lld four-pixel items exceed the 32-bit item index", items);
-        const int grid = grid_for(items, kDecThreads, 8);
+        const bool vec = (reinterpret_cast<uintptr_t>(src) & 7u) == 0 && (d.w & 3) == 0 && (d.left & 3) == 0;
+        // LLIE_INGEST_WAVES (12) waves of the blocks that fit: these write-dominated passes gain from finer items
+        // (1 / 2 / 4 / 8 / 12 / 16 waves: 68.1 / 67.9 / 64.6 / 61.5 / 60.3 / 60.0 us per 12 Mpx frame for raw + aligned,
+        // raw only best at 8-12; tools/time_ingest.py)
+        static const int occ_v = resident_blocks(decode_u16_c3_kernel<true>, kDecThreads);
+        static const int occ_s = resident_blocks(decode_u16_c3_kernel<false>, kDecThreads);
+        const int grid = grid_for(items, kDecThreads, (vec ? occ_v : occ_s) * LLIE_INGEST_WAVES);
         const int quads = d.crop_w >> 2;
         const long long stride = (long long)grid * kDecThreads;
         const int step_rows = (int)(stride / quads), step_quads = (int)(stride % quads);
-        const bool vec = (reinterpret_cast<uintptr_t>(src) & 7u) == 0 && (d.w & 3) == 0 && (d.left & 3) == 0;
         if (vec)
             decode_u16_c3_kernel<true><<<grid, kDecThreads, 0, st>>>(a, step_rows, step_quads);
         else
@@ -232,7 +240,8 @@ extern "C" int llie_linear_to_srgb(const float *x, int64_t n, float *out_srgb, f
     const bool vec = aligned16(x) && (out_srgb == nullptr || aligned16(out_srgb)) &&
                      (out_lpips == nullptr || aligned16(out_lpips));
     const long long items = vec ? (n + 3) / 4 : n;
-    linear_to_srgb_kernel<<<grid_for(items, 256, 8), 256, 0, st>>>(x, n, out_srgb, out_lpips, vec);
+    static const int occ = resident_blocks(linear_to_srgb_kernel, 256);
+    linear_to_srgb_kernel<<<grid_for(items, 256, occ * LLIE_INGEST_WAVES), 256, 0, st>>>(x, n, out_srgb, out_lpips, vec);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
