@@ -6,6 +6,9 @@
 
 #include "common.cuh"
 
+#ifndef LLIE_PIX_WAVES
+#define LLIE_PIX_WAVES 1
+#endif
 #ifndef LLIE_PSNR_WAVES
 #define LLIE_PSNR_WAVES 1
 #endif
@@ -380,7 +383,7 @@ extern "C" int llie_l1_grad(const float *x, const float *y, int64_t n, float gra
     a.vec_ok = llie::aligned16(x) && llie::aligned16(y) && (!out_grad || llie::aligned16(out_grad)) && (n % 4 == 0);
     long long blocks = (n / 4 + 255) / 256;
     static const int occ = llie::resident_blocks(llie::l1_grad_kernel, 256);
-    const long long cap = llie::kNumSM * occ;
+    const long long cap = llie::kNumSM * occ * LLIE_PIX_WAVES;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     llie::Workspace ws(workspace);
@@ -558,7 +561,7 @@ extern "C" int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y
     a.eps = eps; a.scale = grad_scale;
     long long blocks = (a.n_elem / 4 + 255) / 256;
     static const int occ = llie::resident_blocks(llie::pixel_loss_kernel, 256);
-    const long long cap = llie::kNumSM * occ;
+    const long long cap = llie::kNumSM * occ * LLIE_PIX_WAVES;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     llie::Workspace ws(workspace);
