@@ -456,6 +456,11 @@ __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs 
 // right neighbours come from warp shuffles (the two edge lanes of a warp load theirs), so each value is read
 // from memory ~1.1 times instead of 9 and the kernel is bound by HBM, not by address arithmetic.
 constexpr int kSobelRows = 32;
+#ifndef LLIE_SOBEL4_ROWS
+#define LLIE_SOBEL4_ROWS 12
+#endif
+constexpr int kSobel4Rows = LLIE_SOBEL4_ROWS;  // rows per block of the four-column kernel (even): 32 rows left
+// 20 warps per SM in flight on a 12 Mpx plane (37 us); 16 / 12 / 8 rows: 35 / 31 / 31 us (tools/time_sobel.py)
 
 __device__ __forceinline__ float sobel_mag(float v00, float v01, float v02, float v10, float v12, float v20, float v21,
                                            float v22) {
@@ -520,10 +525,10 @@ __global__ void __launch_bounds__(256) sobel_kernel(const float *L, float *g, in
 
 // Four columns per thread (W % 4 == 0, 16-byte aligned planes): one 128-bit load and store per row instead of four
 // 32-bit ones, the outside neighbours by shuffle (warp-edge lanes load them); same sobel_mag per pixel.
-// grid (ceil(W / 256), ceil(H / kSobelRows), planes), 64 threads
+// grid (ceil(W / 256), ceil(H / kSobel4Rows), planes), 64 threads
 __global__ void __launch_bounds__(64) sobel4_kernel(const float *L, float *g, int H, int W) {
     const int x = (blockIdx.x * 64 + threadIdx.x) * 4;
-    const int y0 = blockIdx.y * kSobelRows, y1 = min(y0 + kSobelRows, H);
+    const int y0 = blockIdx.y * kSobel4Rows, y1 = min(y0 + kSobel4Rows, H);
     const long long plane = (long long)H * W;
     const float *p = L + (long long)blockIdx.z * plane;
     float *o = g + (long long)blockIdx.z * plane;
@@ -716,10 +721,11 @@ extern "C" int llie_selftest_srgb_to_linear(const float *in, float *out, int64_t
 extern "C" int llie_sobel_magnitude(const float *l_planes, float *out_g, int64_t planes, int32_t h, int32_t w,
                                     void *stream) {
     LLIE_REQUIRE(l_planes && out_g && planes > 0 && h > 0 && w > 0, "sobel: bad arguments");
-    const int rows = kSobelRows;  // (a one-wave grid of 44-row blocks was slower: 59 vs 45 us at 2848 x 4256)
+    const bool four = (w & 3) == 0 && aligned16(l_planes) && aligned16(out_g);
+    const int rows = four ? kSobel4Rows : kSobelRows;  // (a one-wave grid of 44-row blocks was slower: 59 vs 45 us)
     LLIE_REQUIRE(planes <= 65535 && (h + rows - 1) / rows <= 65535, "sobel: grid too large");
     dim3 grid((w + 255) / 256, (h + rows - 1) / rows, (unsigned)planes);
-    if ((w & 3) == 0 && aligned16(l_planes) && aligned16(out_g))
+    if (four)
         sobel4_kernel<<<grid, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w);
     else
         sobel_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(l_planes, out_g, h, w, rows);
