@@ -35,6 +35,8 @@ struct SelArgs {
     double *psum;                    // [images][gridDim.x]
     SelState *state;                 // [segments]
     int pass;                        // 0, 1, 2
+    unsigned *ticket;                // last-block ticket of the histogram kernel (fold)
+    int fold;                        // 1: one segment -- the last histogram block also runs the scan (no second launch)
 };
 
 // monotone map float bits -> unsigned (total order incl. negatives)
@@ -50,6 +52,8 @@ __device__ __forceinline__ unsigned pass_bins(int pass) { return pass == 2 ? 102
 __device__ __forceinline__ unsigned pass_himask(int pass) {  // bits already decided before this pass
     return pass == 0 ? 0u : (pass == 1 ? 0xffe00000u : 0xfffffc00u);
 }
+
+__device__ void select_scan_body(const SelArgs &a, int images, int blocks_x, int seg);
 
 // grid (bx, images).  Segment = image, or 0 when d.joint.
 __global__ void __launch_bounds__(256) select_hist_kernel(const SelArgs a) {
@@ -161,16 +165,19 @@ __global__ void __launch_bounds__(256) select_hist_kernel(const SelArgs a) {
         const double bs = block_sum<double>(sum, red);
         if (threadIdx.x == 0) a.psum[(size_t)img * gridDim.x + blockIdx.x] = bs;
     }
+    // one segment: the block that finishes last walks the histogram itself (saves the one-block scan launch per pass)
+    if (a.fold && last_block_done(a.ticket, gridDim.x * gridDim.y)) select_scan_body(a, d.images, gridDim.x, 0);
 }
 
 // one block per segment: walk the histogram rows, fix the next digit of every rank
-__global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int images, int blocks_x) {
+// (every value another block of the same launch may have written -- histogram rows, counts, partial sums -- is read
+// with __ldcg: the folded form runs inside the histogram kernel)
+__device__ void select_scan_body(const SelArgs &a, int images, int blocks_x, int seg) {
     __shared__ unsigned long long chunk[256];
     __shared__ unsigned long long newk[kMaxR];
     __shared__ unsigned newp[kMaxR];
     __shared__ double red[32];
     const llie_select_desc &d = a.d;
-    const int seg = blockIdx.x;
     const int nr = 2 * d.nq;
     SelState &st = a.state[seg];
     const unsigned bins = pass_bins(a.pass);
@@ -183,8 +190,9 @@ __global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int i
         if (threadIdx.x == 0) {
             unsigned long long c = 0;
             for (int i = i0; i < i1; ++i) {
-                c += a.img_count[i];
-                a.out_count[i] = (long long)a.img_count[i];
+                const unsigned long long ci = __ldcg(a.img_count + i);
+                c += ci;
+                a.out_count[i] = (long long)ci;
             }
             st.count = c;
             for (int qi = 0; qi < d.nq; ++qi) {
@@ -200,7 +208,7 @@ __global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int i
             double s = 0.0;
             const long long tot = (long long)(i1 - i0) * blocks_x;
             const double *p = a.psum + (size_t)i0 * blocks_x;
-            for (long long b = threadIdx.x; b < tot; b += blockDim.x) s += p[b];
+            for (long long b = threadIdx.x; b < tot; b += blockDim.x) s += __ldcg(p + b);
             s = block_sum<double>(s, red);
             if (threadIdx.x == 0) a.out_sum[seg] = s;
         }
@@ -217,7 +225,7 @@ __global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int i
         unsigned long long bv[8], cs = 0;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            bv[j] = j < per ? row[threadIdx.x * per + j] : 0ull;
+            bv[j] = j < per ? __ldcg(row + threadIdx.x * per + j) : 0ull;
             cs += bv[j];
         }
         const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -285,6 +293,10 @@ __global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int i
     }
 }
 
+__global__ void __launch_bounds__(256) select_scan_kernel(const SelArgs a, int images, int blocks_x) {
+    select_scan_body(a, images, blocks_x, blockIdx.x);
+}
+
 }  // namespace llie
 
 using namespace llie;
@@ -293,7 +305,7 @@ extern "C" size_t llie_select_workspace_bytes(int32_t images, int32_t blocks_hin
     (void)blocks_hint;
     const size_t segs = (size_t)images;
     return segs * kMaxR * kBins * sizeof(unsigned long long) + segs * sizeof(unsigned long long) +
-           segs * sizeof(SelState) + segs * (size_t)(kNumSM * 8) * sizeof(double) + 256;
+           segs * sizeof(SelState) + segs * (size_t)(kNumSM * 8) * sizeof(double) + 256 + 64;  // + ticket
 }
 
 extern "C" int llie_select_quantiles(const llie_select_desc *desc, const float *values, const float *gate,
@@ -329,13 +341,15 @@ extern "C" int llie_select_quantiles(const llie_select_desc *desc, const float *
     a.state = reinterpret_cast<SelState *>(w);
     w += (size_t)d.images * sizeof(SelState);
     a.psum = reinterpret_cast<double *>(((uintptr_t)w + 7) & ~(uintptr_t)7);
+    a.ticket = reinterpret_cast<unsigned *>(a.psum + (size_t)d.images * (kNumSM * 8));  // inside the trailing slack
+    a.fold = segs == 1 ? 1 : 0;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const size_t smem = (size_t)2 * d.nq * kBins * sizeof(unsigned);
     const int passes = d.nq == 0 ? 1 : 3;  // nq == 0: gated count + sum only, one pass
     for (int pass = 0; pass < passes; ++pass) {
         a.pass = pass;
         select_hist_kernel<<<dim3(bx, d.images), 256, smem, st>>>(a);
-        select_scan_kernel<<<segs, 256, 0, st>>>(a, d.images, bx);
+        if (!a.fold) select_scan_kernel<<<segs, 256, 0, st>>>(a, d.images, bx);
     }
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
