@@ -8,12 +8,17 @@ Implemented on sm_100a kernels (fused forward + analytic backward):
     SSIMLoss                      losses.py:146-155   kornia-policy DSSIM, no kornia dependency
     HybridLossPlus                losses.py:223-372   L1 + dE00 + DSSIM + physics (+ injected extras)
 
-Out of scope (stay stock PyTorch in the reference): the VGG19
-`PerceptualLoss` and LPIPS.  `HybridLossPlus` takes them as injected modules (`perceptual_module`,
-`lpips_module`); without one the term is skipped and logged as 0 — nothing here downloads weights.
+Out of the kernel scope (stock PyTorch in the reference too): the VGG19
+`PerceptualLoss` and LPIPS.  `PerceptualLoss` below is the same stock torchvision wrapper (losses.py:32-69), and
+`HybridLoss` / `HybridLossPlus` build it by default exactly as the reference does (losses.py:84, 250) so that a
+drop-in swap keeps the training objective.  When the IMAGENET1K_V1 weights can be neither found in the torch hub
+cache nor downloaded, construction emits ONE `RuntimeWarning` naming the missing term (never a silent 0); an
+explicit `perceptual_module=` (any (gen, tgt) -> scalar module) overrides the default, `perceptual_module=False`
+switches the term off on purpose.
 """
 from __future__ import annotations
 
+import warnings
 from typing import Dict, Optional, Union
 
 import torch
@@ -81,7 +86,7 @@ class PhysicsConsistencyLoss(nn.Module):
         psf = self._psf(c, dev)
         rho_t, rho_s, rho_st = _as_rho(expo_ratio, n, dev)
         cfg = Fn.PhysCfg(nat.PAD["replicate"], False, False, 1e-12, 1, False, bool(self.clamp_align))
-        vec = Fn.PhysProjector.apply(x, a, psf, rho_t, rho_s, rho_st, cfg)
+        vec = Fn.PhysProjector.apply(x, a, psf, rho_t, rho_s, rho_st, cfg)[0]
         out = vec[n]
         return out if home == dev else out.to(home)
 
@@ -139,7 +144,7 @@ class PhysicalConsistencyLossSRGB(nn.Module):
             c = x.shape[1]
             psf = Fn.PreparedPSF(torch.ones(c, 1, 1, 1, dtype=torch.float32, device=dev), Fn.PSF_DEPTHWISE, 1, 1, False)
         cfg = Fn.PhysCfg(nat.PAD["zeros"], False, False, 1e-12, 1, False, True)
-        out = Fn.PhysProjector.apply(x, a, psf, rho_t, rho_s, rho_st, cfg)[n]
+        out = Fn.PhysProjector.apply(x, a, psf, rho_t, rho_s, rho_st, cfg)[0][n]
         return out if home == dev else out.to(home)
 
 
@@ -205,6 +210,68 @@ class SSIMLoss(nn.Module):
         return out if home == dev else out.to(home)
 
 
+class PerceptualLoss(nn.Module):
+    """VGG19 feature distance on sRGB [0,1] inputs (losses.py:32-69): clamp, ImageNet mean / std normalisation,
+    the first 36 layers of torchvision's `vgg19(IMAGENET1K_V1).features`, then MSE (or L1) between the two feature
+    maps.  Stock PyTorch — this term is not part of the kernel path; it is here so that `HybridLoss(Plus)` keeps
+    the reference's objective.  Raises whatever torchvision raises when the weights cannot be obtained."""
+
+    def __init__(self, device: Union[str, torch.device] = "cuda", use_mse: bool = True, reduction: str = "mean"):
+        super().__init__()
+        from torchvision import models
+        feats = models.vgg19(weights=models.VGG19_Weights.IMAGENET1K_V1).features
+        self.vgg = nn.Sequential(*list(feats.children())[:36]).eval()
+        for p in self.vgg.parameters():
+            p.requires_grad = False
+        self.register_buffer("mean", torch.tensor([0.485, 0.456, 0.406], dtype=torch.float32).view(1, 3, 1, 1),
+                             persistent=False)
+        self.register_buffer("std", torch.tensor([0.229, 0.224, 0.225], dtype=torch.float32).view(1, 3, 1, 1),
+                             persistent=False)
+        self.loss_fn = nn.functional.mse_loss if use_mse else nn.functional.l1_loss
+        self.reduction = reduction
+        self.to(_resolve_device(device))
+
+    def forward(self, generated_img: Tensor, target_img: Tensor) -> Tensor:
+        dev = generated_img.device
+        target_img = target_img.to(dev)
+        if next(self.vgg.parameters()).device != dev:
+            self.vgg = self.vgg.to(dev)
+        mean, std = self.mean.to(dev), self.std.to(dev)
+        fg = self.vgg(((generated_img.clamp(0, 1) - mean) / std).float())
+        ft = self.vgg(((target_img.clamp(0, 1) - mean) / std).float())
+        return self.loss_fn(fg, ft, reduction=self.reduction)
+
+
+_perc_warned = False
+_perc_failure: Optional[BaseException] = None   # the attempt is made once per process (it builds a 143 M-parameter net)
+
+
+def _default_perceptual(device, owner: str, weight_desc: str) -> Optional[nn.Module]:
+    """The reference's default VGG term (losses.py:84, 250), or None with ONE RuntimeWarning when its pretrained
+    weights are unobtainable (offline box): the caller's objective then lacks the term and the warning says so."""
+    global _perc_warned, _perc_failure
+    import socket
+    old = socket.getdefaulttimeout()
+    try:
+        if _perc_failure is not None:
+            raise _perc_failure
+        socket.setdefaulttimeout(10.0)        # an offline box must not hang in the download attempt
+        return PerceptualLoss(device=device)
+    except Exception as exc:  # URLError / OSError / RuntimeError from torch.hub, ImportError without torchvision
+        _perc_failure = exc
+        if not _perc_warned:
+            _perc_warned = True
+            warnings.warn(
+                f"{owner}: the VGG19 perceptual term ({weight_desc}) is DISABLED because its IMAGENET1K_V1 weights "
+                f"could not be loaded ({type(exc).__name__}: {exc}). The reference always adds this term "
+                "(NewBP_model/losses.py:84, 250, 337): the objective differs until the weights are in the torch hub "
+                "cache or a module is passed as perceptual_module=. Pass perceptual_module=False to silence this.",
+                RuntimeWarning, stacklevel=3)
+        return None
+    finally:
+        socket.setdefaulttimeout(old)
+
+
 class _L1Mean(nn.Module):
     """nn.L1Loss() (global mean) with its sign/numel gradient from one streaming pass (losses.py:249, 332)."""
 
@@ -216,17 +283,20 @@ class _L1Mean(nn.Module):
 
 class HybridLoss(nn.Module):
     """Legacy L1 + perceptual loss (losses.py:72-89): `forward(generated, target) -> (total, l1, perceptual)`.
-    The L1 term runs on the one-pass value + gradient kernel; the VGG19 perceptual network is out of scope
-     and is injected as `perceptual_module` (None -> the term is 0)."""
+    The L1 term runs on the one-pass value + gradient kernel; the VGG19 perceptual term is the stock
+    `PerceptualLoss` built by default as upstream (`perceptual_module=` overrides, `False` disables; a
+    RuntimeWarning — never a silent 0 — when the pretrained weights are unobtainable)."""
 
     def __init__(self, lambda_l1: float = 1.0, lambda_perceptual: float = 0.1, device: str = "cuda", *,
-                 perceptual_module: Optional[nn.Module] = None):
+                 perceptual_module: Union[nn.Module, None, bool] = None):
         super().__init__()
         self.device = _resolve_device(device)
         self.lambda_l1 = lambda_l1
         self.lambda_perceptual = lambda_perceptual
         self.l1_loss = _L1Mean()
-        self.perceptual_loss = perceptual_module
+        if perceptual_module is None:
+            perceptual_module = _default_perceptual(self.device, "HybridLoss", f"lambda_perceptual={lambda_perceptual}")
+        self.perceptual_loss = perceptual_module if isinstance(perceptual_module, nn.Module) else None
 
     def forward(self, generated_img: Tensor, target_img: Tensor):
         l1_val = self.l1_loss(generated_img, target_img)
@@ -240,9 +310,11 @@ class HybridLoss(nn.Module):
 
 class HybridLossPlus(nn.Module):
     """Pluggable hybrid loss, same constructor / kwargs-only forward / `(total, logs)` contract as
-    losses.py:223-372.  L1, DeltaE00, DSSIM and the physics term run on the sm_100a kernels; the VGG
-    perceptual and LPIPS terms are NOT built here (no weight download) — pass `perceptual_module` /
-    `lpips_module` (any nn.Module mapping (gen, tgt) -> scalar / per-sample tensor) to include them.
+    losses.py:223-372.  L1, DeltaE00, DSSIM and the physics term run on the sm_100a kernels.  The VGG perceptual
+    term is the stock `PerceptualLoss`, built by default exactly as upstream (losses.py:250; `perceptual_module=`
+    overrides it, `perceptual_module=False` disables it; when the pretrained weights are unobtainable the
+    constructor warns once instead of silently dropping the term).  LPIPS is injected as `lpips_module`
+    (any nn.Module mapping (gen, tgt) -> per-sample tensor; upstream builds `lpips.LPIPS` only if `use_lpips`).
 
     The reference checks every term for finiteness as it goes (5-7 host syncs per step); here the terms are
     checked together after the last one (a single sync), raising the same RuntimeError that names the first
@@ -257,10 +329,19 @@ class HybridLossPlus(nn.Module):
                  w_deltaE: float = 0.02, w_ssim: float = 0.05, w_phys: float = 0.10, use_deltaE: bool = True,
                  use_ssim: bool = True, use_lpips: bool = False, use_phys: bool = True, use_uncertainty: bool = False,
                  physics_kernel: Optional[Tensor] = None, physics_psf_module: Optional[nn.Module] = None, *,
-                 perceptual_module: Optional[nn.Module] = None, lpips_module: Optional[nn.Module] = None,
+                 perceptual_module: Union[nn.Module, None, bool] = None, lpips_module: Optional[nn.Module] = None,
                  check_finite: bool = True, fused: bool = True):
         super().__init__()
         device = _resolve_device(device)
+        if perceptual_module is None:
+            if use_uncertainty or w_perc != 0:
+                perceptual_module = _default_perceptual(device, "HybridLossPlus", f"w_perc={w_perc}")
+        if not isinstance(perceptual_module, nn.Module):
+            perceptual_module = None
+        if use_lpips and lpips_module is None:
+            warnings.warn("HybridLossPlus(use_lpips=True) without lpips_module=: the LPIPS term is not built here "
+                          "(pretrained weights; upstream losses.py:266-279) and is DISABLED.", RuntimeWarning,
+                          stacklevel=2)
         self.register_buffer("_zero", torch.tensor(0.0), persistent=False)
         self._zero: Tensor
         self._zero_cache: Dict[torch.device, Tensor] = {}
@@ -278,7 +359,6 @@ class HybridLossPlus(nn.Module):
         self.use_uncertainty = use_uncertainty
         self.check_finite = check_finite
         self.fused = fused          # one autograd node for the kernel terms (falls back to per-term modules when it cannot)
-        self._spec = None
         if use_uncertainty:
             self.log_sigma = nn.ParameterDict({k: nn.Parameter(torch.zeros(()))
                                                for k in ("l1", "perc", "lpips", "de", "ssim", "phys")})
@@ -318,13 +398,13 @@ class HybridLossPlus(nn.Module):
         uncertainty weights, a non-CrosstalkPSF / hooked physics module, unexpected shapes)."""
         if self.use_uncertainty or Bhat_raw.ndim != 4 or Bhat_srgb01.ndim != 4 or Bhat_srgb01.shape[1] != 3:
             return None
-        if self._spec is None:
-            self._spec = dict(w={k: float(v) for k, v in self.w.items()}, use_de=self.deltaE is not None,
-                              de_eps=self.deltaE.eps if self.deltaE is not None else 1e-6,
-                              use_ssim=self.ssim is not None,
-                              ssim_window=self.ssim.window_size if self.ssim is not None else 11,
-                              ssim_max_val=self.ssim.max_val if self.ssim is not None else 1.0)
-        spec = self._spec
+        # rebuilt every call: `self.w` is read per forward like upstream (losses.py:308-316), so weight schedules
+        # that edit the dict take effect, and no per-call tensor is kept on the module
+        spec = dict(w={k: float(v) for k, v in self.w.items()}, use_de=self.deltaE is not None,
+                    de_eps=self.deltaE.eps if self.deltaE is not None else 1e-6,
+                    use_ssim=self.ssim is not None,
+                    ssim_window=self.ssim.window_size if self.ssim is not None else 11,
+                    ssim_max_val=self.ssim.max_val if self.ssim is not None else 1.0)
         spec["phys"] = None
         if self.phys is not None:
             n, c = Bhat_raw.shape[:2]

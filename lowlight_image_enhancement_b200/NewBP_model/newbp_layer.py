@@ -13,6 +13,7 @@
 from __future__ import annotations
 
 import torch
+from torch.autograd.function import once_differentiable
 import torch.nn as nn
 
 from .. import _functional as Fn
@@ -48,6 +49,7 @@ class NewBPFunction(torch.autograd.Function):
         return y if ctx.home == dev else y.to(ctx.home)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, grad_outputs):
         (k,) = ctx.saved_tensors
         gy = nat.stage(grad_outputs, k.device, k.dtype)

@@ -12,6 +12,7 @@ from typing import Optional, Tuple
 
 import torch
 from torch import Tensor
+from torch.autograd.function import once_differentiable
 
 from . import _native as nat
 
@@ -227,20 +228,24 @@ def phys_stream_overlap(enabled: bool) -> None:
 
 
 class PhysProjector(torch.autograd.Function):
-    """vec[N+2] = (per-sample means, batch mean, batch sum) of the loss map; differentiable in pred."""
+    """(vec[N+2], flags, map | None): vec = (per-sample means, batch mean, batch sum) of the loss map, differentiable in
+    pred; `flags` (int32[1], non-finite input bits) and the optional |residual| map are non-differentiable outputs."""
 
     @staticmethod
-    def forward(ctx, pred, obs, psf: PreparedPSF, rho_t, rho_scalar, rho_strides, cfg: PhysCfg):
+    def forward(ctx, pred, obs, psf: PreparedPSF, rho_t, rho_scalar, rho_strides, cfg: PhysCfg, want_map: bool = False):
         p = pred.detach().contiguous()
         o = obs.detach().contiguous()
-        vec, flags, _ = phys_forward(p, o, psf, rho_t, rho_scalar, rho_strides, cfg, False)
+        vec, flags, amap = phys_forward(p, o, psf, rho_t, rho_scalar, rho_strides, cfg, want_map)
         ctx.save_for_backward(p, o)
         ctx.aux = (psf, rho_t, rho_scalar, rho_strides, cfg)
-        ctx.flags = flags
-        return vec
+        ctx.mark_non_differentiable(flags)
+        if amap is not None:
+            ctx.mark_non_differentiable(amap)
+        return vec, flags, amap
 
     @staticmethod
-    def backward(ctx, gvec):
+    @once_differentiable
+    def backward(ctx, gvec, _gflags, _gmap):
         p, o = ctx.saved_tensors
         psf, rho_t, rho_scalar, rho_strides, cfg = ctx.aux
         n, _, h, w = p.shape
@@ -248,7 +253,7 @@ class PhysProjector(torch.autograd.Function):
         count = o.shape[1] * (h - 2 * ph) * (w - 2 * pw)
         g = gvec[:n] + gvec[n] / n + gvec[n + 1]
         grad = phys_backward(p, o, psf, rho_t, rho_scalar, rho_strides, cfg, g.contiguous().float(), 1.0 / count)
-        return grad, None, None, None, None, None, None
+        return grad, None, None, None, None, None, None, None
 
 
 # ------------------------------------------------------------------------------------------------
@@ -539,7 +544,16 @@ def apply_upstream(ctx, grad: Tensor, gout: Tensor) -> Tensor:
     if getattr(ctx, "_llie_scaled", False) or gout.dim() != 0 or not gout.is_cuda or gout.device != grad.device \
             or torch.is_grad_enabled() and gout.requires_grad:
         prev = getattr(ctx, "_llie_prev", None)
-        return grad * (gout if prev is None else gout / prev)
+        if prev is None:
+            return grad * gout
+        # second backward through a retained graph: the buffer holds unit * prev.  A first upstream scalar of 0 (or a
+        # non-finite one) destroyed it; that cannot be undone, so fail loudly instead of returning inf / NaN (this
+        # path is rare and already slow: the one host sync is acceptable)
+        if not bool(torch.isfinite(prev) & (prev != 0)):
+            raise RuntimeError(
+                "backward through a retained graph after an upstream gradient of 0 / inf / NaN: the in-place scaled "
+                "gradient buffer of this loss node cannot be recovered; recompute the loss instead of retaining it")
+        return grad * (gout / prev)
     g = gout.detach().to(torch.float32)
     dev = grad.device
     with torch.cuda.device(dev):
@@ -581,6 +595,7 @@ class DeltaE00LossFn(torch.autograd.Function):
         return (sums.sum() / float(n * h * w)).to(torch.float32)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, gout):
         (grad,) = ctx.saved_tensors
         return apply_upstream(ctx, grad, gout), None, None
@@ -627,6 +642,7 @@ class SSIMLossFn(torch.autograd.Function):
         return tot.to(torch.float32)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, gout):
         x, y, win, coef = ctx.saved_tensors
         dev = x.device
@@ -662,6 +678,7 @@ class L1MeanFn(torch.autograd.Function):
         return (sums[0] / float(a.numel())).to(torch.float32)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, gout):
         (grad,) = ctx.saved_tensors
         return apply_upstream(ctx, grad, gout), None
@@ -676,6 +693,9 @@ def _one(dev: torch.device) -> Tensor:
         t = torch.ones(1, dtype=torch.float32, device=dev)
         _ones[dev] = t
     return t
+
+
+_wvec_cache: dict = {}
 
 
 class HybridFusedFn(torch.autograd.Function):
@@ -775,12 +795,18 @@ class HybridFusedFn(torch.autograd.Function):
         nat.count_launch(launches)
         terms = torch.stack(vals)
         present = [0] + ([1] if spec["use_de"] else []) + ([2] if spec["use_ssim"] else []) + ([3] if ph is not None else [])
-        key = ("_wvec", dev.index)
-        if key not in spec:  # weights are fixed for the lifetime of the module: upload once
-            names = ("l1", "de", "ssim", "phys")
-            spec[key] = (torch.tensor(present, device=dev),
-                         torch.tensor([w[names[i]] for i in present], dtype=torch.float32, device=dev))
-        idx, wvec = spec[key]
+        names = ("l1", "de", "ssim", "phys")
+        # index / weight vectors depend on which terms are present THIS call (A_srgb01 may be None on some batches,
+        # image_restoration_model.py:300) and on the current weights (schedules may edit module.w): cached by value,
+        # never on the module's spec dict
+        key = (dev.index, tuple(present), tuple(float(w[names[i]]) for i in present))
+        cached = _wvec_cache.get(key)
+        if cached is None:
+            if len(_wvec_cache) > 64:
+                _wvec_cache.clear()
+            cached = _wvec_cache[key] = (torch.tensor(present, device=dev),
+                                         torch.tensor(key[2], dtype=torch.float32, device=dev))
+        idx, wvec = cached
         total = (terms.index_select(0, idx) * wvec).sum()
         ctx.save_for_backward(*[t for t in (g_raw, g_srgb) if t is not None])
         ctx.have = (g_raw is not None, g_srgb is not None)
@@ -788,6 +814,7 @@ class HybridFusedFn(torch.autograd.Function):
         return total, terms
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, gtot, _gterms):
         saved = list(ctx.saved_tensors)
         g_raw = saved.pop(0) if ctx.have[0] else None

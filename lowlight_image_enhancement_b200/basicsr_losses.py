@@ -14,6 +14,7 @@ import math
 from typing import Optional
 
 import torch
+from torch.autograd.function import once_differentiable
 import torch.nn as nn
 from torch import Tensor
 
@@ -59,6 +60,7 @@ class _PixelLossFn(torch.autograd.Function):
         return (sums[0] * scale).to(torch.float32)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, gout):
         (grad,) = ctx.saved_tensors
         return grad * gout, None, None, None, None, None
@@ -164,6 +166,7 @@ class _PSNRLossFn(torch.autograd.Function):
         return (scale * torch.log(mse + 1e-8).mean()).to(torch.float32)
 
     @staticmethod
+    @once_differentiable
     def backward(ctx, gout):
         x, y, mse = ctx.saved_tensors
         dev = x.device

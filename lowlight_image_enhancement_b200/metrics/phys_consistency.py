@@ -81,9 +81,9 @@ def _core(pred, obs, *, psf, expo_ratio, reduction, padding, normalize_psf, enfo
     cfg = Fn.PhysCfg(nat.PAD[padding], crop == "valid", robust == "charbonnier", float(eps), 0, bool(clamp01), False)
 
     amap = None
-    if differentiable and p.requires_grad and not return_map:
-        vec = Fn.PhysProjector.apply(p, o, prepared, rho_t, rho_s, rho_st, cfg)
-        flags = None
+    if differentiable and p.requires_grad:
+        # same non-finite input contract and the same optional |residual| map as the no-grad metric
+        vec, flags, amap = Fn.PhysProjector.apply(p, o, prepared, rho_t, rho_s, rho_st, cfg, return_map)
     else:
         vec, flags, amap = Fn.phys_forward(p.detach(), o, prepared, rho_t, rho_s, rho_st, cfg, return_map)
     if flags is not None:

@@ -10,8 +10,9 @@ Follows (paths relative to /root/reference):
   * NewBP_model/losses.py:99-143    DeltaE00Loss._ciede2000 (LOSS variant: eps=1e-6 everywhere,
                                      hue mod 2pi, boolean-mask wraps, sin(dtheta), +eps under final sqrt)
 
-Third-party arithmetic (kornia==0.6.12 color/lab.py::rgb_to_lab, color/rgb.py::rgb_to_linear_rgb,
-color/xyz.py::rgb_to_xyz — not vendored, not installed): restated in `rgb_to_lab`; parity unpinned.
+Third-party arithmetic (kornia==0.6.12 color/lab.py::rgb_to_lab / lab_to_rgb, color/rgb.py::rgb_to_linear_rgb /
+linear_rgb_to_rgb, color/xyz.py::rgb_to_xyz / xyz_to_rgb — not vendored, not installed, probed absent on the GPU
+image too): restated in `rgb_to_lab` / `lab_to_rgb`; parity unpinned.
 """
 from __future__ import annotations
 
@@ -37,6 +38,31 @@ def rgb_to_lab(img: torch.Tensor) -> torch.Tensor:
     f = torch.where(t > thr, torch.pow(t.clamp(min=thr), 1 / 3.0), 7.787 * t + 4.0 / 29.0)
     fx, fy, fz = f[..., 0, :, :], f[..., 1, :, :], f[..., 2, :, :]
     return torch.stack([116.0 * fy - 16.0, 500.0 * (fx - fy), 200.0 * (fy - fz)], dim=-3)
+
+
+def lab_to_rgb(lab: torch.Tensor, clip: bool = True) -> torch.Tensor:
+    """kornia 0.6.12 lab_to_rgb (only the reference's TESTS call it, standard_tests/test_color_error.py:191-192):
+    Lab -> f -> XYZ (times the D65 white) -> linear RGB (inverse matrix) -> sRGB OETF, clipped to [0,1]."""
+    L, a, b = lab[..., 0, :, :], lab[..., 1, :, :], lab[..., 2, :, :]
+    fy = (L + 16.0) / 116.0
+    fx = (a / 500.0) + fy
+    fz = fy - (b / 200.0)
+    if clip:
+        fz = fz.clamp(min=0.0)
+    f = torch.stack([fx, fy, fz], dim=-3)
+    xyz = torch.where(f > 0.2068966, torch.pow(f, 3.0), (f - 4.0 / 29.0) / 7.787)
+    white = torch.tensor([0.95047, 1.0, 1.08883], dtype=xyz.dtype, device=xyz.device)[..., :, None, None]
+    xyz = xyz * white
+    x, y, z = xyz[..., 0, :, :], xyz[..., 1, :, :], xyz[..., 2, :, :]
+    r = 3.2404813432005266 * x + -1.5371515162713185 * y + -0.4985363261688878 * z
+    g = -0.9692549499965682 * x + 1.8759900014898907 * y + 0.0415559265582928 * z
+    bl = 0.0556466391351772 * x + -0.2040413383665112 * y + 1.0573110696453443 * z
+    lin = torch.stack([r, g, bl], dim=-3)
+    thr = 0.0031308
+    rgb = torch.where(lin > thr, 1.055 * torch.pow(lin.clamp(min=thr), 1 / 2.4) - 0.055, 12.92 * lin)
+    if clip:
+        rgb = rgb.clamp(0.0, 1.0)
+    return rgb
 
 
 def _rad(deg: float) -> float:

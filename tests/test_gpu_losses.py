@@ -151,11 +151,11 @@ def test_hybrid_loss_plus_vs_oracle(dev, mode, fused):
     kw = dict(w_l1=1.0, w_de=0.02, w_ssim=0.05, w_phys=0.05)
     if mode == "raw_kernel":
         ora_kw = dict(physics_kernel=kern)
-        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, fused=fused)
+        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, fused=fused, perceptual_module=False)
     else:
         psf = CrosstalkPSF("rgb", kern)
         ora_kw = dict(psf_kernel=psf.kernel.clone())
-        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_psf_module=psf, fused=fused)
+        mod = HybridLossPlus(device="cuda", w_phys=0.05, physics_psf_module=psf, fused=fused, perceptual_module=False)
 
     def ora(dt):
         x = Bhat.to(dt).clone().requires_grad_(True)
@@ -191,14 +191,14 @@ def test_hybrid_loss_plus_behaviour(dev):
     kern = torch.tensor([[.01, .02, .01], [.02, .88, .02], [.01, .02, .01]]).view(1, 1, 3, 3)
     args = dict(B_raw=B, A_raw=B / 100.0, expo_ratio=rho, B_srgb01=B)
     # uncertainty weighting: val * exp(-2 s) + s, learnable log-sigmas receive gradients (losses.py:308-316)
-    mod = HybridLossPlus(device="cuda", use_uncertainty=True, physics_kernel=kern).to(dev)
+    mod = HybridLossPlus(device="cuda", use_uncertainty=True, physics_kernel=kern, perceptual_module=False).to(dev)
     tot, logs = mod(Bhat_raw=x, Bhat_srgb01=x.clamp(0, 1), **args)
     tot.backward()
     assert all(mod.log_sigma[k].grad is not None for k in ("l1", "de", "ssim", "phys"))
     ref = sum(float(logs[k]) for k in ("L1_raw", "DeltaE", "SSIM", "Phys"))
     assert abs(float(tot) - ref) < 1e-5 * ref                         # s = 0 -> plain sum
     # switches
-    mod2 = HybridLossPlus(device="cuda", use_deltaE=False, use_ssim=False, use_phys=False)
+    mod2 = HybridLossPlus(device="cuda", use_deltaE=False, use_ssim=False, use_phys=False, perceptual_module=False)
     tot2, logs2 = mod2(Bhat_raw=x, Bhat_srgb01=x, **args)
     assert "DeltaE" not in logs2 and "SSIM" not in logs2 and "Phys" not in logs2
     assert abs(float(tot2) - float(logs2["L1_raw"])) < 1e-7
@@ -214,7 +214,7 @@ def test_hybrid_loss_plus_behaviour(dev):
     bad = x.detach().clone()
     bad[0, 0, 0, 0] = float("nan")
     with pytest.raises(RuntimeError, match="non-finite values in term 'L1_raw'"):
-        HybridLossPlus(device="cuda", physics_kernel=kern)(Bhat_raw=bad, Bhat_srgb01=bad, **args)
+        HybridLossPlus(device="cuda", physics_kernel=kern, perceptual_module=False)(Bhat_raw=bad, Bhat_srgb01=bad, **args)
 
 
 def test_legacy_hybrid_loss(dev):
@@ -235,7 +235,7 @@ def test_legacy_hybrid_loss(dev):
     ref.backward()
     assert abs(float(tot) - float(ref)) < 1e-6 and abs(float(l1) - float(torch.nn.functional.l1_loss(a, b))) < 1e-7
     assert _rel(x.grad, xr.grad) < 1e-6
-    tot2, _, p2 = HybridLoss(device="cuda")(x.detach(), b.to(dev))
+    tot2, _, p2 = HybridLoss(device="cuda", perceptual_module=False)(x.detach(), b.to(dev))
     assert float(p2) == 0.0 and abs(float(tot2) - float(l1)) < 1e-7
 
 
@@ -263,7 +263,7 @@ def test_upstream_scalar_is_applied_in_place_and_survives_retained_graphs(dev):
 
     de = DeltaE00Loss()
     kern = torch.tensor([[.01, .02, .01], [.02, .88, .02], [.01, .02, .01]], device=dev).view(1, 1, 3, 3)
-    hyb = HybridLossPlus(device=dev, w_phys=0.05, physics_kernel=kern, check_finite=False)
+    hyb = HybridLossPlus(device=dev, w_phys=0.05, physics_kernel=kern, check_finite=False, perceptual_module=False)
     rho = torch.ones(2, 1, 1, 1, device=dev)
     for make in (lambda x: de(x, b),
                  lambda x: hyb(Bhat_raw=x, B_raw=b, A_raw=b * 0.9, expo_ratio=rho, Bhat_srgb01=x, B_srgb01=b)[0]):
@@ -300,3 +300,96 @@ def test_two_column_dssim_kernels_vs_one_column(dev, shape):
     assert abs(float(l0) - float(l2)) <= 1e-6 * abs(float(l2))
     assert float((g0 - g2).abs().max()) <= 2e-6 * float(g2.abs().max())
     assert float(g2.abs().max()) > 0
+
+
+def test_hybrid_fused_terms_and_weights_are_read_per_call(dev):
+    """the fused node must not freeze the set of present terms or the weights on the first call.  The
+    reference allows A_srgb01=None on some batches (image_restoration_model.py:300) and reads self.w on every forward
+    (losses.py:308-316)."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import HybridLossPlus
+    from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import create_crosstalk_psf
+    g = torch.Generator().manual_seed(77)
+    B = torch.rand(2, 3, 40, 48, generator=g).to(dev)
+    x = (B + 0.05 * torch.randn(B.shape, generator=g).to(dev)).clamp(0, 1)
+    A = (B * 0.9).clamp(0, 1)
+    rho = torch.ones(2, 1, 1, 1, device=dev)
+    mod = HybridLossPlus(device="cuda", w_phys=0.10, physics_psf_module=create_crosstalk_psf("rgb", "B2"),
+                         perceptual_module=False)
+    kw = dict(Bhat_raw=x, B_raw=B, A_raw=A, expo_ratio=rho, Bhat_srgb01=x, B_srgb01=B)
+
+    def expect(logs, with_phys):
+        t = mod.w["l1"] * float(logs["L1_raw"]) + mod.w["de"] * float(logs["DeltaE"]) + mod.w["ssim"] * float(logs["SSIM"])
+        return t + (mod.w["phys"] * float(logs["Phys"]) if with_phys else 0.0)
+
+    for with_phys in (True, False, True, False):                      # alternate: present set changes between calls
+        tot, logs = mod(**kw, A_srgb01=A if with_phys else None)
+        assert ("Phys" in logs) == with_phys
+        assert torch.isfinite(tot) and abs(float(tot) - expect(logs, with_phys)) <= 1e-6 * abs(float(tot))
+    mod.w["ssim"] = 0.5                                               # a weight schedule edits the dict in place
+    mod.w["phys"] = 0.0
+    tot, logs = mod(**kw, A_srgb01=A)
+    assert abs(float(tot) - expect(logs, True)) <= 1e-6 * abs(float(tot))
+    # gradient follows the new weights too: d total / dx with w_ssim 0.5 differs from the w_ssim 0.05 one
+    xg = x.clone().requires_grad_(True)
+    mod(**{**kw, "Bhat_raw": xg, "Bhat_srgb01": xg}, A_srgb01=A)[0].backward()
+    g_new = xg.grad.clone()
+    mod.w["ssim"] = 0.05
+    xg = x.clone().requires_grad_(True)
+    mod(**{**kw, "Bhat_raw": xg, "Bhat_srgb01": xg}, A_srgb01=A)[0].backward()
+    assert float((g_new - xg.grad).abs().max()) > 0
+
+
+def test_retained_graph_after_zero_upstream_fails_loudly(dev):
+    """backward twice through a retained graph with an upstream scalar of 0 first must not hand out inf / NaN
+    gradients (the in-place scaled buffer is gone): RuntimeError.  Double backward is refused (once_differentiable)."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import DeltaE00Loss
+    g = torch.Generator().manual_seed(5)
+    b = torch.rand(1, 3, 24, 24, generator=g).to(dev)
+    x = (b + 0.05).clamp(0, 1).requires_grad_(True)
+    loss = DeltaE00Loss()(x, b)
+    (loss * 0.0).backward(retain_graph=True)
+    assert float(x.grad.abs().max()) == 0.0
+    with pytest.raises(RuntimeError, match="retained graph"):
+        (loss * 2.0).backward()
+    x2 = (b + 0.05).clamp(0, 1).requires_grad_(True)
+    (g1,) = torch.autograd.grad(DeltaE00Loss()(x2, b), x2, create_graph=True)
+    with pytest.raises(RuntimeError):
+        g1.sum().backward()
+
+
+@pytest.mark.parametrize("in_dtype", [torch.float32, torch.bfloat16, torch.float16])
+def test_losses_under_autocast(dev, in_dtype):
+    """BASELINE configs[4] / image_restoration_model.py:255-310: the reference calls the hybrid loss inside
+    `autocast`.  Every loss class must (i) compute in fp32 whatever the autocast state, (ii) return an fp32 scalar,
+    (iii) equal the plain fp32 call on the up-cast inputs to 1e-6, (iv) hand back a gradient in the input's dtype."""
+    from lowlight_image_enhancement_b200.NewBP_model.losses import (DeltaE00Loss, HybridLossPlus,
+                                                                   PhysicalConsistencyLossSRGB, PhysicsConsistencyLoss,
+                                                                   SSIMLoss)
+    from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import build_psf_kernels, create_crosstalk_psf
+    g = torch.Generator().manual_seed(123)
+    B = torch.rand(2, 3, 48, 64, generator=g).to(dev)
+    X = (B + 0.05 * torch.randn(B.shape, generator=g).to(dev)).clamp(0, 1).to(in_dtype)
+    A = (B * 0.8).clamp(0, 1)
+    rho = torch.ones(2, 1, 1, 1, device=dev)
+    kern = build_psf_kernels("rgb", "B2")
+    hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, perceptual_module=False)
+    cases = {
+        "de": lambda x: DeltaE00Loss()(x, B),
+        "ssim": lambda x: SSIMLoss()(x, B),
+        "phys_raw": lambda x: PhysicsConsistencyLoss(kern)(x, A, rho),
+        "phys_srgb": lambda x: PhysicalConsistencyLossSRGB(create_crosstalk_psf("rgb", "B2").to(dev))(x, A, rho),
+        "hybrid": lambda x: hyb(Bhat_raw=x, B_raw=B, A_raw=A, expo_ratio=rho, Bhat_srgb01=x.clamp(0, 1), B_srgb01=B)[0],
+    }
+    for name, fn in cases.items():
+        xa = X.clone().requires_grad_(True)
+        with torch.autocast("cuda", dtype=torch.bfloat16 if in_dtype != torch.float16 else torch.float16):
+            va = fn(xa)
+        va.backward()
+        xf = X.float().clone().requires_grad_(True)
+        vf = fn(xf)
+        vf.backward()
+        assert va.dtype == torch.float32 and va.ndim == 0, name
+        assert abs(float(va) - float(vf)) <= 1e-6 * abs(float(vf)), (name, float(va), float(vf))
+        assert xa.grad.dtype == in_dtype, name
+        ref = xf.grad.to(in_dtype).float()
+        assert float((xa.grad.float() - ref).abs().max()) <= 1e-6 * float(ref.abs().max()) + 1e-12, name
