@@ -56,8 +56,9 @@ int llie_check_device(void);
 /* Diagnostic knobs for A/B measurements (process-wide, not thread-safe; defaults are the product). */
 #define LLIE_TUNE_PHYS_PATH 1 /* 0 TMA row ring (default) | 1 TMA tile ring | 2 generic only | 3 register prefetch */
 #define LLIE_TUNE_PHYS_ROWS 2 /* rows per warp chunk of the rolling path; 0 = heuristic */
-#define LLIE_TUNE_SSIM_PATH 3 /* 0 auto (two-column streaming kernel for statistics-only 11-tap calls, else the
-                                 one-column streaming kernel) | 1 shared-memory tile kernel | 2 one-column streaming */
+#define LLIE_TUNE_SSIM_PATH 3 /* 0 auto (TMA row ring + packed FP32 kernel for statistics-only / loss-forward 11-tap
+                                 calls, else the one-column streaming kernel) | 1 shared-memory tile kernel |
+                                 2 one-column streaming | 3 two-column cp.async streaming kernel (round-1 default) */
 #define LLIE_TUNE_SSIM_SEG_ROWS 4 /* output rows per CTA of the streaming SSIM kernel; 0 = heuristic */
 #define LLIE_TUNE_PHYS_PDL 5 /* 1 (default): ring kernels are launched with programmatic stream serialization, so the
                                 prologue of a kernel overlaps the tail of the previous one | 0 plain launches */
@@ -193,6 +194,9 @@ int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const void *y, do
  *          metrics/ssim.py:246-311 (SSIMEvaluator -> torchmetrics 1.2.0 _ssim_update),
  *          NewBP_model/losses.py:146-155 (SSIMLoss -> kornia 0.6.12 ssim_loss), forward value.
  * The K x K window of all three is the outer product of `win1d` (K normalised taps, device memory).
+ * `win1d_host` is a HOST copy of the same K taps (or NULL): the default 11-tap kernels (TMA row ring + packed FP32,
+ * csrc/ssim_ring.cu) take the taps by value in their kernel parameters; without it the call runs on the kernels that
+ * read the device copy (same results to rounding).
  * ------------------------------------------------------------------------ */
 #define LLIE_SSIM_MAX_K 15
 typedef struct llie_ssim_desc {
@@ -209,7 +213,8 @@ typedef struct llie_ssim_desc {
 /*   out_sum   [n * co] doubles, co = luma ? 1 : c;  out_map NULL or [n, co, h, w] SSIM map
  *   out_flags [1] int: bit0 non-finite in x, bit1 in y */
 int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                    double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream);
+                    const float *win1d_host, double *out_sum, float *out_map, int32_t *out_flags, void *workspace,
+                    void *stream);
 
 /* Differentiable (D)SSIM, kornia policy (reflect border, same size, no variance clamp): forward as
  * llie_ssim_stats plus out_coef [3][n*c][h][w] = grad_scale * dLossMap/dS * (A1, A2, A3), the per-window
@@ -219,8 +224,8 @@ int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, 
  * [n,c,h,w] map (reduction 'none'); with `accumulate` the result is added to out_grad (fused hybrid loss).
  * replaces kornia.losses.SSIMLoss autograd (losses.py:146-155). */
 int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                           float grad_scale, double *out_sum, float *out_map, float *out_coef, int32_t *out_flags,
-                           void *workspace, void *stream);
+                           const float *win1d_host, float grad_scale, double *out_sum, float *out_map, float *out_coef,
+                           int32_t *out_flags, void *workspace, void *stream);
 int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
                             const float *coef, const float *grad_out, int32_t grad_out_is_map, int32_t accumulate,
                             float *out_grad, void *stream);

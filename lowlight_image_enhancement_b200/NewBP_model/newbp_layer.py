@@ -33,6 +33,17 @@ class NewBPFunction(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, input, kernel, padding, groups):
+        # dtype contract of F.conv2d under autocast (newbp_layer.py:13 runs inside the caller's autocast region): CUDA
+        # operands are rounded to the autocast dtype, products are accumulated in fp32, the result is returned in the
+        # autocast dtype.  The kernel below computes in fp32 on the rounded operands, i.e. the same arithmetic.
+        lowp = None
+        ctx.in_dtype = input.dtype
+        if input.is_cuda and input.is_floating_point() and torch.is_autocast_enabled("cuda") \
+                and input.dtype != torch.float64:
+            lowp = torch.get_autocast_dtype("cuda")
+            input = input.to(lowp)
+            kernel = kernel.to(lowp)
+        ctx.lowp = lowp
         if input.dtype not in (torch.float32, torch.float64):
             input = input.float()
         dev = nat.cuda_device_for(input, kernel)
@@ -46,6 +57,8 @@ class NewBPFunction(torch.autograd.Function):
         ctx.groups = groups
         ctx.x_shape = tuple(x.shape)
         y = Fn.newbp_conv(x, k, padding, groups)
+        if lowp is not None:
+            y = y.to(lowp)
         return y if ctx.home == dev else y.to(ctx.home)
 
     @staticmethod
@@ -54,6 +67,8 @@ class NewBPFunction(torch.autograd.Function):
         (k,) = ctx.saved_tensors
         gy = nat.stage(grad_outputs, k.device, k.dtype)
         gx = Fn.newbp_adjoint(gy, k, ctx.padding, ctx.groups, ctx.x_shape)
+        if ctx.lowp is not None:
+            gx = gx.to(ctx.lowp).to(ctx.in_dtype)   # rounded like the half conv_transpose2d, in the caller's dtype
         return (gx if ctx.home == k.device else gx.to(ctx.home)), None, None, None
 
 
@@ -104,7 +119,6 @@ class CrosstalkPSF(nn.Module):
         self.register_buffer("kernel", k, persistent=True)
         self.kernel: torch.Tensor
 
-    @torch.amp.custom_fwd(device_type="cuda", cast_inputs=torch.float32)
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         assert x.shape[1] == 3, "CrosstalkPSF expects sRGB inputs (3 channels)."
         k = self.kernel

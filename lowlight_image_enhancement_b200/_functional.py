@@ -367,9 +367,18 @@ def window_1d(kind: str, k: int, sigma: float, dev: torch.device) -> Tensor:
             g = g / g.sum()
         else:
             raise ValueError(kind)
-        w = g.to(torch.float32).contiguous().to(dev)
+        g32 = g.to(torch.float32).contiguous()
+        w = g32.to(dev)
+        # host copy of the same taps: the TMA-ring SSIM kernels take them by value in their kernel parameters
+        w._llie_host = (nat.C.c_float * g32.numel())(*g32.tolist())
         _win_cache[key] = w
     return w
+
+
+def win_host(win: Tensor):
+    """ctypes float array with the host copy of a `window_1d` tensor's taps (None for foreign tensors: the call then
+    runs on the kernels that read the device copy)."""
+    return getattr(win, "_llie_host", None)
 
 
 def ssim_stats(x: Tensor, y: Tensor, win: Tensor, *, pad_mode: int, c1: float, c2: float, eps: float,
@@ -386,8 +395,8 @@ def ssim_stats(x: Tensor, y: Tensor, win: Tensor, *, pad_mode: int, c1: float, c
     d = nat.SsimDesc(n, c, h, w, int(win.numel()), pad_mode, int(luma), int(clamp_in), int(clamp_var),
                      int(interior), int(loss_map), float(c1), float(c2), float(eps))
     with torch.cuda.device(dev):
-        rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(sums), nat.ptr(smap),
-                                       nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+        rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), win_host(win), nat.ptr(sums),
+                                       nat.ptr(smap), nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
     nat.check(rc, "llie_ssim_stats")
     nat.count_launch()
     return sums, flags, smap
@@ -623,14 +632,15 @@ class SSIMLossFn(torch.autograd.Function):
         with torch.cuda.device(dev):
             if need_grad:
                 coef = torch.empty((3, n, c, h, w), dtype=torch.float32, device=dev)
-                rc = nat.lib().llie_ssim_loss_forward(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), scale, nat.ptr(sums),
+                rc = nat.lib().llie_ssim_loss_forward(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), win_host(win), scale, nat.ptr(sums),
                                                       nat.ptr(smap), nat.ptr(coef), nat.ptr(flags),
                                                       nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
                 ctx.save_for_backward(x, y, win, coef)
                 ctx.desc = d
             else:
-                rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(sums), nat.ptr(smap),
-                                               nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+                rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), win_host(win), nat.ptr(sums),
+                                               nat.ptr(smap), nat.ptr(flags), nat.ptr(nat.workspace(dev)),
+                                               nat.stream_ptr(dev))
         nat.check(rc, "llie_ssim_loss_forward")
         nat.count_launch()
         ctx.reduction = reduction
@@ -768,7 +778,7 @@ class HybridFusedFn(torch.autograd.Function):
                 sss = torch.empty((n, c), dtype=torch.float64, device=dev)
                 if need_srgb:
                     coef = torch.empty((3, n, c, h, wd), dtype=torch.float32, device=dev)
-                    nat.check(lib.llie_ssim_loss_forward(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win),
+                    nat.check(lib.llie_ssim_loss_forward(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), win_host(win),
                                                          w["ssim"] / float(xs.numel()), nat.ptr(sss), None,
                                                          nat.ptr(coef), nat.ptr(flags), ws, st), "llie_ssim_loss_forward")
                     acc = 1 if g_srgb is not None else 0
@@ -779,8 +789,8 @@ class HybridFusedFn(torch.autograd.Function):
                               "llie_ssim_loss_backward")
                     launches += 2
                 else:
-                    nat.check(lib.llie_ssim_stats(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), nat.ptr(sss), None,
-                                                  nat.ptr(flags), ws, st), "llie_ssim_stats")
+                    nat.check(lib.llie_ssim_stats(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), win_host(win), nat.ptr(sss),
+                                                  None, nat.ptr(flags), ws, st), "llie_ssim_stats")
                     launches += 1
                 vals[2] = (sss.sum() / float(xs.numel())).to(torch.float32)
             if ph is not None and ph["srgb"]:

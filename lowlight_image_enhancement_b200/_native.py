@@ -93,11 +93,11 @@ _SIGNATURES = {
     "llie_newbp_forward": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_adjoint": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_psnr_stats": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
-    "llie_ssim_stats": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_ssim_stats": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_sqerr": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_loss_grad": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, C.c_float, _VP, _VP, _VP, _VP, _VP]),
-    "llie_ssim_loss_forward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, C.c_float, _VP, _VP, _VP, _VP, _VP,
+    "llie_ssim_loss_forward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, C.c_float, _VP, _VP, _VP, _VP, _VP,
                                          _VP]),
     "llie_ssim_loss_backward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP,
                                           _VP]),

@@ -12,25 +12,11 @@
 // Roofline: this kernel is bound by the FP32 FMA pipe, not by HBM: 2 x 5 x K FMAs per element
 // (110 for K = 11) against 8 bytes of traffic (SSIM section).
 #include "common.cuh"
+#include "ssim_common.cuh"
 
 namespace llie {
 
 constexpr int STH = 32, STW = 64, SNT = 256;
-
-struct SsimArgs {
-    llie_ssim_desc d;
-    const float *x, *y, *win;
-    double *out_sum;
-    float *out_map;
-    float *coef;       // NULL or [3][planes][H][W]: dLoss/dS * (A1, A2, A3) for ssim_loss_bwd_kernel
-    float coef_scale;  // 1 / numel for reduction 'mean'
-    int *out_flags;
-    double *part;  // [planes][tiles_per_plane]
-    int *pflag;    // [gridDim.x]
-    unsigned *ticket;
-    int tiles_x, tiles_y, co;
-    int seg_rows;  // streaming kernel: output rows per CTA
-};
 
 __device__ __forceinline__ float ssim_load(const SsimArgs &a, const float *base, long long plane_stride, int sy,
                                            int sx, float &chk) {
@@ -1247,7 +1233,8 @@ using namespace llie;
 // grid then runs in waves of `slots` resident CTAs, and a wave that is only partly filled costs a full segment time
 // (e.g. 918 CTAs on 888 slots = 3 waves for 2.07 waves of work).  Pick, among 1..4 waves, the segment count whose
 // (slot fill) x (useful rows / rows incl. the `halo` warm-up rows) is best, with at least `min_rows` rows per segment.
-static int pick_seg_rows(long long cols, int h, int slots, int min_rows, int halo) {
+namespace llie {
+int pick_seg_rows(long long cols, int h, int slots, int min_rows, int halo) {
     int best_rows = h;
     double best = -1.0;
     for (int waves = 1; waves <= 4; ++waves) {
@@ -1266,10 +1253,11 @@ static int pick_seg_rows(long long cols, int h, int slots, int min_rows, int hal
     }
     return best_rows;
 }
+}  // namespace llie
 
-static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d, double *out_sum,
-                        float *out_map, float *coef, float coef_scale, int32_t *out_flags, void *workspace,
-                        void *stream) {
+static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
+                        const float *win1d_host, double *out_sum, float *out_map, float *coef, float coef_scale,
+                        int32_t *out_flags, void *workspace, void *stream) {
     LLIE_REQUIRE(desc && x && y && win1d && out_sum && out_flags && workspace, "ssim_stats: null pointer");
     const llie_ssim_desc &d = *desc;
     LLIE_REQUIRE(d.n > 0 && d.c > 0 && d.h > 0 && d.w > 0, "ssim_stats: empty tensor");
@@ -1287,11 +1275,14 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
     a.co = d.luma ? 1 : d.c;
     Workspace ws(workspace);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    // default: TMA row ring + packed FP32 (ssim_ring.cu) for the 11-tap window of all three reference policies
+    if (g_ssim_path == 0 && ssim_ring_eligible(d, x, y, win1d_host, out_map != nullptr, coef))
+        return ssim_ring_forward(a, win1d_host, workspace, st);
     long long grid;
     const bool stream_ok = g_ssim_path != 1 && !d.luma;
     // statistics only (no map / coefficient planes), the 11-tap window of all three reference policies
     // (the loss-coefficient planes are written by the four-map instantiation: no variance clamp on that path)
-    const bool stream2_ok = stream_ok && g_ssim_path == 0 && d.ksize == 11 && out_map == nullptr &&
+    const bool stream2_ok = stream_ok && (g_ssim_path == 0 || g_ssim_path == 3) && d.ksize == 11 && out_map == nullptr &&
                             (coef == nullptr || !d.clamp_var);
     if (stream2_ok) {
         // strips of 256 columns x row segments sized for ~2 resident waves (148 SMs x 3 CTAs), >= 64 rows each
@@ -1354,18 +1345,20 @@ void ssim_tune(int key, int value) {
 }  // namespace llie
 
 extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                               double *out_sum, float *out_map, int32_t *out_flags, void *workspace, void *stream) {
-    return ssim_forward(desc, x, y, win1d, out_sum, out_map, nullptr, 0.f, out_flags, workspace, stream);
+                               const float *win1d_host, double *out_sum, float *out_map, int32_t *out_flags,
+                               void *workspace, void *stream) {
+    return ssim_forward(desc, x, y, win1d, win1d_host, out_sum, out_map, nullptr, 0.f, out_flags, workspace, stream);
 }
 
 extern "C" int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                                      float grad_scale, double *out_sum, float *out_map, float *out_coef,
-                                      int32_t *out_flags, void *workspace, void *stream) {
+                                      const float *win1d_host, float grad_scale, double *out_sum, float *out_map,
+                                      float *out_coef, int32_t *out_flags, void *workspace, void *stream) {
     LLIE_REQUIRE(desc && out_coef, "ssim_loss_forward: null pointer");
     LLIE_REQUIRE(desc->pad_mode == LLIE_PAD_REFLECT && !desc->luma && !desc->clamp_var && !desc->interior,
                  "ssim_loss_forward: the differentiable path is the kornia policy (reflect, same size, no clamps)");
     LLIE_REQUIRE(desc->ksize / 2 < desc->h && desc->ksize / 2 < desc->w, "ssim_loss_forward: reflect pad >= image");
-    return ssim_forward(desc, x, y, win1d, out_sum, out_map, out_coef, grad_scale, out_flags, workspace, stream);
+    return ssim_forward(desc, x, y, win1d, win1d_host, out_sum, out_map, out_coef, grad_scale, out_flags, workspace,
+                        stream);
 }
 
 extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
@@ -1383,7 +1376,7 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
     a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map; a.accumulate = accumulate;
     a.x = x; a.y = y; a.win = win1d; a.coef = coef; a.gout = grad_out; a.out_grad = out_grad;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (g_ssim_path == 0 && !grad_out_is_map && d.ksize == 11) {
+    if ((g_ssim_path == 0 || g_ssim_path == 3) && !grad_out_is_map && d.ksize == 11) {
         a.tiles_x = div_up(d.w, S2W);
         const long long cols = (long long)d.n * d.c * a.tiles_x;
         const int rows = g_ssim_seg_rows > 0 ? (g_ssim_seg_rows < d.h ? g_ssim_seg_rows : d.h)

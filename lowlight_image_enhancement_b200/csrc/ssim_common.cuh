@@ -1,0 +1,29 @@
+// Argument blocks shared by the SSIM kernels of ssim.cu (tile / cp.async streaming kernels) and ssim_ring.cu (TMA row
+// ring + packed-FP32 kernels).
+#pragma once
+#include "common.cuh"
+
+namespace llie {
+
+struct SsimArgs {
+    llie_ssim_desc d;
+    const float *x, *y, *win;
+    double *out_sum;
+    float *out_map;
+    float *coef;       // NULL or [3][planes][H][W]: dLoss/dS * (A1, A2, A3) for ssim_loss_bwd_kernel
+    float coef_scale;  // 1 / numel for reduction 'mean'
+    int *out_flags;
+    double *part;  // [planes][tiles_per_plane]
+    int *pflag;    // [gridDim.x]
+    unsigned *ticket;
+    int tiles_x, tiles_y, co;
+    int seg_rows;  // streaming kernel: output rows per CTA
+};
+
+// launchers of ssim_ring.cu; `eligible` tells ssim.cu whether the ring kernels take this problem
+bool ssim_ring_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host, bool want_map,
+                        const float *coef);
+int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaStream_t st);
+int pick_seg_rows(long long cols, int h, int slots, int min_rows, int halo);
+
+}  // namespace llie

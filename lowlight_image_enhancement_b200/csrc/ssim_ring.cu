@@ -1,0 +1,411 @@
+// 11-tap separable SSIM statistics on a TMA-fed row ring with packed FP32 arithmetic (sm_100a) — the default
+// kernel behind every statistics-only SSIM entry point and the DSSIM loss forward (reference functions: see ssim.cu).
+//
+// Shape of the computation (unchanged from ssim_stream2_kernel, ssim.cu): a CTA owns a 256-column strip x a row
+// segment of one (n, c) plane; each of its 128 threads owns TWO adjacent output columns and marches down the segment;
+// per input row it runs the horizontal pass of the moment maps (x, y, x^2 + y^2, xy; five maps with the variance clamp
+// of ssim_linear) and scatters the results into 11 rolling vertical accumulators per map held in registers.
+// What is new here:
+//   * Packed FP32 (fma.rn.f32x2 / mul.rn.f32x2, SASS FFMA2 / FMUL2): the two columns of a thread share one 64-bit
+//     accumulator.  Vertical pass: acc(c0|c1) += g[j] * h(c0|c1) with a broadcast weight; horizontal pass: the value
+//     at window position p is a broadcast operand and the weight is the pair (g[p-1], g[p-2]) - position p is tap
+//     p - 1 of the left column and tap p - 2 of the right one.  88 scalar multiply-adds per element become 46 issue
+//     slots; the x^2 + y^2 / xy products are formed on the register pairs the 64-bit shared-memory loads deliver.
+//   * Window taps travel in the kernel parameters (constant bank operands): no registers, no loads.
+//   * Rows arrive by TMA: one lane issues two cp.async.bulk copies per row (x and y segments, 16-byte aligned
+//     supersets of the strip) that complete on an mbarrier; the <= 5 + 5 padded columns of a border strip are fetched
+//     by per-lane 4-byte cp.async that report to the SAME mbarrier (cp.async.mbarrier.arrive.noinc), so reflect /
+//     replicate / circular padding costs the consumers nothing and zero padding is a ring that starts zeroed.  The
+//     producing duty rotates over the four warps (row r is issued six rows ahead by warp r mod 4); slots are handed
+//     back through a second mbarrier per slot.  No CTA-wide barrier in the row loop (except with `clamp_in`, whose
+//     in-place clamp of the landed row needs one).
+// Same operation order per output as ssim_stream2_kernel -> equal to it to rounding (tests: <= 1e-6 relative).
+#include "ssim_common.cuh"
+#include "tma.cuh"
+
+namespace llie {
+namespace {
+
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t pack2(float lo, float hi) {
+    f2_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f2_t v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f2_t bc2(float v) { return pack2(v, v); }
+__device__ __forceinline__ f2_t fma2(f2_t a, f2_t b, f2_t c) {
+    f2_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f2_t mul2(f2_t a, f2_t b) {
+    f2_t d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f2_t add2(f2_t a, f2_t b) {
+    f2_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f2_t ld2(const float *p) {  // 8-byte aligned shared-memory pair
+    const float2 v = *reinterpret_cast<const float2 *>(p);
+    return pack2(v.x, v.y);
+}
+
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void cp_async4_to(uint32_t dst, const float *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+// the executing thread's earlier cp.async copies arrive on `bar` when they have landed (count pre-accounted at init)
+__device__ __forceinline__ void cp_async_arrive_noinc(uint64_t *bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+constexpr int RK = 11, RP = 5;
+constexpr int RT = 128;                  // 4 warps, all consumers; the producing duty rotates
+constexpr int RCOLS = 256;               // output columns per strip (two per thread)
+constexpr int RLEAD = 8;                 // ring row index 0 <-> image column x0 - 8 (16-byte aligned in global memory)
+constexpr int RROW = RCOLS + 2 * RLEAD;  // floats per ring row
+constexpr int RD = 8;                    // ring depth (rows)
+constexpr int RPF = 6;                   // rows issued ahead of the row being consumed
+constexpr int NPOS = 14;                 // window positions of a thread: image columns gx - 6 .. gx + 7 (7 aligned pairs)
+constexpr int HALO0 = 8;                 // lanes HALO0 .. HALO0 + 19 of the producing warp fetch the padded columns
+
+struct RingTaps {       // by value in the kernel parameters -> constant-bank operands
+    float2 wp[NPOS];    // position p: (tap p - 1 for column gx, tap p - 2 for column gx + 1), zero outside 0..10
+    float g[RK];        // vertical taps
+};
+
+template <bool MAPS5, bool COEF, bool CLAMP>
+__global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, const RingTaps tp) {
+    constexpr int M = MAPS5 ? 5 : 4;
+    __shared__ __align__(128) float ring[RD][2][RROW];
+    __shared__ __align__(8) uint64_t full[RD], empty[RD];
+    __shared__ double red[32];
+    const llie_ssim_desc &d = a.d;
+    const int H = d.h, W = d.w, tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+    const int tpp = a.tiles_x * a.tiles_y;
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int seg = trem / a.tiles_x, strip = trem - seg * a.tiles_x;
+    const int x0 = strip * RCOLS, y0 = seg * a.seg_rows;
+    const int rows_out = min(a.seg_rows, H - y0);
+    const int nrows_in = rows_out + 2 * RP;
+    const long long plane_elems = (long long)H * W;
+    const float *xb = a.x + (long long)plane * plane_elems;
+    const float *yb = a.y + (long long)plane * plane_elems;
+
+    // ---- producer geometry: the aligned column range of a row this strip reads, and this lane's padded column
+    const int cx0 = max(x0 - RLEAD, 0), cx1 = min(x0 + RCOLS + RLEAD, W);
+    const uint32_t row_bytes = (uint32_t)(cx1 - cx0) * 4u;
+    const int doff = cx0 - (x0 - RLEAD);
+    int hsrc = -1, hdst = 0;
+    const int hl = lane - HALO0;
+    const int htensor = hl >= 10 ? 1 : 0;
+    if (hl >= 0 && hl < 20) {
+        const int h = hl - 10 * htensor;  // 0..4 left of the image, 5..9 right of it
+        const int col = h < 5 ? -1 - h : W + (h - 5);
+        const bool need = h < 5 ? (x0 == 0) : (col <= x0 + RCOLS - 1 + RP);
+        hsrc = need ? pad_index(col, W, d.pad_mode) : -1;
+        hdst = col - (x0 - RLEAD);
+    }
+    const bool halo_lane = hsrc >= 0;
+    const int nhalo = __popc(__ballot_sync(0xffffffffu, halo_lane));
+    const float *hbase = (htensor ? yb : xb) + max(hsrc, 0);
+
+    {   // the ring starts zeroed: columns no copy ever writes (outside the image under zero padding, beyond the
+        // right edge of a partial strip) read as zero for the whole kernel
+        float4 *r4 = reinterpret_cast<float4 *>(&ring[0][0][0]);
+        for (int i = tid; i < RD * 2 * RROW / 4; i += RT) r4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tid == 0) {
+#pragma unroll
+            for (int s = 0; s < RD; ++s) {
+                mbar_init(&full[s], 1 + nhalo);
+                mbar_init(&empty[s], RT / 32);
+            }
+            mbar_fence_init();
+        }
+        fence_proxy_async();  // generic-proxy zero fill before the async-proxy (TMA) writes to the same bytes
+        __syncthreads();
+    }
+
+    auto issue_row = [&](int r) {  // executed by ONE whole warp
+        const int slot = r & (RD - 1), use = r / RD;
+        if (use > 0) mbar_wait(&empty[slot], (uint32_t)(use - 1) & 1u);
+        const int sy = pad_index(y0 - RP + r, H, d.pad_mode);
+        float *dst = &ring[slot][0][0];
+        if (sy >= 0) {
+            const long long ro = (long long)sy * W;
+            if (lane == 0) {
+                mbar_expect_tx(&full[slot], 2u * row_bytes);
+                bulk_g2s(dst + doff, xb + ro + cx0, row_bytes, &full[slot]);
+                bulk_g2s(dst + RROW + doff, yb + ro + cx0, row_bytes, &full[slot]);
+            }
+            if (halo_lane) {
+                cp_async4_to(smem_u32(dst + htensor * RROW + hdst), hbase + ro);
+                cp_async_arrive_noinc(&full[slot]);
+            }
+        } else {  // a row of zero padding
+            float4 *r4 = reinterpret_cast<float4 *>(dst);
+            for (int i = lane; i < 2 * RROW / 4; i += 32) r4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0 || halo_lane) mbar_arrive(&full[slot]);
+        }
+    };
+
+    const int gx = x0 + 2 * tid;  // first of the two output columns (even)
+    const int lo_y = d.interior ? RP : 0, hi_y = d.interior ? H - RP : H;
+    float cm[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) cm[c] = (gx + c < W && (!d.interior || (gx + c >= RP && gx + c < W - RP))) ? 1.f : 0.f;
+    const f2_t CM = pack2(cm[0], cm[1]);
+    const f2_t C1 = bc2(d.c1), C2 = bc2(d.c2), EPS = bc2(d.eps), TWO = bc2(2.f), NEG1 = bc2(-1.f);
+    f2_t acc[M][RK];
+#pragma unroll
+    for (int q = 0; q < M; ++q)
+#pragma unroll
+        for (int j = 0; j < RK; ++j) acc[q][j] = 0ull;
+    f2_t facc = 0ull, chkx = 0ull, chky = 0ull;
+    const long long cstride = (long long)d.n * a.co * plane_elems;
+    long long off = ((long long)plane * H + y0) * W + gx;  // COEF: first element of the next completed row
+
+#pragma unroll
+    for (int r = 0; r < RPF; ++r)
+        if (r < nrows_in && (r & 3) == wrp) issue_row(r);
+
+    for (int base = 0; base < nrows_in; base += RK) {
+#pragma unroll
+        for (int ii = 0; ii < RK; ++ii) {
+            const int i = base + ii;
+            if (i >= nrows_in) break;  // uniform
+            if ((i & 3) == wrp && i + RPF < nrows_in) issue_row(i + RPF);
+            const int slot = i & (RD - 1);
+            mbar_wait(&full[slot], (uint32_t)(i / RD) & 1u);
+            float *rx = &ring[slot][0][0], *ry = rx + RROW;
+            if (CLAMP) {
+                // in-place clamp of the landed row (each thread its own two columns, the first eight threads the
+                // 2 x 8 lead / trail cells), finite check on the raw values of the owned columns
+                float2 *px = reinterpret_cast<float2 *>(rx + RLEAD) + tid, *py = reinterpret_cast<float2 *>(ry + RLEAD) + tid;
+                float2 vx = *px, vy = *py;
+                chkx = fma2(pack2(vx.x, vx.y), 0ull, chkx);
+                chky = fma2(pack2(vy.x, vy.y), 0ull, chky);
+                vx.x = fminf(fmaxf(vx.x, 0.f), 1.f); vx.y = fminf(fmaxf(vx.y, 0.f), 1.f);
+                vy.x = fminf(fmaxf(vy.x, 0.f), 1.f); vy.y = fminf(fmaxf(vy.y, 0.f), 1.f);
+                *px = vx;
+                *py = vy;
+                if (tid < 8) {
+                    const int s = tid < 4 ? 2 * tid : RLEAD + RCOLS + 2 * (tid - 4);
+                    float2 *qx = reinterpret_cast<float2 *>(rx + s), *qy = reinterpret_cast<float2 *>(ry + s);
+                    float2 ux = *qx, uy = *qy;
+                    ux.x = fminf(fmaxf(ux.x, 0.f), 1.f); ux.y = fminf(fmaxf(ux.y, 0.f), 1.f);
+                    uy.x = fminf(fmaxf(uy.x, 0.f), 1.f); uy.y = fminf(fmaxf(uy.y, 0.f), 1.f);
+                    *qx = ux;
+                    *qy = uy;
+                }
+                fence_proxy_async();  // these generic writes precede the TMA refill of the slot
+                __syncthreads();
+            }
+            // ---- horizontal pass: 7 aligned pairs per tensor = window positions 0..13 (image columns gx-6 .. gx+7)
+            const float *wx = rx + 2 * tid + 2, *wy = ry + 2 * tid + 2;
+            f2_t h[M];
+#pragma unroll
+            for (int q = 0; q < M; ++q) h[q] = 0ull;
+#pragma unroll
+            for (int k = 0; k < NPOS / 2; ++k) {
+                const f2_t X = ld2(wx + 2 * k), Y = ld2(wy + 2 * k);
+                if (!CLAMP && k == 3) {  // positions 6, 7 are the thread's own columns
+                    chkx = fma2(X, 0ull, chkx);
+                    chky = fma2(Y, 0ull, chky);
+                }
+                f2_t mm[M];
+                mm[0] = X;
+                mm[1] = Y;
+                if (MAPS5) {
+                    mm[2] = mul2(X, X);
+                    mm[3] = mul2(Y, Y);
+                    mm[4] = mul2(X, Y);
+                } else {
+                    mm[2] = fma2(X, X, mul2(Y, Y));
+                    mm[3] = mul2(X, Y);
+                }
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int p = 2 * k + e;
+                    if (p < 1 || p > RK + 1) continue;  // positions 0 and 13 carry no tap
+                    const f2_t w = pack2(tp.wp[p].x, tp.wp[p].y);
+#pragma unroll
+                    for (int q = 0; q < M; ++q) {
+                        float lo, hi;
+                        unpack2(mm[q], lo, hi);
+                        h[q] = fma2(bc2(e ? hi : lo), w, h[q]);
+                    }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[slot]);  // this warp has consumed row i
+            // ---- vertical scatter: input row i feeds output rows o = i - j with tap j; slot(o) = o mod 11 = (ii - j) mod 11
+#pragma unroll
+            for (int j = 0; j < RK; ++j) {
+                const int sl = (ii - j + RK) % RK;
+                const f2_t gj = bc2(tp.g[j]);
+#pragma unroll
+                for (int q = 0; q < M; ++q) acc[q][sl] = (j == 0) ? mul2(gj, h[q]) : fma2(gj, h[q], acc[q][sl]);
+            }
+            if (i >= RK - 1) {  // output row o = i - 10 is complete
+                const int sl = (ii + 1) % RK;
+                const int gy = y0 + i - (RK - 1);
+                const f2_t MX = acc[0][sl], MY = acc[1][sl];
+                const f2_t mx2 = mul2(MX, MX), my2 = mul2(MY, MY), mxy = mul2(MX, MY);
+                f2_t vsum, sxy;
+                if (MAPS5) {
+                    f2_t sx = fma2(mx2, NEG1, acc[2][sl]), sy = fma2(my2, NEG1, acc[3][sl]);
+                    if (d.clamp_var) {
+                        float a0, a1, b0, b1;
+                        unpack2(sx, a0, a1);
+                        unpack2(sy, b0, b1);
+                        sx = pack2(fmaxf(a0, 0.f), fmaxf(a1, 0.f));
+                        sy = pack2(fmaxf(b0, 0.f), fmaxf(b1, 0.f));
+                    }
+                    vsum = add2(sx, sy);
+                    sxy = fma2(mxy, NEG1, acc[4][sl]);
+                } else {
+                    vsum = fma2(my2, NEG1, fma2(mx2, NEG1, acc[2][sl]));
+                    sxy = fma2(mxy, NEG1, acc[3][sl]);
+                }
+                const f2_t n1 = fma2(mxy, TWO, C1), n2 = fma2(sxy, TWO, C2);
+                const f2_t d1 = add2(add2(mx2, my2), C1), d2 = add2(vsum, C2);
+                const f2_t NUM = mul2(n1, n2), DEN = fma2(d1, d2, EPS);
+                float nu[2], de[2], sv[2];
+                unpack2(NUM, nu[0], nu[1]);
+                unpack2(DEN, de[0], de[1]);
+#pragma unroll
+                for (int c = 0; c < 2; ++c) sv[c] = __fdiv_rn(nu[c], de[c]);
+                if (COEF) {  // dLoss/dS times the sensitivities of S to mu_x, E[x^2], E[xy] (ssim_stream_kernel)
+                    float mx[2], my[2], n1v[2], n2v[2], d1v[2], d2v[2], cf[3][2];
+                    unpack2(MX, mx[0], mx[1]);
+                    unpack2(MY, my[0], my[1]);
+                    unpack2(n1, n1v[0], n1v[1]);
+                    unpack2(n2, n2v[0], n2v[1]);
+                    unpack2(d1, d1v[0], d1v[1]);
+                    unpack2(d2, d2v[0], d2v[1]);
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) {
+                        const float l = (1.f - sv[c]) * 0.5f;
+                        const float up =
+                            (!d.loss_map) ? a.coef_scale : ((l >= 0.f && l <= 1.f) ? -0.5f * a.coef_scale : 0.f);
+                        const float inv = 1.f / de[c];
+                        const float a3 = 2.f * n1v[c] * inv;
+                        const float a2 = -sv[c] * d1v[c] * inv;
+                        const float dmu = 2.f * (my[c] * n2v[c] - sv[c] * mx[c] * d2v[c]) * inv;
+                        const float a1 = dmu - 2.f * mx[c] * a2 - my[c] * a3;
+                        cf[0][c] = up * a1;
+                        cf[1][c] = up * a2;
+                        cf[2][c] = up * a3;
+                    }
+                    if (gx < W) {  // W is even and gx is even: both columns are inside, the pair is 8-byte aligned
+                        float *cp = a.coef + off;
+#pragma unroll
+                        for (int q = 0; q < 3; ++q)
+                            *reinterpret_cast<float2 *>(cp + q * cstride) = make_float2(cf[q][0], cf[q][1]);
+                    }
+                    off += W;
+                }
+                if (d.loss_map) {
+#pragma unroll
+                    for (int c = 0; c < 2; ++c) sv[c] = fminf(fmaxf((1.f - sv[c]) * 0.5f, 0.f), 1.f);
+                }
+                if (gy >= lo_y && gy < hi_y) facc = fma2(pack2(sv[0], sv[1]), CM, facc);
+            }
+        }
+    }
+    float f0, f1, cx0f, cx1f, cy0f, cy1f;
+    unpack2(facc, f0, f1);
+    unpack2(chkx, cx0f, cx1f);
+    unpack2(chky, cy0f, cy1f);
+    const double bs = block_sum<double>((double)f0 + (double)f1, red);
+    int flag = 0;
+    if (!(cx0f == 0.f) || !(cx1f == 0.f)) flag |= 1;
+    if (!(cy0f == 0.f) || !(cy1f == 0.f)) flag |= 2;
+    const int f = block_or(flag, reinterpret_cast<int *>(red));
+    if (tid == 0) {
+        a.part[blockIdx.x] = bs;
+        a.pflag[blockIdx.x] = f;
+    }
+    if (!last_block_done(a.ticket, gridDim.x)) return;
+    const int planes = d.n * a.co;
+    for (int pl = wrp; pl < planes; pl += RT / 32) {
+        const double *p = a.part + (size_t)pl * tpp;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int b = lane;
+        for (; b + 96 < tpp; b += 128) {
+            s0 += __ldcg(p + b);
+            s1 += __ldcg(p + b + 32);
+            s2 += __ldcg(p + b + 64);
+            s3 += __ldcg(p + b + 96);
+        }
+        for (; b < tpp; b += 32) s0 += __ldcg(p + b);
+        const double sm_ = warp_sum((s0 + s1) + (s2 + s3));
+        if (lane == 0) a.out_sum[pl] = sm_;
+    }
+    int fl = 0;
+    for (int b = tid; b < (int)gridDim.x; b += RT) fl |= __ldcg(a.pflag + b);
+    const int ff = block_or(fl, reinterpret_cast<int *>(red));
+    if (tid == 0) *a.out_flags = ff;
+}
+
+}  // namespace
+
+bool ssim_ring_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host, bool want_map,
+                        const float *coef) {
+    return win_host != nullptr && d.ksize == RK && !d.luma && !want_map && (d.w & 3) == 0 && aligned16(x) &&
+           aligned16(y) && (coef == nullptr || (!d.clamp_var && (reinterpret_cast<uintptr_t>(coef) & 7u) == 0));
+}
+
+int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaStream_t st) {
+    const llie_ssim_desc &d = a.d;
+    RingTaps tp;
+    for (int p = 0; p < NPOS; ++p) {
+        tp.wp[p].x = (p - 1 >= 0 && p - 1 < RK) ? win_host[p - 1] : 0.f;
+        tp.wp[p].y = (p - 2 >= 0 && p - 2 < RK) ? win_host[p - 2] : 0.f;
+    }
+    for (int j = 0; j < RK; ++j) tp.g[j] = win_host[j];
+    a.tiles_x = div_up(d.w, RCOLS);
+    const long long cols = (long long)d.n * a.co * a.tiles_x;
+    a.seg_rows = pick_seg_rows(cols, d.h, kNumSM * 3, 64, RK - 1);
+    a.tiles_y = div_up(d.h, a.seg_rows);
+    const long long grid = cols * a.tiles_y;
+    Workspace ws(workspace);
+    LLIE_REQUIRE(grid <= 0x7fffffffLL && (size_t)grid * (sizeof(double) + sizeof(int)) <= ws.scratch_bytes,
+                 "ssim_stats: workspace too small for %lld tiles", grid);
+    a.part = reinterpret_cast<double *>(ws.scratch);
+    a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)grid * sizeof(double));
+    a.ticket = ws.tickets;
+    const bool clamp = d.clamp_in != 0;
+    if (a.coef != nullptr) {
+        if (clamp) ssim_ring_kernel<false, true, true><<<(int)grid, RT, 0, st>>>(a, tp);
+        else ssim_ring_kernel<false, true, false><<<(int)grid, RT, 0, st>>>(a, tp);
+    } else if (d.clamp_var) {
+        if (clamp) ssim_ring_kernel<true, false, true><<<(int)grid, RT, 0, st>>>(a, tp);
+        else ssim_ring_kernel<true, false, false><<<(int)grid, RT, 0, st>>>(a, tp);
+    } else {
+        if (clamp) ssim_ring_kernel<false, false, true><<<(int)grid, RT, 0, st>>>(a, tp);
+        else ssim_ring_kernel<false, false, false><<<(int)grid, RT, 0, st>>>(a, tp);
+    }
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+}  // namespace llie

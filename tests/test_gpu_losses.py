@@ -391,5 +391,8 @@ def test_losses_under_autocast(dev, in_dtype):
         assert va.dtype == torch.float32 and va.ndim == 0, name
         assert abs(float(va) - float(vf)) <= 1e-6 * abs(float(vf)), (name, float(va), float(vf))
         assert xa.grad.dtype == in_dtype, name
+        # a half-precision leaf accumulates its two incoming gradients (raw + sRGB branch of the hybrid loss) in ITS
+        # dtype, so the comparison with the rounded fp32 gradient allows two ulps of that dtype
         ref = xf.grad.to(in_dtype).float()
-        assert float((xa.grad.float() - ref).abs().max()) <= 1e-6 * float(ref.abs().max()) + 1e-12, name
+        tol = {torch.float32: 1e-6, torch.bfloat16: 2.0 ** -7, torch.float16: 2.0 ** -9}[in_dtype]
+        assert float((xa.grad.float() - ref).abs().max()) <= tol * float(ref.abs().max()) + 1e-12, name

@@ -279,7 +279,8 @@ def test_adapters(dev):
     assert abs(lm.edge_deltae2000_mean(p, t) - re_["mean"]) < 5e-3   # mask ties may differ on random floats
 
 
-@pytest.mark.parametrize("shape", [(2, 3, 64, 300), (1, 3, 257, 513), (1, 1, 40, 11), (1, 3, 700, 1030)])
+@pytest.mark.parametrize("shape", [(2, 3, 64, 300), (1, 3, 257, 513), (1, 1, 40, 11), (1, 3, 700, 1030), (1, 3, 300, 1032),
+                                   (1, 2, 130, 260), (2, 1, 75, 516), (1, 1, 11, 12), (1, 1, 23, 256)])
 @pytest.mark.parametrize("pad", ["reflect", "replicate", "circular", "zeros"])
 @pytest.mark.parametrize("policy", ["linear", "torchmetrics", "kornia_loss"])
 def test_two_column_ssim_kernel_vs_one_column(shape, pad, policy):
@@ -305,13 +306,16 @@ def test_two_column_ssim_kernel_vs_one_column(shape, pad, policy):
     try:
         nat.check(nat.lib().llie_tune(3, 2), "llie_tune")
         ref, fref, _ = Fn.ssim_stats(xd, yd, win, **kw)
-        nat.check(nat.lib().llie_tune(3, 0), "llie_tune")
+        nat.check(nat.lib().llie_tune(3, 3), "llie_tune")          # round-1 default: two-column cp.async kernel
+        two, ftwo, _ = Fn.ssim_stats(xd, yd, win, **kw)
+        nat.check(nat.lib().llie_tune(3, 0), "llie_tune")          # default: TMA row ring + packed FP32 (W % 4 == 0)
         got, fgot, _ = Fn.ssim_stats(xd, yd, win, **kw)
     finally:
         nat.check(nat.lib().llie_tune(3, 0), "llie_tune")
-    assert int(fref) == int(fgot) == 0
+    assert int(fref) == int(fgot) == int(ftwo) == 0
     # (five-map instantiation: the same per-pixel values; the float32 per-thread partial sums group differently)
     assert torch.allclose(ref, got, rtol=1e-6, atol=0), (ref, got)
+    assert torch.allclose(ref, two, rtol=1e-6, atol=0), (ref, two)
     if policy == "torchmetrics" and pad == "reflect":
         h, w = shape[2] - 10, shape[3] - 10
         want = quality.ssim_torchmetrics(x, y, compute_dtype=torch.float64)
