@@ -187,6 +187,20 @@ typedef struct llie_psnr_desc {
 int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const void *y, double *out,
                     void *out_minmax, int32_t *out_flags, void *workspace, void *stream);
 
+/* llie_psnr_stats without a caller-owned workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernel, same outputs as llie_psnr_stats; its scratch (ticket +
+ * per-block partial records) is a file-scope `static __device__` array of LLIE_PSNR_STATIC_SCRATCH_BYTES that every
+ * GPU loading the library holds until exit.  Limits: n * c <= LLIE_PSNR_STATIC_MAX_SLOTS planes (LLIE_EINVAL with a
+ * message beyond that); the grid is capped so that n * c * blocks-per-plane <= LLIE_PSNR_STATIC_MAX_SLOTS.  The call
+ * issues one cudaMemsetAsync (ticket header) and one kernel on `stream`; it calls no cudaMalloc / cudaFree.  All calls
+ * on a device SHARE the array: calls that overlap on the GPU (other streams, concurrently replayed graphs) race --
+ * serialise them on one stream or use llie_psnr_stats with one workspace per stream. */
+#define LLIE_PSNR_STATIC_MAX_SLOTS 8192
+#define LLIE_PSNR_STATIC_SCRATCH_BYTES (256 + LLIE_PSNR_STATIC_MAX_SLOTS * 32) /* 262 400 bytes per device */
+int llie_psnr_stats_static(const llie_psnr_desc *desc, const void *x, const void *y, double *out,
+                           void *out_minmax, int32_t *out_flags, void *stream);
+
 /* ------------------------------------------------------------------------
  * Gaussian / uniform-window SSIM statistics: per-(n, c) float64 sums of the SSIM map (or of the DSSIM
  * loss map) over the full image or its interior, one fused separable-filter kernel.

@@ -93,6 +93,7 @@ _SIGNATURES = {
     "llie_newbp_forward": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_newbp_adjoint": (C.c_int, [C.POINTER(ConvDesc), _VP, _VP, _VP, _VP]),
     "llie_psnr_stats": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_psnr_stats_static": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_ssim_stats": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_sqerr": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -277,6 +277,90 @@ extern "C" int llie_psnr_stats(const llie_psnr_desc *desc, const void *x, const 
     return LLIE_OK;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// llie_psnr_stats_static: the same kernel and outputs as llie_psnr_stats, for callers that can neither allocate nor
+// carry a workspace (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The scratch the kernel
+// needs -- the "last block" ticket and the per-block partial records -- lives in ONE file-scope device array per GPU
+// that loads the library (LLIE_PSNR_STATIC_SCRATCH_BYTES, held until the process exits).  No counterpart in the
+// reference.
+//   * In host code `g_psnr_static_scratch` is only a stand-in for the symbol: its device address is looked up once per
+//     device, with that device current, by cudaGetSymbolAddress and cached; the kernel receives that pointer.
+//   * The entry point calls no cudaMalloc / cudaFree / allocating routine; cudaMemsetAsync on the caller's stream
+//     clears the ticket header before every launch (the array keeps the previous call's contents; the partial
+//     records are fully rewritten by the launch that reads them).
+//   * Every call on a device shares the array: calls that overlap on the GPU (different streams, or graphs replayed
+//     concurrently) RACE on it.  Serialise them on one stream, or use llie_psnr_stats with one workspace per stream.
+namespace llie {
+constexpr size_t kPsnrStaticSlots = LLIE_PSNR_STATIC_MAX_SLOTS;
+constexpr size_t kPsnrStaticBytes = LLIE_PSNR_STATIC_SCRATCH_BYTES;
+static_assert(kPsnrStaticBytes >= kWsHeaderBytes + kPsnrStaticSlots * (3 * sizeof(double) + sizeof(int)),
+              "static scratch too small for its slot count");
+static __device__ __align__(256) unsigned char g_psnr_static_scratch[kPsnrStaticBytes];
+constexpr int kMaxDevices = 64;
+static unsigned char *g_psnr_static_ptr[kMaxDevices];  // device address of the array, per device (0 = not looked up)
+}  // namespace llie
+
+extern "C" int llie_psnr_stats_static(const llie_psnr_desc *desc, const void *x, const void *y, double *out,
+                                      void *out_minmax, int32_t *out_flags, void *stream) {
+    LLIE_REQUIRE(desc && x && y && out && out_flags, "psnr_stats_static: null pointer");
+    LLIE_REQUIRE(desc->n > 0 && desc->c > 0 && desc->plane > 0, "psnr_stats_static: empty tensor");
+    LLIE_REQUIRE(desc->dtype == 0 || desc->dtype == 1, "psnr_stats_static: dtype must be 0 (f32) or 1 (f64)");
+    LLIE_REQUIRE(desc->data_range > 0 && desc->eps > 0, "psnr_stats_static: data_range and eps must be positive");
+    const long long nc = (long long)desc->n * desc->c;
+    LLIE_REQUIRE(nc <= (long long)kPsnrStaticSlots,
+                 "psnr_stats_static: n*c = %lld planes exceed the static scratch (LLIE_PSNR_STATIC_MAX_SLOTS = %d "
+                 "partial records, %d bytes per device); use llie_psnr_stats with a caller-owned workspace",
+                 nc, (int)kPsnrStaticSlots, (int)kPsnrStaticBytes);
+    int dev = -1;
+    LLIE_CUDA_OK(cudaGetDevice(&dev));
+    LLIE_REQUIRE(dev >= 0 && dev < kMaxDevices, "psnr_stats_static: device index %d out of range", dev);
+    unsigned char *base = g_psnr_static_ptr[dev];
+    if (base == nullptr) {  // once per device, that device current (benign race: every thread stores the same value)
+        void *p = nullptr;
+        LLIE_CUDA_OK(cudaGetSymbolAddress(&p, g_psnr_static_scratch));
+        LLIE_REQUIRE(p != nullptr, "psnr_stats_static: cudaGetSymbolAddress returned a null address");
+        base = g_psnr_static_ptr[dev] = static_cast<unsigned char *>(p);
+    }
+    PsnrArgs a{};
+    a.d = *desc;
+    a.x = x; a.y = y; a.out = out; a.out_minmax = out_minmax; a.out_flags = out_flags;
+    const int vn = desc->dtype ? 2 : 4;
+    const size_t esz = desc->dtype ? 8 : 4;
+    a.vec_ok = aligned16(x) && aligned16(y) && ((desc->plane * esz) % 16 == 0);
+    const long long per_block = 256LL * vn * 4;
+    static int occ[2] = {0, 0};
+    if (occ[desc->dtype] == 0) {
+        int o = 0;
+        if (desc->dtype == 0)
+            LLIE_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, psnr_stats_kernel<float>, 256, 0));
+        else
+            LLIE_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, psnr_stats_kernel<double>, 256, 0));
+        occ[desc->dtype] = o < 1 ? 1 : o;
+    }
+    // the grid of llie_psnr_stats (one wave of resident blocks), capped by the slots the static array holds
+    long long G = ((long long)kNumSM * occ[desc->dtype] * LLIE_PSNR_WAVES) / nc;
+    const long long maxg = (desc->plane + per_block - 1) / per_block;
+    if (G > maxg) G = maxg;
+    if (G * nc > (long long)kPsnrStaticSlots) G = (long long)kPsnrStaticSlots / nc;
+    if (G < 1) G = 1;
+    const size_t slots = (size_t)nc * (size_t)G;
+    unsigned char *scratch = base + kWsHeaderBytes;
+    a.part_sum = reinterpret_cast<double *>(scratch);
+    a.part_min = a.part_sum + slots;
+    a.part_max = a.part_min + slots;
+    a.part_flag = reinterpret_cast<int *>(a.part_max + slots);
+    a.ticket = reinterpret_cast<unsigned *>(base);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    LLIE_CUDA_OK(cudaMemsetAsync(base, 0, kWsHeaderBytes, st));  // tickets must start at zero; no allocation
+    dim3 grid((unsigned)G, (unsigned)nc);
+    if (desc->dtype == 0)
+        psnr_stats_kernel<float><<<grid, 256, 0, st>>>(a);
+    else
+        psnr_stats_kernel<double><<<grid, 256, 0, st>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
 
 // ---------------------------------------------------------------------------------------------------
 // nn.L1Loss (global mean) value + gradient in one streaming pass (NewBP_model/losses.py:249, 332):
