@@ -56,6 +56,19 @@ __device__ __forceinline__ f2_t ld2(const float *p) {  // 8-byte aligned shared-
     return pack2(v.x, v.y);
 }
 
+// n / d for a finite d > 0 (the SSIM denominator is >= c1 * c2 > 0), branch-free: SFU reciprocal refined by one Newton
+// step, quotient corrected with the exact FMA remainder (Markstein) - the correctly rounded quotient except for rare
+// 1-ulp cases, against ~14 instructions + a guarded slow-path call for the IEEE division instruction sequence.
+__device__ __forceinline__ float rcp_pos(float d) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    return fmaf(fmaf(-d, r, 1.f), r, r);
+}
+__device__ __forceinline__ float div_pos(float n, float d, float r) {
+    const float q = n * r;
+    return fmaf(fmaf(-d, q, n), r, q);
+}
+
 __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(smem_dst)),
@@ -87,6 +100,25 @@ struct RingTaps {       // by value in the kernel parameters -> constant-bank op
     float2 wp[NPOS];    // position p: (tap p - 1 for column gx, tap p - 2 for column gx + 1), zero outside 0..10
     float g[RK];        // vertical taps
 };
+
+// Vertical scatter of one input row whose index is II modulo 11: the row feeds output rows o = i - j with tap j, and the
+// accumulator slot of output row o is o mod 11 = (II - j) mod 11 - static here, so the 11 slots per map stay in
+// registers.  The slot of the row this input completes, (II + 1) mod 11, is handed out in `done`.
+// The row loop is NOT unrolled by 11 (that body is 64 KB of SASS, more than the instruction cache holds: ncu showed
+// 2.6 `no_instruction` stall cycles per issued instruction, 43 % issue-active); only this scatter exists in 11 copies,
+// picked by a CTA-uniform switch (0.27 `no_instruction`, 56 % issue-active, 333 -> 311 us per 3 x 2848 x 4256 pair).
+template <int II, int M>
+__device__ __forceinline__ void scatter_row(f2_t (&acc)[M][RK], const f2_t (&h)[M], f2_t (&done)[M], const RingTaps &tp) {
+#pragma unroll
+    for (int j = 0; j < RK; ++j) {
+        const int sl = (II - j + RK) % RK;
+        const f2_t gj = bc2(tp.g[j]);
+#pragma unroll
+        for (int q = 0; q < M; ++q) acc[q][sl] = (j == 0) ? mul2(gj, h[q]) : fma2(gj, h[q], acc[q][sl]);
+    }
+#pragma unroll
+    for (int q = 0; q < M; ++q) done[q] = acc[q][(II + 1) % RK];
+}
 
 template <bool MAPS5, bool COEF, bool CLAMP>
 __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, const RingTaps tp) {
@@ -186,11 +218,10 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
     for (int r = 0; r < RPF; ++r)
         if (r < nrows_in && (r & 3) == wrp) issue_row(r);
 
-    for (int base = 0; base < nrows_in; base += RK) {
-#pragma unroll
-        for (int ii = 0; ii < RK; ++ii) {
-            const int i = base + ii;
-            if (i >= nrows_in) break;  // uniform
+    int ii = 0;  // i mod 11
+#pragma unroll 1
+    for (int i = 0; i < nrows_in; ++i) {
+        {
             if ((i & 3) == wrp && i + RPF < nrows_in) issue_row(i + RPF);
             const int slot = i & (RD - 1);
             mbar_wait(&full[slot], (uint32_t)(i / RD) & 1u);
@@ -256,22 +287,29 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[slot]);  // this warp has consumed row i
-            // ---- vertical scatter: input row i feeds output rows o = i - j with tap j; slot(o) = o mod 11 = (ii - j) mod 11
-#pragma unroll
-            for (int j = 0; j < RK; ++j) {
-                const int sl = (ii - j + RK) % RK;
-                const f2_t gj = bc2(tp.g[j]);
-#pragma unroll
-                for (int q = 0; q < M; ++q) acc[q][sl] = (j == 0) ? mul2(gj, h[q]) : fma2(gj, h[q], acc[q][sl]);
+            // ---- vertical scatter (11 static variants, CTA-uniform switch)
+            f2_t done[M];
+            switch (ii) {
+                case 0: scatter_row<0, M>(acc, h, done, tp); break;
+                case 1: scatter_row<1, M>(acc, h, done, tp); break;
+                case 2: scatter_row<2, M>(acc, h, done, tp); break;
+                case 3: scatter_row<3, M>(acc, h, done, tp); break;
+                case 4: scatter_row<4, M>(acc, h, done, tp); break;
+                case 5: scatter_row<5, M>(acc, h, done, tp); break;
+                case 6: scatter_row<6, M>(acc, h, done, tp); break;
+                case 7: scatter_row<7, M>(acc, h, done, tp); break;
+                case 8: scatter_row<8, M>(acc, h, done, tp); break;
+                case 9: scatter_row<9, M>(acc, h, done, tp); break;
+                default: scatter_row<10, M>(acc, h, done, tp); break;
             }
+            ii = ii == RK - 1 ? 0 : ii + 1;
             if (i >= RK - 1) {  // output row o = i - 10 is complete
-                const int sl = (ii + 1) % RK;
                 const int gy = y0 + i - (RK - 1);
-                const f2_t MX = acc[0][sl], MY = acc[1][sl];
+                const f2_t MX = done[0], MY = done[1];
                 const f2_t mx2 = mul2(MX, MX), my2 = mul2(MY, MY), mxy = mul2(MX, MY);
                 f2_t vsum, sxy;
                 if (MAPS5) {
-                    f2_t sx = fma2(mx2, NEG1, acc[2][sl]), sy = fma2(my2, NEG1, acc[3][sl]);
+                    f2_t sx = fma2(mx2, NEG1, done[2]), sy = fma2(my2, NEG1, done[3]);
                     if (d.clamp_var) {
                         float a0, a1, b0, b1;
                         unpack2(sx, a0, a1);
@@ -280,19 +318,22 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
                         sy = pack2(fmaxf(b0, 0.f), fmaxf(b1, 0.f));
                     }
                     vsum = add2(sx, sy);
-                    sxy = fma2(mxy, NEG1, acc[4][sl]);
+                    sxy = fma2(mxy, NEG1, done[4]);
                 } else {
-                    vsum = fma2(my2, NEG1, fma2(mx2, NEG1, acc[2][sl]));
-                    sxy = fma2(mxy, NEG1, acc[3][sl]);
+                    vsum = fma2(my2, NEG1, fma2(mx2, NEG1, done[2]));
+                    sxy = fma2(mxy, NEG1, done[3]);
                 }
                 const f2_t n1 = fma2(mxy, TWO, C1), n2 = fma2(sxy, TWO, C2);
                 const f2_t d1 = add2(add2(mx2, my2), C1), d2 = add2(vsum, C2);
                 const f2_t NUM = mul2(n1, n2), DEN = fma2(d1, d2, EPS);
-                float nu[2], de[2], sv[2];
+                float nu[2], de[2], sv[2], rinv[2];
                 unpack2(NUM, nu[0], nu[1]);
                 unpack2(DEN, de[0], de[1]);
 #pragma unroll
-                for (int c = 0; c < 2; ++c) sv[c] = __fdiv_rn(nu[c], de[c]);
+                for (int c = 0; c < 2; ++c) {
+                    rinv[c] = rcp_pos(de[c]);
+                    sv[c] = div_pos(nu[c], de[c], rinv[c]);
+                }
                 if (COEF) {  // dLoss/dS times the sensitivities of S to mu_x, E[x^2], E[xy] (ssim_stream_kernel)
                     float mx[2], my[2], n1v[2], n2v[2], d1v[2], d2v[2], cf[3][2];
                     unpack2(MX, mx[0], mx[1]);
@@ -306,7 +347,7 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
                         const float l = (1.f - sv[c]) * 0.5f;
                         const float up =
                             (!d.loss_map) ? a.coef_scale : ((l >= 0.f && l <= 1.f) ? -0.5f * a.coef_scale : 0.f);
-                        const float inv = 1.f / de[c];
+                        const float inv = rinv[c];
                         const float a3 = 2.f * n1v[c] * inv;
                         const float a2 = -sv[c] * d1v[c] * inv;
                         const float dmu = 2.f * (my[c] * n2v[c] - sv[c] * mx[c] * d2v[c]) * inv;
