@@ -349,11 +349,18 @@ typedef struct llie_eval_desc {
     double data_range;       /* PSNR peak */
     int32_t k;               /* metric slots in acc */
     int32_t slot_psnr, slot_ssim, slot_de_mean, slot_de_p95, slot_edge;
+    /* channel-wise family (metrics/channelwise.py:113-302), c == 3: */
+    int32_t slot_cpsnr;        /* cpsnr_rgb(reduction='mean')                                   <- psnr_table */
+    int32_t slot_rgb_psnr[4];  /* rgb_psnr(reduction='mean')['R' | 'G' | 'B' | 'mean']            <- psnr_table */
+    int32_t slot_rgb_ssim[4];  /* rgb_ssim(reduction='mean')['R' | 'G' | 'B' | 'mean']            <- rgb_ssim_sums */
 } llie_eval_desc;
+/*   psnr_table     [n + 2, LLIE_PSNR_COLS(3)] float64 as written by llie_psnr_stats(cast_first = 1)
+ *   rgb_ssim_sums  [n, 3] float64 SSIM-map sums over hw pixels of the ssim_linear policy (llie_ssim_stats, clamp_var) */
 int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const double *ssim_sums,
                          const double *de_sums, const float *de_p95, const double *edge_sum,
-                         const int64_t *edge_counts, const int32_t *flags0, const int32_t *flags1,
-                         const int32_t *flags2, const int32_t *flags3, double *acc, void *stream);
+                         const int64_t *edge_counts, const double *psnr_table, const double *rgb_ssim_sums,
+                         const int32_t *flags0, const int32_t *flags1, const int32_t *flags2, const int32_t *flags3,
+                         const int32_t *flags4, const int32_t *flags5, double *acc, void *stream);
 
 /* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the
  * < 1 ulp claim can be checked against a float64 pow from the test-suite. */

@@ -68,7 +68,8 @@ class EvalDesc(C.Structure):
     _fields_ = [("n", C.c_int32), ("c", C.c_int32), ("hw", C.c_int64), ("ssim_c", C.c_int32),
                 ("ssim_count", C.c_int64), ("data_range", C.c_double), ("k", C.c_int32), ("slot_psnr", C.c_int32),
                 ("slot_ssim", C.c_int32), ("slot_de_mean", C.c_int32), ("slot_de_p95", C.c_int32),
-                ("slot_edge", C.c_int32)]
+                ("slot_edge", C.c_int32), ("slot_cpsnr", C.c_int32), ("slot_rgb_psnr", C.c_int32 * 4),
+                ("slot_rgb_ssim", C.c_int32 * 4)]
 
 
 class SelectDesc(C.Structure):
@@ -109,7 +110,8 @@ _SIGNATURES = {
     "llie_tile_merge": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _VP, _VP]),
     "llie_decode_u16": (C.c_int, [C.POINTER(DecodeDesc), _VP, _VP, C.c_float, _VP, _VP, _VP]),
     "llie_linear_to_srgb": (C.c_int, [_VP, C.c_int64, _VP, _VP, _VP]),
-    "llie_eval_accumulate": (C.c_int, [C.POINTER(EvalDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_eval_accumulate": (C.c_int, [C.POINTER(EvalDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP,
+                                       _VP, _VP, _VP, _VP]),
     "llie_selftest_div_const": (C.c_int, [C.c_int32, C.c_uint32, C.c_uint64, _VP, _VP]),
     "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),

@@ -19,7 +19,7 @@ int cuda_fail(cudaError_t e, const char *what) {
 }
 }  // namespace llie
 
-extern "C" int llie_abi_version(void) { return 2; }  // 2: SSIM entry points take a host copy of the window taps
+extern "C" int llie_abi_version(void) { return 3; }  // 2: SSIM entry points take a host copy of the window taps; 3: llie_eval_accumulate channel-wise slots
 extern "C" const char *llie_last_error(void) { return llie::g_err; }
 extern "C" size_t llie_workspace_bytes(void) { return llie::kWsBytes; }
 extern "C" int llie_check_device(void) {

@@ -13,7 +13,8 @@ struct EvalAccArgs {
     const double *sqerr, *ssim_sums, *de_sums, *edge_sum;
     const float *de_p95;
     const long long *edge_counts;
-    const int *flags[4];
+    const double *psnr_table, *rgb_ssim_sums;
+    const int *flags[6];
     double *acc;
 };
 
@@ -49,8 +50,30 @@ __global__ void eval_accumulate_kernel(const EvalAccArgs a) {
         for (int i = 0; i < n; ++i) cnt += a.edge_counts[i];
         a.acc[d.slot_edge] += a.edge_sum[0] / (double)cnt;
     }
+    if (a.psnr_table != nullptr) {  // channelwise.py:113-222, reduction 'mean' = table row n; columns see llie_b200.h
+        const double *row = a.psnr_table + (size_t)n * 9;
+        if (d.slot_cpsnr >= 0) a.acc[d.slot_cpsnr] += row[7];
+        for (int c = 0; c < 3; ++c)
+            if (d.slot_rgb_psnr[c] >= 0) a.acc[d.slot_rgb_psnr[c]] += row[3 + c];
+        if (d.slot_rgb_psnr[3] >= 0) a.acc[d.slot_rgb_psnr[3]] += row[6];
+    }
+    if (a.rgb_ssim_sums != nullptr) {  // channelwise.py:262-295: float32 per-(image, channel) means, batch mean
+        float ch[3] = {0.f, 0.f, 0.f}, mean = 0.f;
+        for (int i = 0; i < n; ++i) {
+            float m = 0.f;
+            for (int c = 0; c < 3; ++c) {
+                const float v = (float)(a.rgb_ssim_sums[i * 3 + c] / (double)d.hw);
+                ch[c] += v;
+                m += v;
+            }
+            mean += m / 3.f;
+        }
+        for (int c = 0; c < 3; ++c)
+            if (d.slot_rgb_ssim[c] >= 0) a.acc[d.slot_rgb_ssim[c]] += (double)(n > 1 ? ch[c] / (float)n : ch[c]);
+        if (d.slot_rgb_ssim[3] >= 0) a.acc[d.slot_rgb_ssim[3]] += (double)(n > 1 ? mean / (float)n : mean);
+    }
     int fl = 0;
-    for (int k = 0; k < 4; ++k)
+    for (int k = 0; k < 6; ++k)
         if (a.flags[k] != nullptr) fl |= *a.flags[k];
     a.acc[d.k] += 1.0;
     a.acc[d.k + 1] += fl != 0 ? 1.0 : 0.0;
@@ -60,12 +83,25 @@ __global__ void eval_accumulate_kernel(const EvalAccArgs a) {
 
 extern "C" int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const double *ssim_sums,
                                     const double *de_sums, const float *de_p95, const double *edge_sum,
-                                    const int64_t *edge_counts, const int32_t *flags0, const int32_t *flags1,
-                                    const int32_t *flags2, const int32_t *flags3, double *acc, void *stream) {
+                                    const int64_t *edge_counts, const double *psnr_table,
+                                    const double *rgb_ssim_sums, const int32_t *flags0, const int32_t *flags1,
+                                    const int32_t *flags2, const int32_t *flags3, const int32_t *flags4,
+                                    const int32_t *flags5, double *acc, void *stream) {
     LLIE_REQUIRE(desc != nullptr && acc != nullptr, "eval_accumulate: null pointer");
     const llie_eval_desc &d = *desc;
     LLIE_REQUIRE(d.n >= 1 && d.k >= 1, "eval_accumulate: empty batch / no metric slots");
-    const int slots[5] = {d.slot_psnr, d.slot_ssim, d.slot_de_mean, d.slot_de_p95, d.slot_edge};
+    const int slots[14] = {d.slot_psnr, d.slot_ssim, d.slot_de_mean, d.slot_de_p95, d.slot_edge, d.slot_cpsnr,
+                           d.slot_rgb_psnr[0], d.slot_rgb_psnr[1], d.slot_rgb_psnr[2], d.slot_rgb_psnr[3],
+                           d.slot_rgb_ssim[0], d.slot_rgb_ssim[1], d.slot_rgb_ssim[2], d.slot_rgb_ssim[3]};
+    bool want_tab = d.slot_cpsnr >= 0, want_rs = false;
+    for (int q = 0; q < 4; ++q) {
+        want_tab = want_tab || d.slot_rgb_psnr[q] >= 0;
+        want_rs = want_rs || d.slot_rgb_ssim[q] >= 0;
+    }
+    LLIE_REQUIRE((!want_tab || (psnr_table && d.c == 3)) && (!want_rs || (rgb_ssim_sums && d.c == 3)),
+                 "eval_accumulate: a channel-wise metric needs its table / sums and 3-channel images");
+    if (!want_tab) psnr_table = nullptr;
+    if (!want_rs) rgb_ssim_sums = nullptr;
     for (int s : slots) LLIE_REQUIRE(s >= -1 && s < d.k, "eval_accumulate: slot %d outside [0, %d)", s, d.k);
     LLIE_REQUIRE(d.slot_psnr < 0 || sqerr, "eval_accumulate: linear_psnr needs the squared-error sums");
     LLIE_REQUIRE(d.slot_ssim < 0 || (ssim_sums && d.ssim_c >= 1 && d.ssim_count >= 1),
@@ -74,7 +110,8 @@ extern "C" int llie_eval_accumulate(const llie_eval_desc *desc, const double *sq
                      (d.slot_edge < 0 || (edge_sum && edge_counts)),
                  "eval_accumulate: a requested colour metric has no input");
     llie::EvalAccArgs a{d, sqerr, ssim_sums, de_sums, edge_sum, de_p95,
-                        reinterpret_cast<const long long *>(edge_counts), {flags0, flags1, flags2, flags3}, acc};
+                        reinterpret_cast<const long long *>(edge_counts), psnr_table, rgb_ssim_sums,
+                        {flags0, flags1, flags2, flags3, flags4, flags5}, acc};
     llie::eval_accumulate_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;

@@ -16,13 +16,14 @@ clamps) and run the same kernels.
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Callable, Dict, Iterable, List, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
 from torch import Tensor
 
-__all__ = ["METRIC_FUNCTIONS", "ShardedMeans", "TileGrid", "shard_indices", "image_metrics", "accumulate_image_metrics",
+__all__ = ["METRIC_FUNCTIONS", "C4_METRICS", "ShardedMeans", "TileGrid", "shard_indices", "image_metrics", "accumulate_image_metrics",
            "evaluate_pairs"]
 
 
@@ -105,13 +106,74 @@ def _edge_mean(pred, target, flags, *, q: float = 0.85, shared: Optional[_Colour
 
 _COLOUR = {"deltae2000_mean": (False, False), "deltae2000_p95": (True, False), "edge_deltae2000_mean": (True, True)}
 
+
+# ---- channel-wise family (metrics/channelwise.py:113-302; BASELINE configs[3] lists CPSNR and RGB-SSIM next to the
+# adapters).  One PSNR-table launch serves cpsnr_rgb and the four rgb_psnr values, one five-map SSIM launch the four
+# rgb_ssim values; `cache` is the per-pair dict `image_metrics` hands to every function of the family.
+_RGB_PSNR = {"cpsnr_rgb": 7, "rgb_psnr_R": 3, "rgb_psnr_G": 4, "rgb_psnr_B": 5, "rgb_psnr_mean": 6}   # table columns
+_RGB_SSIM = {"rgb_ssim_R": 0, "rgb_ssim_G": 1, "rgb_ssim_B": 2, "rgb_ssim_mean": 3}
+
+
+def _rgb_table(pred, target, flags, cache, data_range: float = 1.0, eps: float = 1e-12):
+    """[n + 2, 9] float64 table of llie_psnr_stats (float64 cast first, channelwise.py:146-150); row n = batch mean."""
+    from . import _functional as Fn
+    key = ("psnr_table", float(data_range), float(eps))
+    if key not in cache:
+        if pred.shape[1] != 3:
+            raise ValueError(f"RGB metrics require tensors with 3 channels; received shape {tuple(pred.shape)}.")
+        n, c, h, w = pred.shape
+        table, fl, _ = Fn.psnr_stats(pred, target, n, c, h * w, cast_first=True, clamp_hi=None,
+                                     data_range=float(data_range), eps=float(eps))
+        flags |= fl
+        cache[key] = table
+    return cache[key]
+
+
+def _rgb_ssim_sums(pred, target, flags, cache, data_range: float = 1.0):
+    """[n, 3] float64 SSIM-map sums of the ssim_linear policy (reflect, same size, variance clamp, eps 1e-12)."""
+    from . import _functional as Fn
+    from . import _native as nat
+    key = ("rgb_ssim", float(data_range))
+    if key not in cache:
+        if pred.shape[1] != 3:
+            raise ValueError(f"RGB metrics require tensors with 3 channels; received shape {tuple(pred.shape)}.")
+        win = Fn.window_1d("linear", 11, 1.5, pred.device)
+        sums, fl, _ = Fn.ssim_stats(pred, target, win, pad_mode=nat.PAD["reflect"], c1=(0.01 * data_range) ** 2,
+                                    c2=(0.03 * data_range) ** 2, eps=1e-12, clamp_var=True)
+        flags |= fl
+        cache[key] = sums
+    return cache[key]
+
+
+def _make_rgb_psnr(col: int):
+    def fn(pred, target, flags, *, cache=None, data_range: float = 1.0, eps: float = 1e-12) -> Tensor:
+        table = _rgb_table(pred, target, flags, {} if cache is None else cache, data_range, eps)
+        return table[pred.shape[0], col]
+    return fn
+
+
+def _make_rgb_ssim(idx: int):
+    def fn(pred, target, flags, *, cache=None, data_range: float = 1.0) -> Tensor:
+        sums = _rgb_ssim_sums(pred, target, flags, {} if cache is None else cache, data_range)
+        per = (sums / float(pred.shape[-2] * pred.shape[-1])).to(torch.float32)      # [n, 3] float32 scores
+        v = per.mean(dim=1) if idx == 3 else per[:, idx]
+        return v.mean().double()
+    return fn
+
+
 METRIC_FUNCTIONS: Dict[str, Callable[..., Tensor]] = {
     "linear_psnr": _psnr,
     "linear_ssim": _ssim,
     "deltae2000_mean": _de_mean,
     "deltae2000_p95": _de_p95,
     "edge_deltae2000_mean": _edge_mean,
+    **{name: _make_rgb_psnr(col) for name, col in _RGB_PSNR.items()},
+    **{name: _make_rgb_ssim(idx) for name, idx in _RGB_SSIM.items()},
 }
+
+# every metric BASELINE configs[3] names: PSNR / SSIM / CPSNR / RGB-PSNR / RGB-SSIM / dE00 (mean) + edge dE00
+C4_METRICS = ["linear_psnr", "linear_ssim", "cpsnr_rgb", "rgb_psnr_mean", "rgb_ssim_mean", "deltae2000_mean",
+              "edge_deltae2000_mean"]
 
 
 @torch.no_grad()
@@ -132,15 +194,19 @@ def image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], flags: Opt
         shared = _ColourPass(p, t, flags, any(_COLOUR[n][0] for n in colour), any(_COLOUR[n][1] for n in colour),
                              want_sqerr=ride_psnr)
     vals = []
+    cache: dict = {}
     for name in names:
         kw = dict(opts.get(name, {}))
         if (name in _COLOUR or name == "linear_psnr") and shared is not None:
             kw["shared"] = shared
+        if name in _RGB_PSNR or name in _RGB_SSIM:
+            kw["cache"] = cache
         vals.append(METRIC_FUNCTIONS[name](p, t, flags, **kw).reshape(()))
     return torch.stack(vals)
 
 
-_FAST = ("linear_psnr", "linear_ssim", "deltae2000_mean", "deltae2000_p95", "edge_deltae2000_mean")
+_FAST = ("linear_psnr", "linear_ssim", "deltae2000_mean", "deltae2000_p95", "edge_deltae2000_mean",
+         *_RGB_PSNR, *_RGB_SSIM)
 
 
 _side: Dict[int, "torch.cuda.Stream"] = {}
@@ -168,7 +234,12 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
     if any(n not in _FAST for n in names) or len(set(names)) != len(names) or names != acc.names:
         return False
     p, t, dev = _stage_pair(pred, target)
-    if acc.vec.device != dev or p.shape[1] != 3 and ("linear_psnr" in names or any(n in _COLOUR for n in names)):
+    rgbp = [nm for nm in names if nm in _RGB_PSNR]
+    rgbs = [nm for nm in names if nm in _RGB_SSIM]
+    if acc.vec.device != dev or p.shape[1] != 3 and ("linear_psnr" in names or rgbp or rgbs or
+                                                      any(n in _COLOUR for n in names)):
+        return False
+    if any(opts.get(nm) for nm in rgbp + rgbs):   # non-default data_range / eps: the generic path handles them
         return False
     colour = [n for n in names if n in _COLOUR]
     if "linear_psnr" in names and not colour:
@@ -217,18 +288,30 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
         thr, _, _ = Fn.select_quantiles(grad.view(n, h * w), [q], joint=False)
         _, ecnt, esum = Fn.select_quantiles(dmap.view(n, h * w), [], joint=True, gate=grad.view(n, h * w),
                                             gate_thr=thr.view(n).contiguous(), want_sum=True)
-    while len(fl) < 4:
+    table = rsums = None
+    if rgbp:
+        table, f, _ = Fn.psnr_stats(p, t, n, c, h * w, cast_first=True, clamp_hi=None, data_range=1.0, eps=1e-12)
+        fl.append(f)
+    if rgbs:
+        cache: dict = {}
+        f = torch.zeros(1, dtype=torch.int32, device=dev)
+        rsums = _rgb_ssim_sums(p, t, f, cache)
+        fl.append(f)
+    while len(fl) < 6:
         fl.append(None)
     if joined is not None:
         main.wait_stream(joined)
     d = nat.EvalDesc(n, c, h * w, ssim_c, ssim_count, float(opts.get("linear_psnr", {}).get("data_range", 1.0)),
                      len(names), slot.get("linear_psnr", -1), slot.get("linear_ssim", -1),
                      slot.get("deltae2000_mean", -1), slot.get("deltae2000_p95", -1),
-                     slot.get("edge_deltae2000_mean", -1))
+                     slot.get("edge_deltae2000_mean", -1), slot.get("cpsnr_rgb", -1),
+                     (C.c_int32 * 4)(*[slot.get(f"rgb_psnr_{k}", -1) for k in ("R", "G", "B", "mean")]),
+                     (C.c_int32 * 4)(*[slot.get(f"rgb_ssim_{k}", -1) for k in ("R", "G", "B", "mean")]))
     with torch.cuda.device(dev):
         rc = nat.lib().llie_eval_accumulate(d, nat.ptr(sq), nat.ptr(ssim_sums), nat.ptr(sums), nat.ptr(p95),
-                                            nat.ptr(esum), nat.ptr(ecnt), nat.ptr(fl[0]), nat.ptr(fl[1]),
-                                            nat.ptr(fl[2]), nat.ptr(fl[3]), nat.ptr(acc.vec), nat.stream_ptr(dev))
+                                            nat.ptr(esum), nat.ptr(ecnt), nat.ptr(table), nat.ptr(rsums),
+                                            nat.ptr(fl[0]), nat.ptr(fl[1]), nat.ptr(fl[2]), nat.ptr(fl[3]),
+                                            nat.ptr(fl[4]), nat.ptr(fl[5]), nat.ptr(acc.vec), nat.stream_ptr(dev))
     nat.check(rc, "llie_eval_accumulate")
     nat.count_launch()
     return True

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"{s} declared in include/llie_b200.h but not exported"
     assert sorted(_native.declared_symbols()) == syms, "ctypes signatures out of sync with the header"
-    assert lib.llie_abi_version() == 2
+    assert lib.llie_abi_version() == 3
     assert lib.llie_workspace_bytes() >= 1 << 20
 
 

@@ -99,7 +99,7 @@ def test_device_metrics_equal_adapters():
     from lowlight_image_enhancement_b200 import lowlight_metrics as lm
     from lowlight_image_enhancement_b200.eval import METRIC_FUNCTIONS, image_metrics
     dev = torch.device("cuda:0")
-    names = sorted(METRIC_FUNCTIONS)
+    names = sorted(k for k in METRIC_FUNCTIONS if hasattr(lm, k))      # the five adapter names
     g = torch.Generator().manual_seed(12)
     pairs = []
     for i in range(5):
@@ -176,3 +176,58 @@ def test_tile_merge_equals_host_average():
     ref = preds / cnt
     got = g.merge(outs.to(dev))
     assert got.is_cuda and torch.equal(got.cpu(), ref)
+
+
+def _oracle_metrics(pred, gt):
+    """All fourteen driver metrics of one pair from the CPU oracle (float64 where the reference is float64)."""
+    from oracle import colour, quality
+    pc, gc = pred.clamp(0, 1), gt.clamp(0, 1)                          # the colour adapters clamp (lowlight_metrics.py:236)
+    rp = quality.rgb_psnr(pred, gt)
+    rs = quality.rgb_ssim(pred, gt)
+    out = {"linear_psnr": float(quality.calculate_psnr(gt, pred, 1.0)),
+           "linear_ssim": float(quality.ssim_torchmetrics(pred, gt, compute_dtype=torch.float64).mean()),
+           "cpsnr_rgb": float(quality.cpsnr_rgb(pred, gt)),
+           "deltae2000_mean": colour.de00_summary(pc, gc, percentiles=())["mean"],
+           "deltae2000_p95": colour.de00_summary(pc, gc, percentiles=(95.0,))["p95"],
+           "edge_deltae2000_mean": colour.edge_stats(pc, gc, q=0.85)["mean"]}
+    for k in ("R", "G", "B", "mean"):
+        out[f"rgb_psnr_{k}"] = float(rp[k])
+        out[f"rgb_ssim_{k}"] = float(rs[k])
+    return out
+
+
+@pytest.mark.gpu
+def test_evaluate_pairs_all_metrics_vs_oracle():
+    """the sharded driver (one-launch epilogue AND the generic path) against the ORACLE, not against the
+    repo's own adapters, for every metric BASELINE configs[3] names plus the per-channel values.  Tolerances of
+    BASELINE.json: 1e-5 relative PSNR / SSIM, 1e-4 absolute dE00; the edge mean allows mask ties on random floats."""
+    from lowlight_image_enhancement_b200.eval import C4_METRICS, METRIC_FUNCTIONS, ShardedMeans, image_metrics
+    from lowlight_image_enhancement_b200.eval import accumulate_image_metrics
+    dev = torch.device("cuda:0")
+    names = list(METRIC_FUNCTIONS)
+    assert set(C4_METRICS) <= set(names) and len(names) == 14
+    g = torch.Generator().manual_seed(2024)
+    pairs, want = [], {k: 0.0 for k in names}
+    for i in range(4):
+        gt = torch.rand(1, 3, 48 + 4 * i, 64 + 8 * i, generator=g)     # W % 4 == 0: the TMA-ring SSIM kernels
+        gt = torch.round(255 * torch.nn.functional.avg_pool2d(gt, 5, 1, 2)) / 255
+        pred = torch.round(255 * (gt + 0.04 * torch.randn(gt.shape, generator=g)).clamp(0, 1)) / 255
+        pairs.append((pred.to(dev), gt.to(dev)))
+        for k, v in _oracle_metrics(pred, gt).items():
+            want[k] += v / 4
+
+    def check(res):
+        assert res["count"] == 4 and res["nonfinite_inputs"] == 0
+        for k in names:
+            if k.startswith("deltae"):
+                assert abs(res[k] - want[k]) < 1e-4, (k, res[k], want[k])
+            elif k.startswith("edge"):
+                assert abs(res[k] - want[k]) < 5e-3, (k, res[k], want[k])
+            else:
+                assert res[k] == pytest.approx(want[k], rel=1e-5), (k, res[k], want[k])
+
+    check(evaluate_pairs(pairs, names, device=dev))                     # fast path: llie_eval_accumulate
+    acc = ShardedMeans(names, dev)
+    assert accumulate_image_metrics(pairs[0][0], pairs[0][1], names, acc)   # ... and it really is the fast path
+    check(evaluate_pairs(pairs, names, device=dev, metric_fn=image_metrics))  # generic path, same kernels
+    check({**evaluate_pairs(pairs, C4_METRICS, device=dev), **{k: want[k] for k in names if k not in C4_METRICS}})
