@@ -62,6 +62,32 @@ __device__ __forceinline__ V cbrt_fast(V t) {
     const V e = fma_(y0 * y0, y0, -t);                   // y0^3 - t
     return fma_(-e, cst<V>(1.0f / 3.0f) * z, y0);
 }
+// value and derivative t^(-2/3) / 3 (the derivative is the Newton scale factor, no division)
+template <class V>
+__device__ __forceinline__ V cbrt_fast_d(V t, V &dt) {
+    const V z = vex2(cst<V>(-2.0f / 3.0f) * vlg2(t));
+    const V y0 = t * z;
+    const V e = fma_(y0 * y0, y0, -t);
+    dt = cst<V>(1.0f / 3.0f) * z;
+    return fma_(-e, dt, y0);
+}
+template <class V>
+__device__ __forceinline__ V lab_f_d(V t, V &dt) {
+    V dc;
+    const V c = cbrt_fast_d(t, dc);
+    const auto hi_ = m_gt(t, cst<V>(0.008856f));
+    dt = vsel(hi_, dc, cst<V>(7.787f));
+    return vsel(hi_, c, fmac(t, 7.787f, 4.0f / 29.0f));
+}
+// sRGB channel -> linear with derivative (autograd of where(c > .04045, pow(.., 2.4), c / 12.92))
+template <class V>
+__device__ __forceinline__ V srgb_to_linear_d(V c, V &dc) {
+    const V base = DEM_DIVC(c + 0.055f, 1.055f);
+    const V v = pow24(base);
+    const auto hi_ = m_gt(c, cst<V>(0.04045f));
+    dc = vsel(hi_, cst<V>(2.4f / 1.055f) * (v * rcp_n(base)), cst<V>(1.0f / 12.92f));   // 2.4 base^1.4 / 1.055
+    return vsel(hi_, v, DEM_DIVC(c, 12.92f));
+}
 __device__ __forceinline__ float cbrt_exact(float t) { return cbrtf(t); }
 __device__ __forceinline__ F2 cbrt_exact(F2 t) { return f2(cbrtf(lo(t)), cbrtf(hi(t))); }
 
@@ -170,23 +196,28 @@ __device__ __forceinline__ V de00(V L1, V a1, V b1, V L2, V a2, V b2, const DeCo
     const V c1p = vsqrt0(n1 + eps), c2p = vsqrt0(n2 + eps);
     const V r1 = vrsqrt0(vmax(n1, cst<V>(1e-30f))), r2 = vrsqrt0(vmax(n2, cst<V>(1e-30f)));
     const V zero = cst<V>(0.0f);
-    const V u1x = vsel(m_gt(n1, zero), a1p * r1, cst<V>(1.0f)), u1y = b1 * r1;
-    const V u2x = vsel(m_gt(n2, zero), a2p * r2, cst<V>(1.0f)), u2y = b2 * r2;
+    // (both components through the select: a grey colour is the CONSTANT (1, 0), zero gradient like ATen's atan2(0, 0))
+    const auto chro1 = m_gt(n1, zero), chro2 = m_gt(n2, zero);
+    const V u1x = vsel(chro1, a1p * r1, cst<V>(1.0f)), u1y = vsel(chro1, b1 * r1, zero);
+    const V u2x = vsel(chro2, a2p * r2, cst<V>(1.0f)), u2y = vsel(chro2, b2 * r2, zero);
     const V dL = L2 - L1, dC = c2p - c1p;
-    // dH = 2 sqrt(C1' C2' + eps) sin(dh / 2)
-    const V s = fma_(u1y, u2x, -(u1x * u2y));               // sin(h1 - h2) (unit vectors: a grey colour counts as hue 0)
+    // signed half-angle sine and mean-hue direction from w = u1 + u2 (|w| = 2 |cos(dh / 2)|) and d = u2 - u1
+    // (|d| = 2 |sin(dh / 2)|, |w|^2 + |d|^2 = 4).  The larger of the two carries the precision:
+    //   hues less than a right angle apart: sin(dh / 2) = sin(dh) / (2 cos(dh / 2)) = -s / |w|,  direction = w
+    //   else:                               sin(dh / 2) = sgn |d| / 2,  direction = sgn (d_y, -d_x)  (d turned by 90deg
+    //                                       to the side the signed half-angle says)
+    // One reciprocal square root of max(|w|^2, |d|^2) >= 2 serves both; every branch is smooth in the inputs (the dual
+    // numbers of the loss gradient differentiate the selected one), no square root of a possibly zero argument.
+    const V s = cross2(u1y, u2x, u1x, u2y);                 // sin(h1 - h2) (unit vectors: a grey colour counts as hue 0)
     const V ddx = u2x - u1x, ddy = u2y - u1y;
-    const V dabs = vsqrt0(fma_(ddx, ddx, ddy * ddy));       // 2 |sin(dh / 2)|
-    const V dH = vsqrt0(fma_(c1p, c2p, eps)) * vsel(m_gt(s, zero), -dabs, dabs);
-    // mean hue direction: w = u1 + u2 (|w| = 2 |cos(dh / 2)|) when the hues are less than a right angle apart, else
-    // the perpendicular of u2 - u1 turned to the side the signed half-angle says (|u2 - u1| = 2 |sin(dh / 2)|): either
-    // vector has a squared norm >= 2, so the direction keeps full precision for near-opposite hues too
     const V wx = u1x + u2x, wy = u1y + u2y;
     const V wn2 = fma_(wx, wx, wy * wy), dn2 = fma_(ddx, ddx, ddy * ddy);
     const auto use_d = m_gt(dn2, wn2);
     const V sg = vsel(m_gt(s, zero), cst<V>(-1.0f), cst<V>(1.0f));
     const V vx = vsel(use_d, sg * ddy, wx), vy = vsel(use_d, -(sg * ddx), wy);
     const V rw = vrsqrt0(vmax(dn2, wn2));
+    const V sin_half = vsel(use_d, cst<V>(0.5f) * sg * dn2, -s) * rw;
+    const V dH = cst<V>(2.0f) * vsqrt0(fma_(c1p, c2p, eps)) * sin_half;
     const V ch = vx * rw, sh = vy * rw;
     const V T = t_weight(ch, sh);
     const V th = atan2_poly(vy, vx);

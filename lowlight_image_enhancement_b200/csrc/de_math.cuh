@@ -51,6 +51,13 @@ __device__ __forceinline__ F2 operator-(float s, F2 a) { return fma_(a, f2(-1.f,
 
 __device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
 
+// a b - c d with BOTH products rounded (no FMA contraction): exactly 0 when (a, b) == (d, c) -- the sine of the
+// angle between two identical unit vectors must vanish so that dE00(x, x) is exactly 0
+__device__ __forceinline__ float cross2(float a, float b, float c, float d) {
+    return __fsub_rn(__fmul_rn(a, b), __fmul_rn(c, d));
+}
+__device__ __forceinline__ F2 cross2(F2 a, F2 b, F2 c, F2 d) { return (a * b) - (c * d); }
+
 // constant broadcast
 template <class V> __device__ __forceinline__ V cst(float c);
 template <> __device__ __forceinline__ float cst<float>(float c) { return c; }
@@ -94,6 +101,10 @@ __device__ __forceinline__ bool m_gt(float x, float y) { return x > y; }
 __device__ __forceinline__ M2 m_gt(F2 x, F2 y) { return {lo(x) > lo(y), hi(x) > hi(y)}; }
 __device__ __forceinline__ bool m_lt(float x, float y) { return x < y; }
 __device__ __forceinline__ M2 m_lt(F2 x, F2 y) { return {lo(x) < lo(y), hi(x) < hi(y)}; }
+__device__ __forceinline__ bool m_ge(float x, float y) { return x >= y; }   // false for NaN
+__device__ __forceinline__ M2 m_ge(F2 x, F2 y) { return {lo(x) >= lo(y), hi(x) >= hi(y)}; }
+__device__ __forceinline__ bool m_le(float x, float y) { return x <= y; }
+__device__ __forceinline__ M2 m_le(F2 x, F2 y) { return {lo(x) <= lo(y), hi(x) <= hi(y)}; }
 __device__ __forceinline__ bool m_neg(float x) { return (__float_as_uint(x) >> 31) != 0u; }  // sign bit (-0 counts)
 __device__ __forceinline__ M2 m_neg(F2 x) { return {m_neg(lo(x)), m_neg(hi(x))}; }
 __device__ __forceinline__ bool m_and(bool p, bool q) { return p && q; }

@@ -15,11 +15,15 @@
 
 #include "common.cuh"
 #include "de_core.cuh"
+#include "de_dual.cuh"
 
 // grid = LLIE_DE_WAVES waves of resident blocks: one wave leaves the slowest SM's blocks as the tail (402 us per 12 Mpx
 // pair), 1.6 waves as before 383, four waves let the block scheduler even it out (366); 8 is no better
 #ifndef LLIE_DE_WAVES
 #define LLIE_DE_WAVES 4
+#endif
+#ifndef LLIE_DEGRAD_WAVES
+#define LLIE_DEGRAD_WAVES 2
 #endif
 namespace llie {
 
@@ -37,147 +41,6 @@ __device__ __forceinline__ float div_const(float x, float c, float rc) {
     return fmaf(r, rc, q);
 }
 #define DIVC(x, C) div_const((x), (C), 1.0f / (C))
-
-// b^2.4 for b in [0.09, 1] as (b * b^(1/5))^2.  The fifth root starts from the SFU estimate
-// exp2(0.2 log2 b) (~1e-6 relative) and takes one Newton step whose residual b - y^5 is evaluated with
-// FMA error terms; the correction is kept as a separate term through the final square, so the result is
-// rounded once: < 1 ulp against double pow (tests/test_gpu_ssim_colour.py::test_srgb_to_linear_ulp).
-__device__ __forceinline__ float pow24(float b) {
-    const float y = exp2f(0.2f * __log2f(b));
-    const float y2 = y * y, e2 = fmaf(y, y, -y2);          // y^2 = y2 + e2 exactly
-    const float y4 = y2 * y2;
-    const float e4 = fmaf(y2, y2, -y4) + 2.0f * y2 * e2;   // y^4 = y4 + e4 (+ O(e2^2))
-    const float r = fmaf(-y4, y, b) - e4 * y;              // b - y^5
-    const float dy = __fdividef(r, 5.0f * y4);             // Newton correction, |dy| ~ 1e-6 y
-    const float p = b * y, ep = fmaf(b, y, -p);            // b y = p + ep exactly
-    const float lo = fmaf(b, dy, ep);                      // b (y + dy) = p + lo
-    return fmaf(p, p, 2.0f * p * lo);
-}
-__device__ __forceinline__ float srgb_to_linear(float c) {
-    return c > 0.04045f ? pow24(DIVC(c + 0.055f, 1.055f)) : DIVC(c, 12.92f);
-}
-__device__ __forceinline__ float lab_f(float t) {
-    return t > 0.008856f ? cbrtf(t) : 7.787f * t + 4.0f / 29.0f;
-}
-
-// T = 1 - 0.17 cos(h - 30deg) + 0.24 cos 2h + 0.32 cos(3h + 6deg) - 0.20 cos(4h - 63deg) and dT/dh from one
-// sincosf and multiple-angle identities
-__device__ __forceinline__ float t_weight(float hb, float *dt) {
-    float s1, c1;
-    sincosf(hb, &s1, &c1);
-    const float c2 = fmaf(2.0f * c1, c1, -1.0f), s2 = 2.0f * s1 * c1;
-    const float c3 = c1 * fmaf(4.0f * c1, c1, -3.0f), s3 = s1 * fmaf(4.0f * c1, c1, -1.0f);
-    const float c4 = fmaf(2.0f * c2, c2, -1.0f), s4 = 2.0f * s2 * c2;
-    constexpr float C30 = 0.86602540378443865f, S30 = 0.5f;
-    constexpr float C6 = 0.99452189536827334f, S6 = 0.10452846326765347f;
-    constexpr float C63 = 0.45399049973954675f, S63 = 0.89100652418836786f;
-    const float ca = c1 * C30 + s1 * S30, sa = s1 * C30 - c1 * S30;  // h - 30
-    const float cb = c3 * C6 - s3 * S6, sb = s3 * C6 + c3 * S6;      // 3h + 6
-    const float cc = c4 * C63 + s4 * S63, sc = s4 * C63 - c4 * S63;  // 4h - 63
-    if (dt) *dt = 0.17f * sa - 0.48f * s2 - 0.96f * sb + 0.80f * sc;
-    return 1.0f - 0.17f * ca + 0.24f * c2 + 0.32f * cb - 0.20f * cc;
-}
-// kornia 0.6.12 rgb_to_lab
-__device__ __forceinline__ void rgb_to_lab(float r, float g, float b, float &L, float &A, float &B) {
-    r = srgb_to_linear(r);
-    g = srgb_to_linear(g);
-    b = srgb_to_linear(b);
-    const float x = 0.412453f * r + 0.357580f * g + 0.180423f * b;
-    const float y = 0.212671f * r + 0.715160f * g + 0.072169f * b;
-    const float z = 0.019334f * r + 0.119193f * g + 0.950227f * b;
-    const float fx = lab_f(DIVC(x, 0.95047f)), fy = lab_f(y), fz = lab_f(DIVC(z, 1.08883f));
-    L = 116.0f * fy - 16.0f;
-    A = 500.0f * (fx - fy);
-    B = 200.0f * (fy - fz);
-}
-
-__device__ __forceinline__ float pow7(float v) {
-    const float v2 = v * v, v4 = v2 * v2;
-    return v4 * v2 * v;
-}
-__device__ __forceinline__ float deg2rad(float d) { return d * (kPi / 180.0f); }
-
-// METRIC variant (color_error.py:105-210)
-__device__ float de00_metric(float L1, float a1, float b1, float L2, float a2, float b2, float kL, float kC, float kH,
-                             float eps) {
-    const float c1 = sqrtf(a1 * a1 + b1 * b1 + eps), c2 = sqrtf(a2 * a2 + b2 * b2 + eps);
-    const float cb = 0.5f * (c1 + c2);
-    const float cb7 = pow7(cb);
-    const float k25 = 6103515625.0f;
-    const float g = 0.5f * (1.0f - sqrtf(cb7 / (cb7 + k25 + eps)));
-    const float a1p = (1.0f + g) * a1, a2p = (1.0f + g) * a2;
-    const float c1p = sqrtf(a1p * a1p + b1 * b1 + eps), c2p = sqrtf(a2p * a2p + b2 * b2 + eps);
-    const float h1 = atan2f(b1, a1p), h2 = atan2f(b2, a2p);
-    const float dL = L2 - L1, dC = c2p - c1p;
-    const bool ok = (c1p * c2p) != 0.0f;
-    const float df = h2 - h1;
-    float dh = 0.0f;
-    if (ok && fabsf(df) <= kPi) dh = df;
-    if (ok && df > kPi) dh = df - 2.0f * kPi;
-    if (ok && df < -kPi) dh = df + 2.0f * kPi;
-    const float dH = 2.0f * sqrtf(c1p * c2p + eps) * sinf(dh / 2.0f);
-    const float Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
-    const float hs = h1 + h2, ad = fabsf(h1 - h2);
-    float hb;
-    if (!ok)
-        hb = hs;
-    else if (ad <= kPi)
-        hb = 0.5f * hs;
-    else if (hs < 2.0f * kPi)
-        hb = 0.5f * (hs + 2.0f * kPi);
-    else
-        hb = 0.5f * (hs - 2.0f * kPi);
-    const float t = t_weight(hb, nullptr);
-    const float q = DIVC(DIVC(hb * 180.0f, kPi) - 275.0f, 25.0f);
-    const float dth = deg2rad(30.0f) * expf(-(q * q));
-    const float Cb7 = pow7(Cb);
-    const float rc = 2.0f * sqrtf(Cb7 / (Cb7 + k25 + eps));
-    const float rt = -sinf(2.0f * dth) * rc;
-    const float l50 = (Lb - 50.0f) * (Lb - 50.0f);
-    const float sL = 1.0f + (0.015f * l50) / sqrtf(20.0f + l50 + eps);
-    const float sC = 1.0f + 0.045f * Cb;
-    const float sH = 1.0f + 0.015f * Cb * t;
-    const float lt = dL / (kL * sL + eps), ct = dC / (kC * sC + eps), ht = dH / (kH * sH + eps);
-    return sqrtf(fmaxf(lt * lt + ct * ct + ht * ht + rt * ct * ht, 0.0f));
-}
-
-// torch's `%` on floats (python modulo: result takes the sign of the divisor)
-__device__ __forceinline__ float pymod(float a, float m) {
-    float r = fmodf(a, m);
-    if (r != 0.0f && ((r < 0.0f) != (m < 0.0f))) r += m;
-    return r;
-}
-
-// LOSS variant (losses.py:99-136)
-__device__ float de00_loss(float L1, float a1, float b1, float L2, float a2, float b2, float eps) {
-    const float c1 = sqrtf(a1 * a1 + b1 * b1 + eps), c2 = sqrtf(a2 * a2 + b2 * b2 + eps);
-    const float cb = 0.5f * (c1 + c2);
-    const float cb7 = pow7(cb);
-    const float k25 = 6103515625.0f;
-    const float g = 0.5f * (1.0f - sqrtf(cb7 / (cb7 + k25 + eps)));
-    const float a1p = (1.0f + g) * a1, a2p = (1.0f + g) * a2;
-    const float c1p = sqrtf(a1p * a1p + b1 * b1 + eps), c2p = sqrtf(a2p * a2p + b2 * b2 + eps);
-    const float h1 = pymod(atan2f(b1, a1p), 2.0f * kPi), h2 = pymod(atan2f(b2, a2p), 2.0f * kPi);
-    const float dL = L2 - L1, dC = c2p - c1p;
-    float dh = h2 - h1;
-    dh = dh - (dh > kPi ? 2.0f * kPi : 0.0f) + (dh < -kPi ? 2.0f * kPi : 0.0f);
-    const float dH = 2.0f * sqrtf(c1p * c2p + eps) * sinf(dh / 2.0f);
-    const float Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
-    const float hs = h1 + h2;
-    const float hb = hs / 2.0f - (fabsf(h1 - h2) > kPi ? kPi : 0.0f) + (hs < 0.0f ? 2.0f * kPi : 0.0f);
-    const float t = t_weight(hb, nullptr);
-    const float q = DIVC((hb * (180.0f / kPi)) - 275.0f, 25.0f);
-    const float dro = 30.0f * expf(-(q * q));
-    const float Cb7 = pow7(Cb);
-    const float rc = 2.0f * sqrtf(Cb7 / (Cb7 + k25 + eps));
-    const float l50 = (Lb - 50.0f) * (Lb - 50.0f);
-    const float sL = 1.0f + (0.015f * l50) / sqrtf(20.0f + l50 + eps);
-    const float sC = 1.0f + 0.045f * Cb;
-    const float sH = 1.0f + 0.015f * Cb * t;
-    const float rt = -sinf(deg2rad(dro)) * rc;
-    const float lt = dL / sL, ct = dC / sC, ht = dH / sH;
-    return sqrtf(lt * lt + ct * ct + ht * ht + rt * ct * ht + eps);
-}
 
 struct DeArgs {
     llie_deltae_desc d;
@@ -311,112 +174,11 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------
-// LOSS variant with its gradient w.r.t. (L1, a1, b1): forward-mode duals with three tangents carried in
-// registers next to the value, so the ~60-op chain of losses.py:99-136 is differentiated in the same pass
-// that evaluates it (autograd: ~40 saved planes and ~90 replayed kernels).  Each rule is the one ATen's
-// autograd applies (sqrt: g/(2 sqrt); atan2: (x dy - y dx)/(x^2 + y^2), 0 at the origin like ATen;
-// `%`, comparisons and masks carry no gradient).
-struct D3 {
-    float v, x, y, z;
-};
-__device__ __forceinline__ D3 dconst(float v) { return {v, 0.f, 0.f, 0.f}; }
-__device__ __forceinline__ D3 operator+(D3 a, D3 b) { return {a.v + b.v, a.x + b.x, a.y + b.y, a.z + b.z}; }
-__device__ __forceinline__ D3 operator-(D3 a, D3 b) { return {a.v - b.v, a.x - b.x, a.y - b.y, a.z - b.z}; }
-__device__ __forceinline__ D3 operator+(D3 a, float b) { return {a.v + b, a.x, a.y, a.z}; }
-__device__ __forceinline__ D3 operator-(D3 a, float b) { return {a.v - b, a.x, a.y, a.z}; }
-__device__ __forceinline__ D3 operator-(float a, D3 b) { return {a - b.v, -b.x, -b.y, -b.z}; }
-__device__ __forceinline__ D3 operator-(D3 a) { return {-a.v, -a.x, -a.y, -a.z}; }
-__device__ __forceinline__ D3 operator*(float s, D3 a) { return {s * a.v, s * a.x, s * a.y, s * a.z}; }
-__device__ __forceinline__ D3 operator*(D3 a, D3 b) {
-    return {a.v * b.v, fmaf(a.x, b.v, a.v * b.x), fmaf(a.y, b.v, a.v * b.y), fmaf(a.z, b.v, a.v * b.z)};
-}
-__device__ __forceinline__ D3 operator/(D3 a, D3 b) {
-    const float inv = 1.0f / b.v, q = a.v * inv;
-    return {q, (a.x - q * b.x) * inv, (a.y - q * b.y) * inv, (a.z - q * b.z) * inv};
-}
-__device__ __forceinline__ D3 dchain(float v, float dv, D3 a) { return {v, dv * a.x, dv * a.y, dv * a.z}; }
-__device__ __forceinline__ D3 dsqrt(D3 a) {
-    const float r = sqrtf(a.v);
-    return dchain(r, 0.5f / r, a);
-}
-__device__ __forceinline__ D3 dsin(D3 a) {
-    float s, c;
-    sincosf(a.v, &s, &c);
-    return dchain(s, c, a);
-}
-__device__ __forceinline__ D3 dexp(D3 a) {
-    const float e = expf(a.v);
-    return dchain(e, e, a);
-}
-__device__ __forceinline__ D3 dpow7(D3 a) {
-    const float v2 = a.v * a.v, v3 = v2 * a.v, v6 = v3 * v3;
-    return dchain(v6 * a.v, 7.0f * v6, a);
-}
-__device__ __forceinline__ D3 datan2(D3 y, D3 x) {
-    const float den = x.v * x.v + y.v * y.v;
-    const float r = den == 0.0f ? 0.0f : 1.0f / den;  // ATen: zero gradient at the origin
-    return {atan2f(y.v, x.v), (x.v * y.x - y.v * x.x) * r, (x.v * y.y - y.v * x.y) * r, (x.v * y.z - y.v * x.z) * r};
-}
-
-// dE00 (loss variant) and d dE00 / d(L1, a1, b1); (L2, a2, b2) are constants
-__device__ D3 de00_loss_dual(float L1f, float a1f, float b1f, float L2, float a2, float b2, float eps) {
-    const D3 L1{L1f, 1.f, 0.f, 0.f}, a1{a1f, 0.f, 1.f, 0.f}, b1{b1f, 0.f, 0.f, 1.f};
-    const float k25 = 6103515625.0f;
-    const D3 c1 = dsqrt(a1 * a1 + b1 * b1 + eps);
-    const float c2 = sqrtf(a2 * a2 + b2 * b2 + eps);
-    const D3 cb = 0.5f * (c1 + c2);
-    const D3 cb7 = dpow7(cb);
-    const D3 g = 0.5f * (1.0f - dsqrt(cb7 / (cb7 + (k25 + eps))));
-    const D3 g1 = g + 1.0f;
-    const D3 a1p = g1 * a1, a2p = a2 * g1;
-    const D3 c1p = dsqrt(a1p * a1p + b1 * b1 + eps), c2p = dsqrt(a2p * a2p + (b2 * b2 + eps));
-    D3 h1 = datan2(b1, a1p), h2 = datan2(dconst(b2), a2p);
-    h1.v = pymod(h1.v, 2.0f * kPi);
-    h2.v = pymod(h2.v, 2.0f * kPi);
-    const D3 dL = L2 - L1, dC = c2p - c1p;
-    D3 dh = h2 - h1;
-    dh.v = dh.v - (dh.v > kPi ? 2.0f * kPi : 0.0f) + (dh.v < -kPi ? 2.0f * kPi : 0.0f);
-    const D3 dH = 2.0f * (dsqrt(c1p * c2p + eps) * dsin(0.5f * dh));
-    const D3 Lb = 0.5f * (L1 + L2), Cb = 0.5f * (c1p + c2p);
-    const D3 hs = h1 + h2;
-    D3 hb = 0.5f * hs;
-    hb.v = hs.v / 2.0f - (fabsf(h1.v - h2.v) > kPi ? kPi : 0.0f) + (hs.v < 0.0f ? 2.0f * kPi : 0.0f);
-    float dtdh;
-    const float tv = t_weight(hb.v, &dtdh);
-    const D3 t = dchain(tv, dtdh, hb);
-    const D3 q = (1.0f / 25.0f) * ((180.0f / kPi) * hb - 275.0f);
-    const D3 dro = 30.0f * dexp(-(q * q));
-    const D3 Cb7 = dpow7(Cb);
-    const D3 rc = 2.0f * dsqrt(Cb7 / (Cb7 + (k25 + eps)));
-    const D3 l50 = (Lb - 50.0f) * (Lb - 50.0f);
-    const D3 sL = (0.015f * l50) / dsqrt(l50 + (20.0f + eps)) + 1.0f;
-    const D3 sC = 0.045f * Cb + 1.0f;
-    const D3 sH = 0.015f * (Cb * t) + 1.0f;
-    const D3 rt = -(dsin((kPi / 180.0f) * dro) * rc);
-    const D3 lt = dL / sL, ct = dC / sC, ht = dH / sH;
-    return dsqrt(lt * lt + ct * ct + ht * ht + rt * (ct * ht) + eps);
-}
-
-// sRGB channel -> linear with derivative (autograd of where(c > .04045, pow(.., 2.4), c / 12.92))
-__device__ __forceinline__ float srgb_to_linear_d(float c, float &dc) {
-    if (c > 0.04045f) {
-        const float base = DIVC(c + 0.055f, 1.055f), v = pow24(base);
-        dc = (2.4f / 1.055f) * (v / base);  // 2.4 base^1.4 / 1.055
-        return v;
-    }
-    dc = 1.0f / 12.92f;
-    return DIVC(c, 12.92f);
-}
-__device__ __forceinline__ float lab_f_d(float t, float &dt) {
-    if (t > 0.008856f) {
-        const float v = cbrtf(t);
-        dt = (1.0f / 3.0f) * (v / t);  // t^(-2/3) / 3
-        return v;
-    }
-    dt = 7.787f;
-    return 7.787f * t + 4.0f / 29.0f;
-}
-
+// LOSS variant with its gradient w.r.t. x: the generic formula of de_core.cuh evaluated on forward-mode duals with three
+// tangents (d/dL1, d/da1, d/db1; de_dual.cuh), then chained through the closed-form Lab Jacobian and the clamp mask, so
+// value and gradient come out of ONE pass (24 B/px read, 12 B/px written) and backward is a scale by the upstream
+// scalar.  ATen's rules where they matter for parity: zero hue gradient for a grey colour (atan2(0, 0)), where()-style
+// clamp masks.
 struct DeGradArgs {
     int n, h, w, clamp_in;
     float eps, scale;
@@ -429,7 +191,58 @@ struct DeGradArgs {
     unsigned *ticket;
 };
 
-// losses.py:138-143 value (per-image sums) + `scale` * d dE / d x, one pass: 24 B/px read, 12 B/px written
+// one pixel group (S = float: 1 pixel, S = dem::F2: 2 pixels): dE00 value and scale * d dE00 / d (r, g, b) of x
+template <class S>
+__device__ __forceinline__ S de_grad_pixel(const DeGradArgs &a, S r0, S r1, S r2, S t0, S t1, S t2, S &g0, S &g1, S &g2) {
+    using namespace dem;
+    using D = Dual3<S>;
+    S p0 = r0, p1 = r1, p2 = r2;
+    const S zero = cst<S>(0.f), one = cst<S>(1.f);
+    auto m0 = m_ge(one, zero), m1 = m0, m2 = m0;  // clamp pass-through masks (ATen: min <= x <= max), all true
+    if (a.clamp_in) {
+        m0 = m_and(m_ge(r0, zero), m_le(r0, one));
+        m1 = m_and(m_ge(r1, zero), m_le(r1, one));
+        m2 = m_and(m_ge(r2, zero), m_le(r2, one));
+        p0 = vsat(p0); p1 = vsat(p1); p2 = vsat(p2);
+        t0 = vsat(t0); t1 = vsat(t1); t2 = vsat(t2);
+    }
+    S d0, d1, d2;
+    const S l0 = srgb_to_linear_d(p0, d0), l1 = srgb_to_linear_d(p1, d1), l2 = srgb_to_linear_d(p2, d2);
+    const S X = fmav(l2, 0.180423f, fmav(l1, 0.357580f, cst<S>(0.412453f) * l0));
+    const S Y = fmav(l2, 0.072169f, fmav(l1, 0.715160f, cst<S>(0.212671f) * l0));
+    const S Z = fmav(l2, 0.950227f, fmav(l1, 0.119193f, cst<S>(0.019334f) * l0));
+    S dfx, dfy, dfz;
+    const S fx = lab_f_d(DEM_DIVC(X, 0.95047f), dfx), fy = lab_f_d(Y, dfy), fz = lab_f_d(DEM_DIVC(Z, 1.08883f), dfz);
+    const S L1 = fmac(fy, 116.0f, -16.0f), A1 = cst<S>(500.0f) * (fx - fy), B1 = cst<S>(200.0f) * (fy - fz);
+    // the target goes through the SAME value arithmetic (identical images -> identical Lab)
+    S u0, u1, u2, e0, e1, e2;
+    const S k0 = srgb_to_linear_d(t0, u0), k1 = srgb_to_linear_d(t1, u1), k2 = srgb_to_linear_d(t2, u2);
+    const S X2 = fmav(k2, 0.180423f, fmav(k1, 0.357580f, cst<S>(0.412453f) * k0));
+    const S Y2 = fmav(k2, 0.072169f, fmav(k1, 0.715160f, cst<S>(0.212671f) * k0));
+    const S Z2 = fmav(k2, 0.950227f, fmav(k1, 0.119193f, cst<S>(0.019334f) * k0));
+    const S fx2 = lab_f_d(DEM_DIVC(X2, 0.95047f), e0), fy2 = lab_f_d(Y2, e1), fz2 = lab_f_d(DEM_DIVC(Z2, 1.08883f), e2);
+    const S L2 = fmac(fy2, 116.0f, -16.0f), A2 = cst<S>(500.0f) * (fx2 - fy2), B2 = cst<S>(200.0f) * (fy2 - fz2);
+    const D de = de00<1>(D{L1, one, zero, zero}, D{A1, zero, one, zero}, D{B1, zero, zero, one}, dual_const<S>(L2),
+                         dual_const<S>(A2), dual_const<S>(B2), DeConsts{1.f, 1.f, 1.f, a.eps});
+    // reverse through Lab -> f -> XYZ -> linear -> sRGB
+    const S gfx = cst<S>(500.0f) * de.y;
+    const S gfy = fmav(de.z, 200.0f, fmav(de.y, -500.0f, cst<S>(116.0f) * de.x));
+    const S gfz = cst<S>(-200.0f) * de.z;
+    const S gX = DEM_DIVC(gfx * dfx, 0.95047f), gY = gfy * dfy, gZ = DEM_DIVC(gfz * dfz, 1.08883f);
+    const S gl0 = fmav(gZ, 0.019334f, fmav(gY, 0.212671f, cst<S>(0.412453f) * gX));
+    const S gl1 = fmav(gZ, 0.119193f, fmav(gY, 0.715160f, cst<S>(0.357580f) * gX));
+    const S gl2 = fmav(gZ, 0.950227f, fmav(gY, 0.072169f, cst<S>(0.180423f) * gX));
+    // where()-style masking: a clamped-away channel gets exactly 0 even when the chain holds NaN
+    const S sc = cst<S>(a.scale);
+    g0 = vsel(m0, sc * gl0 * d0, zero);
+    g1 = vsel(m1, sc * gl1 * d1, zero);
+    g2 = vsel(m2, sc * gl2 * d2, zero);
+    return de.v;
+}
+
+// losses.py:138-143 value (per-image sums) + `scale` * d dE / d x, one pass.  VEC: 4 pixels per thread and step
+// (128-bit loads / stores, two packed-pair dual evaluations); needs plane % 4 == 0 and 16-byte aligned tensors.
+template <bool VEC>
 __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs a) {
     __shared__ double red[32];
     const int n = blockIdx.y, G = gridDim.x;
@@ -437,43 +250,44 @@ __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs 
     const float *x0 = a.x + (long long)n * 3 * plane, *y0 = a.y + (long long)n * 3 * plane;
     float *g0 = a.out_grad + (long long)n * 3 * plane;
     float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
-         i += (long long)G * blockDim.x) {
-        const float r0 = __ldcs(x0 + i), r1 = __ldcs(x0 + plane + i), r2 = __ldcs(x0 + 2 * plane + i);
-        float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
-        chk_x = fmaf(r0, 0.f, fmaf(r1, 0.f, fmaf(r2, 0.f, chk_x)));
-        chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
-        float p0 = r0, p1 = r1, p2 = r2;
-        float m0 = 1.f, m1 = 1.f, m2 = 1.f;  // clamp pass-through masks (ATen: min <= x <= max)
-        if (a.clamp_in) {
-            m0 = (r0 >= 0.f && r0 <= 1.f) ? 1.f : 0.f;
-            m1 = (r1 >= 0.f && r1 <= 1.f) ? 1.f : 0.f;
-            m2 = (r2 >= 0.f && r2 <= 1.f) ? 1.f : 0.f;
-            p0 = fminf(fmaxf(p0, 0.f), 1.f); p1 = fminf(fmaxf(p1, 0.f), 1.f); p2 = fminf(fmaxf(p2, 0.f), 1.f);
-            t0 = fminf(fmaxf(t0, 0.f), 1.f); t1 = fminf(fmaxf(t1, 0.f), 1.f); t2 = fminf(fmaxf(t2, 0.f), 1.f);
+    if (VEC) {
+        using dem::F2;
+        const long long groups = plane >> 2;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (long long)G * blockDim.x) {
+            float4 p[3], t[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                p[c] = __ldcs(reinterpret_cast<const float4 *>(x0 + c * plane) + i);
+                t[c] = __ldcs(reinterpret_cast<const float4 *>(y0 + c * plane) + i);
+                chk_x = fmaf(p[c].x, 0.f, fmaf(p[c].y, 0.f, fmaf(p[c].z, 0.f, fmaf(p[c].w, 0.f, chk_x))));
+                chk_y = fmaf(t[c].x, 0.f, fmaf(t[c].y, 0.f, fmaf(t[c].z, 0.f, fmaf(t[c].w, 0.f, chk_y))));
+            }
+            F2 ga[3], gb[3];
+            const F2 da = de_grad_pixel<F2>(a, dem::f2(p[0].x, p[0].y), dem::f2(p[1].x, p[1].y), dem::f2(p[2].x, p[2].y),
+                                            dem::f2(t[0].x, t[0].y), dem::f2(t[1].x, t[1].y), dem::f2(t[2].x, t[2].y),
+                                            ga[0], ga[1], ga[2]);
+            const F2 db = de_grad_pixel<F2>(a, dem::f2(p[0].z, p[0].w), dem::f2(p[1].z, p[1].w), dem::f2(p[2].z, p[2].w),
+                                            dem::f2(t[0].z, t[0].w), dem::f2(t[1].z, t[1].w), dem::f2(t[2].z, t[2].w),
+                                            gb[0], gb[1], gb[2]);
+            acc += (dem::lo(da) + dem::hi(da)) + (dem::lo(db) + dem::hi(db));
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                __stcs(reinterpret_cast<float4 *>(g0 + c * plane) + i,
+                       make_float4(dem::lo(ga[c]), dem::hi(ga[c]), dem::lo(gb[c]), dem::hi(gb[c])));
         }
-        float d0, d1, d2;
-        const float l0 = srgb_to_linear_d(p0, d0), l1 = srgb_to_linear_d(p1, d1), l2 = srgb_to_linear_d(p2, d2);
-        const float X = 0.412453f * l0 + 0.357580f * l1 + 0.180423f * l2;
-        const float Y = 0.212671f * l0 + 0.715160f * l1 + 0.072169f * l2;
-        const float Z = 0.019334f * l0 + 0.119193f * l1 + 0.950227f * l2;
-        float dfx, dfy, dfz;
-        const float fx = lab_f_d(DIVC(X, 0.95047f), dfx), fy = lab_f_d(Y, dfy), fz = lab_f_d(DIVC(Z, 1.08883f), dfz);
-        const float L1 = 116.0f * fy - 16.0f, A1 = 500.0f * (fx - fy), B1 = 200.0f * (fy - fz);
-        float L2, A2, B2;
-        rgb_to_lab(t0, t1, t2, L2, A2, B2);
-        const D3 de = de00_loss_dual(L1, A1, B1, L2, A2, B2, a.eps);
-        acc += de.v;
-        // reverse through Lab -> f -> XYZ -> linear -> sRGB
-        const float gfx = 500.0f * de.y, gfy = 116.0f * de.x - 500.0f * de.y + 200.0f * de.z, gfz = -200.0f * de.z;
-        const float gX = DIVC(gfx * dfx, 0.95047f), gY = gfy * dfy, gZ = DIVC(gfz * dfz, 1.08883f);
-        const float gl0 = 0.412453f * gX + 0.212671f * gY + 0.019334f * gZ;
-        const float gl1 = 0.357580f * gX + 0.715160f * gY + 0.119193f * gZ;
-        const float gl2 = 0.180423f * gX + 0.072169f * gY + 0.950227f * gZ;
-        // where()-style masking: a clamped-away channel gets exactly 0 even when the chain holds NaN
-        __stcs(g0 + i, m0 != 0.f ? a.scale * gl0 * d0 : 0.f);
-        __stcs(g0 + plane + i, m1 != 0.f ? a.scale * gl1 * d1 : 0.f);
-        __stcs(g0 + 2 * plane + i, m2 != 0.f ? a.scale * gl2 * d2 : 0.f);
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
+             i += (long long)G * blockDim.x) {
+            const float r0 = __ldcs(x0 + i), r1 = __ldcs(x0 + plane + i), r2 = __ldcs(x0 + 2 * plane + i);
+            const float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
+            chk_x = fmaf(r0, 0.f, fmaf(r1, 0.f, fmaf(r2, 0.f, chk_x)));
+            chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
+            float q0, q1, q2;
+            acc += de_grad_pixel<float>(a, r0, r1, r2, t0, t1, t2, q0, q1, q2);
+            __stcs(g0 + i, q0);
+            __stcs(g0 + plane + i, q1);
+            __stcs(g0 + 2 * plane + i, q2);
+        }
     }
     const double bs = block_sum<double>((double)acc, red);
     int flag = 0;
@@ -702,9 +516,12 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
     a.eps = desc->eps; a.scale = grad_scale;
     a.x = x; a.y = y; a.out_sum = out_sum; a.out_grad = out_grad; a.out_flags = out_flags;
     const long long plane = (long long)desc->h * desc->w;
-    static const int occ = resident_blocks(deltae_loss_grad_kernel, 256);
-    int G = kNumSM * occ / desc->n;  // one wave: the training-size batches gain nothing from more, the hybrid step loses
-    const long long maxg = (plane + 255) / 256;
+    const bool vec = (plane & 3) == 0 && aligned16(x) && aligned16(y) && aligned16(out_grad);
+    static const int occ_v = resident_blocks(deltae_loss_grad_kernel<true>, 256);
+    static const int occ_s = resident_blocks(deltae_loss_grad_kernel<false>, 256);
+    const int occ = vec ? occ_v : occ_s;
+    int G = kNumSM * occ * LLIE_DEGRAD_WAVES / desc->n;
+    const long long maxg = ((vec ? plane / 4 : plane) + 255) / 256;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;
     Workspace ws(workspace);
@@ -714,7 +531,10 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
     a.pflag = reinterpret_cast<int *>(ws.scratch + slots * sizeof(double));
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
-    deltae_loss_grad_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    if (vec)
+        deltae_loss_grad_kernel<true><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    else
+        deltae_loss_grad_kernel<false><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
@@ -722,7 +542,7 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
 namespace llie {
 __global__ void srgb_to_linear_kernel(const float *in, float *out, long long n) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
-        out[i] = srgb_to_linear(in[i]);
+        out[i] = dem::srgb_to_linear<float>(in[i]);
 }
 }  // namespace llie
 

@@ -113,7 +113,7 @@ def main():
             print(name, out[name], flush=True)
 
         de, ss = DeltaE00Loss(), SSIMLoss()
-        hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, check_finite=False)
+        hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, check_finite=False, perceptual_module=False)
 
         def run(mod):
             def f(i):

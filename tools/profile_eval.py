@@ -22,7 +22,7 @@ n = 16
 B = torch.rand(n, 3, 512, 512, device=dev)
 x = (B + 0.05 * torch.randn_like(B)).clamp(0, 1).requires_grad_(True)
 kern = torch.tensor([[.01, .02, .01], [.02, .88, .02], [.01, .02, .01]], device=dev).view(1, 1, 3, 3)
-hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern)
+hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, perceptual_module=False)
 for _ in range(2):
     tot, logs = hyb(Bhat_raw=x, B_raw=B, A_raw=B * 0.9, expo_ratio=torch.ones(n, 1, 1, 1, device=dev), Bhat_srgb01=x,
                     B_srgb01=B)

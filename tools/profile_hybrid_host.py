@@ -14,7 +14,7 @@ xs = [(B + 0.05 * torch.randn_like(B)).clamp(0, 1) for _ in range(4)]
 A = (B * 0.9).contiguous()
 rho = torch.ones(n, 1, 1, 1, device=dev)
 kern = torch.tensor([[.01, .02, .01], [.02, .88, .02], [.01, .02, .01]], device=dev).view(1, 1, 3, 3).repeat(3, 1, 1, 1)
-hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, check_finite=False)
+hyb = HybridLossPlus(device="cuda", w_phys=0.05, physics_kernel=kern, check_finite=False, perceptual_module=False)
 
 
 def step(i):

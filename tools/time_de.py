@@ -15,4 +15,14 @@ def lg(i):
 
 
 tg = bench.timed_warm(lg, 30, dev) / 30
+xo = [torch.rand(16, 3, 511, 513, device=dev) for _ in range(6)]    # odd plane: the one-pixel-per-thread kernels
+
+
+def lgo(i):
+    a = xo[i % 3].requires_grad_(True)
+    Fn.DeltaE00LossFn.apply(a, xo[3 + i % 3], 1e-12)
+
+
+tgo = bench.timed_warm(lgo, 30, dev) / 30
+print(f"loss_grad scalar path (16x3x511x513) {tgo*1e3:.1f} us")
 print(f"deltae {t*1e3:.1f} us  all4 {ta*1e3:.1f} us  loss_grad {tg*1e3:.1f} us")
