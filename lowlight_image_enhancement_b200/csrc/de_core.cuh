@@ -181,8 +181,9 @@ struct DeConsts {
 // VARIANT 0: metrics/color_error.py:105-210 (eps inside sqrt / denominators, hue in (-pi, pi], sin(2 dtheta),
 //            clamp >= 0 under the final sqrt);  VARIANT 1: NewBP_model/losses.py:99-136 (eps = 1e-6 inside every
 //            sqrt and under the final sqrt, hue in [0, 2 pi), sin(dtheta), plain divisions by S_L, S_C, S_H)
+// Chroma / hue part: Q = (dC' / (kC S_C))^2 + (dH' / (kH S_H))^2 + R_T (dC' / ..)(dH' / ..) -- independent of L1, L2
 template <int VARIANT, class V>
-__device__ __forceinline__ V de00(V L1, V a1, V b1, V L2, V a2, V b2, const DeConsts k) {
+__device__ __forceinline__ V de00_chroma_hue(V a1, V b1, V a2, V b2, const DeConsts k) {
     const V eps = cst<V>(k.eps);
     const float k25 = 6103515625.0f;
     const V c1 = vsqrt0(fma_(a1, a1, fma_(b1, b1, eps))), c2 = vsqrt0(fma_(a2, a2, fma_(b2, b2, eps)));
@@ -200,7 +201,7 @@ __device__ __forceinline__ V de00(V L1, V a1, V b1, V L2, V a2, V b2, const DeCo
     const auto chro1 = m_gt(n1, zero), chro2 = m_gt(n2, zero);
     const V u1x = vsel(chro1, a1p * r1, cst<V>(1.0f)), u1y = vsel(chro1, b1 * r1, zero);
     const V u2x = vsel(chro2, a2p * r2, cst<V>(1.0f)), u2y = vsel(chro2, b2 * r2, zero);
-    const V dL = L2 - L1, dC = c2p - c1p;
+    const V dC = c2p - c1p;
     // signed half-angle sine and mean-hue direction from w = u1 + u2 (|w| = 2 |cos(dh / 2)|) and d = u2 - u1
     // (|d| = 2 |sin(dh / 2)|, |w|^2 + |d|^2 = 4).  The larger of the two carries the precision:
     //   hues less than a right angle apart: sin(dh / 2) = sin(dh) / (2 cos(dh / 2)) = -s / |w|,  direction = w
@@ -231,29 +232,41 @@ __device__ __forceinline__ V de00(V L1, V a1, V b1, V L2, V a2, V b2, const DeCo
                                       : m_and(mixed, m_or(m_and(neg2, spos), m_and(neg1, sneg)));
     const auto lift = VARIANT == 0 ? m_and(crosses, m_neg(th)) : m_and(m_not(crosses), m_neg(th));
     const V hb = vsel(lift, th + 2.0f * kPiF, th);
-    const V Lb = cst<V>(0.5f) * (L1 + L2), Cb = cst<V>(0.5f) * (c1p + c2p);
+    const V Cb = cst<V>(0.5f) * (c1p + c2p);
     const V q = fmac(hb, 180.0f / (kPiF * 25.0f), -11.0f);   // (deg(hbar) - 275) / 25
     const V ex = vex2(q * q * cst<V>(-1.4426950408889634f));
     const V Cb7 = pow7(Cb);
     const V rc = cst<V>(2.0f) * vsqrt0(Cb7 * vrcp0(Cb7 + k25));
     const V rt = VARIANT == 0 ? -(sin_small(cst<V>(kPiF / 3.0f) * ex) * rc)      // -sin(2 dtheta) RC
                               : -(sin_small(cst<V>(kPiF / 6.0f) * ex) * rc);     // -sin(dtheta) RC
-    const V l50 = (Lb - 50.0f) * (Lb - 50.0f);
-    const V sL = fma_(cst<V>(0.015f) * l50, vrsqrt0(l50 + 20.0f + eps), cst<V>(1.0f));
     const V sC = fmac(Cb, 0.045f, 1.0f);
     const V sH = fma_(cst<V>(0.015f) * Cb, T, cst<V>(1.0f));
-    V lt, ct, ht;
+    V ct, ht;
     if (VARIANT == 0) {
-        lt = dL * rcp_n(fmav(sL, k.kL, eps));
         ct = dC * rcp_n(fmav(sC, k.kC, eps));
         ht = dH * rcp_n(fmav(sH, k.kH, eps));
     } else {
-        lt = dL * rcp_n(sL);
         ct = dC * rcp_n(sC);
         ht = dH * rcp_n(sH);
     }
-    const V sum = fma_(lt, lt, fma_(ct, ct, fma_(ht, ht, rt * ct * ht)));
-    return VARIANT == 0 ? vsqrt0(vmax(sum, zero)) : vsqrt0(sum + eps);
+    return fma_(ct, ct, fma_(ht, ht, rt * ct * ht));
+}
+
+// Lightness part: dL' / (kL S_L)
+template <int VARIANT, class V>
+__device__ __forceinline__ V de00_lightness(V L1, V L2, const DeConsts k) {
+    const V eps = cst<V>(k.eps);
+    const V dL = L2 - L1, Lb = cst<V>(0.5f) * (L1 + L2);
+    const V l50 = (Lb - 50.0f) * (Lb - 50.0f);
+    const V sL = fma_(cst<V>(0.015f) * l50, vrsqrt0(l50 + 20.0f + eps), cst<V>(1.0f));
+    return VARIANT == 0 ? dL * rcp_n(fmav(sL, k.kL, eps)) : dL * rcp_n(sL);
+}
+
+template <int VARIANT, class V>
+__device__ __forceinline__ V de00(V L1, V a1, V b1, V L2, V a2, V b2, const DeConsts k) {
+    const V lt = de00_lightness<VARIANT>(L1, L2, k);
+    const V sum = fma_(lt, lt, de00_chroma_hue<VARIANT>(a1, b1, a2, b2, k));
+    return VARIANT == 0 ? vsqrt0(vmax(sum, cst<V>(0.0f))) : vsqrt0(sum + cst<V>(k.eps));
 }
 
 }  // namespace dem

@@ -195,7 +195,8 @@ struct DeGradArgs {
 template <class S>
 __device__ __forceinline__ S de_grad_pixel(const DeGradArgs &a, S r0, S r1, S r2, S t0, S t1, S t2, S &g0, S &g1, S &g2) {
     using namespace dem;
-    using D = Dual3<S>;
+    using D2 = Dual<S, 2>;
+    using D1 = Dual<S, 1>;
     S p0 = r0, p1 = r1, p2 = r2;
     const S zero = cst<S>(0.f), one = cst<S>(1.f);
     auto m0 = m_ge(one, zero), m1 = m0, m2 = m0;  // clamp pass-through masks (ATen: min <= x <= max), all true
@@ -222,12 +223,21 @@ __device__ __forceinline__ S de_grad_pixel(const DeGradArgs &a, S r0, S r1, S r2
     const S Z2 = fmav(k2, 0.950227f, fmav(k1, 0.119193f, cst<S>(0.019334f) * k0));
     const S fx2 = lab_f_d(DEM_DIVC(X2, 0.95047f), e0), fy2 = lab_f_d(Y2, e1), fz2 = lab_f_d(DEM_DIVC(Z2, 1.08883f), e2);
     const S L2 = fmac(fy2, 116.0f, -16.0f), A2 = cst<S>(500.0f) * (fx2 - fy2), B2 = cst<S>(200.0f) * (fy2 - fz2);
-    const D de = de00<1>(D{L1, one, zero, zero}, D{A1, zero, one, zero}, D{B1, zero, zero, one}, dual_const<S>(L2),
-                         dual_const<S>(A2), dual_const<S>(B2), DeConsts{1.f, 1.f, 1.f, a.eps});
+    // dE = sqrt(lt^2 + Q + eps): Q (chroma / hue) with tangents (d/da1, d/db1), lt (lightness) with d/dL1
+    const DeConsts kc{1.f, 1.f, 1.f, a.eps};
+    const D2 Q = de00_chroma_hue<1>(dual_var<S, 2>(A1, 0), dual_var<S, 2>(B1, 1), dual_const<S, 2>(A2),
+                                    dual_const<S, 2>(B2), kc);
+    const D1 lt = de00_lightness<1>(dual_var<S, 1>(L1, 0), dual_const<S, 1>(L2), kc);
+    const S sum = fma_(lt.v, lt.v, Q.v) + a.eps;
+    const S rE = vrsqrt0(sum);
+    const S E0 = sum * rE;
+    const S dE = fma_(fma_(-E0, E0, sum), cst<S>(0.5f) * rE, E0);     // sqrt(sum), Newton-refined
+    const S hE = cst<S>(0.5f) * rE;                                    // 1 / (2 sqrt(sum))
+    const S deL = cst<S>(2.0f) * lt.v * lt.t[0] * hE, deA = Q.t[0] * hE, deB = Q.t[1] * hE;
     // reverse through Lab -> f -> XYZ -> linear -> sRGB
-    const S gfx = cst<S>(500.0f) * de.y;
-    const S gfy = fmav(de.z, 200.0f, fmav(de.y, -500.0f, cst<S>(116.0f) * de.x));
-    const S gfz = cst<S>(-200.0f) * de.z;
+    const S gfx = cst<S>(500.0f) * deA;
+    const S gfy = fmav(deB, 200.0f, fmav(deA, -500.0f, cst<S>(116.0f) * deL));
+    const S gfz = cst<S>(-200.0f) * deB;
     const S gX = DEM_DIVC(gfx * dfx, 0.95047f), gY = gfy * dfy, gZ = DEM_DIVC(gfz * dfz, 1.08883f);
     const S gl0 = fmav(gZ, 0.019334f, fmav(gY, 0.212671f, cst<S>(0.412453f) * gX));
     const S gl1 = fmav(gZ, 0.119193f, fmav(gY, 0.715160f, cst<S>(0.357580f) * gX));
@@ -237,12 +247,14 @@ __device__ __forceinline__ S de_grad_pixel(const DeGradArgs &a, S r0, S r1, S r2
     g0 = vsel(m0, sc * gl0 * d0, zero);
     g1 = vsel(m1, sc * gl1 * d1, zero);
     g2 = vsel(m2, sc * gl2 * d2, zero);
-    return de.v;
+    return dE;
 }
 
-// losses.py:138-143 value (per-image sums) + `scale` * d dE / d x, one pass.  VEC: 4 pixels per thread and step
-// (128-bit loads / stores, two packed-pair dual evaluations); needs plane % 4 == 0 and 16-byte aligned tensors.
-template <bool VEC>
+// losses.py:138-143 value (per-image sums) + `scale` * d dE / d x, one pass, one pixel per thread and step in scalar
+// FP32.  The dual arithmetic is bound by the FP32 pipe itself (68 % pipe-active, 50 % issue-active in ncu): FFMA2
+// issues at half rate, so packing two pixels per thread saves issue slots this kernel is not short of and costs
+// occupancy (174 vs 75 registers: 184 vs 175 us at 16x3x512x512; four scalar pixels per thread behind 128-bit loads:
+// 104 registers, 180 us).
 __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs a) {
     __shared__ double red[32];
     const int n = blockIdx.y, G = gridDim.x;
@@ -250,44 +262,16 @@ __global__ void __launch_bounds__(256) deltae_loss_grad_kernel(const DeGradArgs 
     const float *x0 = a.x + (long long)n * 3 * plane, *y0 = a.y + (long long)n * 3 * plane;
     float *g0 = a.out_grad + (long long)n * 3 * plane;
     float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
-    if (VEC) {
-        using dem::F2;
-        const long long groups = plane >> 2;
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (long long)G * blockDim.x) {
-            float4 p[3], t[3];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                p[c] = __ldcs(reinterpret_cast<const float4 *>(x0 + c * plane) + i);
-                t[c] = __ldcs(reinterpret_cast<const float4 *>(y0 + c * plane) + i);
-                chk_x = fmaf(p[c].x, 0.f, fmaf(p[c].y, 0.f, fmaf(p[c].z, 0.f, fmaf(p[c].w, 0.f, chk_x))));
-                chk_y = fmaf(t[c].x, 0.f, fmaf(t[c].y, 0.f, fmaf(t[c].z, 0.f, fmaf(t[c].w, 0.f, chk_y))));
-            }
-            F2 ga[3], gb[3];
-            const F2 da = de_grad_pixel<F2>(a, dem::f2(p[0].x, p[0].y), dem::f2(p[1].x, p[1].y), dem::f2(p[2].x, p[2].y),
-                                            dem::f2(t[0].x, t[0].y), dem::f2(t[1].x, t[1].y), dem::f2(t[2].x, t[2].y),
-                                            ga[0], ga[1], ga[2]);
-            const F2 db = de_grad_pixel<F2>(a, dem::f2(p[0].z, p[0].w), dem::f2(p[1].z, p[1].w), dem::f2(p[2].z, p[2].w),
-                                            dem::f2(t[0].z, t[0].w), dem::f2(t[1].z, t[1].w), dem::f2(t[2].z, t[2].w),
-                                            gb[0], gb[1], gb[2]);
-            acc += (dem::lo(da) + dem::hi(da)) + (dem::lo(db) + dem::hi(db));
-#pragma unroll
-            for (int c = 0; c < 3; ++c)
-                __stcs(reinterpret_cast<float4 *>(g0 + c * plane) + i,
-                       make_float4(dem::lo(ga[c]), dem::hi(ga[c]), dem::lo(gb[c]), dem::hi(gb[c])));
-        }
-    } else {
-        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane;
-             i += (long long)G * blockDim.x) {
-            const float r0 = __ldcs(x0 + i), r1 = __ldcs(x0 + plane + i), r2 = __ldcs(x0 + 2 * plane + i);
-            const float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
-            chk_x = fmaf(r0, 0.f, fmaf(r1, 0.f, fmaf(r2, 0.f, chk_x)));
-            chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
-            float q0, q1, q2;
-            acc += de_grad_pixel<float>(a, r0, r1, r2, t0, t1, t2, q0, q1, q2);
-            __stcs(g0 + i, q0);
-            __stcs(g0 + plane + i, q1);
-            __stcs(g0 + 2 * plane + i, q2);
-        }
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane; i += (long long)G * blockDim.x) {
+        const float r0 = __ldcs(x0 + i), r1 = __ldcs(x0 + plane + i), r2 = __ldcs(x0 + 2 * plane + i);
+        const float t0 = __ldcs(y0 + i), t1 = __ldcs(y0 + plane + i), t2 = __ldcs(y0 + 2 * plane + i);
+        chk_x = fmaf(r0, 0.f, fmaf(r1, 0.f, fmaf(r2, 0.f, chk_x)));
+        chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
+        float q0, q1, q2;
+        acc += de_grad_pixel<float>(a, r0, r1, r2, t0, t1, t2, q0, q1, q2);
+        __stcs(g0 + i, q0);
+        __stcs(g0 + plane + i, q1);
+        __stcs(g0 + 2 * plane + i, q2);
     }
     const double bs = block_sum<double>((double)acc, red);
     int flag = 0;
@@ -516,12 +500,9 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
     a.eps = desc->eps; a.scale = grad_scale;
     a.x = x; a.y = y; a.out_sum = out_sum; a.out_grad = out_grad; a.out_flags = out_flags;
     const long long plane = (long long)desc->h * desc->w;
-    const bool vec = (plane & 3) == 0 && aligned16(x) && aligned16(y) && aligned16(out_grad);
-    static const int occ_v = resident_blocks(deltae_loss_grad_kernel<true>, 256);
-    static const int occ_s = resident_blocks(deltae_loss_grad_kernel<false>, 256);
-    const int occ = vec ? occ_v : occ_s;
+    static const int occ = resident_blocks(deltae_loss_grad_kernel, 256);
     int G = kNumSM * occ * LLIE_DEGRAD_WAVES / desc->n;
-    const long long maxg = ((vec ? plane / 4 : plane) + 255) / 256;
+    const long long maxg = (plane + 255) / 256;
     if (G > maxg) G = (int)maxg;
     if (G < 1) G = 1;
     Workspace ws(workspace);
@@ -531,10 +512,7 @@ extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *
     a.pflag = reinterpret_cast<int *>(ws.scratch + slots * sizeof(double));
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
-    if (vec)
-        deltae_loss_grad_kernel<true><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
-    else
-        deltae_loss_grad_kernel<false><<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    deltae_loss_grad_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
