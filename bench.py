@@ -323,7 +323,7 @@ def run_ours(args, rank, world, dev):
     clk.__enter__()
     clk.load.set()
     # Headline = the DEFAULT launch mode of the product (what phys_cons_raw, the loss classes and autograd run): every
-    # launch is ordered after the previous grid.  The stream-overlap contract (LLIE_TUNE_PHYS_OVERLAP, loops over
+    # launch is ordered after the previous grid.  The stream-overlap contract (llie_phys_desc.stream_overlap, loops over
     # independent batches only) is measured next to it and reported as `stream_overlap`, not as `value`.
     # (the flag is a kernel argument: frozen into a graph at capture time)
     g_step = GraphLoop(step, K, dev)
@@ -342,13 +342,10 @@ def run_ours(args, rank, world, dev):
     launches = (2 if args.two_pass else 1) * K * rounds
     overlap = None
     if not (args.no_overlap or args.no_pdl):
-        Fn.phys_stream_overlap(True)
-        try:
+        with Fn.phys_stream_overlap():  # per-call promise, scoped: everything outside this block is default mode
             g_o = GraphLoop(fused, K, dev)
             overlap = g_o.per_step(K, 50.0, 5)[0]
             del g_o
-        finally:
-            Fn.phys_stream_overlap(False)  # everything below (autograd e2e leg, eval, losses) is default mode
     if world > 1:
         t = torch.tensor([ms_step], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -438,7 +435,7 @@ def run_ours(args, rank, world, dev):
                      "traffic_source": traffic_src, "peak_source": peak_src, "algorithmic_bytes_per_launch": bytes_b,
                      "us_per_launch": round(roof["us"] * 1e3, 2), "launch_mode": "default (serialised)"},
         "stream_overlap": (None if overlap is None else {
-            "contract": "LLIE_TUNE_PHYS_OVERLAP: loops over independent batches only (never under autograd)",
+            "contract": "llie_phys_desc.stream_overlap, per call: loops over independent batches only (never under autograd)",
             "us_per_launch": round(overlap * 1e3, 2), "value": round(world * mpix / (overlap / 1e3), 1), "unit": "Mpix/s",
             "frac": round(bytes_b / (overlap * 1e-3) / 1e9 / peak, 4)}),
         "kernels": [

@@ -53,23 +53,19 @@ size_t llie_workspace_bytes(void);
 /* 0 if the current device is compute capability 10.x, else LLIE_ENOSM100 */
 int llie_check_device(void);
 
-/* Diagnostic knobs for A/B measurements (process-wide, not thread-safe; defaults are the product). */
-#define LLIE_TUNE_PHYS_PATH 1 /* 0 TMA row ring (default) | 1 TMA tile ring | 2 generic only | 3 register prefetch */
-#define LLIE_TUNE_PHYS_ROWS 2 /* rows per warp chunk of the rolling path; 0 = heuristic */
+/* Diagnostic knobs for A/B measurements.  Process-wide (relaxed atomics: setting one while another thread launches is
+ * not a data race, but it does change that thread's kernel choice); the defaults are the product and no product code
+ * path sets them.  Anything a caller may legitimately vary per call is a descriptor field, not a knob
+ * (llie_phys_desc.stream_overlap). */
+#define LLIE_TUNE_PHYS_PATH 1 /* 0 TMA row ring (default) | 2 generic kernels only */
+#define LLIE_TUNE_PHYS_ROWS 2 /* rows per item of the row-ring kernels; 0 = heuristic */
 #define LLIE_TUNE_SSIM_PATH 3 /* 0 auto (TMA row ring + packed FP32 kernel for statistics-only / loss-forward 11-tap
                                  calls, else the one-column streaming kernel) | 1 shared-memory tile kernel |
                                  2 one-column streaming | 3 two-column cp.async streaming kernel (round-1 default) */
 #define LLIE_TUNE_SSIM_SEG_ROWS 4 /* output rows per CTA of the streaming SSIM kernel; 0 = heuristic */
 #define LLIE_TUNE_PHYS_PDL 5 /* 1 (default): ring kernels are launched with programmatic stream serialization, so the
                                 prologue of a kernel overlaps the tail of the previous one | 0 plain launches */
-#define LLIE_TUNE_PHYS_OVERLAP 6 /* 0 (default) | 1: stream-overlap CONTRACT for loops of phys calls over independent
-                                    batches (dataset evaluation, benchmarks): the caller guarantees that the kernel
-                                    launched right before a phys call on the same stream writes none of the call's
-                                    buffers pred, obs, psf, rho, gout, grad, map and reads none of grad / map (the small
-                                    outputs out_mean / out_sum / out_flags are written after the wait and may be shared).  The ring kernels then wait for
-                                    the previous grid only before they touch the shared workspace, so launch i + 1 streams
-                                    and computes on the SMs the early finishers of launch i have left.  Never set it under
-                                    autograd (gout comes from the previous kernel). */
+/* key 6 (process-wide stream overlap, ABI 2) is gone: llie_phys_desc.stream_overlap */
 int llie_tune(int key, int value);
 
 /* ------------------------------------------------------------------------
@@ -89,6 +85,14 @@ typedef struct llie_phys_desc {
     int32_t rho_side;       /* 0: rho multiplies K*pred (metric)  1: rho multiplies obs (loss) */
     int32_t clip_y;         /* clamp sY*(K*pred) to [0,1] */
     int32_t clip_a;         /* clamp sA*obs to [0,1] */
+    int32_t stream_overlap; /* 0 (default) | 1: PER-CALL stream-overlap contract for loops of phys calls over independent
+                               batches (dataset evaluation, benchmarks).  The caller guarantees that the kernel launched
+                               right before this call on the same stream writes none of the call's buffers pred, obs,
+                               psf, rho, gout, grad, map and reads none of grad / map (out_mean / out_sum / out_flags
+                               are written after the wait and may be shared).  The row-ring kernels then wait for the
+                               previous grid only before they touch the shared workspace, so this launch streams and
+                               computes on the SMs the early finishers of the previous one have left.  Never set it
+                               under autograd (gout comes from the previous kernel).  Ignored by the generic kernels. */
     float eps;
     float rho_scalar;       /* used when rho == NULL */
     /* element strides of the rho tensor for (n, c, y, x); 0 = broadcast */
@@ -212,7 +216,7 @@ int llie_psnr_stats_static(const llie_psnr_desc *desc, const void *x, const void
  * csrc/ssim_ring.cu) take the taps by value in their kernel parameters; without it the call runs on the kernels that
  * read the device copy (same results to rounding).
  * ------------------------------------------------------------------------ */
-#define LLIE_SSIM_MAX_K 15
+#define LLIE_SSIM_MAX_K 63 /* 1..15 taps: unrolled kernels; 17..63: the runtime-window instantiation of the tile kernels */
 typedef struct llie_ssim_desc {
     int32_t n, c, h, w;   /* c = channels of the input tensors */
     int32_t ksize;        /* odd, <= LLIE_SSIM_MAX_K, <= min(h, w) */

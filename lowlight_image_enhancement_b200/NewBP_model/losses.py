@@ -194,8 +194,8 @@ class SSIMLoss(nn.Module):
         super().__init__()
         if window_size <= 0 or window_size % 2 == 0:
             raise ValueError(f"window_size must be a positive odd integer; received {window_size}.")
-        if window_size > 15:
-            raise NotImplementedError("the CUDA SSIM kernels support odd windows up to 15")
+        if window_size > nat.SSIM_MAX_K:
+            raise NotImplementedError(f"the CUDA SSIM kernels take odd windows up to {nat.SSIM_MAX_K}")
         if reduction not in ("mean", "sum", "none"):
             raise ValueError(f"Invalid reduction option: {reduction}")
         self.window_size, self.max_val, self.reduction = int(window_size), float(max_val), reduction

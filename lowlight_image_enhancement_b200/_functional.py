@@ -6,6 +6,8 @@ No arithmetic on image-sized tensors happens in Python.
 """
 from __future__ import annotations
 
+import contextlib
+import threading
 import warnings
 from dataclasses import dataclass
 from typing import Optional, Tuple
@@ -152,7 +154,8 @@ class PhysCfg:
 def _desc(cfg: PhysCfg, pred: Tensor, c_out: int, psf: PreparedPSF, rho_scalar: float, strides) -> nat.PhysDesc:
     n, c_in, h, w = pred.shape
     return nat.PhysDesc(n, c_in, c_out, h, w, psf.kh, psf.kw, psf.layout, cfg.pad_mode, int(cfg.crop_valid),
-                        int(cfg.robust), cfg.rho_side, int(cfg.clip_y), int(cfg.clip_a), cfg.eps, rho_scalar,
+                        int(cfg.robust), cfg.rho_side, int(cfg.clip_y), int(cfg.clip_a),
+                        1 if getattr(_overlap_scope, "on", False) else 0, cfg.eps, rho_scalar,
                         strides[0], strides[1], strides[2], strides[3])
 
 
@@ -221,10 +224,22 @@ def phys_value_and_grad(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t, rho_
     return buf[: n + 2], flags, grad
 
 
-def phys_stream_overlap(enabled: bool) -> None:
-    """Process-wide stream-overlap contract of the phys ring kernels (LLIE_TUNE_PHYS_OVERLAP, include/llie_b200.h):
-    enable only around loops of phys calls over independent buffers, never under autograd."""
-    nat.check(nat.lib().llie_tune(6, 1 if enabled else 0), "llie_tune")
+_overlap_scope = threading.local()
+
+
+@contextlib.contextmanager
+def phys_stream_overlap():
+    """Scope in which every phys call of THIS thread carries llie_phys_desc.stream_overlap = 1 (include/llie_b200.h):
+    the caller promises that consecutive phys launches on the stream work on independent buffers (dataset loops,
+    benchmarks), so launch i + 1 may start under the tail of launch i.  Per call and per thread by construction:
+    nothing outside the `with` block is affected, and autograd backward passes, which run on the engine's own
+    threads, never see it (their upstream gradient comes from the previous kernel, which the contract forbids)."""
+    prev = getattr(_overlap_scope, "on", False)
+    _overlap_scope.on = True
+    try:
+        yield
+    finally:
+        _overlap_scope.on = prev
 
 
 class PhysProjector(torch.autograd.Function):

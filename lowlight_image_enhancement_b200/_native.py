@@ -28,7 +28,7 @@ class PhysDesc(C.Structure):
         ("n", C.c_int32), ("c_in", C.c_int32), ("c_out", C.c_int32), ("h", C.c_int32), ("w", C.c_int32),
         ("kh", C.c_int32), ("kw", C.c_int32), ("psf_layout", C.c_int32), ("pad_mode", C.c_int32),
         ("crop_valid", C.c_int32), ("robust", C.c_int32), ("rho_side", C.c_int32), ("clip_y", C.c_int32),
-        ("clip_a", C.c_int32), ("eps", C.c_float), ("rho_scalar", C.c_float),
+        ("clip_a", C.c_int32), ("stream_overlap", C.c_int32), ("eps", C.c_float), ("rho_scalar", C.c_float),
         ("rho_sn", C.c_int64), ("rho_sc", C.c_int64), ("rho_sh", C.c_int64), ("rho_sw", C.c_int64),
     ]
 
@@ -76,6 +76,7 @@ class SelectDesc(C.Structure):
     _fields_ = [("images", C.c_int32), ("per_image", C.c_int64), ("nq", C.c_int32), ("joint", C.c_int32)]
 
 
+SSIM_MAX_K = 63  # LLIE_SSIM_MAX_K (include/llie_b200.h)
 PAD = {"zeros": 0, "constant": 0, "reflect": 1, "replicate": 2, "circular": 3}
 
 _VP = C.c_void_p

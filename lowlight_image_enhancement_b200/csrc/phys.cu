@@ -8,10 +8,11 @@
 // and the residual derivative + conv_transpose2d adjoint (newbp_layer.py:16-21) into one backward pass.
 //
 // Two code paths, both parity-tested:
-//   * tile path    depthwise 3x3, W % 4 == 0, 16-byte aligned planes: shared-memory halo tiles
-//                  (128-float rows, 128-bit LDS, rolling 3-row register window), HBM-bound.
-//   * generic path any kh x kw, dense cross-channel PSFs, arbitrary W / alignment / rho strides.
+//   * row ring     (phys_ring.cu) depthwise 3x3, W % 4 == 0, 16-byte aligned planes: persistent CTAs stream rows
+//                  through a TMA ring in shared memory, HBM-bound.
+//   * generic path (this file) any kh x kw, dense cross-channel PSFs, arbitrary W / alignment / rho strides.
 #include "phys_common.cuh"
+#include <atomic>
 
 namespace llie {
 
@@ -211,7 +212,8 @@ static int grid_x_for(int n, int work_items) {
 
 void ssim_tune(int key, int value);  // ssim.cu
 
-int g_phys_path = 0;  // 0 TMA row ring (default), 1 TMA tile ring, 2 generic only, 3 register prefetch (llie_tune)
+static std::atomic<int> g_phys_path{0};  // 0 TMA row ring (default) | 2 generic kernels only (llie_tune, diagnostic)
+static inline bool ring_enabled() { return g_phys_path.load(std::memory_order_relaxed) == 0; }
 
 }  // namespace llie
 
@@ -219,10 +221,19 @@ using namespace llie;
 
 extern "C" int llie_tune(int key, int value) {
     switch (key) {
-        case LLIE_TUNE_PHYS_PATH: g_phys_path = value; return LLIE_OK;
-        case LLIE_TUNE_PHYS_ROWS: phys_roll_set_rows(value); phys_ring_set_rows(value); return LLIE_OK;
+        case LLIE_TUNE_PHYS_PATH:
+            if (value != 0 && value != 2) {
+                llie::set_error("llie_tune: LLIE_TUNE_PHYS_PATH takes 0 (row ring) or 2 (generic kernels), got %d", value);
+                return LLIE_EINVAL;
+            }
+            g_phys_path.store(value, std::memory_order_relaxed);
+            return LLIE_OK;
+        case LLIE_TUNE_PHYS_ROWS: phys_ring_set_rows(value); return LLIE_OK;
         case LLIE_TUNE_PHYS_PDL: phys_ring_set_pdl(value); return LLIE_OK;
-        case LLIE_TUNE_PHYS_OVERLAP: phys_ring_set_overlap(value); return LLIE_OK;
+        case 6:
+            llie::set_error("llie_tune: key 6 (process-wide stream overlap) was removed in ABI 3; set "
+                            "llie_phys_desc.stream_overlap on the calls that meet the contract");
+            return LLIE_EINVAL;
         case LLIE_TUNE_SSIM_PATH:
         case LLIE_TUNE_SSIM_SEG_ROWS: ssim_tune(key, value); return LLIE_OK;
         default: break;
@@ -244,9 +255,7 @@ extern "C" int llie_phys_forward(const llie_phys_desc *desc, const float *pred, 
     Workspace ws(workspace);
     a.ticket = ws.tickets;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (g_phys_path == 0 && phys_ring_eligible(a)) return launch_phys_fwd_ring(a, workspace, st);
-    if (g_phys_path == 3 && phys_roll_eligible(a)) return launch_phys_fwd_roll(a, workspace, st);
-    if (g_phys_path == 1 && phys_tma_eligible(a)) return launch_phys_fwd_tma(a, workspace, st);
+    if (ring_enabled() && phys_ring_eligible(a)) return launch_phys_fwd_ring(a, workspace, st);
     long long items = (long long)desc->c_out * desc->h * desc->w;
     const int gx = grid_x_for(desc->n, (int)((items + 255) / 256));
     const size_t need = (size_t)desc->n * gx * (sizeof(double) + sizeof(int));
@@ -265,10 +274,7 @@ extern "C" int llie_phys_backward_needs_scratch(const llie_phys_desc *desc, cons
     PhysArgs a{};
     a.d = *desc;
     a.pred = pred; a.obs = obs; a.rho = rho;
-    if (g_phys_path == 0) return (phys_ring_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
-    if (g_phys_path == 3) return (phys_roll_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
-    if (g_phys_path == 1) return (phys_tma_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
-    return 1;
+    return (ring_enabled() && phys_ring_eligible(a) && aligned16(grad_pred)) ? 0 : 1;
 }
 
 extern "C" int llie_phys_backward(const llie_phys_desc *desc, const float *pred, const float *obs, const float *psf,
@@ -283,12 +289,8 @@ extern "C" int llie_phys_backward(const llie_phys_desc *desc, const float *pred,
     a.grad = grad_pred; a.scratch = scratch;
     fill_domain(a);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (g_phys_path == 0 && phys_ring_eligible(a) && aligned16(grad_pred)) {
+    if (ring_enabled() && phys_ring_eligible(a) && aligned16(grad_pred)) {
         return launch_phys_bwd_ring(a, st);
-    } else if (g_phys_path == 3 && phys_roll_eligible(a) && aligned16(grad_pred)) {
-        return launch_phys_bwd_roll(a, st);
-    } else if (g_phys_path == 1 && phys_tma_eligible(a) && aligned16(grad_pred)) {
-        return launch_phys_bwd_tma(a, nullptr, st);
     } else {
         LLIE_REQUIRE(scratch != nullptr, "phys_backward: this PSF/shape needs the scratch buffer");
         LLIE_REQUIRE(desc->kh / 2 <= 16 && desc->kw / 2 <= 16, "phys_backward: PSF larger than 33x33 unsupported");
@@ -317,7 +319,7 @@ extern "C" int llie_phys_value_and_grad(const llie_phys_desc *desc, const float 
     a.grad = grad_pred; a.scratch = scratch;
     a.out_mean = out_mean; a.out_sum = out_sum; a.out_map = nullptr; a.out_flags = out_flags;
     fill_domain(a);
-    if (g_phys_path == 0 && phys_ring_eligible(a) && aligned16(grad_pred))
+    if (ring_enabled() && phys_ring_eligible(a) && aligned16(grad_pred))
         return launch_phys_fused_ring(a, workspace, reinterpret_cast<cudaStream_t>(stream));
     // shapes the fused kernel does not take: the two single-purpose passes, same results
     if (int rc = llie_phys_forward(desc, pred, obs, psf, rho, out_mean, out_sum, nullptr, out_flags, workspace, stream))

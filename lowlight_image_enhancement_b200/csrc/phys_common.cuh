@@ -1,5 +1,5 @@
-// Shared declarations of the physics-consistency kernels (generic path in phys.cu, TMA tile path in
-// phys_tma.cu).
+// Shared declarations of the physics-consistency kernels (generic path in phys.cu, TMA row-ring path in
+// phys_ring.cu).
 #pragma once
 #include "common.cuh"
 
@@ -87,17 +87,5 @@ int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st);
 int launch_phys_fused_ring(PhysArgs &a, void *workspace, cudaStream_t st);
 void phys_ring_set_rows(int r);
 void phys_ring_set_pdl(int on);
-void phys_ring_set_overlap(int on);
-
-// register-rolling path (phys_roll.cu)
-bool phys_roll_eligible(const PhysArgs &a);
-int launch_phys_fwd_roll(PhysArgs &a, void *workspace, cudaStream_t st);
-int launch_phys_bwd_roll(PhysArgs &a, cudaStream_t st);
-void phys_roll_set_rows(int r);
-
-// tile path entry points (phys_tma.cu); return LLIE_OK or an error code
-bool phys_tma_eligible(const PhysArgs &a);
-int launch_phys_fwd_tma(PhysArgs &a, void *workspace, cudaStream_t st);
-int launch_phys_bwd_tma(PhysArgs &a, void *workspace, cudaStream_t st);
 
 }  // namespace llie

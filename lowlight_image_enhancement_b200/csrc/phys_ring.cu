@@ -24,6 +24,7 @@
 //             (mirror / edge fold) is applied in-register on the image-edge lanes and through two
 //             virtual rows on the first / last chunk of a plane.
 #include "phys_common.cuh"
+#include <atomic>
 #include <type_traits>
 
 #include "tma.cuh"
@@ -65,7 +66,7 @@ struct RingGeom {
     double *part;  // [items] per-item partial sums
     double *samp;  // [n] per-sample sums (finalize scratch)
     int *pflag;    // [gridDim.x]
-    int early;     // stream-overlap contract (LLIE_TUNE_PHYS_OVERLAP): only the workspace depends on the previous kernel
+    int early;     // stream-overlap contract (llie_phys_desc.stream_overlap): only the workspace depends on the previous kernel
 };
 
 struct Item {
@@ -794,16 +795,15 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
 // ------------------------------------------------------------------------------------------------
 // host
 // ------------------------------------------------------------------------------------------------
-static int g_ring_rows = 0;  // 0 = heuristic; set through llie_tune(LLIE_TUNE_PHYS_ROWS, r)
-void phys_ring_set_rows(int r) { g_ring_rows = r; }
-static int g_ring_pdl = 1;   // programmatic dependent launch of the ring kernels (llie_tune(LLIE_TUNE_PHYS_PDL, 0|1))
-void phys_ring_set_pdl(int on) { g_ring_pdl = on ? 1 : 0; }
-// stream-overlap contract (llie_tune(LLIE_TUNE_PHYS_OVERLAP, 1)): the caller guarantees that no buffer of a ring launch
-// except the workspace is read or written by the kernel launched right before it on the same stream.  The kernels then
-// wait for the previous grid only where they touch the workspace, so the CTAs of launch i + 1 stream and compute on
-// the SMs that the early finishers of launch i have left (and under its last-CTA finalize).
-static int g_ring_overlap = 0;
-void phys_ring_set_overlap(int on) { g_ring_overlap = on ? 1 : 0; }
+// Diagnostic knobs (llie_tune): relaxed atomics, so that a sweep thread and a launching thread never race on them.
+static std::atomic<int> g_ring_rows{0};  // 0 = heuristic (LLIE_TUNE_PHYS_ROWS)
+void phys_ring_set_rows(int r) { g_ring_rows.store(r, std::memory_order_relaxed); }
+static std::atomic<int> g_ring_pdl{1};   // programmatic dependent launch of the ring kernels (LLIE_TUNE_PHYS_PDL)
+void phys_ring_set_pdl(int on) { g_ring_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
+// Stream-overlap contract (llie_phys_desc.stream_overlap, a PER-CALL promise): no buffer of this ring launch except the
+// workspace is read or written by the kernel launched right before it on the same stream.  The kernels then wait for
+// the previous grid only where they touch the workspace, so the CTAs of launch i + 1 stream and compute on the SMs
+// that the early finishers of launch i have left (and under its last-CTA finalize).
 
 static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     RingGeom g{};
@@ -811,9 +811,10 @@ static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     const long long cols = (long long)d.n * d.c_out * g.groups;  // independent column strips
     const int slots = kNumSM * kCtasPerSM;
     int chunks;
-    const bool overlap = g_ring_pdl && g_ring_overlap;
-    if (g_ring_rows > 0) {
-        chunks = d.h / g_ring_rows;
+    const int tune_rows = g_ring_rows.load(std::memory_order_relaxed);
+    const bool overlap = g_ring_pdl.load(std::memory_order_relaxed) && d.stream_overlap != 0;
+    if (tune_rows > 0) {
+        chunks = d.h / tune_rows;
     } else if (overlap) {
         // stream-overlap loops: several launches are resident at once (launch i + 1 starts as soon as every CTA of
         // launch i has started), so the machine is filled ACROSS launches and a CTA should live long: ~128-row items
@@ -866,7 +867,7 @@ bool phys_ring_eligible(const PhysArgs &a) {
         cfg.stream = ST;                                                                                         \
         cudaLaunchAttribute attr[1];                                                                             \
         attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;                                         \
-        attr[0].val.programmaticStreamSerializationAllowed = g_ring_pdl;                                         \
+        attr[0].val.programmaticStreamSerializationAllowed = g_ring_pdl.load(std::memory_order_relaxed);                                         \
         cfg.attrs = attr;                                                                                        \
         cfg.numAttrs = 1;                                                                                        \
         LLIE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, __VA_ARGS__));                                               \

@@ -12,6 +12,7 @@
 // Roofline: this kernel is bound by the FP32 FMA pipe, not by HBM: 2 x 5 x K FMAs per element
 // (110 for K = 11) against 8 bytes of traffic (SSIM section).
 #include "common.cuh"
+#include <atomic>
 #include "ssim_common.cuh"
 
 namespace llie {
@@ -37,16 +38,21 @@ __device__ __forceinline__ float ssim_load(const SsimArgs &a, const float *base,
     return v;
 }
 
+// K > 0: window size known at compile time (taps in registers, fully unrolled passes).  K == 0: any odd window up to
+// LLIE_SSIM_MAX_K read from the descriptor (taps in shared memory, rolled loops) -- the windows above 15 taps that the
+// reference accepts but nobody trains with; same arithmetic, same summation order.
 template <int K>
-__global__ void __launch_bounds__(SNT, 2) ssim_stats_kernel(const SsimArgs a) {
-    constexpr int P = K / 2;
-    constexpr int XR = STH + 2 * P;           // rows of the input tile / of the horizontal-pass output
-    constexpr int XP = (STW + 2 * P) | 1;     // odd pitches: lanes walk rows without bank conflicts
+__global__ void __launch_bounds__(SNT, K ? 2 : 1) ssim_stats_kernel(const SsimArgs a) {
+    const int KK = K ? K : a.d.ksize;
+    const int P = KK / 2;
+    const int XR = STH + 2 * P;           // rows of the input tile / of the horizontal-pass output
+    const int XP = (STW + 2 * P) | 1;     // odd pitches: lanes walk rows without bank conflicts
     constexpr int HP = STW + 1;
     extern __shared__ __align__(16) float sm[];
     float *sX = sm, *sY = sX + XR * XP;
     float *sH = sY + XR * XP;  // [5][XR][HP]
     __shared__ double red[32];
+    __shared__ float sg[K ? 1 : LLIE_SSIM_MAX_K];
     const llie_ssim_desc &d = a.d;
     const int H = d.h, W = d.w;
     const int tid = threadIdx.x;
@@ -62,9 +68,11 @@ __global__ void __launch_bounds__(SNT, 2) ssim_stats_kernel(const SsimArgs a) {
     const float *xb = a.x + ((long long)n * d.c + (d.luma ? 0 : c)) * plane_elems;
     const float *yb = a.y + ((long long)n * d.c + (d.luma ? 0 : c)) * plane_elems;
 
-    float g[K];
+    float g[K ? K : 1];
 #pragma unroll
     for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
+    if (K == 0 && tid < KK) sg[tid] = __ldg(a.win + tid);
+#define SSIM_TAP(j) (K ? g[K ? (j) : 0] : sg[j])
 
     // ---- (A) padded input tile
     float chk_x = 0.f, chk_y = 0.f;
@@ -88,19 +96,20 @@ __global__ void __launch_bounds__(SNT, 2) ssim_stats_kernel(const SsimArgs a) {
         float ax[4], ay[4], axx[4], ayy[4], axy[4];
 #pragma unroll
         for (int o = 0; o < 4; ++o) ax[o] = ay[o] = axx[o] = ayy[o] = axy[o] = 0.f;
-#pragma unroll
-        for (int u = 0; u < K + 3; ++u) {
+#pragma unroll(K ? K + 3 : 1)
+        for (int u = 0; u < KK + 3; ++u) {
             const float xv = px[u], yv = py[u];
             const float xx = xv * xv, yy = yv * yv, xy = xv * yv;
 #pragma unroll
             for (int o = 0; o < 4; ++o) {
                 const int j = u - o;
-                if (j >= 0 && j < K) {
-                    ax[o] = fmaf(g[j], xv, ax[o]);
-                    ay[o] = fmaf(g[j], yv, ay[o]);
-                    axx[o] = fmaf(g[j], xx, axx[o]);
-                    ayy[o] = fmaf(g[j], yy, ayy[o]);
-                    axy[o] = fmaf(g[j], xy, axy[o]);
+                if (j >= 0 && j < KK) {
+                    const float gj = SSIM_TAP(j);
+                    ax[o] = fmaf(gj, xv, ax[o]);
+                    ay[o] = fmaf(gj, yv, ay[o]);
+                    axx[o] = fmaf(gj, xx, axx[o]);
+                    ayy[o] = fmaf(gj, yy, ayy[o]);
+                    axy[o] = fmaf(gj, xy, axy[o]);
                 }
             }
         }
@@ -124,13 +133,13 @@ __global__ void __launch_bounds__(SNT, 2) ssim_stats_kernel(const SsimArgs a) {
         const float *h = sH + q * XR * HP + (rg * 8) * HP + col;
 #pragma unroll
         for (int o = 0; o < 8; ++o) m[q][o] = 0.f;
-#pragma unroll
-        for (int u = 0; u < K + 7; ++u) {
+#pragma unroll(K ? K + 7 : 1)
+        for (int u = 0; u < KK + 7; ++u) {
             const float v = h[u * HP];
 #pragma unroll
             for (int o = 0; o < 8; ++o) {
                 const int j = u - o;
-                if (j >= 0 && j < K) m[q][o] = fmaf(g[j], v, m[q][o]);
+                if (j >= 0 && j < KK) m[q][o] = fmaf(SSIM_TAP(j), v, m[q][o]);
             }
         }
     }
@@ -211,7 +220,7 @@ __global__ void __launch_bounds__(SNT, 2) ssim_stats_kernel(const SsimArgs a) {
 
 template <int K>
 static int launch_ssim(const SsimArgs &a, int grid, cudaStream_t st) {
-    constexpr int P = K / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
+    const int P = (K ? K : a.d.ksize) / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
     const size_t smem = (size_t)(2 * XR * XP + 5 * XR * HP) * sizeof(float);
     LLIE_CUDA_OK(cudaFuncSetAttribute(ssim_stats_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ssim_stats_kernel<K><<<grid, SNT, smem, st>>>(a);
@@ -686,8 +695,8 @@ static int launch_ssim_stream2(const SsimArgs &a, int grid, cudaStream_t st) {
     return LLIE_OK;
 }
 
-int g_ssim_path = 0;      // 0 auto: two-column streaming kernel where eligible, else streaming | 1 tile kernel | 2 one-column streaming
-int g_ssim_seg_rows = 0;  // 0 = heuristic
+static std::atomic<int> g_ssim_path_a{0};      // 0 auto: two-column streaming kernel where eligible, else streaming | 1 tile kernel | 2 one-column streaming
+static std::atomic<int> g_ssim_seg_rows_a{0};  // 0 = heuristic
 
 // ---------------------------------------------------------------------------------------------------
 // Backward of the (D)SSIM sum w.r.t. x (kornia policy: reflect border, "same" size):
@@ -698,17 +707,16 @@ int g_ssim_seg_rows = 0;  // 0 = heuristic
 // Same tiling as the forward kernel: (A) coefficient tile with halo (zeros outside the image) -> smem,
 // (B) horizontal pass + column folds, (C) vertical pass + row folds, combine with x, y (8 B/elem read).
 struct SsimBwdArgs {
-    int n, c, h, w, clamp_in, gout_is_map, accumulate;
+    int n, c, h, w, ksize, clamp_in, gout_is_map, accumulate;
     const float *x, *y, *win, *coef;
     const float *gout;  // device scalar (upstream gradient of the reduced loss) or a [n,c,h,w] map
     float *out_grad;
     int tiles_x, tiles_y;
 };
 
-template <int K>
-__device__ __forceinline__ float fold_extra(const float *line, int stride, int q, int o0, int L, const float *sg) {
+__device__ __forceinline__ float fold_extra(int P, const float *line, int stride, int q, int o0, int L,
+                                            const float *sg) {
     // line[(p - o0) * stride] holds the zero-extended sequence at image coordinate p
-    constexpr int P = K / 2;
     float e = 0.f;
     if (q >= 1 && q <= P)
         for (int p = 0; p <= P - q && p < L; ++p) e = fmaf(sg[p + q + P], line[(p - o0) * stride], e);
@@ -720,15 +728,16 @@ __device__ __forceinline__ float fold_extra(const float *line, int stride, int q
 }
 
 template <int K>
-__global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs a) {
-    constexpr int P = K / 2;
-    constexpr int XR = STH + 2 * P;
-    constexpr int XP = (STW + 2 * P) | 1;
+__global__ void __launch_bounds__(SNT, K ? 2 : 1) ssim_loss_bwd_kernel(const SsimBwdArgs a) {
+    const int KK = K ? K : a.ksize;   // K == 0: runtime window (see ssim_stats_kernel)
+    const int P = KK / 2;
+    const int XR = STH + 2 * P;
+    const int XP = (STW + 2 * P) | 1;
     constexpr int HP = STW + 1;
     extern __shared__ __align__(16) float sm[];
     float *sC = sm;                   // [3][XR][XP]
     float *sH = sC + 3 * XR * XP;     // [3][XR][HP]
-    __shared__ float sg[K];
+    __shared__ float sg[K ? K : LLIE_SSIM_MAX_K];
     const int H = a.h, W = a.w, tid = threadIdx.x;
     const int tpp = a.tiles_x * a.tiles_y;
     const int plane = blockIdx.x / tpp;
@@ -741,10 +750,10 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
     const float *gm = a.gout_is_map ? a.gout + (long long)plane * plane_elems : nullptr;
     const float gs = a.gout_is_map ? 1.f : __ldg(a.gout);
 
-    float g[K];
+    float g[K ? K : 1];
 #pragma unroll
     for (int j = 0; j < K; ++j) g[j] = __ldg(a.win + j);
-    if (tid < K) sg[tid] = __ldg(a.win + tid);
+    if (tid < KK) sg[tid] = __ldg(a.win + tid);
 
     // ---- (A) coefficient tiles, zero outside the image
     for (int idx = tid; idx < XR * (STW + 2 * P); idx += SNT) {
@@ -774,13 +783,13 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
             const float *px = sC + q * XR * XP + r * XP + cg * 4;
 #pragma unroll
             for (int o = 0; o < 4; ++o) acc[q][o] = 0.f;
-#pragma unroll
-            for (int u = 0; u < K + 3; ++u) {
+#pragma unroll(K ? K + 3 : 1)
+            for (int u = 0; u < KK + 3; ++u) {
                 const float v = px[u];
 #pragma unroll
                 for (int o = 0; o < 4; ++o) {
                     const int j = u - o;
-                    if (j >= 0 && j < K) acc[q][o] = fmaf(g[j], v, acc[q][o]);
+                    if (j >= 0 && j < KK) acc[q][o] = fmaf(SSIM_TAP(j), v, acc[q][o]);
                 }
             }
         }
@@ -791,7 +800,7 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
                 if (qx < W && (qx <= P || qx >= W - 1 - P)) {
 #pragma unroll
                     for (int q = 0; q < 3; ++q)
-                        acc[q][o] += fold_extra<K>(sC + q * XR * XP + r * XP, 1, qx, x0 - P, W, sg);
+                        acc[q][o] += fold_extra(P, sC + q * XR * XP + r * XP, 1, qx, x0 - P, W, sg);
                 }
             }
         }
@@ -813,13 +822,13 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
         const float *h = sH + q * XR * HP + (rg * 8) * HP + col;
 #pragma unroll
         for (int o = 0; o < 8; ++o) m[q][o] = 0.f;
-#pragma unroll
-        for (int u = 0; u < K + 7; ++u) {
+#pragma unroll(K ? K + 7 : 1)
+        for (int u = 0; u < KK + 7; ++u) {
             const float v = h[u * HP];
 #pragma unroll
             for (int o = 0; o < 8; ++o) {
                 const int j = u - o;
-                if (j >= 0 && j < K) m[q][o] = fmaf(g[j], v, m[q][o]);
+                if (j >= 0 && j < KK) m[q][o] = fmaf(SSIM_TAP(j), v, m[q][o]);
             }
         }
     }
@@ -833,9 +842,9 @@ __global__ void __launch_bounds__(SNT, 2) ssim_loss_bwd_kernel(const SsimBwdArgs
         if (gy >= H) break;
         float g1 = m[0][o], g2 = m[1][o], g3 = m[2][o];
         if (fold_y && (gy <= P || gy >= H - 1 - P)) {
-            g1 += fold_extra<K>(sH + col, HP, gy, y0 - P, H, sg);
-            g2 += fold_extra<K>(sH + XR * HP + col, HP, gy, y0 - P, H, sg);
-            g3 += fold_extra<K>(sH + 2 * XR * HP + col, HP, gy, y0 - P, H, sg);
+            g1 += fold_extra(P, sH + col, HP, gy, y0 - P, H, sg);
+            g2 += fold_extra(P, sH + XR * HP + col, HP, gy, y0 - P, H, sg);
+            g3 += fold_extra(P, sH + 2 * XR * HP + col, HP, gy, y0 - P, H, sg);
         }
         const long long off = (long long)gy * W + gx;
         const float xr = __ldg(xb + off);
@@ -1217,7 +1226,7 @@ static int launch_ssim_bwd_stream2(const SsimBwdArgs &a, int grid, int seg_rows,
 
 template <int K>
 static int launch_ssim_bwd(const SsimBwdArgs &a, int grid, cudaStream_t st) {
-    constexpr int P = K / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
+    const int P = (K ? K : a.ksize) / 2, XR = STH + 2 * P, XP = (STW + 2 * P) | 1, HP = STW + 1;
     const size_t smem = (size_t)(3 * XR * XP + 3 * XR * HP) * sizeof(float);
     LLIE_CUDA_OK(cudaFuncSetAttribute(ssim_loss_bwd_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ssim_loss_bwd_kernel<K><<<grid, SNT, smem, st>>>(a);
@@ -1275,11 +1284,13 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
     a.co = d.luma ? 1 : d.c;
     Workspace ws(workspace);
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int g_ssim_path = g_ssim_path_a.load(std::memory_order_relaxed);  // diagnostic knobs, read once per call
+    const int g_ssim_seg_rows = g_ssim_seg_rows_a.load(std::memory_order_relaxed);
     // default: TMA row ring + packed FP32 (ssim_ring.cu) for the 11-tap window of all three reference policies
     if (g_ssim_path == 0 && ssim_ring_eligible(d, x, y, win1d_host, out_map != nullptr, coef))
         return ssim_ring_forward(a, win1d_host, workspace, st);
     long long grid;
-    const bool stream_ok = g_ssim_path != 1 && !d.luma;
+    const bool stream_ok = g_ssim_path != 1 && !d.luma && d.ksize <= 15;
     // statistics only (no map / coefficient planes), the 11-tap window of all three reference policies
     // (the loss-coefficient planes are written by the four-map instantiation: no variance clamp on that path)
     const bool stream2_ok = stream_ok && (g_ssim_path == 0 || g_ssim_path == 3) && d.ksize == 11 && out_map == nullptr &&
@@ -1333,14 +1344,15 @@ static int ssim_forward(const llie_ssim_desc *desc, const float *x, const float 
         case 9: return launch_ssim<9>(a, (int)grid, st);
         case 11: return launch_ssim<11>(a, (int)grid, st);
         case 13: return launch_ssim<13>(a, (int)grid, st);
-        default: return launch_ssim<15>(a, (int)grid, st);
+        case 15: return launch_ssim<15>(a, (int)grid, st);
+        default: return launch_ssim<0>(a, (int)grid, st);  // 17..LLIE_SSIM_MAX_K taps: runtime-window instantiation
     }
 }
 
 namespace llie {
 void ssim_tune(int key, int value) {
-    if (key == LLIE_TUNE_SSIM_PATH) g_ssim_path = value;
-    if (key == LLIE_TUNE_SSIM_SEG_ROWS) g_ssim_seg_rows = value;
+    if (key == LLIE_TUNE_SSIM_PATH) g_ssim_path_a.store(value, std::memory_order_relaxed);
+    if (key == LLIE_TUNE_SSIM_SEG_ROWS) g_ssim_seg_rows_a.store(value, std::memory_order_relaxed);
 }
 }  // namespace llie
 
@@ -1373,9 +1385,11 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
     LLIE_REQUIRE(d.ksize / 2 < d.h && d.ksize / 2 < d.w && d.ksize <= d.h && d.ksize <= d.w,
                  "ssim_loss_backward: window larger than the image");
     SsimBwdArgs a{};
-    a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map; a.accumulate = accumulate;
+    a.n = d.n; a.c = d.c; a.h = d.h; a.w = d.w; a.ksize = d.ksize; a.clamp_in = d.clamp_in; a.gout_is_map = grad_out_is_map; a.accumulate = accumulate;
     a.x = x; a.y = y; a.win = win1d; a.coef = coef; a.gout = grad_out; a.out_grad = out_grad;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    const int g_ssim_path = g_ssim_path_a.load(std::memory_order_relaxed);
+    const int g_ssim_seg_rows = g_ssim_seg_rows_a.load(std::memory_order_relaxed);
     if ((g_ssim_path == 0 || g_ssim_path == 3) && !grad_out_is_map && d.ksize == 11) {
         a.tiles_x = div_up(d.w, S2W);
         const long long cols = (long long)d.n * d.c * a.tiles_x;
@@ -1386,7 +1400,7 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
         LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
         return launch_ssim_bwd_stream2<11>(a, (int)grid, rows, st);
     }
-    if (g_ssim_path != 1 && !grad_out_is_map) {
+    if (g_ssim_path != 1 && !grad_out_is_map && d.ksize <= 15) {
         a.tiles_x = div_up(d.w, SW);
         const long long cols = (long long)d.n * d.c * a.tiles_x;
         int segs = (int)((148LL * 5 * 3 + cols - 1) / cols);
@@ -1419,6 +1433,7 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
         case 9: return launch_ssim_bwd<9>(a, (int)grid, st);
         case 11: return launch_ssim_bwd<11>(a, (int)grid, st);
         case 13: return launch_ssim_bwd<13>(a, (int)grid, st);
-        default: return launch_ssim_bwd<15>(a, (int)grid, st);
+        case 15: return launch_ssim_bwd<15>(a, (int)grid, st);
+        default: return launch_ssim_bwd<0>(a, (int)grid, st);
     }
 }

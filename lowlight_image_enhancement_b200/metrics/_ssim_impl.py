@@ -30,8 +30,8 @@ def _stats(pred: Tensor, target: Tensor, *, data_range, kernel_size, sigma, k1, 
     if h < kernel_size or w < kernel_size:
         raise ValueError(
             f"Spatial dimensions must be >= kernel_size. Got H={h}, W={w}, kernel_size={kernel_size}.")
-    if kernel_size > 15:
-        raise NotImplementedError("the CUDA SSIM kernel supports odd windows up to 15x15")
+    if kernel_size > nat.SSIM_MAX_K:
+        raise NotImplementedError(f"the CUDA SSIM kernels take odd windows up to {nat.SSIM_MAX_K}x{nat.SSIM_MAX_K}")
     if padding == "reflect" and (kernel_size // 2 >= h or kernel_size // 2 >= w):
         raise RuntimeError("Padding size should be less than the corresponding input dimension")
     home = pred.device

@@ -101,8 +101,8 @@ def torchmetrics_ssim_scores(pred: Tensor, target: Tensor, *, data_range: float,
     n, c, h, w = pred.shape
     gk = int(3.5 * sigma + 0.5) * 2 + 1
     pad = (gk - 1) // 2
-    if gk > 15:
-        raise NotImplementedError("the CUDA SSIM kernel supports Gaussian supports up to 15 taps (sigma <= 2.07)")
+    if gk > nat.SSIM_MAX_K:
+        raise NotImplementedError(f"the CUDA SSIM kernels take Gaussian supports up to {nat.SSIM_MAX_K} taps (sigma <= 8.9)")
     if h <= 2 * pad or w <= 2 * pad:
         raise ValueError(f"Images of size {(h, w)} are too small for a {gk}x{gk} SSIM window.")
     sums, count, _ = ssim_sums_torchmetrics(pred, target, data_range=data_range, sigma=sigma, k1=k1, k2=k2, luma=luma)
@@ -116,8 +116,8 @@ def ssim_sums_torchmetrics(pred: Tensor, target: Tensor, *, data_range: float, s
     n, c, h, w = pred.shape
     gk = int(3.5 * sigma + 0.5) * 2 + 1
     pad = (gk - 1) // 2
-    if gk > 15:
-        raise NotImplementedError("the CUDA SSIM kernel supports Gaussian supports up to 15 taps (sigma <= 2.07)")
+    if gk > nat.SSIM_MAX_K:
+        raise NotImplementedError(f"the CUDA SSIM kernels take Gaussian supports up to {nat.SSIM_MAX_K} taps (sigma <= 8.9)")
     if h <= 2 * pad or w <= 2 * pad:
         raise ValueError(f"Images of size {(h, w)} are too small for a {gk}x{gk} SSIM window.")
     win = Fn.window_1d("torchmetrics", gk, float(sigma), pred.device)

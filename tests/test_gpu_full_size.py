@@ -50,8 +50,13 @@ def test_c2_phys_cons_raw_full_size():
     keep = ~near
     err = (x.grad - xr.grad).abs()[keep].max() / xr.grad.abs().max()
     assert float(err) < 1e-5, float(err)
-    flips = ((x.grad - xr.grad).abs() > 1e-5 * xr.grad.abs().max()) & near
-    assert int(flips.sum()) <= int(near.sum())
+    # ... and bound what a flipped sign can do there: one residual whose sign differs moves the gradient of an input
+    # pixel by 2 k_tap rho / numel, all nine residuals of a neighbourhood by at most 2 sum|k| rho / numel
+    # (sum|k| = 1 for the normalised PSF); only a small fraction of the flagged pixels may differ at all
+    d_near = (x.grad - xr.grad).abs()[near]
+    assert float(d_near.max()) <= 2.0 * float(rho.max()) / pred.numel() * (1 + 1e-3)
+    flips = d_near > 1e-5 * xr.grad.abs().max()
+    assert int(flips.sum()) <= 0.25 * int(near.sum()) and int(flips.sum()) < 5000, (int(flips.sum()), int(near.sum()))
 
 
 def test_c3_hybrid_full_size():
@@ -137,7 +142,8 @@ def test_c4_eval_full_resolution():
     assert float(e_mine.max()) <= max(1e-4, 2.0 * float(e_ref.max())), (float(e_mine.max()), float(e_ref.max()))
     del r64, e_mine, e_ref, lab_p, lab_g
     assert abs(lm.deltae2000_mean(pred, gt) - float(ref_map.mean())) < 1e-4
-    assert abs(lm.deltae2000_p95(pred, gt) - float(torch.quantile(ref_map.flatten()[::4], 0.95))) < 5e-3  # strided: torch.quantile caps at 16 M
+    # 12.1 M values: under torch.quantile's 16 M cap, so the reference's own full-population percentile is the oracle
+    assert abs(lm.deltae2000_p95(pred, gt) - float(torch.quantile(ref_map.flatten(), 0.95))) < 1e-4
     out = edge_deltaE2000_stats(pred, gt, q=0.85)
     # the reference's own torch.quantile refuses > 16 M elements per row only on some builds; 12.1 M is fine
     ref = colour.edge_stats(pred, gt, q=0.85)

@@ -93,7 +93,10 @@ def test_deltae_loss_contracts(dev):
 
 @pytest.mark.parametrize("shape,ws", [((2, 3, 37, 53), 11), ((1, 3, 128, 96), 11), ((2, 1, 11, 11), 11),
                                       ((1, 3, 33, 130), 7), ((1, 2, 70, 64), 3), ((1, 1, 16, 15), 15),
-                                      ((1, 3, 12, 200), 5)])
+                                      ((1, 3, 12, 200), 5),
+                                      # windows above 15 taps: runtime-window tile kernels (forward and adjoint)
+                                      ((1, 3, 40, 97), 17), ((1, 2, 70, 140), 21), ((1, 1, 64, 66), 31),
+                                      ((1, 1, 80, 130), 63)])
 def test_ssim_loss_value_and_grad(dev, shape, ws):
     from lowlight_image_enhancement_b200.NewBP_model.losses import SSIMLoss
 

@@ -280,7 +280,7 @@ def test_phys_value_and_grad_equals_two_passes(dev, padding, crop, robust, clip,
 
 @pytest.mark.parametrize("shape", [(8, 3, 512, 512), (2, 3, 96, 640), (4, 3, 130, 252)])
 def test_phys_stream_overlap_is_bit_identical(dev, shape):
-    """LLIE_TUNE_PHYS_OVERLAP (launch i + 1 waits for launch i only before it touches the shared workspace, and work
+    """llie_phys_desc.stream_overlap, set per call by `with Fn.phys_stream_overlap():` (launch i + 1 waits for launch i only before it touches the shared workspace, and work
     items grow to ~128 rows): a mixed back-to-back sequence of fused / forward / backward launches over rotating,
     disjoint buffer sets must return what fully serialised launches return -- gradients bit for bit, loss vectors to
     1e-6 relative (the item partition, hence the grouping of the float32 partial sums, differs between the modes) --
@@ -320,8 +320,21 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
 
     ref = sequence(2)
     torch.cuda.synchronize(dev)
-    try:
-        Fn.phys_stream_overlap(True)
+    want = {}
+    for i in range(pool):
+        v, _, gr = Fn.phys_value_and_grad(preds[i], obss[i], psf, rho, 0.0, st, cfg, gout, 0.37)
+        want[i] = (v.clone(), gr.clone())
+    torch.cuda.synchronize(dev)
+    keep = []
+
+    def burst():
+        for i in range(4 * pool):
+            b = i % pool
+            vec, _, _ = Fn.phys_value_and_grad(preds[b], obss[b], psf, rho, 0.0, st, cfg, gout, 0.37, out=grads[b])
+            keep.append(vec)
+
+    with Fn.phys_stream_overlap():
+        assert Fn._desc(cfg, preds[0], shape[1], psf, 0.0, st).stream_overlap == 1
         # (the .clone() kernels sit between the phys launches here: they read what the launch before them wrote, and
         # they are ordinary launches, so every phys kernel still waits for them -- this leg checks the flag's plumbing)
         got = sequence(2)
@@ -329,22 +342,8 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
         for r, o in zip(ref, got):
             assert all(same(a, b) for a, b in zip(r, o))
         # back-to-back phys launches only (the overlap proper): stream, then graph replay
-        def burst():
-            for i in range(4 * pool):
-                b = i % pool
-                vec, _, _ = Fn.phys_value_and_grad(preds[b], obss[b], psf, rho, 0.0, st, cfg, gout, 0.37, out=grads[b])
-                keep.append(vec)
-
-        keep = []
         burst()
         torch.cuda.synchronize(dev)
-        want = {}
-        for i in range(pool):
-            Fn.phys_stream_overlap(False)
-            v, _, gr = Fn.phys_value_and_grad(preds[i], obss[i], psf, rho, 0.0, st, cfg, gout, 0.37)
-            want[i] = (v.clone(), gr.clone())
-        torch.cuda.synchronize(dev)
-        Fn.phys_stream_overlap(True)
         first = [v.clone() for v in keep]
         for i, v in enumerate(keep):
             assert same(v, want[i % pool][0]), i
@@ -353,10 +352,10 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
         side = torch.cuda.Stream(dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
-            keep = []
+            keep.clear()
             burst()  # warm-up on the capture stream (workspace of that stream)
             side.synchronize()
-            keep = []
+            keep.clear()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=side):
                 burst()
@@ -369,5 +368,35 @@ def test_phys_stream_overlap_is_bit_identical(dev, shape):
             assert torch.equal(v, first[i]), i  # overlapped launches are reproducible bit for bit
         for b in range(pool):
             assert torch.equal(grads[b], want[b][1]), b
-    finally:
-        Fn.phys_stream_overlap(False)
+    # the scope is per call: nothing leaks out of the `with` block
+    assert Fn._desc(cfg, preds[0], shape[1], psf, 0.0, st).stream_overlap == 0
+
+
+def test_phys_stream_overlap_scope_is_per_thread_and_skips_autograd(dev, monkeypatch):
+    """The overlap promise is a field of each call's descriptor, set from a thread-local scope: another thread and the
+    autograd engine's backward threads (whose upstream gradient comes from the previous kernel) never carry it."""
+    import threading
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw
+    seen = []
+    real = Fn._desc
+
+    def spy(*a, **k):
+        d = real(*a, **k)
+        seen.append((threading.current_thread() is threading.main_thread(), d.stream_overlap))
+        return d
+
+    monkeypatch.setattr(Fn, "_desc", spy)
+    g = torch.Generator().manual_seed(3)
+    pred = torch.rand(2, 3, 64, 64, generator=g).to(dev).requires_grad_(True)
+    obs = torch.rand(2, 3, 64, 64, generator=g).to(dev)
+    psf = psf_ops.canonical_kernels("rgb").to(dev)
+    with Fn.phys_stream_overlap():
+        out = phys_cons_raw(pred, obs, psf, 1.2, differentiable=True)
+        out.backward()
+        t = threading.Thread(target=lambda: phys_cons_raw(pred.detach(), obs, psf, 1.2))
+        t.start()
+        t.join()
+    assert (True, 1) in seen                       # forward in the scope's thread
+    assert all(ov == 0 for main, ov in seen if not main) and any(not main for main, _ in seen)
+    assert pred.grad is not None and torch.isfinite(pred.grad).all()

@@ -113,6 +113,33 @@ def test_ssim_wrapper_behaviour(dev):
     assert 0.9999 <= ident["mean"] <= 1.0001
 
 
+@pytest.mark.parametrize("k,shape,pad", [(17, (2, 3, 40, 97), "reflect"), (21, (1, 3, 70, 140), "replicate"),
+                                          (31, (1, 2, 64, 64), "circular"), (63, (1, 1, 80, 130), "constant"),
+                                          (25, (1, 3, 33, 66), "reflect")])
+def test_ssim_wide_windows_vs_oracle(dev, k, shape, pad):
+    """Odd windows above 15 taps (the reference takes any odd kernel_size, metrics/linear.py:170-176) run on the
+    runtime-window instantiation of the tile kernels: per-channel scores vs the float64 oracle, all three policies."""
+    from lowlight_image_enhancement_b200.metrics.linear import ssim_linear
+    from lowlight_image_enhancement_b200.metrics.ssim import calculate_ssim_per_image, SSIMEvaluator
+    g = torch.Generator().manual_seed(k + shape[3])
+    tgt = torch.rand(shape, generator=g)
+    pred = (tgt + 0.08 * torch.randn(shape, generator=g)).clamp(0, 1)
+    sigma = k / 6.0
+    kw = dict(kernel_size=k, sigma=sigma, padding=pad, reduction="none", channel_aggregate="none")
+    ref = quality.ssim_linear(pred.double(), tgt.double(), **kw)
+    out = ssim_linear(pred.to(dev), tgt.to(dev), **kw)
+    np.testing.assert_allclose(_np(out), _np(ref), rtol=1e-5, atol=0)
+    box = dict(kw, gaussian=False)
+    np.testing.assert_allclose(_np(ssim_linear(pred.to(dev), tgt.to(dev), **box)),
+                               _np(quality.ssim_linear(pred.double(), tgt.double(), **box)), rtol=1e-5, atol=0)
+    if pad == "reflect":   # torchmetrics policy: the support follows sigma (gk = 2 int(3.5 sigma + 0.5) + 1)
+        s = (k - 1) / 7.0
+        assert int(3.5 * s + 0.5) * 2 + 1 == k
+        ev = SSIMEvaluator(data_range=1.0, sigma=s, kernel_size=k)(tgt.to(dev), pred.to(dev))
+        rt = quality.ssim_torchmetrics(pred.double(), tgt.double(), data_range=1.0, sigma=s, kernel_size=k)
+        np.testing.assert_allclose(ev["per_image"], _np(rt), rtol=1e-5, atol=0)
+
+
 # ------------------------------------------------------------------ CIEDE2000
 def test_de00_lab_inputs_vs_golden(golden, dev):
     """Both formulas on Lab inputs (the part of the path pinned by the reference's own functions)."""

@@ -50,7 +50,7 @@ def graph_time(fn):
 elems = n * c * h * w
 res = []
 rows_list = [int(v) for v in os.environ.get("SWEEP_ROWS", "0,8,12,16,24,32,64").split(",")]
-configs = ([("tma", 1, 0), ("roll", 3, 0)] if os.environ.get("SWEEP_TMA") else []) + [("ring", 0, r) for r in rows_list]
+configs = ([("generic", 2, 0)] if os.environ.get("SWEEP_GENERIC") else []) + [("ring", 0, r) for r in rows_list]
 print("lib:", nat.LIB_PATH, "shape:", shape)
 for name, path, rows in configs:
     nat.lib().llie_tune(1, path); nat.lib().llie_tune(2, rows)
