@@ -245,7 +245,7 @@ int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const flo
                            const float *win1d_host, float grad_scale, double *out_sum, float *out_map, float *out_coef,
                            int32_t *out_flags, void *workspace, void *stream);
 int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                            const float *coef, const float *grad_out, int32_t grad_out_is_map, int32_t accumulate,
+                            const float *win1d_host, const float *coef, const float *grad_out, int32_t grad_out_is_map, int32_t accumulate,
                             float *out_grad, void *stream);
 
 /* ------------------------------------------------------------------------
@@ -269,6 +269,12 @@ int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, do
 int llie_deltae_sqerr(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
                       double *out_sqerr, float *out_map, float *out_l, int32_t *out_flags, void *workspace,
                       void *stream);
+/* ... plus out_sqerr_rgb[n, 3] = the same float64 sums per channel (out_sqerr may be NULL): the CPSNR / RGB-PSNR family
+ * (metrics/channelwise.py:113-222: float64 difference of the raw inputs, per-channel MSE) rides on the colour pass too,
+ * and the dataset driver needs no llie_psnr_stats launch (one full read of both images less per pair). */
+int llie_deltae_sqerr_rgb(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                          double *out_sqerr, double *out_sqerr_rgb, float *out_map, float *out_l,
+                          int32_t *out_flags, void *workspace, void *stream);
 
 /* DeltaE00Loss forward + analytic backward in ONE pass (variant 1, sRGB inputs): per-image sums of dE00 and
  * out_grad[n,3,h,w] = grad_scale * d dE00(pixel) / d x (clamp pass-through mask included), i.e. the gradient
@@ -358,12 +364,13 @@ typedef struct llie_eval_desc {
     int32_t slot_rgb_psnr[4];  /* rgb_psnr(reduction='mean')['R' | 'G' | 'B' | 'mean']            <- psnr_table */
     int32_t slot_rgb_ssim[4];  /* rgb_ssim(reduction='mean')['R' | 'G' | 'B' | 'mean']            <- rgb_ssim_sums */
 } llie_eval_desc;
-/*   psnr_table     [n + 2, LLIE_PSNR_COLS(3)] float64 as written by llie_psnr_stats(cast_first = 1)
+/*   psnr_table     [n + 2, LLIE_PSNR_COLS(3)] float64 as written by llie_psnr_stats(cast_first = 1), or NULL with
+ *   sqerr_rgb      [n, 3] float64 per-channel squared-error sums (llie_deltae_sqerr_rgb; data_range 1, eps 1e-12)
  *   rgb_ssim_sums  [n, 3] float64 SSIM-map sums over hw pixels of the ssim_linear policy (llie_ssim_stats, clamp_var) */
 int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const double *ssim_sums,
                          const double *de_sums, const float *de_p95, const double *edge_sum,
-                         const int64_t *edge_counts, const double *psnr_table, const double *rgb_ssim_sums,
-                         const int32_t *flags0, const int32_t *flags1, const int32_t *flags2, const int32_t *flags3,
+                         const int64_t *edge_counts, const double *psnr_table, const double *sqerr_rgb,
+                         const double *rgb_ssim_sums, const int32_t *flags0, const int32_t *flags1, const int32_t *flags2, const int32_t *flags3,
                          const int32_t *flags4, const int32_t *flags5, double *acc, void *stream);
 
 /* Accuracy self-test hook: out[i] = the kernels' sRGB -> linear transfer of in[i] (pow24 path), so that the

@@ -422,9 +422,10 @@ def ssim_stats(x: Tensor, y: Tensor, win: Tensor, *, pad_mode: int, c1: float, c
 # ------------------------------------------------------------------------------------------------
 def deltae(x: Tensor, y: Tensor, *, variant: int, kL: float = 1.0, kC: float = 1.0, kH: float = 1.0,
            eps: float = 1e-12, input_lab: bool = False, clamp_in: bool = False, want_map: bool = False,
-           want_l: bool = False, sqerr_out: Optional[list] = None):
+           want_l: bool = False, sqerr_out: Optional[list] = None, sqerr_rgb: bool = False):
     """Launch llie_deltae on contiguous fp32 CUDA [N,3,H,W].  Returns (sums f64[N], flags, map|None, L|None).
-    `sqerr_out=[]`: the pass also sums (x - y)^2 in float64 per image (llie_deltae_sqerr), appended to the list."""
+    `sqerr_out=[]`: the pass also sums (x - y)^2 in float64 per image (llie_deltae_sqerr), appended to the list;
+    with `sqerr_rgb` the per-channel sums [N, 3] are appended after it (llie_deltae_sqerr_rgb)."""
     dev = x.device
     n, _, h, w = x.shape
     sums = torch.empty(n, dtype=torch.float64, device=dev)
@@ -436,9 +437,16 @@ def deltae(x: Tensor, y: Tensor, *, variant: int, kL: float = 1.0, kC: float = 1
         if sqerr_out is not None:
             sq = torch.empty(n, dtype=torch.float64, device=dev)
             sqerr_out.append(sq)
-            rc = nat.lib().llie_deltae_sqerr(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(sq), nat.ptr(dmap),
-                                             nat.ptr(lpl), nat.ptr(flags), nat.ptr(nat.workspace(dev)),
-                                             nat.stream_ptr(dev))
+            if sqerr_rgb:
+                sqc = torch.empty((n, 3), dtype=torch.float64, device=dev)
+                sqerr_out.append(sqc)
+                rc = nat.lib().llie_deltae_sqerr_rgb(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(sq),
+                                                     nat.ptr(sqc), nat.ptr(dmap), nat.ptr(lpl), nat.ptr(flags),
+                                                     nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+            else:
+                rc = nat.lib().llie_deltae_sqerr(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(sq),
+                                                 nat.ptr(dmap), nat.ptr(lpl), nat.ptr(flags),
+                                                 nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
         else:
             rc = nat.lib().llie_deltae(d, nat.ptr(x), nat.ptr(y), nat.ptr(sums), nat.ptr(dmap), nat.ptr(lpl),
                                        nat.ptr(flags), nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
@@ -652,6 +660,7 @@ class SSIMLossFn(torch.autograd.Function):
                                                       nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
                 ctx.save_for_backward(x, y, win, coef)
                 ctx.desc = d
+                ctx.win_host = win_host(win)
             else:
                 rc = nat.lib().llie_ssim_stats(d, nat.ptr(x), nat.ptr(y), nat.ptr(win), win_host(win), nat.ptr(sums),
                                                nat.ptr(smap), nat.ptr(flags), nat.ptr(nat.workspace(dev)),
@@ -675,8 +684,9 @@ class SSIMLossFn(torch.autograd.Function):
         g = gout.detach().to(torch.float32).contiguous()
         out = torch.empty_like(x)
         with torch.cuda.device(dev):
-            rc = nat.lib().llie_ssim_loss_backward(ctx.desc, nat.ptr(x), nat.ptr(y), nat.ptr(win), nat.ptr(coef),
-                                                   nat.ptr(g), int(is_map), 0, nat.ptr(out), nat.stream_ptr(dev))
+            rc = nat.lib().llie_ssim_loss_backward(ctx.desc, nat.ptr(x), nat.ptr(y), nat.ptr(win), ctx.win_host,
+                                                   nat.ptr(coef), nat.ptr(g), int(is_map), 0, nat.ptr(out),
+                                                   nat.stream_ptr(dev))
         nat.check(rc, "llie_ssim_loss_backward")
         nat.count_launch()
         return out, None, None, None, None
@@ -799,8 +809,8 @@ class HybridFusedFn(torch.autograd.Function):
                     acc = 1 if g_srgb is not None else 0
                     if g_srgb is None:
                         g_srgb = torch.empty_like(xs)
-                    nat.check(lib.llie_ssim_loss_backward(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), nat.ptr(coef),
-                                                          nat.ptr(_one(dev)), 0, acc, nat.ptr(g_srgb), st),
+                    nat.check(lib.llie_ssim_loss_backward(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), win_host(win),
+                                                          nat.ptr(coef), nat.ptr(_one(dev)), 0, acc, nat.ptr(g_srgb), st),
                               "llie_ssim_loss_backward")
                     launches += 2
                 else:

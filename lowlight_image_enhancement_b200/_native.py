@@ -99,11 +99,12 @@ _SIGNATURES = {
     "llie_ssim_stats": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_sqerr": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_deltae_sqerr_rgb": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_loss_grad": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, C.c_float, _VP, _VP, _VP, _VP, _VP]),
     "llie_ssim_loss_forward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, C.c_float, _VP, _VP, _VP, _VP, _VP,
                                          _VP]),
-    "llie_ssim_loss_backward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32, _VP,
-                                          _VP]),
+    "llie_ssim_loss_backward": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, C.c_int32, C.c_int32,
+                                          _VP, _VP]),
     "llie_l1_grad": (C.c_int, [_VP, _VP, C.c_int64, C.c_float, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
     "llie_pixel_loss_grad": (C.c_int, [C.c_int32, _VP, _VP, _VP, C.c_int32, _VP, C.c_int32, C.c_int32, C.c_int64, C.c_float,
                                        C.c_float, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
@@ -112,7 +113,7 @@ _SIGNATURES = {
     "llie_decode_u16": (C.c_int, [C.POINTER(DecodeDesc), _VP, _VP, C.c_float, _VP, _VP, _VP]),
     "llie_linear_to_srgb": (C.c_int, [_VP, C.c_int64, _VP, _VP, _VP]),
     "llie_eval_accumulate": (C.c_int, [C.POINTER(EvalDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP,
-                                       _VP, _VP, _VP, _VP]),
+                                       _VP, _VP, _VP, _VP, _VP]),
     "llie_selftest_div_const": (C.c_int, [C.c_int32, C.c_uint32, C.c_uint64, _VP, _VP]),
     "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),

@@ -52,7 +52,8 @@ struct DeArgs {
     int *pflag;    // [n][G]
     unsigned *ticket;
     double *out_sq;   // NULL or [n]: sum over the 3 channels of (x - y)^2 in float64 (PSNR rides on this pass)
-    double *part_sq;  // [n][G]
+    double *out_sqc;  // NULL or [n][3]: the same sums per channel (CPSNR / RGB-PSNR table, channelwise.py:113-222)
+    double *part_sq;  // [3][n][G]
 };
 
 // One pixel group of the dE00 pass: V = float (1 pixel) or dem::F2 (2 pixels).  Returns dE00 and L of x.
@@ -86,8 +87,8 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
     const long long plane = (long long)d.h * d.w;
     const float *x0 = a.x + (long long)n * 3 * plane, *y0 = a.y + (long long)n * 3 * plane;
     float acc = 0.f, chk_x = 0.f, chk_y = 0.f;
-    double sq = 0.0;
-    const bool want_sq = a.out_sq != nullptr;
+    double sq[3] = {0.0, 0.0, 0.0};
+    const bool want_sq = a.out_sq != nullptr || a.out_sqc != nullptr;
     if (VEC) {
         using dem::F2;
         const long long groups = plane >> 2;
@@ -105,7 +106,7 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
                 if (want_sq) {  // metrics/psnr.py:39-88: both images promoted to float64 before the difference
                     const double e0 = (double)p[c].x - (double)t[c].x, e1 = (double)p[c].y - (double)t[c].y;
                     const double e2 = (double)p[c].z - (double)t[c].z, e3 = (double)p[c].w - (double)t[c].w;
-                    sq = fma(e0, e0, fma(e1, e1, fma(e2, e2, fma(e3, e3, sq))));
+                    sq[c] = fma(e0, e0, fma(e1, e1, fma(e2, e2, fma(e3, e3, sq[c]))));
                 }
             }
             F2 La, Lb;
@@ -131,7 +132,9 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
             chk_y = fmaf(t0, 0.f, fmaf(t1, 0.f, fmaf(t2, 0.f, chk_y)));
             if (want_sq) {
                 const double d0 = (double)p0 - (double)t0, d1 = (double)p1 - (double)t1, d2 = (double)p2 - (double)t2;
-                sq = fma(d0, d0, fma(d1, d1, fma(d2, d2, sq)));
+                sq[0] = fma(d0, d0, sq[0]);
+                sq[1] = fma(d1, d1, sq[1]);
+                sq[2] = fma(d2, d2, sq[2]);
             }
             float L1;
             const float de = de_pixel<VARIANT, EXACT_L, float>(d, p0, p1, p2, t0, t1, t2, L1);
@@ -141,31 +144,57 @@ __global__ void __launch_bounds__(256) deltae_kernel(const DeArgs a) {
         }
     }
     const double bs = block_sum<double>((double)acc, red);
-    double bq = 0.0;
-    if (want_sq) bq = block_sum<double>(sq, red);
+    double bq[3] = {0.0, 0.0, 0.0};
+    if (want_sq) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) bq[c] = block_sum<double>(sq[c], red);
+    }
     int flag = 0;
     if (!(chk_x == 0.f)) flag |= 1;
     if (!(chk_y == 0.f)) flag |= 2;
     const int f = block_or(flag, reinterpret_cast<int *>(red));
     if (threadIdx.x == 0) {
         a.part[(size_t)n * G + blockIdx.x] = bs;
-        if (want_sq) a.part_sq[(size_t)n * G + blockIdx.x] = bq;
+        if (want_sq) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) a.part_sq[((size_t)c * d.n + n) * G + blockIdx.x] = bq[c];
+        }
         a.pflag[(size_t)n * G + blockIdx.x] = f;
     }
     if (!last_block_done(a.ticket, gridDim.x * gridDim.y)) return;
     const int lane = threadIdx.x & 31, wrp = threadIdx.x >> 5;
-    for (int s = wrp; s < d.n * (want_sq ? 2 : 1); s += 8) {
-        const int img = s % d.n;
-        const double *p = (s < d.n ? a.part : a.part_sq) + (size_t)img * G;
-        double s0 = 0.0, s1 = 0.0;
-        int b = lane;
-        for (; b + 32 < G; b += 64) {
-            s0 += __ldcg(p + b);
-            s1 += __ldcg(p + b + 32);
+    // fixed-order sums, one warp per (quantity, image): quantity 0 = dE00, 1..3 = squared error of channel 0..2
+    __shared__ double s_sq[3][8];
+    for (int img0 = 0; img0 < d.n; img0 += 8) {
+        const int imgs = min(8, d.n - img0);
+        for (int s = wrp; s < imgs * (want_sq ? 4 : 1); s += 8) {
+            const int q = s / imgs, img = img0 + s % imgs;
+            const double *p = (q == 0 ? a.part : a.part_sq + (size_t)(q - 1) * d.n * G) + (size_t)img * G;
+            double s0 = 0.0, s1 = 0.0;
+            int b = lane;
+            for (; b + 32 < G; b += 64) {
+                s0 += __ldcg(p + b);
+                s1 += __ldcg(p + b + 32);
+            }
+            for (; b < G; b += 32) s0 += __ldcg(p + b);
+            const double t = warp_sum(s0 + s1);
+            if (lane == 0) {
+                if (q == 0) a.out_sum[img] = t;
+                else s_sq[q - 1][img - img0] = t;
+            }
         }
-        for (; b < G; b += 32) s0 += __ldcg(p + b);
-        const double t = warp_sum(s0 + s1);
-        if (lane == 0) (s < d.n ? a.out_sum : a.out_sq)[img] = t;
+        __syncthreads();
+        if (want_sq && threadIdx.x < imgs) {
+            const int img = img0 + threadIdx.x;
+            const double c0 = s_sq[0][threadIdx.x], c1 = s_sq[1][threadIdx.x], c2 = s_sq[2][threadIdx.x];
+            if (a.out_sq) a.out_sq[img] = (c0 + c1) + c2;
+            if (a.out_sqc) {
+                a.out_sqc[(size_t)img * 3] = c0;
+                a.out_sqc[(size_t)img * 3 + 1] = c1;
+                a.out_sqc[(size_t)img * 3 + 2] = c2;
+            }
+        }
+        __syncthreads();
     }
     int fl = 0;
     for (int b = threadIdx.x; b < G * d.n; b += blockDim.x) fl |= __ldcg(a.pflag + b);
@@ -430,7 +459,7 @@ __global__ void __launch_bounds__(64) sobel4_kernel(const float *L, float *g, in
 using namespace llie;
 
 static int deltae_launch(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
-                         double *out_sq, float *out_map, float *out_l, int32_t *out_flags, void *workspace,
+                         double *out_sq, double *out_sqc, float *out_map, float *out_l, int32_t *out_flags, void *workspace,
                          void *stream) {
     LLIE_REQUIRE(desc && x && y && out_sum && out_flags && workspace, "deltae: null pointer");
     LLIE_REQUIRE(desc->n > 0 && desc->h > 0 && desc->w > 0, "deltae: empty tensor");
@@ -464,11 +493,12 @@ static int deltae_launch(const llie_deltae_desc *desc, const float *x, const flo
     if (G < 1) G = 1;
     Workspace ws(workspace);
     const size_t slots = (size_t)G * desc->n;
-    LLIE_REQUIRE(slots * (2 * sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "deltae: workspace too small");
+    LLIE_REQUIRE(slots * (4 * sizeof(double) + sizeof(int)) <= ws.scratch_bytes, "deltae: workspace too small");
     a.part = reinterpret_cast<double *>(ws.scratch);
     a.part_sq = a.part + slots;
-    a.pflag = reinterpret_cast<int *>(ws.scratch + 2 * slots * sizeof(double));
+    a.pflag = reinterpret_cast<int *>(ws.scratch + 4 * slots * sizeof(double));
     a.out_sq = out_sq;
+    a.out_sqc = out_sqc;
     a.ticket = ws.tickets;
     dim3 grid(G, desc->n);
     kern<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
@@ -478,14 +508,21 @@ static int deltae_launch(const llie_deltae_desc *desc, const float *x, const flo
 
 extern "C" int llie_deltae(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
                            float *out_map, float *out_l, int32_t *out_flags, void *workspace, void *stream) {
-    return deltae_launch(desc, x, y, out_sum, nullptr, out_map, out_l, out_flags, workspace, stream);
+    return deltae_launch(desc, x, y, out_sum, nullptr, nullptr, out_map, out_l, out_flags, workspace, stream);
 }
 
 extern "C" int llie_deltae_sqerr(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
                                  double *out_sqerr, float *out_map, float *out_l, int32_t *out_flags,
                                  void *workspace, void *stream) {
     LLIE_REQUIRE(out_sqerr, "deltae_sqerr: null pointer");
-    return deltae_launch(desc, x, y, out_sum, out_sqerr, out_map, out_l, out_flags, workspace, stream);
+    return deltae_launch(desc, x, y, out_sum, out_sqerr, nullptr, out_map, out_l, out_flags, workspace, stream);
+}
+
+extern "C" int llie_deltae_sqerr_rgb(const llie_deltae_desc *desc, const float *x, const float *y, double *out_sum,
+                                     double *out_sqerr, double *out_sqerr_rgb, float *out_map, float *out_l,
+                                     int32_t *out_flags, void *workspace, void *stream) {
+    LLIE_REQUIRE(out_sqerr_rgb, "deltae_sqerr_rgb: null pointer");
+    return deltae_launch(desc, x, y, out_sum, out_sqerr, out_sqerr_rgb, out_map, out_l, out_flags, workspace, stream);
 }
 
 extern "C" int llie_deltae_loss_grad(const llie_deltae_desc *desc, const float *x, const float *y, float grad_scale,

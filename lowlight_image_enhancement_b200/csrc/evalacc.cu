@@ -13,7 +13,7 @@ struct EvalAccArgs {
     const double *sqerr, *ssim_sums, *de_sums, *edge_sum;
     const float *de_p95;
     const long long *edge_counts;
-    const double *psnr_table, *rgb_ssim_sums;
+    const double *psnr_table, *sqerr_rgb, *rgb_ssim_sums;
     const int *flags[6];
     double *acc;
 };
@@ -57,6 +57,28 @@ __global__ void eval_accumulate_kernel(const EvalAccArgs a) {
             if (d.slot_rgb_psnr[c] >= 0) a.acc[d.slot_rgb_psnr[c]] += row[3 + c];
         if (d.slot_rgb_psnr[3] >= 0) a.acc[d.slot_rgb_psnr[3]] += row[6];
     }
+    if (a.psnr_table == nullptr && a.sqerr_rgb != nullptr) {
+        // the same table row from the per-channel squared-error sums the dE00 pass leaves behind (llie_deltae_sqerr_rgb):
+        // the arithmetic of psnr_stats_kernel's finalize (pointwise.cu) with data_range 1, eps 1e-12 -- the defaults of
+        // channelwise.py:113-222, the only configuration this path is used for
+        double pc[3] = {0.0, 0.0, 0.0}, pmean = 0.0, cps = 0.0;
+        for (int i = 0; i < n; ++i) {
+            double msum = 0.0, psum = 0.0;
+            for (int c = 0; c < 3; ++c) {
+                const double mse = a.sqerr_rgb[i * 3 + c] / (double)d.hw;
+                const double p = 10.0 * log10(1.0 / fmax(mse, 1e-12));
+                pc[c] += p;
+                msum += mse;
+                psum += p;
+            }
+            pmean += psum / 3;
+            cps += 10.0 * log10(1.0 / fmax(msum / 3, 1e-12));
+        }
+        if (d.slot_cpsnr >= 0) a.acc[d.slot_cpsnr] += cps / n;
+        for (int c = 0; c < 3; ++c)
+            if (d.slot_rgb_psnr[c] >= 0) a.acc[d.slot_rgb_psnr[c]] += pc[c] / n;
+        if (d.slot_rgb_psnr[3] >= 0) a.acc[d.slot_rgb_psnr[3]] += pmean / n;
+    }
     if (a.rgb_ssim_sums != nullptr) {  // channelwise.py:262-295: float32 per-(image, channel) means, batch mean
         float ch[3] = {0.f, 0.f, 0.f}, mean = 0.f;
         for (int i = 0; i < n; ++i) {
@@ -83,7 +105,7 @@ __global__ void eval_accumulate_kernel(const EvalAccArgs a) {
 
 extern "C" int llie_eval_accumulate(const llie_eval_desc *desc, const double *sqerr, const double *ssim_sums,
                                     const double *de_sums, const float *de_p95, const double *edge_sum,
-                                    const int64_t *edge_counts, const double *psnr_table,
+                                    const int64_t *edge_counts, const double *psnr_table, const double *sqerr_rgb,
                                     const double *rgb_ssim_sums, const int32_t *flags0, const int32_t *flags1,
                                     const int32_t *flags2, const int32_t *flags3, const int32_t *flags4,
                                     const int32_t *flags5, double *acc, void *stream) {
@@ -98,9 +120,9 @@ extern "C" int llie_eval_accumulate(const llie_eval_desc *desc, const double *sq
         want_tab = want_tab || d.slot_rgb_psnr[q] >= 0;
         want_rs = want_rs || d.slot_rgb_ssim[q] >= 0;
     }
-    LLIE_REQUIRE((!want_tab || (psnr_table && d.c == 3)) && (!want_rs || (rgb_ssim_sums && d.c == 3)),
+    LLIE_REQUIRE((!want_tab || ((psnr_table || sqerr_rgb) && d.c == 3)) && (!want_rs || (rgb_ssim_sums && d.c == 3)),
                  "eval_accumulate: a channel-wise metric needs its table / sums and 3-channel images");
-    if (!want_tab) psnr_table = nullptr;
+    if (!want_tab) psnr_table = sqerr_rgb = nullptr;
     if (!want_rs) rgb_ssim_sums = nullptr;
     for (int s : slots) LLIE_REQUIRE(s >= -1 && s < d.k, "eval_accumulate: slot %d outside [0, %d)", s, d.k);
     LLIE_REQUIRE(d.slot_psnr < 0 || sqerr, "eval_accumulate: linear_psnr needs the squared-error sums");
@@ -110,7 +132,7 @@ extern "C" int llie_eval_accumulate(const llie_eval_desc *desc, const double *sq
                      (d.slot_edge < 0 || (edge_sum && edge_counts)),
                  "eval_accumulate: a requested colour metric has no input");
     llie::EvalAccArgs a{d, sqerr, ssim_sums, de_sums, edge_sum, de_p95,
-                        reinterpret_cast<const long long *>(edge_counts), psnr_table, rgb_ssim_sums,
+                        reinterpret_cast<const long long *>(edge_counts), psnr_table, sqerr_rgb, rgb_ssim_sums,
                         {flags0, flags1, flags2, flags3, flags4, flags5}, acc};
     llie::eval_accumulate_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
     LLIE_CUDA_OK(cudaGetLastError());

@@ -706,13 +706,6 @@ static std::atomic<int> g_ssim_seg_rows_a{0};  // 0 = heuristic
 // taps fold back, out(q) = t(q) + [1 <= q <= P] t(-q) + [W-1-P <= q <= W-2] t(2W-2-q), per axis.
 // Same tiling as the forward kernel: (A) coefficient tile with halo (zeros outside the image) -> smem,
 // (B) horizontal pass + column folds, (C) vertical pass + row folds, combine with x, y (8 B/elem read).
-struct SsimBwdArgs {
-    int n, c, h, w, ksize, clamp_in, gout_is_map, accumulate;
-    const float *x, *y, *win, *coef;
-    const float *gout;  // device scalar (upstream gradient of the reduced loss) or a [n,c,h,w] map
-    float *out_grad;
-    int tiles_x, tiles_y;
-};
 
 __device__ __forceinline__ float fold_extra(int P, const float *line, int stride, int q, int o0, int L,
                                             const float *sg) {
@@ -1374,7 +1367,7 @@ extern "C" int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x
 }
 
 extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
-                                       const float *coef, const float *grad_out, int32_t grad_out_is_map,
+                                       const float *win1d_host, const float *coef, const float *grad_out, int32_t grad_out_is_map,
                                        int32_t accumulate, float *out_grad, void *stream) {
     LLIE_REQUIRE(desc && x && y && win1d && coef && grad_out && out_grad, "ssim_loss_backward: null pointer");
     const llie_ssim_desc &d = *desc;
@@ -1390,6 +1383,8 @@ extern "C" int llie_ssim_loss_backward(const llie_ssim_desc *desc, const float *
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     const int g_ssim_path = g_ssim_path_a.load(std::memory_order_relaxed);
     const int g_ssim_seg_rows = g_ssim_seg_rows_a.load(std::memory_order_relaxed);
+    // default: TMA row ring + packed FP32 (ssim_ring.cu)
+    if (g_ssim_path == 0 && ssim_ring_bwd_eligible(a, win1d_host)) return ssim_ring_backward(a, win1d_host, st);
     if ((g_ssim_path == 0 || g_ssim_path == 3) && !grad_out_is_map && d.ksize == 11) {
         a.tiles_x = div_up(d.w, S2W);
         const long long cols = (long long)d.n * d.c * a.tiles_x;

@@ -20,10 +20,20 @@ struct SsimArgs {
     int seg_rows;  // streaming kernel: output rows per CTA
 };
 
+struct SsimBwdArgs {
+    int n, c, h, w, ksize, clamp_in, gout_is_map, accumulate;
+    const float *x, *y, *win, *coef;
+    const float *gout;  // device scalar (upstream gradient of the reduced loss) or a [n,c,h,w] map
+    float *out_grad;
+    int tiles_x, tiles_y;
+};
+
 // launchers of ssim_ring.cu; `eligible` tells ssim.cu whether the ring kernels take this problem
 bool ssim_ring_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host, bool want_map,
                         const float *coef);
 int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaStream_t st);
+bool ssim_ring_bwd_eligible(const SsimBwdArgs &a, const float *win_host);
+int ssim_ring_backward(SsimBwdArgs &a, const float *win_host, cudaStream_t st);
 int pick_seg_rows(long long cols, int h, int slots, int min_rows, int halo);
 
 }  // namespace llie

@@ -17,8 +17,9 @@
 //     by per-lane 4-byte cp.async that report to the SAME mbarrier (cp.async.mbarrier.arrive.noinc), so reflect /
 //     replicate / circular padding costs the consumers nothing and zero padding is a ring that starts zeroed.  The
 //     producing duty rotates over the four warps (row r is issued six rows ahead by warp r mod 4); slots are handed
-//     back through a second mbarrier per slot.  No CTA-wide barrier in the row loop (except with `clamp_in`, whose
-//     in-place clamp of the landed row needs one).
+//     back through a second mbarrier per slot.  No CTA-wide barrier in the row loop (`clamp_in` clamps the 14 + 14
+//     loaded values in registers: an in-place clamp of the landed row needed a __syncthreads per row and ran the
+//     DSSIM forward at C3 at 179 us instead of the ~120 us the unclamped kernel's rate predicts).
 // Same operation order per output as ssim_stream2_kernel -> equal to it to rounding (tests: <= 1e-6 relative).
 #include "ssim_common.cuh"
 #include "tma.cuh"
@@ -226,29 +227,6 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
             const int slot = i & (RD - 1);
             mbar_wait(&full[slot], (uint32_t)(i / RD) & 1u);
             float *rx = &ring[slot][0][0], *ry = rx + RROW;
-            if (CLAMP) {
-                // in-place clamp of the landed row (each thread its own two columns, the first eight threads the
-                // 2 x 8 lead / trail cells), finite check on the raw values of the owned columns
-                float2 *px = reinterpret_cast<float2 *>(rx + RLEAD) + tid, *py = reinterpret_cast<float2 *>(ry + RLEAD) + tid;
-                float2 vx = *px, vy = *py;
-                chkx = fma2(pack2(vx.x, vx.y), 0ull, chkx);
-                chky = fma2(pack2(vy.x, vy.y), 0ull, chky);
-                vx.x = fminf(fmaxf(vx.x, 0.f), 1.f); vx.y = fminf(fmaxf(vx.y, 0.f), 1.f);
-                vy.x = fminf(fmaxf(vy.x, 0.f), 1.f); vy.y = fminf(fmaxf(vy.y, 0.f), 1.f);
-                *px = vx;
-                *py = vy;
-                if (tid < 8) {
-                    const int s = tid < 4 ? 2 * tid : RLEAD + RCOLS + 2 * (tid - 4);
-                    float2 *qx = reinterpret_cast<float2 *>(rx + s), *qy = reinterpret_cast<float2 *>(ry + s);
-                    float2 ux = *qx, uy = *qy;
-                    ux.x = fminf(fmaxf(ux.x, 0.f), 1.f); ux.y = fminf(fmaxf(ux.y, 0.f), 1.f);
-                    uy.x = fminf(fmaxf(uy.x, 0.f), 1.f); uy.y = fminf(fmaxf(uy.y, 0.f), 1.f);
-                    *qx = ux;
-                    *qy = uy;
-                }
-                fence_proxy_async();  // these generic writes precede the TMA refill of the slot
-                __syncthreads();
-            }
             // ---- horizontal pass: 7 aligned pairs per tensor = window positions 0..13 (image columns gx-6 .. gx+7)
             const float *wx = rx + 2 * tid + 2, *wy = ry + 2 * tid + 2;
             f2_t h[M];
@@ -256,10 +234,17 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
             for (int q = 0; q < M; ++q) h[q] = 0ull;
 #pragma unroll
             for (int k = 0; k < NPOS / 2; ++k) {
-                const f2_t X = ld2(wx + 2 * k), Y = ld2(wy + 2 * k);
-                if (!CLAMP && k == 3) {  // positions 6, 7 are the thread's own columns
+                f2_t X = ld2(wx + 2 * k), Y = ld2(wy + 2 * k);
+                if (k == 3) {  // positions 6, 7 are the thread's own columns: finite check on the raw values
                     chkx = fma2(X, 0ull, chkx);
                     chky = fma2(Y, 0ull, chky);
+                }
+                if (CLAMP) {  // clamp(v, 0, 1) in registers (one FADD.SAT per value; NaN -> 0, flagged above)
+                    float xl, xh, yl, yh;
+                    unpack2(X, xl, xh);
+                    unpack2(Y, yl, yh);
+                    X = pack2(__saturatef(xl), __saturatef(xh));
+                    Y = pack2(__saturatef(yl), __saturatef(yh));
                 }
                 f2_t mm[M];
                 mm[0] = X;
@@ -407,6 +392,251 @@ __global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, cons
     if (tid == 0) *a.out_flags = ff;
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// DSSIM backward on the same skeleton (replaces ssim_bwd_stream2_kernel of ssim.cu as the default for a scalar upstream
+// gradient and the 11-tap window): grad_x = pad^T G^T (A1) + 2 x pad^T G^T (A2) + y pad^T G^T (A3), the three
+// coefficient planes written by the forward kernel filtered with the ADJOINT of the reflect-padded separable window.
+//   * Ring slot = one row of the three coefficient planes (zero outside the image: the ring starts zeroed, rows above /
+//     below the image are zero-filled by the issuing warp) + the x / y (/ old gradient) rows of the output row that
+//     ring entry completes, all by cp.async.bulk on one mbarrier per slot; no halo lanes (zero extension).
+//   * The mirror folds of the adjoint live in the WEIGHTS, as in ssim_bwd_stream2_kernel: a border column's horizontal
+//     taps gain the taps of its mirrored partner (per-thread tap pairs in registers), and the <= 2 x 5 input rows next
+//     to the top / bottom edge of the image scatter with row-dependent vertical weights (CTA-uniform, rare).
+//   * Horizontal and vertical passes in packed FP32 exactly like the forward kernel: 69 FFMA2 per thread-row for two
+//     columns instead of 138 FFMA.
+// Same operation order per output as ssim_bwd_stream2_kernel -> equal to it to rounding.
+struct BwdTaps {
+    float g[RK];
+};
+
+template <int II, class WF>
+__device__ __forceinline__ void scatter_row3(f2_t (&acc)[3][RK], const f2_t (&h)[3], f2_t (&done)[3], WF wf) {
+#pragma unroll
+    for (int j = 0; j < RK; ++j) {
+        const int sl = (II - j + RK) % RK;
+        const f2_t gj = bc2(wf(j));
+#pragma unroll
+        for (int q = 0; q < 3; ++q) acc[q][sl] = (j == 0) ? mul2(gj, h[q]) : fma2(gj, h[q], acc[q][sl]);
+    }
+#pragma unroll
+    for (int q = 0; q < 3; ++q) done[q] = acc[q][(II + 1) % RK];
+}
+
+constexpr size_t ring_bwd_smem(bool accumulate) {
+    return (size_t)RD * (3 * RROW + (accumulate ? 3 : 2) * RCOLS) * sizeof(float);
+}
+
+template <bool ACC>
+__global__ void __launch_bounds__(RT, 3) ssim_ring_bwd_kernel(const SsimBwdArgs a, const BwdTaps tp, int seg_rows) {
+    constexpr int NIO = ACC ? 3 : 2;
+    extern __shared__ __align__(128) unsigned char smraw[];
+    float (*ringc)[3][RROW] = reinterpret_cast<float (*)[3][RROW]>(smraw);
+    float (*ringio)[NIO][RCOLS] = reinterpret_cast<float (*)[NIO][RCOLS]>(smraw + (size_t)RD * 3 * RROW * sizeof(float));
+    __shared__ __align__(8) uint64_t full[RD], empty[RD];
+    const int H = a.h, W = a.w, tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
+    const int tpp = a.tiles_x * a.tiles_y;
+    const int plane = blockIdx.x / tpp;
+    const int trem = blockIdx.x - plane * tpp;
+    const int seg = trem / a.tiles_x, strip = trem - seg * a.tiles_x;
+    const int x0 = strip * RCOLS, y0 = seg * seg_rows;
+    const int rows_out = min(seg_rows, H - y0);
+    const int nrows_in = rows_out + 2 * RP;
+    const long long plane_elems = (long long)H * W;
+    const long long cstride = (long long)a.n * a.c * plane_elems;
+    const float *cb = a.coef + (long long)plane * plane_elems;
+    const float *xb = a.x + (long long)plane * plane_elems;
+    const float *yb = a.y + (long long)plane * plane_elems;
+    float *ob = a.out_grad + (long long)plane * plane_elems;
+
+    const int cx0 = max(x0 - RLEAD, 0), cx1 = min(x0 + RCOLS + RLEAD, W);
+    const uint32_t row_bytes = (uint32_t)(cx1 - cx0) * 4u;
+    const int doff = cx0 - (x0 - RLEAD);
+    const uint32_t io_bytes = (uint32_t)(min(x0 + RCOLS, W) - x0) * 4u;
+
+    {
+        float4 *r4 = reinterpret_cast<float4 *>(smraw);
+        for (int i = tid; i < (int)(ring_bwd_smem(ACC) / 16); i += RT) r4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tid == 0) {
+#pragma unroll
+            for (int s = 0; s < RD; ++s) {
+                mbar_init(&full[s], 1);
+                mbar_init(&empty[s], RT / 32);
+            }
+            mbar_fence_init();
+        }
+        fence_proxy_async();
+        __syncthreads();
+    }
+
+    auto issue_row = [&](int r) {  // executed by ONE whole warp
+        const int slot = r & (RD - 1), use = r / RD;
+        if (use > 0) mbar_wait(&empty[slot], (uint32_t)(use - 1) & 1u);
+        const int sy = y0 - RP + r;
+        const bool in_img = sy >= 0 && sy < H;
+        const bool has_io = r >= RK - 1;  // ring entry r completes output row y0 + r - 10
+        float *dst = &ringc[slot][0][0];
+        if (!in_img) {  // the coefficient planes are zero outside the image
+            float4 *r4 = reinterpret_cast<float4 *>(dst);
+            for (int i = lane; i < 3 * RROW / 4; i += 32) r4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            fence_proxy_async();
+            __syncwarp();
+        }
+        if (lane == 0) {
+            const uint32_t bytes = (in_img ? 3u * row_bytes : 0u) + (has_io ? (uint32_t)NIO * io_bytes : 0u);
+            if (bytes == 0u) {
+                mbar_arrive(&full[slot]);
+            } else {
+                mbar_expect_tx(&full[slot], bytes);
+                if (in_img) {
+                    const float *src = cb + (long long)sy * W + cx0;
+#pragma unroll
+                    for (int m = 0; m < 3; ++m) bulk_g2s(dst + m * RROW + doff, src + m * cstride, row_bytes, &full[slot]);
+                }
+                if (has_io) {
+                    const long long oo = (long long)(y0 + r - (RK - 1)) * W + x0;
+                    float *io = &ringio[slot][0][0];
+                    bulk_g2s(io, xb + oo, io_bytes, &full[slot]);
+                    bulk_g2s(io + RCOLS, yb + oo, io_bytes, &full[slot]);
+                    if (ACC) bulk_g2s(io + 2 * RCOLS, ob + oo, io_bytes, &full[slot]);
+                }
+            }
+        }
+    };
+
+    const int gx = x0 + 2 * tid;
+    // horizontal tap pairs of this thread's two columns with the mirror folds added: position p (image column
+    // gx - 6 + p) carries tap p - 1 of column gx and tap p - 2 of column gx + 1
+    f2_t WP[NPOS];
+    {
+        float gh[2][RK];
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const int gc = gx + c;
+            const bool cin = gc < W;
+#pragma unroll
+            for (int j = 0; j < RK; ++j) {
+                float wj = tp.g[j];
+                const int x = gc - RP + j;
+                if (cin && gc >= 1 && gc <= RP && x >= 0 && j + 2 * gc <= 2 * RP) wj += tp.g[j + 2 * gc];
+                if (cin && gc >= W - 1 - RP && gc <= W - 2 && x <= W - 1 && j + 2 * gc - 2 * W + 2 >= 0)
+                    wj += tp.g[j + 2 * gc - 2 * W + 2];
+                gh[c][j] = wj;
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < NPOS; ++p)
+            WP[p] = pack2((p >= 1 && p <= RK) ? gh[0][(p >= 1 && p <= RK) ? p - 1 : 0] : 0.f,
+                          (p >= 2 && p <= RK + 1) ? gh[1][(p >= 2 && p <= RK + 1) ? p - 2 : 0] : 0.f);
+    }
+    const bool seg_fold = (y0 <= RP) || (y0 + rows_out > H - 1 - RP);
+    const f2_t GS = bc2(__ldg(a.gout)), TWO = bc2(2.f);
+    f2_t acc[3][RK];
+#pragma unroll
+    for (int q = 0; q < 3; ++q)
+#pragma unroll
+        for (int j = 0; j < RK; ++j) acc[q][j] = 0ull;
+
+#pragma unroll
+    for (int r = 0; r < RPF; ++r)
+        if (r < nrows_in && (r & 3) == wrp) issue_row(r);
+
+    int ii = 0;
+#pragma unroll 1
+    for (int i = 0; i < nrows_in; ++i) {
+        if ((i & 3) == wrp && i + RPF < nrows_in) issue_row(i + RPF);
+        const int slot = i & (RD - 1);
+        mbar_wait(&full[slot], (uint32_t)(i / RD) & 1u);
+        f2_t h[3];
+#pragma unroll
+        for (int m = 0; m < 3; ++m) {
+            const float *wc = &ringc[slot][m][0] + 2 * tid + 2;
+            f2_t v = 0ull;
+#pragma unroll
+            for (int k = 0; k < NPOS / 2; ++k) {
+                float lo, hi;
+                unpack2(ld2(wc + 2 * k), lo, hi);
+                if (2 * k >= 1) v = fma2(bc2(lo), WP[2 * k], v);           // position 0 carries no tap
+                if (2 * k + 1 <= RK + 1) v = fma2(bc2(hi), WP[2 * k + 1], v);  // position 13 neither
+            }
+            h[m] = v;
+        }
+        f2_t X = 0ull, Y = 0ull, O = 0ull;
+        if (i >= RK - 1) {
+            X = ld2(&ringio[slot][0][0] + 2 * tid);
+            Y = ld2(&ringio[slot][1][0] + 2 * tid);
+            if (ACC) O = ld2(&ringio[slot][2][0] + 2 * tid);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&empty[slot]);
+        const int p = y0 - RP + i;
+        const bool vfold = seg_fold && (p < RP || p >= H - RP);  // CTA-uniform; only <= 2 x 5 rows of the image
+        f2_t done[3];
+        if (!vfold) {
+            auto wf = [&](int j) { return tp.g[j]; };
+            switch (ii) {
+                case 0: scatter_row3<0>(acc, h, done, wf); break;
+                case 1: scatter_row3<1>(acc, h, done, wf); break;
+                case 2: scatter_row3<2>(acc, h, done, wf); break;
+                case 3: scatter_row3<3>(acc, h, done, wf); break;
+                case 4: scatter_row3<4>(acc, h, done, wf); break;
+                case 5: scatter_row3<5>(acc, h, done, wf); break;
+                case 6: scatter_row3<6>(acc, h, done, wf); break;
+                case 7: scatter_row3<7>(acc, h, done, wf); break;
+                case 8: scatter_row3<8>(acc, h, done, wf); break;
+                case 9: scatter_row3<9>(acc, h, done, wf); break;
+                default: scatter_row3<10>(acc, h, done, wf); break;
+            }
+        } else {
+            float wv[RK];
+#pragma unroll
+            for (int j = 0; j < RK; ++j) {
+                const int y = y0 + i - j;  // output row that tap j of this input row feeds
+                float wj = tp.g[j];
+                if (y >= 1 && y <= RP && p >= 0 && p + y <= RP) wj += tp.g[p + y + RP];
+                if (y >= H - 1 - RP && y <= H - 2 && p <= H - 1 && p >= 2 * H - 2 - y - RP)
+                    wj += tp.g[p - (2 * H - 2 - y) + RP];
+                wv[j] = wj;
+            }
+            auto wf = [&](int j) { return wv[j]; };
+            switch (ii) {
+                case 0: scatter_row3<0>(acc, h, done, wf); break;
+                case 1: scatter_row3<1>(acc, h, done, wf); break;
+                case 2: scatter_row3<2>(acc, h, done, wf); break;
+                case 3: scatter_row3<3>(acc, h, done, wf); break;
+                case 4: scatter_row3<4>(acc, h, done, wf); break;
+                case 5: scatter_row3<5>(acc, h, done, wf); break;
+                case 6: scatter_row3<6>(acc, h, done, wf); break;
+                case 7: scatter_row3<7>(acc, h, done, wf); break;
+                case 8: scatter_row3<8>(acc, h, done, wf); break;
+                case 9: scatter_row3<9>(acc, h, done, wf); break;
+                default: scatter_row3<10>(acc, h, done, wf); break;
+            }
+        }
+        ii = ii == RK - 1 ? 0 : ii + 1;
+        if (i >= RK - 1 && gx < W) {  // W is a multiple of 4 and gx is even: both columns are inside
+            const int oy = y0 + i - (RK - 1);
+            float xr[2], yr[2];
+            unpack2(X, xr[0], xr[1]);
+            unpack2(Y, yr[0], yr[1]);
+            f2_t XV = X, YV = Y;
+            if (a.clamp_in) {
+                XV = pack2(fminf(fmaxf(xr[0], 0.f), 1.f), fminf(fmaxf(xr[1], 0.f), 1.f));
+                YV = pack2(fminf(fmaxf(yr[0], 0.f), 1.f), fminf(fmaxf(yr[1], 0.f), 1.f));
+            }
+            const f2_t t = fma2(YV, done[2], fma2(mul2(TWO, XV), done[1], done[0]));
+            float r0, r1, o0, o1;
+            unpack2(mul2(GS, t), r0, r1);
+            unpack2(O, o0, o1);
+            if (a.clamp_in) {
+                r0 = (xr[0] >= 0.f && xr[0] <= 1.f) ? r0 : 0.f;
+                r1 = (xr[1] >= 0.f && xr[1] <= 1.f) ? r1 : 0.f;
+            }
+            *reinterpret_cast<float2 *>(ob + (long long)oy * W + gx) = make_float2(o0 + r0, o1 + r1);
+        }
+    }
+}
+
 }  // namespace
 
 bool ssim_ring_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host, bool want_map,
@@ -444,6 +674,33 @@ int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaS
     } else {
         if (clamp) ssim_ring_kernel<false, false, true><<<(int)grid, RT, 0, st>>>(a, tp);
         else ssim_ring_kernel<false, false, false><<<(int)grid, RT, 0, st>>>(a, tp);
+    }
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
+bool ssim_ring_bwd_eligible(const SsimBwdArgs &a, const float *win_host) {
+    return win_host != nullptr && a.ksize == RK && !a.gout_is_map && (a.w & 3) == 0 && aligned16(a.x) &&
+           aligned16(a.y) && aligned16(a.coef) && aligned16(a.out_grad);
+}
+
+int ssim_ring_backward(SsimBwdArgs &a, const float *win_host, cudaStream_t st) {
+    BwdTaps tp;
+    for (int j = 0; j < RK; ++j) tp.g[j] = win_host[j];
+    a.tiles_x = div_up(a.w, RCOLS);
+    const long long cols = (long long)a.n * a.c * a.tiles_x;
+    const int rows = pick_seg_rows(cols, a.h, kNumSM * 3, 64, RK - 1);
+    a.tiles_y = div_up(a.h, rows);
+    const long long grid = cols * a.tiles_y;
+    LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
+    if (a.accumulate) {
+        LLIE_CUDA_OK(cudaFuncSetAttribute(ssim_ring_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)ring_bwd_smem(true)));
+        ssim_ring_bwd_kernel<true><<<(int)grid, RT, ring_bwd_smem(true), st>>>(a, tp, rows);
+    } else {
+        LLIE_CUDA_OK(cudaFuncSetAttribute(ssim_ring_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)ring_bwd_smem(false)));
+        ssim_ring_bwd_kernel<false><<<(int)grid, RT, ring_bwd_smem(false), st>>>(a, tp, rows);
     }
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;

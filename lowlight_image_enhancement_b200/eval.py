@@ -244,10 +244,11 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
     colour = [n for n in names if n in _COLOUR]
     if "linear_psnr" in names and not colour:
         return False
+    ride_rgb = bool(rgbp) and bool(colour)   # the CPSNR / RGB-PSNR sums ride on the colour pass: no PSNR launch
     n, c, h, w = p.shape
     slot = {nm: i for i, nm in enumerate(names)}
     fl: List[Optional[Tensor]] = []
-    sq = sums = dmap = lpl = None
+    sq = sqc = sums = dmap = lpl = None
     ssim_sums, ssim_count, ssim_c = None, 1, 1
     main = torch.cuda.current_stream(dev)
     joined = None
@@ -274,9 +275,11 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
     if colour:
         want_map = any(_COLOUR[nm][0] for nm in colour)
         want_l = any(_COLOUR[nm][1] for nm in colour)
-        sql = [] if "linear_psnr" in names else None
-        sums, f, dmap, lpl = Fn.deltae(p, t, variant=0, clamp_in=True, want_map=want_map, want_l=want_l, sqerr_out=sql)
+        sql = [] if ("linear_psnr" in names or ride_rgb) else None
+        sums, f, dmap, lpl = Fn.deltae(p, t, variant=0, clamp_in=True, want_map=want_map, want_l=want_l, sqerr_out=sql,
+                                       sqerr_rgb=ride_rgb)
         sq = sql[0] if sql is not None else None
+        sqc = sql[1] if ride_rgb else None
         fl.append(f)
     p95 = None
     if "deltae2000_p95" in names:
@@ -289,7 +292,7 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
         _, ecnt, esum = Fn.select_quantiles(dmap.view(n, h * w), [], joint=True, gate=grad.view(n, h * w),
                                             gate_thr=thr.view(n).contiguous(), want_sum=True)
     table = rsums = None
-    if rgbp:
+    if rgbp and not ride_rgb:
         table, f, _ = Fn.psnr_stats(p, t, n, c, h * w, cast_first=True, clamp_hi=None, data_range=1.0, eps=1e-12)
         fl.append(f)
     if rgbs:
@@ -309,7 +312,8 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
                      (C.c_int32 * 4)(*[slot.get(f"rgb_ssim_{k}", -1) for k in ("R", "G", "B", "mean")]))
     with torch.cuda.device(dev):
         rc = nat.lib().llie_eval_accumulate(d, nat.ptr(sq), nat.ptr(ssim_sums), nat.ptr(sums), nat.ptr(p95),
-                                            nat.ptr(esum), nat.ptr(ecnt), nat.ptr(table), nat.ptr(rsums),
+                                            nat.ptr(esum), nat.ptr(ecnt), nat.ptr(table), nat.ptr(sqc),
+                                            nat.ptr(rsums),
                                             nat.ptr(fl[0]), nat.ptr(fl[1]), nat.ptr(fl[2]), nat.ptr(fl[3]),
                                             nat.ptr(fl[4]), nat.ptr(fl[5]), nat.ptr(acc.vec), nat.stream_ptr(dev))
     nat.check(rc, "llie_eval_accumulate")

@@ -278,11 +278,14 @@ def test_upstream_scalar_is_applied_in_place_and_survives_retained_graphs(dev):
             assert float((gr - unit * s).abs().max()) <= 2e-6 * abs(s) * float(unit.abs().max()), s
 
 
-@pytest.mark.parametrize("shape", [(2, 3, 64, 300), (1, 3, 257, 513), (1, 1, 40, 11), (1, 3, 33, 47), (16, 3, 512, 512)])
+@pytest.mark.parametrize("shape", [(2, 3, 64, 300), (1, 3, 257, 513), (1, 1, 40, 11), (1, 3, 33, 47), (16, 3, 512, 512),
+                                   (1, 2, 12, 260), (2, 1, 23, 1024), (1, 3, 700, 264)])
 def test_two_column_dssim_kernels_vs_one_column(dev, shape):
-    """SSIMLoss forward (coefficient planes) + backward on the two-column kernels (default for the 11-tap window) against
+    """SSIMLoss forward (coefficient planes) + backward on the default kernels for the 11-tap window (TMA row ring +
+    packed FP32 when W % 4 == 0, else the two-column cp.async kernels) and on the two-column kernels (path 3) against
     the one-column streaming kernels (LLIE_TUNE_SSIM_PATH = 2): same loss to 1e-6 relative, same gradient to 2e-6 of
-    its scale (four moment maps instead of five in forward; identical tap order in backward)."""
+    its scale (four moment maps instead of five in forward; identical tap order in backward).  The small-H shapes put
+    the top and bottom mirror folds into one row segment, W = 260 / 264 a partial strip next to a full one."""
     from lowlight_image_enhancement_b200 import _native as nat
     from lowlight_image_enhancement_b200.NewBP_model.losses import SSIMLoss
     g = torch.Generator().manual_seed(sum(shape))
@@ -291,7 +294,7 @@ def test_two_column_dssim_kernels_vs_one_column(dev, shape):
     crit = SSIMLoss()
     out = {}
     try:
-        for path in (2, 0):
+        for path in (2, 3, 0):
             nat.check(nat.lib().llie_tune(3, path), "llie_tune")
             x = x0.clone().requires_grad_(True)
             loss = crit(x, b)
@@ -299,9 +302,11 @@ def test_two_column_dssim_kernels_vs_one_column(dev, shape):
             out[path] = (loss.detach().clone(), x.grad.clone())
     finally:
         nat.check(nat.lib().llie_tune(3, 0), "llie_tune")
-    (l2, g2), (l0, g0) = out[2], out[0]
-    assert abs(float(l0) - float(l2)) <= 1e-6 * abs(float(l2))
-    assert float((g0 - g2).abs().max()) <= 2e-6 * float(g2.abs().max())
+    l2, g2 = out[2]
+    for path in (3, 0):
+        l0, g0 = out[path]
+        assert abs(float(l0) - float(l2)) <= 1e-6 * abs(float(l2)), path
+        assert float((g0 - g2).abs().max()) <= 2e-6 * float(g2.abs().max()), path
     assert float(g2.abs().max()) > 0
 
 

@@ -1,4 +1,4 @@
-"""torch.profiler view of image_metrics (4 eval metrics) on one full-resolution pair."""
+"""torch.profiler view of image_metrics (4 eval metrics, or the 7 of configs[3] with --c4) on one full-resolution pair."""
 import torch
 from torch.profiler import ProfilerActivity, profile
 
@@ -9,7 +9,10 @@ g = torch.Generator(device=dev).manual_seed(4000)
 gt = torch.round(255 * torch.rand(1, 3, 2848, 4256, device=dev, generator=g)) / 255
 gt = torch.round(255 * torch.nn.functional.avg_pool2d(gt, 5, 1, 2)) / 255
 pred = (gt + 0.03 * torch.randn(gt.shape, device=dev, generator=g)).clamp(0, 1)
-names = ["linear_psnr", "linear_ssim", "deltae2000_mean", "edge_deltae2000_mean"]
+import sys
+from lowlight_image_enhancement_b200.eval import C4_METRICS
+names = list(C4_METRICS) if "--c4" in sys.argv else ["linear_psnr", "linear_ssim", "deltae2000_mean", "edge_deltae2000_mean"]
+print(names)
 for _ in range(3):
     image_metrics(pred, gt, names)
 torch.cuda.synchronize()
