@@ -283,6 +283,8 @@ def run_ours(args, rank, world, dev):
     from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw
     from oracle import psf_ops  # kernel constants for input synthesis only
 
+    if args.prefetch_rows >= 0:
+        nat.check(nat.lib().llie_tune(7, args.prefetch_rows), "llie_tune")  # LLIE_TUNE_PHYS_PREFETCH
     if args.no_pdl:
         nat.check(nat.lib().llie_tune(5, 0), "llie_tune")  # LLIE_TUNE_PHYS_PDL
     if args.ring_rows:
@@ -831,6 +833,7 @@ def main():
     ap.add_argument("--ring-rows", type=int, default=0, help="A/B: rows per work item of the phys ring kernels")
     ap.add_argument("--no-overlap", action="store_true", help="A/B: every launch waits for the previous grid at its top")
     ap.add_argument("--no-pdl", action="store_true", help="A/B: plain launches instead of programmatic dependent launch")
+    ap.add_argument("--prefetch-rows", type=int, default=-1, help="A/B: rows of a ring CTA's first item prefetched into L2 before its grid wait (0 = off)")
     args = ap.parse_args()
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":

@@ -66,6 +66,9 @@ int llie_check_device(void);
 #define LLIE_TUNE_PHYS_PDL 5 /* 1 (default): ring kernels are launched with programmatic stream serialization, so the
                                 prologue of a kernel overlaps the tail of the previous one | 0 plain launches */
 /* key 6 (process-wide stream overlap, ABI 2) is gone: llie_phys_desc.stream_overlap */
+#define LLIE_TUNE_PHYS_PREFETCH 7 /* rows per tensor of its first item that a ring CTA prefetches into L2 before it waits
+                                     for the previous grid (no architectural effect, legal under serialised semantics);
+                                     default 8, 0 = off */
 int llie_tune(int key, int value);
 
 /* ------------------------------------------------------------------------

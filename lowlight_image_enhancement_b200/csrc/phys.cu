@@ -230,6 +230,7 @@ extern "C" int llie_tune(int key, int value) {
             return LLIE_OK;
         case LLIE_TUNE_PHYS_ROWS: phys_ring_set_rows(value); return LLIE_OK;
         case LLIE_TUNE_PHYS_PDL: phys_ring_set_pdl(value); return LLIE_OK;
+        case LLIE_TUNE_PHYS_PREFETCH: phys_ring_set_prefetch(value); return LLIE_OK;
         case 6:
             llie::set_error("llie_tune: key 6 (process-wide stream overlap) was removed in ABI 3; set "
                             "llie_phys_desc.stream_overlap on the calls that meet the contract");

@@ -87,5 +87,6 @@ int launch_phys_bwd_ring(PhysArgs &a, cudaStream_t st);
 int launch_phys_fused_ring(PhysArgs &a, void *workspace, cudaStream_t st);
 void phys_ring_set_rows(int r);
 void phys_ring_set_pdl(int on);
+void phys_ring_set_prefetch(int on);
 
 }  // namespace llie

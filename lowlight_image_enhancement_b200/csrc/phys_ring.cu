@@ -67,6 +67,7 @@ struct RingGeom {
     double *samp;  // [n] per-sample sums (finalize scratch)
     int *pflag;    // [gridDim.x]
     int early;     // stream-overlap contract (llie_phys_desc.stream_overlap): only the workspace depends on the previous kernel
+    int prefetch;  // rows per tensor of the CTA's first item prefetched into L2 before griddepcontrol.wait (LLIE_TUNE_PHYS_PREFETCH)
 };
 
 struct Item {
@@ -255,6 +256,33 @@ __device__ __forceinline__ void produce_slot(float *slot, uint64_t *full, const 
     }
 }
 
+// L2 prefetch of the first rows of this CTA's first item, issued BEFORE griddepcontrol.wait.  A prefetch has no
+// architectural effect (L2 is the point of coherence: whatever the previous kernel still writes to these lines lands in
+// the same L2 lines), so it is legal under the default, fully serialised contract -- unlike the early loads of the
+// stream-overlap mode.  Under programmatic dependent launch the CTAs of launch i + 1 become resident while launch i
+// drains, and their opening rows stream into L2 behind the previous launch's tail.  Measured at C2 (graphs of 200
+// serialised launches): gradient-only kernel 17.4 -> 16.3 us with 8 rows per tensor, forward 14.8 -> 14.7, fused value +
+// gradient unchanged (23.8: its tail is the last-CTA finalize, not the ramp); 16 or more rows per CTA compete with the
+// previous launch's stragglers for DRAM and cost 2-3 us.  Default 8 rows (two ring slots).
+__device__ __forceinline__ void l2_prefetch(const void *p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void prefetch_first_item(const PhysArgs &a, const RingGeom &g, int halo, int lane) {
+    if ((int)blockIdx.x >= g.items) return;
+    const llie_phys_desc &d = a.d;
+    const Item it = decode_item(blockIdx.x, g, d.c_out, d.h);
+    const int cs = it.x0 - 4 < 0 ? 0 : it.x0 - 4;
+    const int ce = it.x0 + kCols + 4 > d.w ? d.w : it.x0 + kCols + 4;
+    const uint32_t bytes = (uint32_t)(ce - cs) * 4u;
+    const int r0 = max(it.ya - halo, 0), r1 = min(min(it.yb + halo, d.h), r0 + g.prefetch);
+    const float *pp = a.pred + (long long)it.plane * d.h * d.w + cs;
+    const float *op = a.obs + (long long)it.plane * d.h * d.w + cs;
+    for (int r = r0 + lane; r < r1; r += 32) {
+        l2_prefetch(pp + (long long)r * d.w, bytes);
+        l2_prefetch(op + (long long)r * d.w, bytes);
+    }
+}
+
 // CTA epilogue: OR of the per-thread flags (one barrier), thread 0 publishes the CTA's flag word and takes a ticket;
 // returns true in ALL threads of the last CTA to arrive.  `early`: thread 0 first waits for the previous grid (the
 // workspace is shared with it; a no-op when it already waited for this CTA's per-item partial).
@@ -391,8 +419,9 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
     const int H = d.h, W = d.w, mode = d.pad_mode;
     const int tid = threadIdx.x, lane = tid & 31, wrp = tid >> 5;
     pdl_launch_dependents();  // the next kernel's CTAs may run their prologue while this grid drains
+    if (!g.early && g.prefetch && wrp == kCons / 32) prefetch_first_item(a, g, 2, lane);
     ring_setup(ring, full, empty, (W % kCols) != 0);
-    if (!g.early) pdl_wait();  // nothing before this line reads or writes global memory
+    if (!g.early) pdl_wait();  // nothing before this line reads or writes global memory (the L2 prefetch has no effect on it)
     int iter = 0;
 
     float chk_p = 0.f, chk_o = 0.f;  // x*0 accumulators: NaN iff a non-finite value went through a clip
@@ -569,9 +598,10 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
     const int fold_bot = mode == LLIE_PAD_REFLECT ? H - 2 : H - 1;  // image row that padded row H reads
     RING_STAMP(threadIdx.x == 0, 0);
     pdl_launch_dependents();
+    if (!g.early && g.prefetch && wrp == kCons / 32) prefetch_first_item(a, g, 4, lane);
     ring_setup(ring, full, empty, (W % kCols) != 0);
     RING_STAMP(threadIdx.x == 0, 1);
-    if (!g.early) pdl_wait();  // nothing before this line reads or writes global memory
+    if (!g.early) pdl_wait();  // nothing before this line reads or writes global memory (the L2 prefetch has no effect on it)
     RING_STAMP(threadIdx.x == 0, 2);
     RingState rs{0, 0u};
 
@@ -800,6 +830,8 @@ static std::atomic<int> g_ring_rows{0};  // 0 = heuristic (LLIE_TUNE_PHYS_ROWS)
 void phys_ring_set_rows(int r) { g_ring_rows.store(r, std::memory_order_relaxed); }
 static std::atomic<int> g_ring_pdl{1};   // programmatic dependent launch of the ring kernels (LLIE_TUNE_PHYS_PDL)
 void phys_ring_set_pdl(int on) { g_ring_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
+static std::atomic<int> g_ring_prefetch{8};  // pre-wait L2 prefetch (LLIE_TUNE_PHYS_PREFETCH)
+void phys_ring_set_prefetch(int rows) { g_ring_prefetch.store(rows < 0 ? 0 : rows, std::memory_order_relaxed); }
 // Stream-overlap contract (llie_phys_desc.stream_overlap, a PER-CALL promise): no buffer of this ring launch except the
 // workspace is read or written by the kernel launched right before it on the same stream.  The kernels then wait for
 // the previous grid only where they touch the workspace, so the CTAs of launch i + 1 stream and compute on the SMs
@@ -839,6 +871,7 @@ static RingGeom make_geom(const llie_phys_desc &d, int &grid) {
     g.items = (int)items;
     grid = items < slots ? (int)items : slots;
     g.early = overlap ? 1 : 0;
+    g.prefetch = g_ring_pdl.load(std::memory_order_relaxed) ? g_ring_prefetch.load(std::memory_order_relaxed) : 0;
     return g;
 }
 
