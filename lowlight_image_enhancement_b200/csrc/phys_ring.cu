@@ -318,25 +318,35 @@ __device__ void ring_finalize(const PhysArgs &a, const RingGeom &g, int *red_i, 
     const int per = g.items_per_sample;
     double *samp = N <= kSmemSamples ? s_samp : g.samp;
     int fl = 0;
+    const bool staged = g.items <= kStageMax;
     {
+        // the first batch of partial loads is issued BEFORE the flag words are consumed: partials and flags then share
+        // one L2 round trip instead of two on the serial tail of the launch
+        double v[8];
+        const int bp = threadIdx.x;
+        if (staged) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = bp + k * NT < g.items ? __ldcg(g.part + bp + k * NT) : 0.0;
+        }
         int fv[4];
         for (int b0 = threadIdx.x; b0 < (int)gridDim.x; b0 += 4 * NT) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) fv[k] = b0 + k * NT < (int)gridDim.x ? __ldcg(g.pflag + b0 + k * NT) : 0;
             fl |= (fv[0] | fv[1]) | (fv[2] | fv[3]);
         }
-    }
-    const bool staged = g.items <= kStageMax;
-    if (staged) {
-        for (int b0 = threadIdx.x; b0 < g.items; b0 += 8 * NT) {
-            double v[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) v[k] = b0 + k * NT < g.items ? __ldcg(g.part + b0 + k * NT) : 0.0;
+        if (staged) {
 #pragma unroll
             for (int k = 0; k < 8; ++k)
-                if (b0 + k * NT < g.items) stage[b0 + k * NT] = v[k];
+                if (bp + k * NT < g.items) stage[bp + k * NT] = v[k];
+            for (int b0 = threadIdx.x + 8 * NT; b0 < g.items; b0 += 8 * NT) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] = b0 + k * NT < g.items ? __ldcg(g.part + b0 + k * NT) : 0.0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (b0 + k * NT < g.items) stage[b0 + k * NT] = v[k];
+            }
+            __syncthreads();
         }
-        __syncthreads();
     }
     RING_STAMP(threadIdx.x == 0, 10);
     const double *src = staged ? stage : g.part;
