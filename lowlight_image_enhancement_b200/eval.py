@@ -402,6 +402,69 @@ def evaluate_pairs(pairs, names: Sequence[str], *, n_items: Optional[int] = None
     return acc.reduce()
 
 
+class ValidationMetrics:
+    """The metric section of `ImageRestorationModel.dist_validation` (image_restoration_model.py:346-351, 416-428,
+    444-464) as an object the reference's loop can hold instead of `self.metric_results`:
+
+        vm = ValidationMetrics(self.opt['val']['metrics'])        # {name: {'type': <metric function>, **kwargs}}
+        for idx, val_data in enumerate(dataloader):               # the reference's own `idx % world_size == rank` loop
+            ...
+            vm.update(visuals['result'], visuals['gt'])           # device tensors: skip the .cpu() of irm:338
+        metrics_dict = vm.reduce()                                 # {name: mean over all images of all ranks}
+
+    Same bookkeeping as the reference -- one running sum per configured NAME (two names may share a metric type with
+    different kwargs), an image count, the division by the reduced count -- but the sums live in one float64 device
+    vector, every image costs no host synchronisation, and the `dist.reduce(dst=0)` of irm:453 becomes one
+    `all_reduce` (every rank gets the means).  `reduce()` also reports `count` and `nonfinite_inputs`."""
+
+    def __init__(self, metrics_opt, device: torch.device | str = "cuda", group=None):
+        if not metrics_opt:
+            raise ValueError("opt['val']['metrics'] is empty")
+        self.names = list(metrics_opt.keys())
+        self.types, self.kwargs = [], []
+        for name in self.names:
+            o = dict(metrics_opt[name])
+            if "type" not in o:
+                raise KeyError(f"metric '{name}' has no 'type' (irm:422)")
+            t = o.pop("type")
+            if t not in METRIC_FUNCTIONS:
+                raise AttributeError(f"metric type '{t}' of '{name}' is not a metric function; available: "
+                                     f"{sorted(METRIC_FUNCTIONS)}")
+            self.types.append(t)
+            self.kwargs.append(o)
+        self.acc = ShardedMeans(self.names, device, group)
+        # the one-launch epilogue keys the accumulator by metric TYPE: usable when no type repeats
+        self._fast = len(set(self.types)) == len(self.types)
+        self._opts = {t: kw for t, kw in zip(self.types, self.kwargs) if kw}
+        self._flags = torch.zeros(1, dtype=torch.int32, device=self.acc.device)
+
+    @torch.no_grad()
+    def update(self, result: Tensor, gt: Tensor) -> None:
+        """`self.metric_results[name] += metric(result, gt, **opt_)` for every configured metric (irm:424-428)."""
+        if result.dim() == 3:
+            result, gt = result.unsqueeze(0), gt.unsqueeze(0)
+        if self._fast and self.acc.device.type == "cuda":
+            self.acc.names = self.types
+            try:
+                if accumulate_image_metrics(result, gt, self.types, self.acc, **self._opts):
+                    return
+            finally:
+                self.acc.names = self.names
+        self._flags.zero_()
+        vals = []
+        cache: dict = {}
+        p, t, _ = _stage_pair(result, gt)
+        for typ, kw in zip(self.types, self.kwargs):
+            kw = dict(kw)
+            if typ in _RGB_PSNR or typ in _RGB_SSIM:
+                kw["cache"] = cache
+            vals.append(METRIC_FUNCTIONS[typ](p, t, self._flags, **kw).reshape(()))
+        self.acc.add(torch.stack(vals), self._flags)
+
+    def reduce(self) -> Dict[str, float]:
+        return self.acc.reduce()
+
+
 # ------------------------------------------------------------------------------------------------
 # tiled inference of the validation driver (irm:167-241): split on the device, merge on the device
 # ------------------------------------------------------------------------------------------------
@@ -440,6 +503,14 @@ class TileGrid:
 
         self.indices = [(i, j) for i in starts(h, self.crop_h, step_i) for j in starts(w, self.crop_w, step_j)]
         self._idx_dev = {}
+
+    @classmethod
+    def from_val_opt(cls, h: int, w: int, val_opt, scale: int = 1) -> "TileGrid":
+        """The grid `ImageRestorationModel.grids` builds from `opt['val']` (irm:172-181): absolute `crop_size_h` /
+        `crop_size_w` when present, else `int(crop_size_{h,w}_ratio * size)`."""
+        ch = val_opt["crop_size_h"] if "crop_size_h" in val_opt else int(val_opt.get("crop_size_h_ratio") * h)
+        cw = val_opt.get("crop_size_w") if "crop_size_w" in val_opt else int(val_opt.get("crop_size_w_ratio") * w)
+        return cls(h, w, ch, cw, scale)
 
     def split(self, lq: Tensor) -> Tensor:
         """[1, C, h/scale, w/scale] -> [T, C, crop_h/scale, crop_w/scale] (tile order = `indices`)."""

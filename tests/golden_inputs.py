@@ -230,3 +230,28 @@ def srgb_inputs():
     x[0, 0, 0, :8] = torch.tensor([0.0, 1.0, 0.0031308, 0.0031307, 0.0031309, 1e-8, 0.5, 0.18])
     x[1, 1, 1, :8] = torch.logspace(-6, 0, 8)
     return x
+
+
+# ---- validation tiling (image_restoration_model.py:167-241): crop grids over odd sizes, ratio-defined crops, a single
+# tile, a super-resolution scale
+TILE_CASES = [
+    dict(h=150, w=250, scale=1, val=dict(crop_size_h=64, crop_size_w=48)),
+    dict(h=64, w=64, scale=1, val=dict(crop_size_h=64, crop_size_w=64)),
+    dict(h=111, w=87, scale=1, val=dict(crop_size_h_ratio=0.5, crop_size_w_ratio=0.4)),
+    dict(h=32, w=320, scale=1, val=dict(crop_size_h=32, crop_size_w=100)),
+    dict(h=128, w=192, scale=2, val=dict(crop_size_h=51, crop_size_w=65)),
+    dict(h=97, w=131, scale=1, val=dict(crop_size_h=48, crop_size_w=48)),
+]
+
+
+def tile_inputs(k):
+    """(lq [1, 3, h / scale, w / scale], outs_fn(T, tiles) -> [T, 3, crop_h, crop_w] seeded network outputs)."""
+    case = TILE_CASES[k]
+    g = torch.Generator().manual_seed(7000 + k)
+    s = case["scale"]
+    lq = torch.rand(1, 3, case["h"] // s, case["w"] // s, generator=g)
+
+    def outs_fn(t, tiles):
+        return torch.rand(t, 3, tiles.shape[-2] * s, tiles.shape[-1] * s, generator=g)
+
+    return lq, outs_fn

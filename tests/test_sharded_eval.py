@@ -4,6 +4,7 @@ CPU part: world_size-2 gloo run of the host logic (image -> rank rule of irm:359
 sums, ONE all-reduce, means as irm:459-464) with an injected host metric function.
 GPU part: the device metric scalars equal the adapters' floats and the driver's means equal the
 serial loop over adapters."""
+import math
 import os
 import socket
 
@@ -161,6 +162,43 @@ def test_tile_grid_indices(h, w, ch, cw):
         assert torch.equal(tiles[t, 0], lq[0, 0, i:i + g.crop_h, j:j + g.crop_w])
 
 
+def _tile_golden():
+    import os
+    import numpy as np
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "tile_vectors.npz"))
+
+
+def test_tile_grid_matches_reference_grids():
+    """Tile origins and the tile batch against the reference's OWN `grids` (image_restoration_model.py:167-213), run
+    unmodified by tests/golden/make_golden_tiles.py: absolute and ratio-defined crops, one tile, scale 2."""
+    from lowlight_image_enhancement_b200.eval import TileGrid
+    from tests.golden_inputs import TILE_CASES, tile_inputs
+    gold = _tile_golden()
+    for k, case in enumerate(TILE_CASES):
+        g = TileGrid.from_val_opt(case["h"], case["w"], case["val"], case["scale"])
+        assert [list(ij) for ij in g.indices] == gold[f"idx{k}"].tolist(), k
+        lq, _ = tile_inputs(k)
+        tiles = g.split(lq)
+        assert list(tiles.shape) == gold[f"tiles_shape{k}"].tolist(), k
+        assert float(tiles.double().sum()) == float(gold[f"tiles_sum{k}"]), k
+
+
+@pytest.mark.gpu
+def test_tile_merge_matches_reference_grids_inverse():
+    """`TileGrid.merge` (llie_tile_merge, one kernel on the device) against the reference's own `grids_inverse`
+    (image_restoration_model.py:215-241: host accumulation, count map, division): bit for bit."""
+    from lowlight_image_enhancement_b200.eval import TileGrid
+    from tests.golden_inputs import TILE_CASES, tile_inputs
+    gold = _tile_golden()
+    dev = torch.device("cuda:0")
+    for k, case in enumerate(TILE_CASES):
+        g = TileGrid.from_val_opt(case["h"], case["w"], case["val"], case["scale"])
+        lq, outs_fn = tile_inputs(k)
+        outs = outs_fn(len(g.indices), g.split(lq))
+        got = g.merge(outs.to(dev))
+        assert got.is_cuda and torch.equal(got.cpu(), torch.from_numpy(gold[f"merged{k}"])), k
+
+
 @pytest.mark.gpu
 def test_tile_merge_equals_host_average():
     """grids_inverse (irm:215-241) on the device: identical fp32 result to the host accumulation."""
@@ -235,3 +273,54 @@ def test_evaluate_pairs_all_metrics_vs_oracle():
     assert accumulate_image_metrics(pairs[0][0], pairs[0][1], names, acc)   # ... and it really is the fast path
     check(evaluate_pairs(pairs, names, device=dev, metric_fn=image_metrics))  # generic path, same kernels
     check({**evaluate_pairs(pairs, C4_METRICS, device=dev), **{k: want[k] for k in names if k not in C4_METRICS}})
+
+
+def test_validation_metrics_option_handling():
+    """ValidationMetrics reads opt['val']['metrics'] like irm:346-351, 420-428: a 'type' per name, unknown types fail
+    the way `getattr(metric_module, type)` does."""
+    from lowlight_image_enhancement_b200.eval import ValidationMetrics
+    with pytest.raises(ValueError):
+        ValidationMetrics({}, device="cpu")
+    with pytest.raises(KeyError):
+        ValidationMetrics({"psnr": {"data_range": 1.0}}, device="cpu")
+    with pytest.raises(AttributeError):
+        ValidationMetrics({"psnr": {"type": "calculate_niqe"}}, device="cpu")
+    vm = ValidationMetrics({"PSNR": {"type": "linear_psnr", "data_range": 1.0}, "SSIM": {"type": "linear_ssim"}},
+                           device="cpu")
+    assert vm.names == ["PSNR", "SSIM"] and vm.types == ["linear_psnr", "linear_ssim"] and vm._fast
+    assert not ValidationMetrics({"a": {"type": "linear_psnr"}, "b": {"type": "linear_psnr", "data_range": 2.0}},
+                                 device="cpu")._fast
+
+
+@pytest.mark.gpu
+def test_validation_metrics_vs_oracle():
+    """The shim for the metric section of dist_validation against the oracle: configured NAMES differ from the metric
+    types (fast path, one-launch epilogue) and one type appears twice with different kwargs (generic path)."""
+    from lowlight_image_enhancement_b200.eval import ValidationMetrics
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(77)
+    opt = {"PSNR": {"type": "linear_psnr", "data_range": 1.0}, "SSIM": {"type": "linear_ssim", "data_range": 1.0},
+           "CPSNR": {"type": "cpsnr_rgb"}, "RGB-SSIM": {"type": "rgb_ssim_mean"}, "dE": {"type": "deltae2000_mean"},
+           "edge dE": {"type": "edge_deltae2000_mean", "q": 0.85}}
+    twice = {"psnr1": {"type": "linear_psnr", "data_range": 1.0}, "psnr2": {"type": "linear_psnr", "data_range": 2.0}}
+    vm, vm2 = ValidationMetrics(opt, dev), ValidationMetrics(twice, dev)
+    want = {k: 0.0 for k in opt}
+    want2 = {"psnr1": 0.0, "psnr2": 0.0}
+    for i in range(3):
+        gt = torch.rand(1, 3, 52 + 4 * i, 72, generator=g)
+        gt = torch.round(255 * torch.nn.functional.avg_pool2d(gt, 5, 1, 2)) / 255
+        pred = torch.round(255 * (gt + 0.04 * torch.randn(gt.shape, generator=g)).clamp(0, 1)) / 255
+        vm.update(pred.to(dev), gt.to(dev))
+        vm2.update(pred[0].to(dev), gt[0].to(dev))                     # [C, H, W] as `visuals['result']` may be
+        o = _oracle_metrics(pred, gt)
+        for name, cfg in opt.items():
+            want[name] += o[cfg["type"]] / 3
+        want2["psnr1"] += o["linear_psnr"] / 3
+        want2["psnr2"] += (o["linear_psnr"] + 20.0 * math.log10(2.0)) / 3
+    res, res2 = vm.reduce(), vm2.reduce()
+    assert res["count"] == 3 and res2["count"] == 3 and res["nonfinite_inputs"] == 0
+    for name in opt:
+        tol = 1e-4 if name == "dE" else (5e-3 if name == "edge dE" else 1e-5 * abs(want[name]))
+        assert abs(res[name] - want[name]) <= tol, (name, res[name], want[name])
+    for name in want2:
+        assert res2[name] == pytest.approx(want2[name], rel=1e-5)
