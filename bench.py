@@ -642,10 +642,20 @@ def run_extra(args, rank, world, dev, clk=None):
     t_fast = timed_warm(lambda i: accumulate_image_metrics(pool[i % 3][0], pool[i % 3][1], C4_METRICS, acc_k), 12,
                         dev) / 12
 
-    def kern(name, t, bpp, bound):
-        return {"kernel": name, "ms": round(t, 4), "Mpix/s": round(px / t / 1e3, 1),
-                "algorithmic_bytes": bpp * px, "achieved_gbs": round(bpp * px / t / 1e6, 1),
-                "frac_hbm": round(bpp * px / t / 1e6 / peak, 4), "bound": bound}
+    # FP32 roofline of the filter kernels: 148 SMs x 128 FP32 lanes x SM clock multiply-adds per second (the packed
+    # FFMA2 form occupies the pipe for two cycles, so it does not raise this peak: tools/micro/pipe_rates.cu)
+    sm_hz = (clk.summary().get("sm_max_mhz") or 1965) * 1e6 if clk is not None else 1965e6
+    peak_fma = 148 * 128 * sm_hz
+
+    def kern(name, t, bpp, bound, fma_per_elem=None):
+        rec = {"kernel": name, "ms": round(t, 4), "Mpix/s": round(px / t / 1e3, 1),
+               "algorithmic_bytes": bpp * px, "achieved_gbs": round(bpp * px / t / 1e6, 1),
+               "frac_hbm": round(bpp * px / t / 1e6 / peak, 4), "bound": bound}
+        if fma_per_elem is not None:   # elements = 3 channels x pixels
+            rate = fma_per_elem * 3 * px / (t * 1e-3)
+            rec.update({"algorithmic_fma_per_element": fma_per_elem, "achieved_tfma": round(rate / 1e12, 2),
+                        "peak_tfma": round(peak_fma / 1e12, 2), "frac_fp32": round(rate / peak_fma, 4)})
+        return rec
     out["eval_c4_detail"] = {
         "workload": "PSNR + SSIM(torchmetrics policy) + CPSNR + RGB-PSNR + RGB-SSIM + dE00 mean + edge dE00 on 1x3x2848x4256 "
                     f"sRGB pairs (BASELINE configs[3]), {per_rank} images per GPU sharded by index, device-side "
@@ -654,8 +664,8 @@ def run_extra(args, rank, world, dev, clk=None):
         "means": {k: (round(v, 6) if isinstance(v, float) else v) for k, v in res.items()},
         "ms_per_image_four_adapters_only": round(ms4, 4),
         "kernels": [kern("psnr_stats_kernel (per-channel table: CPSNR, RGB-PSNR)", t_ps, 24, "hbm"),
-                    kern("ssim_ring_kernel<4 maps> (SSIM, torchmetrics policy)", t_ssim, 24, "fp32 pipe / issue (88 FMA per element)"),
-                    kern("ssim_ring_kernel<5 maps> (RGB-SSIM, ssim_linear policy)", t_ssim5, 24, "fp32 pipe / issue (110 FMA per element)"),
+                    kern("ssim_ring_kernel<4 maps> (SSIM, torchmetrics policy)", t_ssim, 24, "fp32 pipe / issue (88 FMA per element)", 88),
+                    kern("ssim_ring_kernel<5 maps> (RGB-SSIM, ssim_linear policy)", t_ssim5, 24, "fp32 pipe / issue (110 FMA per element)", 110),
                     kern("deltae_kernel", t_de, 24, "instruction issue (fp32 + sfu)"),
                     kern("all 7 metrics of one image, image_metrics (generic path)", t_all, 36, "mixed"),
                     kern("all 7 metrics of one image, accumulate_image_metrics (one-launch epilogue)", t_fast, 36, "mixed")],

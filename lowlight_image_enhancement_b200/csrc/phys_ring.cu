@@ -60,6 +60,21 @@ __device__ __forceinline__ void ring_stamp(int k) {
 #define RING_STAMP(cond, k) do { } while (0)
 #endif
 
+// Row-loop unrolling of the backward slot bodies.  The fused (value + gradient) instantiation carries three slot bodies
+// of four unrolled rows each plus the reduction epilogue: ~100 KB of SASS against 56 KB for the gradient-only kernel, and
+// ncu showed 1.06 `no_instruction` stall cycles per issued instruction on it (none on the gradient-only kernel).  With
+// the GENERAL body rolled and the interior body unrolled by two, the fused launch at C2 goes 25.2 -> 23.1 us
+// stream-launched (tools/micro/ring_trace.cu) and 23.5 -> 21.6 us in bench.py's graphs; rolling the interior body
+// completely changes nothing more, and sending the warm-up slot through the GENERAL body costs 0.7 us.  The same change
+// costs the gradient-only kernel 0.8 us, so it keeps the fully unrolled bodies.
+#ifndef LLIE_RING_UNROLL_G
+#define LLIE_RING_UNROLL_G 1
+#endif
+#ifndef LLIE_RING_UNROLL_I
+#define LLIE_RING_UNROLL_I 2
+#endif
+constexpr int kUnrollG = LLIE_RING_UNROLL_G, kUnrollI = LLIE_RING_UNROLL_I;
+
 struct RingGeom {
     int groups, chunks;  // column groups of 512 px, row chunks per plane (even split of H)
     int items, items_per_sample;
@@ -186,6 +201,25 @@ __device__ __forceinline__ void roll3(const float (&r)[NC + 2], const float (&w)
         u = mid_tap(w[1], ra, rb, u);
         u = fma2(pack2(w[2], w[2]), ev[p + 1], u);
         B[p] = u;
+    }
+}
+
+// sqrt(x) and 1 / sqrt(x) for the Charbonnier penalty and its derivative, x = r^2 + eps^2.  For x in [1e-30, 1e30] (every
+// sane configuration: eps >= 1e-15, |r| <= 1e15): one MUFU.RSQ, a Newton step on the root (<= 1 ulp) and one on the
+// reciprocal root (<= 1 ulp), 7 instructions without a slow path; the IEEE sqrtf + division pair costs ~20 issue slots
+// per element in a kernel that is co-limited by instruction issue.  Outside that range: the IEEE forms.
+__device__ __forceinline__ void sqrt_rsqrt_pos(float x, float &sq, float &rs) {
+    if (x >= 1e-30f && x <= 1e30f) {
+        float r0;
+        asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r0) : "f"(x));
+        const float s0 = x * r0;
+        const float h = 0.5f * r0;
+        const float e = fmaf(-s0, s0, x);        // x - s0^2
+        sq = fmaf(e, h, s0);                     // s0 + e / (2 s0)
+        rs = fmaf(r0, fmaf(-s0, h, 0.5f), r0);   // r0 (1.5 - 0.5 x r0^2)
+    } else {
+        sq = sqrtf(x);
+        rs = 1.f / sq;
     }
 }
 
@@ -524,7 +558,12 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_fwd_ring(const 
                         }
                         const float r = yv - t;
                         mv[i] = fabsf(r);
-                        racc = fmaf(ROBUST ? sqrtf(fmaf(r, r, eps2)) : mv[i], cm[i], racc);
+                        float pen = mv[i];
+                        if (ROBUST) {
+                            float rs_unused;
+                            sqrt_rsqrt_pos(fmaf(r, r, eps2), pen, rs_unused);
+                        }
+                        racc = fmaf(pen, cm[i], racc);
                     }
                     acc = GENERAL ? fmaf(racc, rowmask, acc) : acc + racc;
                     if (map_on && rowmask != 0.f) {
@@ -689,7 +728,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         auto do_slot = [&](auto kind_tag, int kb, const float *sp) {
             constexpr int KIND = decltype(kind_tag)::value;
             constexpr bool GENERAL = KIND == kSlotGeneral, WARM = KIND == kSlotWarm;
-#pragma unroll
+#pragma unroll(!FUSED || WARM ? kG : (GENERAL ? kUnrollG : kUnrollI))
             for (int u = 0; u < kG; ++u) {
                 const int k = kb + u;
                 if (GENERAL && k >= E) break;  // CTA-uniform
@@ -725,10 +764,11 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                         t = clamp01(t);
                     }
                     const float r = yv - t;
-                    if (FUSED && !(WARM && u == 2) && i >= 1 && i <= 4)
-                        lrow = fmaf(ROBUST ? sqrtf(fmaf(r, r, eps2)) : fabsf(r), dm[i - 1], lrow);
+                    float pen = fabsf(r), rsq = 0.f;
+                    if (ROBUST) sqrt_rsqrt_pos(fmaf(r, r, eps2), pen, rsq);
+                    if (FUSED && !(WARM && u == 2) && i >= 1 && i <= 4) lrow = fmaf(pen, dm[i - 1], lrow);
                     if (ROBUST) {
-                        qc[i] = (m != 0.f) ? m * (r / sqrtf(fmaf(r, r, eps2))) : 0.f;
+                        qc[i] = (m != 0.f) ? m * (r * rsq) : 0.f;
                     } else {
                         // m * sign(r), sign(0) = 0 (stale rows hold finite values; m == 0 masks them)
                         qc[i] = (r != 0.f) ? copysignf(m, r) : 0.f;

@@ -42,9 +42,17 @@ int main(int argc, char **argv) {
     const float gscale = 1.f / ((float)n * c * (h - 2) * (w - 2));
     if (argc > 2) llie_tune(LLIE_TUNE_PHYS_PDL, atoi(argv[2]));
     cudaStream_t st; CK(cudaStreamCreate(&st));
+    const int mode = argc > 3 ? atoi(argv[3]) : 0;  // 0 fused value + gradient, 1 gradient only, 2 forward only
+    printf("mode %d (%s)\n", mode, mode == 0 ? "fused value + gradient" : (mode == 1 ? "gradient only" : "forward only"));
     auto step = [&](int i) {
-        int rc = llie_phys_value_and_grad(&d, pred[i % pool], obs[i % pool], psf, rho, gout, 0, gscale, omean, osum, flags,
+        int rc;
+        if (mode == 0)
+            rc = llie_phys_value_and_grad(&d, pred[i % pool], obs[i % pool], psf, rho, gout, 0, gscale, omean, osum, flags,
                                           grad[i % pool], nullptr, ws, st);
+        else if (mode == 1)
+            rc = llie_phys_backward(&d, pred[i % pool], obs[i % pool], psf, rho, gout, 0, gscale, grad[i % pool], nullptr, st);
+        else
+            rc = llie_phys_forward(&d, pred[i % pool], obs[i % pool], psf, rho, omean, osum, nullptr, flags, ws, st);
         if (rc) { printf("rc %d: %s\n", rc, llie_last_error()); exit(1); }
     };
     for (int i = 0; i < 10; ++i) step(i);
