@@ -122,7 +122,7 @@ __device__ __forceinline__ void scatter_row(f2_t (&acc)[M][RK], const f2_t (&h)[
 }
 
 template <bool MAPS5, bool COEF, bool CLAMP>
-__global__ void __launch_bounds__(RT, 3) ssim_ring_kernel(const SsimArgs a, const RingTaps tp) {
+__global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const SsimArgs a, const RingTaps tp) {
     constexpr int M = MAPS5 ? 5 : 4;
     __shared__ __align__(128) float ring[RD][2][RROW];
     __shared__ __align__(8) uint64_t full[RD], empty[RD];
@@ -428,7 +428,7 @@ constexpr size_t ring_bwd_smem(bool accumulate) {
 }
 
 template <bool ACC>
-__global__ void __launch_bounds__(RT, 3) ssim_ring_bwd_kernel(const SsimBwdArgs a, const BwdTaps tp, int seg_rows) {
+__global__ void __launch_bounds__(RT, ACC ? 3 : 4) ssim_ring_bwd_kernel(const SsimBwdArgs a, const BwdTaps tp, int seg_rows) {
     constexpr int NIO = ACC ? 3 : 2;
     extern __shared__ __align__(128) unsigned char smraw[];
     float (*ringc)[3][RROW] = reinterpret_cast<float (*)[3][RROW]>(smraw);
@@ -655,7 +655,9 @@ int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaS
     for (int j = 0; j < RK; ++j) tp.g[j] = win_host[j];
     a.tiles_x = div_up(d.w, RCOLS);
     const long long cols = (long long)d.n * a.co * a.tiles_x;
-    a.seg_rows = pick_seg_rows(cols, d.h, kNumSM * 3, 64, RK - 1);
+    // resident CTAs per SM: 4 at 128 registers (a few spilled words, 2-4 % faster than 3 at 148) except for the five-map
+    // variant, whose 168 registers would spill 128 bytes (362 instead of 322 us per C4 pair)
+    a.seg_rows = pick_seg_rows(cols, d.h, kNumSM * (d.clamp_var ? 3 : 4), 64, RK - 1);
     a.tiles_y = div_up(d.h, a.seg_rows);
     const long long grid = cols * a.tiles_y;
     Workspace ws(workspace);
@@ -689,7 +691,8 @@ int ssim_ring_backward(SsimBwdArgs &a, const float *win_host, cudaStream_t st) {
     for (int j = 0; j < RK; ++j) tp.g[j] = win_host[j];
     a.tiles_x = div_up(a.w, RCOLS);
     const long long cols = (long long)a.n * a.c * a.tiles_x;
-    const int rows = pick_seg_rows(cols, a.h, kNumSM * 3, 64, RK - 1);
+    // 4 resident CTAs per SM at 128 registers, 3 for the accumulating variant (its spills cost more than the warps gain)
+    const int rows = pick_seg_rows(cols, a.h, kNumSM * (a.accumulate ? 3 : 4), 64, RK - 1);
     a.tiles_y = div_up(a.h, rows);
     const long long grid = cols * a.tiles_y;
     LLIE_REQUIRE(grid <= 0x7fffffffLL, "ssim_loss_backward: too many tiles");
