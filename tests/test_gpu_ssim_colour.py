@@ -407,3 +407,23 @@ def test_private_helpers_the_reference_tests_import(golden, dev):
     lch = torch.rand(2, 1, 33, 48, generator=g) * 100
     assert float((_sobel_magnitude(lch.to(dev)).cpu() - colour.sobel_magnitude(lch)).abs().max()) <= 1e-4
     assert _deg2rad(180.0) == pytest.approx(np.pi)
+
+
+@pytest.mark.parametrize("shape", [(1, 3, 33, 47), (10, 3, 24, 40), (3, 3, 64, 64)])
+def test_deltae_pass_squared_error_sums(dev, shape):
+    """llie_deltae_sqerr / _sqerr_rgb: the float64 squared-error sums that ride on the dE00 pass (whole image and per
+    channel, raw unclamped inputs, metrics/psnr.py:39-88 and channelwise.py:113-150) against torch float64, for more
+    images than the finalize handles per round (8) and for the scalar (W % 4 != 0) path."""
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    g = torch.Generator().manual_seed(sum(shape))
+    x = (torch.rand(shape, generator=g) * 1.2 - 0.1).to(dev)
+    y = torch.rand(shape, generator=g).to(dev)
+    out = []
+    sums, flags, _, _ = Fn.deltae(x, y, variant=0, clamp_in=True, sqerr_out=out, sqerr_rgb=True)
+    sq, sqc = out
+    ref = ((x.double() - y.double()) ** 2).sum(dim=(2, 3))
+    np.testing.assert_allclose(_np(sqc), _np(ref), rtol=1e-12)
+    np.testing.assert_allclose(_np(sq), _np(ref.sum(dim=1)), rtol=1e-12)
+    only = []
+    sums2, _, _, _ = Fn.deltae(x, y, variant=0, clamp_in=True, sqerr_out=only)
+    assert torch.equal(sums, sums2) and torch.equal(only[0], sq) and int(flags) == 0
