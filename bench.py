@@ -537,6 +537,7 @@ def run_ours(args, rank, world, dev):
              "achieved_gbs": round(ach_u, 1), "frac": round(ach_u / peak, 4), "traffic": ncu_traffic("phys_fused_ring")[0]}],
         "e2e": {"value": round(e2e_val, 1), "unit": "Mpix/s", "h2d_bytes_per_step": 2 * 4 * elems,
                 "d2h_bytes_per_step": 4, "steps": Ke,
+                "h2d_gbs_per_gpu": round(2 * 4 * elems * Ke / (ms_e * 1e-3) / 1e9, 1),   # the leg is bound by this link
                 "api": "metrics.phys_consistency.phys_cons_raw(differentiable=True)+backward, double-buffered uploads"},
         "e2e_u16_obs": {"value": round(e2e_u16_val, 1), "unit": "Mpix/s", "h2d_bytes_per_step": 2 * elems,
                         "d2h_bytes_per_step": 4, "steps": Ke,
