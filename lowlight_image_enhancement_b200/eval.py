@@ -252,6 +252,7 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
     ssim_sums, ssim_count, ssim_c = None, 1, 1
     main = torch.cuda.current_stream(dev)
     joined = None
+    rsums_side = f_rs = None
     if "linear_ssim" in names:
         kw = opts.get("linear_ssim", {})
         # SSIM shares nothing with the colour / edge chain but the inputs: on a side stream (own workspace) its CTAs
@@ -267,6 +268,13 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
             for x_ in (p, t):
                 x_.record_stream(side)
             joined = side
+            if rgbs:   # the second SSIM policy follows on the same side stream: the chain's small Sobel / select
+                # kernels then run under FMA-bound SSIM work for their whole length, not only under the first launch
+                with torch.cuda.stream(side):
+                    f_rs = torch.zeros(1, dtype=torch.int32, device=dev)
+                    rsums_side = _rgb_ssim_sums(p, t, f_rs, {})
+                for x_ in (rsums_side, f_rs):
+                    x_.record_stream(main)
         else:
             ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
                                                               sigma=1.5, k1=0.01, k2=0.03)
@@ -295,7 +303,10 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
     if rgbp and not ride_rgb:
         table, f, _ = Fn.psnr_stats(p, t, n, c, h * w, cast_first=True, clamp_hi=None, data_range=1.0, eps=1e-12)
         fl.append(f)
-    if rgbs:
+    if rgbs and rsums_side is not None:
+        rsums = rsums_side
+        fl.append(f_rs)
+    elif rgbs:
         cache: dict = {}
         f = torch.zeros(1, dtype=torch.int32, device=dev)
         rsums = _rgb_ssim_sums(p, t, f, cache)
