@@ -295,9 +295,9 @@ __device__ __forceinline__ void produce_slot(float *slot, uint64_t *full, const 
 // the same L2 lines), so it is legal under the default, fully serialised contract -- unlike the early loads of the
 // stream-overlap mode.  Under programmatic dependent launch the CTAs of launch i + 1 become resident while launch i
 // drains, and their opening rows stream into L2 behind the previous launch's tail.  Measured at C2 (graphs of 200
-// serialised launches): gradient-only kernel 17.4 -> 16.3 us with 8 rows per tensor, forward 14.8 -> 14.7, fused value +
-// gradient unchanged (23.8: its tail is the last-CTA finalize, not the ramp); 16 or more rows per CTA compete with the
-// previous launch's stragglers for DRAM and cost 2-3 us.  Default 8 rows (two ring slots).
+// serialised launches, final round-2 kernels): fused value + gradient 22.3 -> 21.5 us with 8 rows per tensor, gradient-only
+// 17.5 -> 16.4, forward 14.6 -> 14.3; 16 or more rows per CTA compete with the previous launch's stragglers for DRAM
+// and give the gain back (24 rows: 22.8 / 17.6 / 15.5).  Default 8 rows (two ring slots).
 __device__ __forceinline__ void l2_prefetch(const void *p, uint32_t bytes) {
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
 }
