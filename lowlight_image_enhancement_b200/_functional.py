@@ -160,16 +160,19 @@ def _desc(cfg: PhysCfg, pred: Tensor, c_out: int, psf: PreparedPSF, rho_scalar: 
 
 
 def phys_forward(pred: Tensor, obs: Tensor, psf: PreparedPSF, rho_t: Optional[Tensor], rho_scalar: float,
-                 rho_strides, cfg: PhysCfg, want_map: bool):
+                 rho_strides, cfg: PhysCfg, want_map: bool, out: Optional[Tensor] = None):
     """Launch llie_phys_forward.  pred/obs: contiguous fp32 CUDA NCHW.
-    Returns (vec[N+2] fp32 = per-sample means | batch mean | batch sum, flags int32[1], map or None)."""
+    Returns (vec[N+2] fp32 = per-sample means | batch mean | batch sum, flags int32[1], map or None).
+    `out`: a caller-owned contiguous fp32 [N + 3] buffer for the results (no allocation between launches)."""
     dev = pred.device
     n, c_in, h, w = pred.shape
     c_out = obs.shape[1]
     ph, pw = (psf.kh // 2, psf.kw // 2) if cfg.crop_valid else (0, 0)
     if cfg.crop_valid and (h <= 2 * ph or w <= 2 * pw):
         raise ValueError("crop='valid' leaves an empty comparison region for this PSF/image size.")
-    buf = torch.empty(n + 3, dtype=torch.float32, device=dev)
+    buf = torch.empty(n + 3, dtype=torch.float32, device=dev) if out is None else out
+    if buf.numel() != n + 3 or buf.dtype != torch.float32 or not buf.is_contiguous():
+        raise ValueError("phys_forward: `out` must be a contiguous float32 buffer of n + 3 elements")
     flags = buf[n + 2:].view(torch.int32)
     amap = torch.empty((n, c_out, h - 2 * ph, w - 2 * pw), dtype=torch.float32, device=dev) if want_map else None
     d = _desc(cfg, pred, c_out, psf, rho_scalar, rho_strides)

@@ -413,6 +413,93 @@ def evaluate_pairs(pairs, names: Sequence[str], *, n_items: Optional[int] = None
     return acc.reduce()
 
 
+@torch.no_grad()
+def evaluate_phys_consistency(batches, psf: Tensor, *, srgb: bool = False, padding: str = "reflect",
+                              normalize_psf: bool = True, enforce_nonnegative: bool = False, crop: str = "valid",
+                              robust: str = "none", clamp01: bool = True, eps: float = 1e-12,
+                              rank: Optional[int] = None, world_size: Optional[int] = None, group=None,
+                              shard: str = "interleave", overlap: bool = True) -> Dict[str, float]:
+    """Dataset-level physics-consistency error: `phys_cons_raw` (or `phys_cons_srgb` with `srgb=True`; same keyword
+    arguments, metrics/phys_consistency.py:260-368) over a SEQUENCE of resident batches `(pred, obs, expo_ratio)`,
+    sharded across ranks like `evaluate_pairs`, reduced with one all-reduce and ONE host synchronisation.
+
+    This is the loop the stream-overlap contract of `llie_phys_desc.stream_overlap` exists for, and the one place in the
+    package that makes the promise itself: the batches are contiguous float32 CUDA tensors that exist before the loop
+    starts (a lazily produced batch would be written by the kernel right before its phys launch, which the contract
+    forbids -- generators are rejected), every launch writes its results into its own row of a preallocated table and
+    nothing else is enqueued between the launches.  The first launch of the loop is an ordinary, fully ordered one (the
+    kernel before it is unknown); launches 2 .. B carry the per-call flag, so their CTAs start under the tail of the
+    previous launch (8.3 instead of 14.3 us per C2 batch for the forward kernel).  Per-image values equal
+    those of a loop over `phys_cons_raw(..., reduction='none')` to 1e-6 relative (overlapped launches cut the planes into
+    longer work items, which regroups the float32 partial sums); `overlap=False` reproduces them bit for bit.
+    Returns {'phys_cons_mean': mean over all images of all ranks, 'count': images, 'nonfinite_inputs': batches flagged}."""
+    from . import _functional as Fn
+    from . import _native as nat
+    if not hasattr(batches, "__len__") or not hasattr(batches, "__getitem__"):
+        raise TypeError("evaluate_phys_consistency needs a sequence of resident batches, not an iterator")
+    for name, val, allowed in (("padding", padding, {"reflect", "replicate", "zeros"}), ("crop", crop, {"valid", "same"}),
+                               ("robust", robust, {"none", "charbonnier"})):
+        if val not in allowed:
+            raise ValueError(f"Unsupported {name} '{val}'.")
+    if eps <= 0:
+        raise ValueError(f"`eps` must be positive, received {eps}.")
+    if rank is None or world_size is None:
+        on = dist.is_available() and dist.is_initialized()
+        rank = dist.get_rank(group) if on else 0
+        world_size = dist.get_world_size(group) if on else 1
+    mine = shard_indices(len(batches), rank, world_size, shard)
+    dev = None
+    todo = []
+    for i in mine:
+        pred, obs, rho = batches[i]
+        if pred.dim() == 3:
+            pred, obs = pred.unsqueeze(0), obs.unsqueeze(0)
+        if not (pred.is_cuda and obs.is_cuda and pred.dtype == torch.float32 and obs.dtype == torch.float32 and
+                pred.is_contiguous() and obs.is_contiguous()) or pred.shape != obs.shape:
+            raise ValueError("evaluate_phys_consistency: batches must be contiguous float32 CUDA tensors of one shape "
+                             "(stage them before the loop)")
+        dev = pred.device if dev is None else dev
+        todo.append((pred, obs, rho))
+    acc = torch.zeros(3, dtype=torch.float64, device=dev if dev is not None else "cuda")  # sum of means, images, flagged
+    if todo:
+        n_max = max(p.shape[0] for p, _, _ in todo)
+        table = torch.zeros((len(todo), n_max + 3), dtype=torch.float32, device=dev)
+        cfg = Fn.PhysCfg(nat.PAD[padding], crop == "valid", robust == "charbonnier", float(eps), 0,
+                         bool(clamp01) if srgb else False, False)
+        prepared, rhos = {}, []
+        for pred, obs, rho in todo:   # everything that allocates or launches torch kernels happens BEFORE the loop
+            key = (pred.shape[1], obs.shape[1])
+            if key not in prepared:
+                prepared[key] = Fn.prepare_psf(psf, key[0], key[1], dev, normalize=normalize_psf,
+                                               nonneg=enforce_nonnegative, eps=eps)
+                if prepared[key].zero_sum:
+                    Fn.warn_zero_sum()
+            rhos.append(Fn.normalise_rho(rho, *pred.shape, dev))
+        for b, ((pred, obs, _), (rho_t, rho_s, rho_st)) in enumerate(zip(todo, rhos)):
+            n = pred.shape[0]
+            row = table[b, : n + 3]
+            if overlap and b > 0:
+                with Fn.phys_stream_overlap():
+                    Fn.phys_forward(pred, obs, prepared[(pred.shape[1], obs.shape[1])], rho_t, rho_s, rho_st, cfg, False,
+                                    out=row)
+            else:
+                Fn.phys_forward(pred, obs, prepared[(pred.shape[1], obs.shape[1])], rho_t, rho_s, rho_st, cfg, False,
+                                out=row)
+        # one pass over the table after the loop: per-image means are columns 0 .. n - 1 of each row, the flag word sits
+        # at column n + 2 (int32 bits)
+        nvec = torch.tensor([p.shape[0] for p, _, _ in todo], device=dev)
+        cols = torch.arange(n_max + 3, device=dev).unsqueeze(0)
+        acc[0] = torch.where(cols < nvec.unsqueeze(1), table.double(), torch.zeros((), dtype=torch.float64, device=dev)).sum()
+        acc[1] = nvec.sum()
+        acc[2] = (table.view(torch.int32).gather(1, (nvec + 2).unsqueeze(1)) != 0).sum()
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+    s, cnt, bad = acc.tolist()
+    if bad:
+        raise ValueError(f"{int(bad)} batch(es) contain NaN or Inf values in `pred` or `obs`.")
+    return {"phys_cons_mean": s / cnt if cnt > 0 else float("nan"), "count": int(cnt), "nonfinite_inputs": int(bad)}
+
+
 class ValidationMetrics:
     """The metric section of `ImageRestorationModel.dist_validation` (image_restoration_model.py:346-351, 416-428,
     444-464) as an object the reference's loop can hold instead of `self.metric_results`:

@@ -324,3 +324,42 @@ def test_validation_metrics_vs_oracle():
         assert abs(res[name] - want[name]) <= tol, (name, res[name], want[name])
     for name in want2:
         assert res2[name] == pytest.approx(want2[name], rel=1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("srgb", [False, True])
+def test_evaluate_phys_consistency_matches_metric_loop(srgb):
+    """The dataset-level phys-consistency driver (the one product loop that makes the stream-overlap promise itself)
+    against a plain loop over phys_cons_raw / phys_cons_srgb: serialised launches bit for bit, overlapped launches to
+    1e-6 relative; iterators, host tensors and non-finite inputs are rejected."""
+    from lowlight_image_enhancement_b200.eval import evaluate_phys_consistency
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw, phys_cons_srgb
+    from oracle import psf_ops
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(5)
+    psf = psf_ops.canonical_kernels("rgb").to(dev)
+    batches = []
+    for n in (4, 2, 8, 1, 3, 8):
+        pred = torch.rand(n, 3, 128, 256, generator=g)
+        rho = torch.rand(n, generator=g) + 0.5
+        obs = (pred * rho.view(-1, 1, 1, 1) * 0.9 + 0.05 * torch.randn(pred.shape, generator=g)).clamp(0, 1.2)
+        batches.append((pred.to(dev), obs.to(dev), rho.to(dev)))
+    fn = phys_cons_srgb if srgb else phys_cons_raw
+    per = torch.cat([fn(p, o, psf, r, reduction="none", crop="same", robust="charbonnier", eps=1e-3) for p, o, r in batches])
+    want = float(per.double().mean())
+    kw = dict(srgb=srgb, crop="same", robust="charbonnier", eps=1e-3)
+    ser = evaluate_phys_consistency(batches, psf, overlap=False, **kw)
+    ovl = evaluate_phys_consistency(batches, psf, overlap=True, **kw)
+    assert ser["count"] == ovl["count"] == 26 and ser["nonfinite_inputs"] == 0
+    assert ser["phys_cons_mean"] == pytest.approx(want, rel=1e-14)      # same float32 per-image values, float64 sums
+    assert ovl["phys_cons_mean"] == pytest.approx(want, rel=1e-6)
+    half = evaluate_phys_consistency(batches, psf, rank=1, world_size=2, **kw)        # shard of rank 1: batches 1, 3, 5
+    assert half["count"] == 2 + 1 + 8
+    with pytest.raises(TypeError):
+        evaluate_phys_consistency(iter(batches), psf, **kw)
+    with pytest.raises(ValueError):
+        evaluate_phys_consistency([(batches[0][0].cpu(), batches[0][1].cpu(), 1.0)], psf, **kw)
+    bad = batches[2][0].clone()
+    bad[1, 0, 5, 5] = float("nan")
+    with pytest.raises(ValueError):
+        evaluate_phys_consistency(batches[:2] + [(bad, batches[2][1], batches[2][2])], psf, **kw)
