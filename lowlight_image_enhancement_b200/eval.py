@@ -475,16 +475,25 @@ def evaluate_phys_consistency(batches, psf: Tensor, *, srgb: bool = False, paddi
                 if prepared[key].zero_sum:
                     Fn.warn_zero_sum()
             rhos.append(Fn.normalise_rho(rho, *pred.shape, dev))
-        for b, ((pred, obs, _), (rho_t, rho_s, rho_st)) in enumerate(zip(todo, rhos)):
-            n = pred.shape[0]
-            row = table[b, : n + 3]
-            if overlap and b > 0:
-                with Fn.phys_stream_overlap():
-                    Fn.phys_forward(pred, obs, prepared[(pred.shape[1], obs.shape[1])], rho_t, rho_s, rho_st, cfg, False,
-                                    out=row)
-            else:
-                Fn.phys_forward(pred, obs, prepared[(pred.shape[1], obs.shape[1])], rho_t, rho_s, rho_st, cfg, False,
-                                out=row)
+        # the loop: descriptor + pointers + ONE foreign call per batch (the generic `Fn.phys_forward` wrapper costs ~34 us
+        # of Python per launch, more than a C2-sized launch takes); host work of batch b + 1 runs under the kernel of b
+        with torch.cuda.device(dev):
+            ws, st, fwd, ptr = nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev), nat.lib().llie_phys_forward, nat.ptr
+            for b, ((pred, obs, _), (rho_t, rho_s, rho_st)) in enumerate(zip(todo, rhos)):
+                n, c_in, h, w = pred.shape
+                pp = prepared[(c_in, obs.shape[1])]
+                ph, pw = (pp.kh // 2, pp.kw // 2) if cfg.crop_valid else (0, 0)
+                if cfg.crop_valid and (h <= 2 * ph or w <= 2 * pw):
+                    raise ValueError("crop='valid' leaves an empty comparison region for this PSF/image size.")
+                if padding == "reflect" and (pp.kh // 2 >= h or pp.kw // 2 >= w):
+                    raise RuntimeError("Padding size should be less than the corresponding input dimension")
+                d = Fn._desc(cfg, pred, obs.shape[1], pp, rho_s, rho_st)
+                d.stream_overlap = 1 if (overlap and b > 0) else 0
+                base = table.data_ptr() + 4 * b * (n_max + 3)
+                rc = fwd(d, ptr(pred), ptr(obs), ptr(pp.weights), ptr(rho_t), base, None, None, base + 4 * (n + 2), ws, st)
+                if rc:
+                    nat.check(rc, "llie_phys_forward")
+        nat.count_launch(len(todo))
         # one pass over the table after the loop: per-image means are columns 0 .. n - 1 of each row, the flag word sits
         # at column n + 2 (int32 bits)
         nvec = torch.tensor([p.shape[0] for p, _, _ in todo], device=dev)
