@@ -400,3 +400,30 @@ def test_phys_stream_overlap_scope_is_per_thread_and_skips_autograd(dev, monkeyp
     assert (True, 1) in seen                       # forward in the scope's thread
     assert all(ov == 0 for main, ov in seen if not main) and any(not main for main, _ in seen)
     assert pred.grad is not None and torch.isfinite(pred.grad).all()
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 64, 256), (1, 3, 13, 8), (4, 3, 50, 516), (3, 1, 24, 260)])
+def test_newbp_depthwise3_fast_path_equals_generic(dev, shape):
+    """The four-column depthwise 3x3 kernel (16-byte aligned planes, W % 4 == 0) against the generic one-thread-per-output
+    kernel, reached through a view whose base address breaks the alignment: forward and adjoint bit for bit, and both
+    against F.conv2d / F.conv_transpose2d (newbp_layer.py:9-21)."""
+    import torch.nn.functional as F
+    from lowlight_image_enhancement_b200.NewBP_model.newbp_layer import NewBPFunction
+    g = torch.Generator().manual_seed(sum(shape))
+    n, c, h, w = shape
+    x = torch.randn(shape, generator=g).to(dev)
+    k = (torch.rand(c, 1, 3, 3, generator=g) - 0.3).to(dev)
+    gy = torch.randn(shape, generator=g).to(dev)
+    store = torch.empty(x.numel() + 1, device=dev)
+    x_un = store[1:].view(shape)           # 4-byte aligned only: the generic kernel takes it
+    x_un.copy_(x)
+    outs = []
+    for inp in (x, x_un):
+        t = inp.detach().requires_grad_(True)
+        y = NewBPFunction.apply(t, k, 1, c)
+        y.backward(gy)
+        outs.append((y.detach().clone(), t.grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    ref = F.conv2d(x.double(), k.double(), padding=1, groups=c)
+    rgx = F.conv_transpose2d(gy.double(), k.double(), padding=1, groups=c)
+    assert _rel(outs[0][0], ref.cpu()) < 1e-6 and _rel(outs[0][1], rgx.cpu()) < 1e-6
