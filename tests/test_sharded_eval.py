@@ -363,3 +363,24 @@ def test_evaluate_phys_consistency_matches_metric_loop(srgb):
     bad[1, 0, 5, 5] = float("nan")
     with pytest.raises(ValueError):
         evaluate_phys_consistency(batches[:2] + [(bad, batches[2][1], batches[2][2])], psf, **kw)
+
+
+@pytest.mark.gpu
+def test_tile_merge_many_overlapping_tiles():
+    """More than 64 tiles over one 8 x 128 output rectangle: the kernel's culled list overflows and it falls back to the
+    scan over all tiles; arbitrary (unordered, duplicated) origins, same fp32 result as the host accumulation."""
+    from lowlight_image_enhancement_b200.eval import TileGrid
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(11)
+    h, w, th, tw = 40, 150, 24, 100
+    grid = TileGrid(h, w, th, tw)
+    grid.indices = [(int(torch.randint(0, h - th + 1, (1,), generator=g)), int(torch.randint(0, w - tw + 1, (1,), generator=g)))
+                    for _ in range(90)] + [(0, 0), (h - th, w - tw), (0, w - tw), (h - th, 0)]
+    grid._idx_dev = {}
+    outs = torch.rand(len(grid.indices), 2, th, tw, generator=g)
+    preds, cnt = torch.zeros(1, 2, h, w), torch.zeros(1, 1, h, w)
+    for t, (i, j) in enumerate(grid.indices):
+        preds[0, :, i:i + th, j:j + tw] += outs[t]
+        cnt[0, 0, i:i + th, j:j + tw] += 1.0
+    got = grid.merge(outs.to(dev))
+    assert torch.equal(got.cpu(), preds / cnt)
