@@ -341,6 +341,11 @@ int llie_decode_u16(const llie_decode_desc *desc, const uint16_t *src, const flo
  * replaces metrics/evaluation.py:27-38 (_linear_to_srgb) and :50-52 (_norm_to_lpips_range). */
 int llie_linear_to_srgb(const float *x, int64_t n, float *out_srgb, float *out_lpips, void *stream);
 
+/* BT.601 luma plane of [n, 3, plane] float32 images: y = 0.2989 r + 0.5870 g + 0.1140 b with every product and sum
+ * rounded separately, the value of the eager expression in metrics/ssim.py:116-127 (_to_luma_bt601; color_space='y'
+ * of SSIMEvaluator).  y: [n, 1, plane]. */
+int llie_luma_bt601(const float *x, int32_t n, int64_t plane, float *y, void *stream);
+
 /* ------------------------------------------------------------------------
  * Per-pair epilogue of the sharded evaluation driver: adapter values from the raw device sums, added to the rank's
  * running vector acc = [k metric sums, pair count, pairs with non-finite input] (float64), one launch, no host sync.

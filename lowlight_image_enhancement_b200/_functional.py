@@ -458,6 +458,20 @@ def deltae(x: Tensor, y: Tensor, *, variant: int, kL: float = 1.0, kC: float = 1
     return sums, flags, dmap, lpl
 
 
+def luma_bt601(x: Tensor) -> Tensor:
+    """[N, 3, H, W] fp32 CUDA contiguous -> [N, 1, H, W] BT.601 luma, rounded like the reference's eager expression
+    (llie_luma_bt601, metrics/ssim.py:116-127)."""
+    n, c, h, w = x.shape
+    if c != 3:
+        raise ValueError(f"color_space='y' expects 3-channel RGB input, got C={c}.")
+    out = torch.empty((n, 1, h, w), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = nat.lib().llie_luma_bt601(nat.ptr(x), n, h * w, nat.ptr(out), nat.stream_ptr(x.device))
+    nat.check(rc, "llie_luma_bt601")
+    nat.count_launch()
+    return out
+
+
 def sobel_magnitude(l_planes: Tensor) -> Tensor:
     """[..., H, W] fp32 CUDA -> Sobel magnitude of every plane (zero padding)."""
     dev = l_planes.device

@@ -114,6 +114,7 @@ _SIGNATURES = {
     "llie_linear_to_srgb": (C.c_int, [_VP, C.c_int64, _VP, _VP, _VP]),
     "llie_eval_accumulate": (C.c_int, [C.POINTER(EvalDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP,
                                        _VP, _VP, _VP, _VP, _VP]),
+    "llie_luma_bt601": (C.c_int, [_VP, C.c_int32, C.c_int64, _VP, _VP]),
     "llie_selftest_div_const": (C.c_int, [C.c_int32, C.c_uint32, C.c_uint64, _VP, _VP]),
     "llie_selftest_srgb_to_linear": (C.c_int, [_VP, _VP, C.c_int64, _VP]),
     "llie_sobel_magnitude": (C.c_int, [_VP, _VP, C.c_int64, C.c_int32, C.c_int32, _VP]),

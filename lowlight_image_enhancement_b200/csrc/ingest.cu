@@ -245,3 +245,42 @@ extern "C" int llie_linear_to_srgb(const float *x, int64_t n, float *out_srgb, f
     LLIE_CUDA_OK(cudaGetLastError());
     return LLIE_OK;
 }
+
+// BT.601 luma of [n, 3, plane] float32 images -> [n, 1, plane] (metrics/ssim.py:116-127 `_to_luma_bt601`):
+//   y = 0.2989 r + 0.5870 g + 0.1140 b   with every product and sum rounded separately (no FMA contraction), i.e. the
+// value ATen's eager `0.2989 * r + 0.5870 * g + 0.1140 * b` produces.  One streaming pass, 16 B per pixel.
+namespace llie {
+__global__ void __launch_bounds__(256) luma_bt601_kernel(const float *__restrict__ x, long long plane, float *__restrict__ y,
+                                                         bool vec) {
+    const int n = blockIdx.y;
+    const float *r = x + (long long)n * 3 * plane, *g = r + plane, *b = g + plane;
+    float *o = y + (long long)n * plane;
+    auto f = [](float rv, float gv, float bv) {
+        return __fadd_rn(__fadd_rn(__fmul_rn(0.2989f, rv), __fmul_rn(0.5870f, gv)), __fmul_rn(0.1140f, bv));
+    };
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    if (vec) {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane / 4; i += stride) {
+            const float4 rv = ldg_stream4(r + 4 * i), gv = ldg_stream4(g + 4 * i), bv = ldg_stream4(b + 4 * i);
+            *reinterpret_cast<float4 *>(o + 4 * i) =
+                make_float4(f(rv.x, gv.x, bv.x), f(rv.y, gv.y, bv.y), f(rv.z, gv.z, bv.z), f(rv.w, gv.w, bv.w));
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < plane; i += stride)
+            o[i] = f(__ldg(r + i), __ldg(g + i), __ldg(b + i));
+    }
+}
+}  // namespace llie
+
+extern "C" int llie_luma_bt601(const float *x, int32_t n, int64_t plane, float *y, void *stream) {
+    LLIE_REQUIRE(x != nullptr && y != nullptr && n > 0 && n <= 65535 && plane > 0, "llie_luma_bt601: bad arguments");
+    const bool vec = llie::aligned16(x) && llie::aligned16(y) && (plane % 4) == 0;
+    const long long items = vec ? plane / 4 : plane;
+    long long gx = (items + 255) / 256;
+    const long long cap = (long long)llie::kNumSM * 8 * 4 / n + 1;
+    if (gx > cap) gx = cap;
+    dim3 grid((unsigned)gx, (unsigned)n);
+    llie::luma_bt601_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(x, plane, y, vec);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}

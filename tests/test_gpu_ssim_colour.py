@@ -427,3 +427,15 @@ def test_deltae_pass_squared_error_sums(dev, shape):
     only = []
     sums2, _, _, _ = Fn.deltae(x, y, variant=0, clamp_in=True, sqerr_out=only)
     assert torch.equal(sums, sums2) and torch.equal(only[0], sq) and int(flags) == 0
+
+
+@pytest.mark.parametrize("shape", [(2, 3, 33, 47), (1, 3, 64, 256)])
+def test_luma_bt601_equals_eager_expression(dev, shape):
+    """llie_luma_bt601 against the reference's eager expression (metrics/ssim.py:116-127) evaluated by ATen on the same
+    device: bit for bit (separately rounded products and sums), vector and scalar path."""
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    x = (torch.rand(shape, generator=torch.Generator().manual_seed(shape[3])) * 300 - 20).to(dev)
+    want = 0.2989 * x[:, 0:1] + 0.5870 * x[:, 1:2] + 0.1140 * x[:, 2:3]
+    assert torch.equal(Fn.luma_bt601(x.contiguous()), want)
+    with pytest.raises(ValueError):
+        Fn.luma_bt601(x[:, :2].contiguous())
