@@ -112,6 +112,48 @@ def _oracle_diff(pred, obs, dense, rho, *, padding, crop, robust, eps, reduction
     return per.mean(0) if reduction == "mean" else per.sum(0)
 
 
+@pytest.mark.parametrize("padding", ["reflect", "replicate", "zeros"])
+@pytest.mark.parametrize("crop", ["valid", "same"])
+@pytest.mark.parametrize("ksize", [3, 5, 7])
+@pytest.mark.parametrize("shape", [(2, 3, 8, 7), (1, 3, 19, 515), (2, 3, 37, 50), (1, 3, 9, 257), (3, 3, 64, 6)])
+def test_phys_generic_kernels_interior_and_border(dev, padding, crop, ksize, shape):
+    """Generic kernels (W % 4 != 0 keeps the row ring out): the interior sweep in row batches (3x3, 5x5), the
+    per-row interior path of partial units, the compact border phase and the run-time-size body (7x7) against autograd
+    of the oracle -- value, map and gradient; planes smaller than one unit, more than two strips, H not a multiple of
+    the unit height, planes that are all border."""
+    from lowlight_image_enhancement_b200.metrics.phys_consistency import phys_cons_raw
+    if crop == "valid" and min(shape[-2:]) <= 2 * (ksize // 2):
+        pytest.skip("valid crop leaves nothing")
+    g = torch.Generator().manual_seed(sum(shape) * 7 + ksize + len(padding))
+    pred = torch.rand(shape, generator=g)
+    k = torch.rand(3, 1, ksize, ksize, generator=g) + 0.05
+    k = k / k.sum((-2, -1), keepdim=True)
+    rho = torch.tensor([0.9, 1.1, 1.3][: shape[0]])
+    dense = psf_ops.embed_dense(k)
+    obs = (pred * rho.view(-1, 1, 1, 1) + 0.05 * torch.randn(shape, generator=g)).clamp(0, 1.2)
+    kw = dict(padding=padding, crop=crop, robust="none", eps=1e-12, reduction="mean")
+    xr = pred.clone().requires_grad_(True)
+    ref = _oracle_diff(xr, obs, dense, rho, clamp01=False, **kw)
+    ref.backward()
+    x = pred.to(dev).requires_grad_(True)
+    val, mp = phys_cons_raw(x.detach(), obs.to(dev), k.to(dev), rho.to(dev), return_map=True, **kw)
+    assert _rel(val, ref) < RTOL
+    ph = ksize // 2
+    import torch.nn.functional as F
+    kd = psf_ops.prepare_dense_psf(dense, 3, 3, torch.float32, True, False, 1e-12)
+    y = F.conv2d(pred, kd, padding=ph) if padding == "zeros" else F.conv2d(F.pad(pred, (ph, ph, ph, ph), mode=padding), kd)
+    want = (y * rho.view(-1, 1, 1, 1) - obs).abs()
+    if crop == "valid":
+        want = want[..., ph:-ph, ph:-ph]
+    assert mp.shape == want.shape and float((mp.cpu() - want).abs().max()) < 2e-6
+    out = phys_cons_raw(x, obs.to(dev), k.to(dev), rho.to(dev), differentiable=True, **kw)
+    out.backward()
+    assert _rel(out, ref) < RTOL
+    # |r| is sign-like: a residual at the fp32 rounding level of the tap sum may take the other sign in the oracle
+    bad = ((x.grad.cpu() - xr.grad).abs() > 2e-5 * float(xr.grad.abs().max())).float().mean()
+    assert float(bad) < 2e-3, float(bad)
+
+
 @pytest.mark.parametrize("case_i", [5, 6, 7, 8])
 def test_phys_generic_path_gradient(dev, case_i):
     """Generic path (dense / 5x5 / 3x5 / spatial rho): gradient vs oracle autograd."""
