@@ -635,6 +635,9 @@ def run_extra(args, rank, world, dev, clk=None):
                                                       k1=0.01, k2=0.03), 12, dev) / 12
     t_ssim5 = timed_warm(lambda i: Fn.ssim_stats(pool[i % 3][0], pool[i % 3][1], win_l, pad_mode=nat_.PAD["reflect"],
                                                  c1=1e-4, c2=9e-4, eps=1e-12, clamp_var=True), 12, dev) / 12
+    win_t = Fn.window_1d("torchmetrics", 11, 1.5, dev)
+    t_dual = timed_warm(lambda i: Fn.ssim_stats_dual(pool[i % 3][0], pool[i % 3][1], win_l, win_t, c1=1e-4, c2=9e-4,
+                                                     eps=1e-12, c1_b=1e-4, c2_b=9e-4), 12, dev) / 12
     t_de = timed_warm(lambda i: Fn.deltae(pool[i % 3][0], pool[i % 3][1], variant=0, clamp_in=True), 12, dev) / 12
     t_ps = timed_warm(lambda i: Fn.psnr_stats(pool[i % 3][0], pool[i % 3][1], 1, 3, px, cast_first=True, clamp_hi=None,
                                          data_range=1.0, eps=1e-12), 24, dev) / 24
@@ -667,6 +670,8 @@ def run_extra(args, rank, world, dev, clk=None):
         "kernels": [kern("psnr_stats_kernel (per-channel table: CPSNR, RGB-PSNR)", t_ps, 24, "hbm"),
                     kern("ssim_ring_kernel<4 maps> (SSIM, torchmetrics policy)", t_ssim, 24, "fp32 pipe / issue (88 FMA per element)", 88),
                     kern("ssim_ring_kernel<5 maps> (RGB-SSIM, ssim_linear policy)", t_ssim5, 24, "fp32 pipe / issue (110 FMA per element)", 110),
+                    kern("ssim_ring_kernel<5 maps, DUAL> (both policies from one pass: what the driver launches)", t_dual, 24,
+                         "fp32 pipe / issue (110 FMA per element + second formula)", 110),
                     kern("deltae_kernel", t_de, 24, "instruction issue (fp32 + sfu)"),
                     kern("all 7 metrics of one image, image_metrics (generic path)", t_all, 36, "mixed"),
                     kern("all 7 metrics of one image, accumulate_image_metrics (one-launch epilogue)", t_fast, 36, "mixed")],

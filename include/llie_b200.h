@@ -237,6 +237,23 @@ int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, 
                     const float *win1d_host, double *out_sum, float *out_map, int32_t *out_flags, void *workspace,
                     void *stream);
 
+/* Two SSIM policies of one image pair from ONE pass (the evaluation driver asks for both `linear_ssim`, torchmetrics
+ * policy, and `rgb_ssim`, ssim_linear policy: metrics/ssim.py:188-538 and metrics/channelwise.py:226-302).
+ * `desc` / `win1d` describe the first policy exactly as for llie_ssim_stats (reflect border, same size, variance
+ * clamp); the second is the interior-crop policy (no clamp, no eps) with constants c1_b / c2_b whose normalised 1-D
+ * window is the first one's up to rounding: tap_sum_ratio = sum(taps_b) / sum(taps_a) in double.  The two windows
+ * differ by <= 5 ulp per tap; only the difference of their SUMS is visible in the score (1e-4 on flat images, where
+ * E[x^2] - mu^2 cancels), and it is applied in closed form: moments scale by r = ratio^2, central moments become
+ * r (var - (r - 1) mu^2).  Measured against a float64 evaluation with the second window: <= 3e-9 relative.
+ *   out_sum    [n * c] doubles, first policy over h x w;  out_sum_b [n * c] doubles over (h - 10) x (w - 10)
+ * llie_ssim_stats_dual_eligible: 1 when this pair of tensors can take the call (11 taps, W % 4 == 0, 16-byte aligned
+ * planes, host copy of the taps, reflect padding, clamp_var, no input clamp / luma / interior), else 0: make two
+ * llie_ssim_stats calls. */
+int llie_ssim_stats_dual_eligible(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d_host);
+int llie_ssim_stats_dual(const llie_ssim_desc *desc, float c1_b, float c2_b, double tap_sum_ratio, const float *x,
+                         const float *y, const float *win1d, const float *win1d_host, double *out_sum,
+                         double *out_sum_b, int32_t *out_flags, void *workspace, void *stream);
+
 /* Differentiable (D)SSIM, kornia policy (reflect border, same size, no variance clamp): forward as
  * llie_ssim_stats plus out_coef [3][n*c][h][w] = grad_scale * dLossMap/dS * (A1, A2, A3), the per-window
  * sensitivities of S to (mu_x, E[x^2], E[xy]); backward folds them through the adjoint of reflect-pad o

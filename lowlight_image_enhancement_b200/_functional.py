@@ -7,6 +7,7 @@ No arithmetic on image-sized tensors happens in Python.
 from __future__ import annotations
 
 import contextlib
+import math
 import threading
 import warnings
 from dataclasses import dataclass
@@ -418,6 +419,50 @@ def ssim_stats(x: Tensor, y: Tensor, win: Tensor, *, pad_mode: int, c1: float, c
     nat.check(rc, "llie_ssim_stats")
     nat.count_launch()
     return sums, flags, smap
+
+
+def ssim_stats_dual(x: Tensor, y: Tensor, win: Tensor, win_b: Tensor, *, c1: float, c2: float, eps: float,
+                    c1_b: float, c2_b: float):
+    """Both evaluation policies from one pass (llie_ssim_stats_dual): the ssim_linear policy with window `win`
+    (reflect, same size, variance clamp, `eps`) and the torchmetrics policy (interior crop, no clamp, no eps) whose
+    window `win_b` equals `win` up to rounding -- only the ratio of the tap sums enters.  Returns (sums [N, C] of the
+    first policy over H x W, sums [N, C] of the second over (H - 10) x (W - 10), flags), or None when the tensors cannot
+    take the fused pass (the caller then makes the two `ssim_stats` calls)."""
+    dev = x.device
+    n, c, h, w = x.shape
+    if win.numel() != win_b.numel() or win_host(win) is None:
+        return None
+    d = nat.SsimDesc(n, c, h, w, int(win.numel()), nat.PAD["reflect"], 0, 0, 1, 0, 0, float(c1), float(c2), float(eps))
+    lib = nat.lib()
+    if not lib.llie_ssim_stats_dual_eligible(d, nat.ptr(x), nat.ptr(y), win_host(win)):
+        return None
+    ratio = _tap_sum_ratio(win, win_b)
+    sums = torch.empty((n, c), dtype=torch.float64, device=dev)
+    sums_b = torch.empty((n, c), dtype=torch.float64, device=dev)
+    flags = torch.empty(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.llie_ssim_stats_dual(d, float(c1_b), float(c2_b), ratio, nat.ptr(x), nat.ptr(y), nat.ptr(win),
+                                      win_host(win), nat.ptr(sums), nat.ptr(sums_b), nat.ptr(flags),
+                                      nat.ptr(nat.workspace(dev)), nat.stream_ptr(dev))
+    nat.check(rc, "llie_ssim_stats_dual")
+    nat.count_launch()
+    return sums, sums_b, flags
+
+
+_ratio_cache: dict = {}
+
+
+def _tap_sum_ratio(win: Tensor, win_b: Tensor) -> float:
+    """sum(win_b) / sum(win) in float64 from the host copies of two `window_1d` tensors (cached per pair)."""
+    key = (id(win), id(win_b))
+    r = _ratio_cache.get(key)
+    if r is None:
+        ha, hb = win_host(win), win_host(win_b)
+        if ha is None or hb is None:
+            ha, hb = win.double().cpu().tolist(), win_b.double().cpu().tolist()
+        r = math.fsum(float(v) for v in hb) / math.fsum(float(v) for v in ha)
+        _ratio_cache[key] = r
+    return r
 
 
 # ------------------------------------------------------------------------------------------------

@@ -97,6 +97,9 @@ _SIGNATURES = {
     "llie_psnr_stats": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_psnr_stats_static": (C.c_int, [C.POINTER(PsnrDesc), _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_ssim_stats": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    "llie_ssim_stats_dual_eligible": (C.c_int, [C.POINTER(SsimDesc), _VP, _VP, _VP]),
+    "llie_ssim_stats_dual": (C.c_int, [C.POINTER(SsimDesc), C.c_float, C.c_float, C.c_double, _VP, _VP, _VP, _VP, _VP,
+                                       _VP, _VP, _VP, _VP]),
     "llie_deltae": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_sqerr": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     "llie_deltae_sqerr_rgb": (C.c_int, [C.POINTER(DeltaEDesc), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -478,8 +478,8 @@ static void fill_domain(PhysArgs &a) {
 }
 
 static int grid_x_for(int n, int work_items) {
-    // persistent-style grid: ~8 resident CTAs of 256 threads per SM, split evenly over samples
-    int per_sample = div_up(kNumSM * 8, n);
+    // persistent-style grid: one wave of the 4 resident CTAs of 256 threads per SM, split evenly over samples
+    int per_sample = div_up(kNumSM * 4, n);
     if (per_sample > work_items) per_sample = work_items;
     if (per_sample < 1) per_sample = 1;
     return per_sample;

@@ -1355,6 +1355,33 @@ extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const
     return ssim_forward(desc, x, y, win1d, win1d_host, out_sum, out_map, nullptr, 0.f, out_flags, workspace, stream);
 }
 
+extern "C" int llie_ssim_stats_dual_eligible(const llie_ssim_desc *desc, const float *x, const float *y,
+                                            const float *win1d_host) {
+    return desc != nullptr && g_ssim_path_a.load(std::memory_order_relaxed) == 0 &&
+           ssim_ring_dual_eligible(*desc, x, y, win1d_host);
+}
+
+extern "C" int llie_ssim_stats_dual(const llie_ssim_desc *desc, float c1_b, float c2_b, double tap_sum_ratio,
+                                    const float *x, const float *y, const float *win1d, const float *win1d_host,
+                                    double *out_sum, double *out_sum_b, int32_t *out_flags, void *workspace,
+                                    void *stream) {
+    LLIE_REQUIRE(desc && x && y && win1d && out_sum && out_sum_b && out_flags && workspace, "ssim_stats_dual: null pointer");
+    LLIE_REQUIRE(llie_ssim_stats_dual_eligible(desc, x, y, win1d_host),
+                 "ssim_stats_dual: needs the 11-tap ring kernel (W %% 4 == 0, 16-byte aligned planes, host taps), reflect "
+                 "padding, the variance clamp and images larger than the window; make two llie_ssim_stats calls instead");
+    LLIE_REQUIRE(tap_sum_ratio > 0.999 && tap_sum_ratio < 1.001, "ssim_stats_dual: the two windows must both be normalised");
+    SsimArgs a{};
+    a.d = *desc;
+    a.x = x; a.y = y; a.win = win1d;
+    a.out_sum = out_sum; a.out_sum2 = out_sum_b; a.out_flags = out_flags;
+    a.co = desc->c;
+    const double r = tap_sum_ratio * tap_sum_ratio;  // a moment is filtered along both axes
+    a.dual_c1 = c1_b; a.dual_c2 = c2_b;
+    a.dual_r = (float)r; a.dual_2r = (float)(2.0 * r); a.dual_r2 = (float)(r * r); a.dual_2r2 = (float)(2.0 * r * r);
+    a.dual_neg_eps = (float)(1.0 - r);
+    return ssim_ring_forward(a, win1d_host, workspace, reinterpret_cast<cudaStream_t>(stream));
+}
+
 extern "C" int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
                                       const float *win1d_host, float grad_scale, double *out_sum, float *out_map,
                                       float *out_coef, int32_t *out_flags, void *workspace, void *stream) {

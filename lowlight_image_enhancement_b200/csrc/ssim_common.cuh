@@ -18,6 +18,11 @@ struct SsimArgs {
     unsigned *ticket;
     int tiles_x, tiles_y, co;
     int seg_rows;  // streaming kernel: output rows per CTA
+    // second policy evaluated from the same five moments (llie_ssim_stats_dual): the interior-crop policy whose taps sum
+    // to sqrt(r) times this window's, r = dual_r; moments scale by r, central moments by r after a -eps * mean^2
+    // correction (eps = r - 1)
+    double *out_sum2, *part2;
+    float dual_c1, dual_c2, dual_r, dual_2r, dual_r2, dual_2r2, dual_neg_eps;
 };
 
 struct SsimBwdArgs {
@@ -32,6 +37,7 @@ struct SsimBwdArgs {
 bool ssim_ring_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host, bool want_map,
                         const float *coef);
 int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaStream_t st);
+bool ssim_ring_dual_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host);
 bool ssim_ring_bwd_eligible(const SsimBwdArgs &a, const float *win_host);
 int ssim_ring_backward(SsimBwdArgs &a, const float *win_host, cudaStream_t st);
 int pick_seg_rows(long long cols, int h, int slots, int min_rows, int halo);

@@ -121,8 +121,9 @@ __device__ __forceinline__ void scatter_row(f2_t (&acc)[M][RK], const f2_t (&h)[
     for (int q = 0; q < M; ++q) done[q] = acc[q][(II + 1) % RK];
 }
 
-template <bool MAPS5, bool COEF, bool CLAMP>
+template <bool MAPS5, bool COEF, bool CLAMP, bool DUAL = false>
 __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const SsimArgs a, const RingTaps tp) {
+    static_assert(!DUAL || (MAPS5 && !COEF), "the second policy is evaluated from the five-map statistics");
     constexpr int M = MAPS5 ? 5 : 4;
     __shared__ __align__(128) float ring[RD][2][RROW];
     __shared__ __align__(8) uint64_t full[RD], empty[RD];
@@ -205,6 +206,9 @@ __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const Ssim
 #pragma unroll
     for (int c = 0; c < 2; ++c) cm[c] = (gx + c < W && (!d.interior || (gx + c >= RP && gx + c < W - RP))) ? 1.f : 0.f;
     const f2_t CM = pack2(cm[0], cm[1]);
+    // DUAL: column mask of the interior crop the second policy averages over
+    const f2_t CM2 = pack2((gx >= RP && gx < W - RP) ? 1.f : 0.f, (gx + 1 >= RP && gx + 1 < W - RP) ? 1.f : 0.f);
+    f2_t facc2 = 0ull;
     const f2_t C1 = bc2(d.c1), C2 = bc2(d.c2), EPS = bc2(d.eps), TWO = bc2(2.f), NEG1 = bc2(-1.f);
     f2_t acc[M][RK];
 #pragma unroll
@@ -295,6 +299,20 @@ __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const Ssim
                 f2_t vsum, sxy;
                 if (MAPS5) {
                     f2_t sx = fma2(mx2, NEG1, done[2]), sy = fma2(my2, NEG1, done[3]);
+                    if (DUAL) {
+                        // second policy: its taps are this window's up to <= 5 ulp per tap and a different tap SUM, and
+                        // only the sum matters: M' = r M, var' = r (var - eps mu^2), no clamp, no eps
+                        const f2_t NE = bc2(a.dual_neg_eps), B = add2(mx2, my2);
+                        const f2_t n1b = fma2(mxy, bc2(a.dual_2r2), bc2(a.dual_c1));
+                        const f2_t d1b = fma2(B, bc2(a.dual_r2), bc2(a.dual_c1));
+                        const f2_t n2b = fma2(fma2(mxy, NE, fma2(mxy, NEG1, done[4])), bc2(a.dual_2r), bc2(a.dual_c2));
+                        const f2_t d2b = fma2(fma2(B, NE, add2(sx, sy)), bc2(a.dual_r), bc2(a.dual_c2));
+                        float nb[2], db[2];
+                        unpack2(mul2(n1b, n2b), nb[0], nb[1]);
+                        unpack2(mul2(d1b, d2b), db[0], db[1]);
+                        const float s0 = div_pos(nb[0], db[0], rcp_pos(db[0])), s1 = div_pos(nb[1], db[1], rcp_pos(db[1]));
+                        if (gy >= RP && gy < H - RP) facc2 = fma2(pack2(s0, s1), CM2, facc2);
+                    }
                     if (d.clamp_var) {
                         float a0, a1, b0, b1;
                         unpack2(sx, a0, a1);
@@ -362,6 +380,12 @@ __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const Ssim
     unpack2(chkx, cx0f, cx1f);
     unpack2(chky, cy0f, cy1f);
     const double bs = block_sum<double>((double)f0 + (double)f1, red);
+    if (DUAL) {
+        float g0, g1;
+        unpack2(facc2, g0, g1);
+        const double bs2 = block_sum<double>((double)g0 + (double)g1, red);
+        if (tid == 0) a.part2[blockIdx.x] = bs2;
+    }
     int flag = 0;
     if (!(cx0f == 0.f) || !(cx1f == 0.f)) flag |= 1;
     if (!(cy0f == 0.f) || !(cy1f == 0.f)) flag |= 2;
@@ -385,6 +409,13 @@ __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const Ssim
         for (; b < tpp; b += 32) s0 += __ldcg(p + b);
         const double sm_ = warp_sum((s0 + s1) + (s2 + s3));
         if (lane == 0) a.out_sum[pl] = sm_;
+        if (DUAL) {
+            const double *p2 = a.part2 + (size_t)pl * tpp;
+            double t0 = 0.0;
+            for (int b2 = lane; b2 < tpp; b2 += 32) t0 += __ldcg(p2 + b2);
+            t0 = warp_sum(t0);
+            if (lane == 0) a.out_sum2[pl] = t0;
+        }
     }
     int fl = 0;
     for (int b = tid; b < (int)gridDim.x; b += RT) fl |= __ldcg(a.pflag + b);
@@ -645,6 +676,11 @@ bool ssim_ring_eligible(const llie_ssim_desc &d, const float *x, const float *y,
            aligned16(y) && (coef == nullptr || (!d.clamp_var && (reinterpret_cast<uintptr_t>(coef) & 7u) == 0));
 }
 
+bool ssim_ring_dual_eligible(const llie_ssim_desc &d, const float *x, const float *y, const float *win_host) {
+    return ssim_ring_eligible(d, x, y, win_host, false, nullptr) && d.clamp_var && !d.clamp_in && !d.interior &&
+           !d.loss_map && d.pad_mode == LLIE_PAD_REFLECT && d.h > 2 * RP && d.w > 2 * RP;
+}
+
 int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaStream_t st) {
     const llie_ssim_desc &d = a.d;
     RingTaps tp;
@@ -661,13 +697,16 @@ int ssim_ring_forward(SsimArgs &a, const float *win_host, void *workspace, cudaS
     a.tiles_y = div_up(d.h, a.seg_rows);
     const long long grid = cols * a.tiles_y;
     Workspace ws(workspace);
-    LLIE_REQUIRE(grid <= 0x7fffffffLL && (size_t)grid * (sizeof(double) + sizeof(int)) <= ws.scratch_bytes,
+    LLIE_REQUIRE(grid <= 0x7fffffffLL && (size_t)grid * (2 * sizeof(double) + sizeof(int)) <= ws.scratch_bytes,
                  "ssim_stats: workspace too small for %lld tiles", grid);
     a.part = reinterpret_cast<double *>(ws.scratch);
-    a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)grid * sizeof(double));
+    a.part2 = a.part + grid;
+    a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)grid * 2 * sizeof(double));
     a.ticket = ws.tickets;
     const bool clamp = d.clamp_in != 0;
-    if (a.coef != nullptr) {
+    if (a.out_sum2 != nullptr) {
+        ssim_ring_kernel<true, false, false, true><<<(int)grid, RT, 0, st>>>(a, tp);
+    } else if (a.coef != nullptr) {
         if (clamp) ssim_ring_kernel<false, true, true><<<(int)grid, RT, 0, st>>>(a, tp);
         else ssim_ring_kernel<false, true, false><<<(int)grid, RT, 0, st>>>(a, tp);
     } else if (d.clamp_var) {

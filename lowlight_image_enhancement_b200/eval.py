@@ -145,6 +145,23 @@ def _rgb_ssim_sums(pred, target, flags, cache, data_range: float = 1.0):
     return cache[key]
 
 
+def _dual_ssim_sums(pred, target, data_range_tm: float):
+    """`linear_ssim` (torchmetrics policy, sigma 1.5) and `rgb_ssim` (ssim_linear policy, data_range 1) of a 3-channel
+    pair from one pass: (rgb sums [n, 3], torchmetrics sums [n, 3], elements per image of the latter, flags), or None
+    when the pair cannot take the fused kernel (the caller then launches the two policies separately)."""
+    from . import _functional as Fn
+    if pred.shape[1] != 3:
+        return None
+    n, c, h, w = pred.shape
+    dual = Fn.ssim_stats_dual(pred, target, Fn.window_1d("linear", 11, 1.5, pred.device),
+                              Fn.window_1d("torchmetrics", 11, 1.5, pred.device), c1=0.01 ** 2, c2=0.03 ** 2, eps=1e-12,
+                              c1_b=(0.01 * data_range_tm) ** 2, c2_b=(0.03 * data_range_tm) ** 2)
+    if dual is None:
+        return None
+    rsums, tsums, flags = dual
+    return rsums, tsums, c * (h - 10) * (w - 10), flags
+
+
 def _make_rgb_psnr(col: int):
     def fn(pred, target, flags, *, cache=None, data_range: float = 1.0, eps: float = 1e-12) -> Tensor:
         table = _rgb_table(pred, target, flags, {} if cache is None else cache, data_range, eps)
@@ -261,23 +278,34 @@ def accumulate_image_metrics(pred: Tensor, target: Tensor, names: Sequence[str],
         if side is not None:
             side.wait_stream(main)
             with torch.cuda.stream(side):
-                ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
-                                                                  sigma=1.5, k1=0.01, k2=0.03)
+                dual = _dual_ssim_sums(p, t, float(kw.get("data_range", 1.0))) if rgbs else None
+                if dual is not None:   # both policies from one pass over the pair (csrc/ssim_ring.cu, DUAL)
+                    rsums_side, ssim_sums, ssim_count, f = dual
+                    f_rs = f
+                else:
+                    ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
+                                                                      sigma=1.5, k1=0.01, k2=0.03)
             for x_ in (ssim_sums, f):
                 x_.record_stream(main)
             for x_ in (p, t):
                 x_.record_stream(side)
             joined = side
-            if rgbs:   # the second SSIM policy follows on the same side stream: the chain's small Sobel / select
-                # kernels then run under FMA-bound SSIM work for their whole length, not only under the first launch
+            if rgbs and dual is None:   # the second SSIM policy follows on the same side stream: the chain's small
+                # Sobel / select kernels then run under FMA-bound SSIM work for their whole length
                 with torch.cuda.stream(side):
                     f_rs = torch.zeros(1, dtype=torch.int32, device=dev)
                     rsums_side = _rgb_ssim_sums(p, t, f_rs, {})
+            if rgbs:
                 for x_ in (rsums_side, f_rs):
                     x_.record_stream(main)
         else:
-            ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
-                                                              sigma=1.5, k1=0.01, k2=0.03)
+            dual = _dual_ssim_sums(p, t, float(kw.get("data_range", 1.0))) if rgbs else None
+            if dual is not None:
+                rsums_side, ssim_sums, ssim_count, f = dual
+                f_rs = f
+            else:
+                ssim_sums, ssim_count, f = ssim_sums_torchmetrics(p, t, data_range=float(kw.get("data_range", 1.0)),
+                                                                  sigma=1.5, k1=0.01, k2=0.03)
         ssim_c = ssim_sums.shape[1]
         fl.append(f)
     if colour:

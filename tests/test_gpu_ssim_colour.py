@@ -439,3 +439,61 @@ def test_luma_bt601_equals_eager_expression(dev, shape):
     assert torch.equal(Fn.luma_bt601(x.contiguous()), want)
     with pytest.raises(ValueError):
         Fn.luma_bt601(x[:, :2].contiguous())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kind", ["noise", "natural", "dark", "flat", "const"])
+@pytest.mark.parametrize("shape", [(1, 3, 64, 128), (2, 3, 70, 252), (1, 3, 300, 516)])
+def test_ssim_dual_policies_from_one_pass(dev, shape, kind):
+    """llie_ssim_stats_dual: the ssim_linear policy (rgb_ssim) and the torchmetrics policy (linear_ssim) from one pass
+    over the pair.  The first policy's sums are those of the single-policy kernel; the second's -- evaluated from the
+    first window's moments with the tap-SUM correction -- agree with the float64 oracle of the torchmetrics policy to
+    1e-5 on textured images.  On flat images E[x^2] - mu^2 cancels to the fp32 rounding level of the moments, and
+    that level against C2 = 9e-4 is ~1e-3 of the score for ANY fp32 evaluation order (measured on 0.9 / 0.7 constant
+    images: single-policy kernel 8.0e-4, this one 9.2e-4 from the float64 oracle): both are held to 2e-3 there."""
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    from lowlight_image_enhancement_b200 import _native as nat
+    g = torch.Generator().manual_seed(sum(shape) + len(kind))
+    n, c, h, w = shape
+    if kind == "noise":
+        tgt = torch.rand(shape, generator=g)
+        pred = (tgt + 0.1 * torch.randn(shape, generator=g)).clamp(0, 1)
+    elif kind in ("natural", "dark"):
+        low = torch.rand(n, c, h // 8 + 2, w // 8 + 2, generator=g)
+        tgt = torch.nn.functional.interpolate(low, size=(h, w), mode="bicubic", align_corners=False).clamp(0, 1)
+        pred = (tgt + 0.03 * torch.randn(shape, generator=g)).clamp(0, 1)
+        if kind == "dark":
+            tgt, pred = tgt * 0.02, pred * 0.02
+    elif kind == "flat":
+        tgt = torch.full(shape, 0.8) + 1e-4 * torch.randn(shape, generator=g)
+        pred = torch.full(shape, 0.8)
+    else:
+        tgt, pred = torch.full(shape, 0.7), torch.full(shape, 0.9)
+    x, y = pred.to(dev), tgt.to(dev)
+    wl, wt = Fn.window_1d("linear", 11, 1.5, dev), Fn.window_1d("torchmetrics", 11, 1.5, dev)
+    dual = Fn.ssim_stats_dual(x, y, wl, wt, c1=1e-4, c2=9e-4, eps=1e-12, c1_b=1e-4, c2_b=9e-4)
+    assert dual is not None
+    rs, ts, fl = dual
+    assert int(fl.item()) == 0
+    rs1, _, _ = Fn.ssim_stats(x, y, wl, pad_mode=nat.PAD["reflect"], c1=1e-4, c2=9e-4, eps=1e-12, clamp_var=True)
+    ts1, _, _ = Fn.ssim_stats(x, y, wt, pad_mode=nat.PAD["reflect"], c1=1e-4, c2=9e-4, eps=0.0, interior=True)
+    assert torch.equal(rs, rs1)
+    cnt = c * (h - 10) * (w - 10)
+    got = (ts.sum(1) / cnt).cpu()
+    one = (ts1.sum(1) / cnt).cpu()
+    ref = quality.ssim_torchmetrics(pred.double(), tgt.double(), data_range=1.0).double()
+    tol = 2e-3 if kind in ("flat", "const") else 1e-5
+    assert float(((got - ref).abs() / ref.abs()).max()) < tol
+    assert float(((one - ref).abs() / ref.abs()).max()) < tol
+    if kind not in ("flat", "const"):
+        assert float(((got - one).abs() / one.abs()).max()) < 3e-6
+
+
+@pytest.mark.gpu
+def test_ssim_dual_falls_back_when_not_eligible(dev):
+    from lowlight_image_enhancement_b200 import _functional as Fn
+    wl, wt = Fn.window_1d("linear", 11, 1.5, dev), Fn.window_1d("torchmetrics", 11, 1.5, dev)
+    x = torch.rand(1, 3, 40, 50, device=dev)   # W % 4 != 0: the ring kernel does not take it
+    assert Fn.ssim_stats_dual(x, x.clone(), wl, wt, c1=1e-4, c2=9e-4, eps=1e-12, c1_b=1e-4, c2_b=9e-4) is None
+    x = torch.rand(1, 3, 10, 64, device=dev)   # nothing left of the interior crop
+    assert Fn.ssim_stats_dual(x, x.clone(), wl, wt, c1=1e-4, c2=9e-4, eps=1e-12, c1_b=1e-4, c2_b=9e-4) is None
