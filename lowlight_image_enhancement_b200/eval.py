@@ -54,11 +54,16 @@ def _psnr(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.
     return table[0, 4]
 
 
-def _ssim(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.0) -> Tensor:
-    """lowlight_metrics.py:217-220 -> SSIMEvaluator (torchmetrics policy), mean over the batch's images."""
+def _ssim(pred: Tensor, target: Tensor, flags: Tensor, *, data_range: float = 1.0, cache=None) -> Tensor:
+    """lowlight_metrics.py:217-220 -> SSIMEvaluator (torchmetrics policy), mean over the batch's images.  `cache`
+    (image_metrics): the sums may already be there, left by the one-pass evaluation of both SSIM policies."""
     from .metrics.ssim import ssim_sums_torchmetrics
-    sums, count, fl = ssim_sums_torchmetrics(pred, target, data_range=float(data_range), sigma=1.5, k1=0.01, k2=0.03)
-    flags |= fl
+    hit = None if cache is None else cache.get(("linear_ssim", float(data_range)))
+    if hit is not None:
+        sums, count = hit
+    else:
+        sums, count, fl = ssim_sums_torchmetrics(pred, target, data_range=float(data_range), sigma=1.5, k1=0.01, k2=0.03)
+        flags |= fl
     return (sums.sum(dim=1) / float(count)).to(torch.float32).double().mean()
 
 
@@ -212,11 +217,20 @@ def image_metrics(pred: Tensor, target: Tensor, names: Sequence[str], flags: Opt
                              want_sqerr=ride_psnr)
     vals = []
     cache: dict = {}
+    rgbs = [nm for nm in names if nm in _RGB_SSIM]
+    if "linear_ssim" in names and rgbs and not any(opts.get(nm) for nm in rgbs):
+        # both SSIM policies of the pair from one pass (csrc/ssim_ring.cu, DUAL); None: the adapters launch their own
+        dr = float(opts.get("linear_ssim", {}).get("data_range", 1.0))
+        dual = _dual_ssim_sums(p, t, dr)
+        if dual is not None:
+            cache[("rgb_ssim", 1.0)], tsums, tcount, fl = dual
+            cache[("linear_ssim", dr)] = (tsums, tcount)
+            flags |= fl
     for name in names:
         kw = dict(opts.get(name, {}))
         if (name in _COLOUR or name == "linear_psnr") and shared is not None:
             kw["shared"] = shared
-        if name in _RGB_PSNR or name in _RGB_SSIM:
+        if name in _RGB_PSNR or name in _RGB_SSIM or name == "linear_ssim":
             kw["cache"] = cache
         vals.append(METRIC_FUNCTIONS[name](p, t, flags, **kw).reshape(()))
     return torch.stack(vals)
