@@ -87,7 +87,13 @@ for it in range(cases):
     frac = float((d[chroma_ok] > 1e-4).double().mean()) if chroma_ok.any() else 0.0
     check("de00_map", frac < 2e-3 and float(d.mean()) < 3e-5, ((n, h, w), frac, float(d.mean()), float(d.max())))
     es, er = edge_deltaE2000_stats(pr8.to(dev), gt8.to(dev), q=0.85), colour.edge_stats(pr8, gt8, q=0.85)
-    check("edge", es["count"] == er["count"] and abs(es["mean"] - er["mean"]) < 2e-4,
+    # the mask count is bit-exact GIVEN the L plane (stage test test_sobel_quantile_count_bit_exact); end to end it also
+    # depends on the last bit of L = 116 f(Y) - 16, where this library's x^2.4 / cbrt (< 1 ulp) and the host libm of the
+    # CPU oracle may round differently: a pixel whose gradient sits on the threshold can then change sides (seen once
+    # in ~700 cases: 69 291 against 69 292 pixels).  One flip per image is tolerated and reported, more is a failure.
+    if es["count"] != er["count"]:
+        print("edge count differs by", es["count"] - er["count"], "of", er["count"], (n, h, w), flush=True)
+    check("edge", abs(es["count"] - er["count"]) <= n and abs(es["mean"] - er["mean"]) < 2e-4,
           ((n, h, w), es["count"], er["count"], es["mean"], er["mean"]))
     # ---- DeltaE00Loss value + gradient
     xr = pr8.double().requires_grad_(True)
