@@ -250,16 +250,23 @@ __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const Ssim
                     X = pack2(__saturatef(xl), __saturatef(xh));
                     Y = pack2(__saturatef(yl), __saturatef(yh));
                 }
-                f2_t mm[M];
-                mm[0] = X;
-                mm[1] = Y;
-                if (MAPS5) {
-                    mm[2] = mul2(X, X);
-                    mm[3] = mul2(Y, Y);
-                    mm[4] = mul2(X, Y);
-                } else {
-                    mm[2] = fma2(X, X, mul2(Y, Y));
-                    mm[3] = mul2(X, Y);
+                // the products as SCALAR multiplies: every value enters the horizontal pass broadcast to both lanes
+                // of an FFMA2 (a register operand form, no move), and ptxas turns a packed product that is only ever
+                // read one lane at a time into one half-rate FMUL2 per lane (36 per row instead of 21); 36 full-rate
+                // FMULs are half the pipe time of those
+                float v[M][2];
+                unpack2(X, v[0][0], v[0][1]);
+                unpack2(Y, v[1][0], v[1][1]);
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    if (MAPS5) {
+                        v[2][e] = __fmul_rn(v[0][e], v[0][e]);
+                        v[3][e] = __fmul_rn(v[1][e], v[1][e]);
+                        v[4][e] = __fmul_rn(v[0][e], v[1][e]);
+                    } else {
+                        v[2][e] = __fmaf_rn(v[0][e], v[0][e], __fmul_rn(v[1][e], v[1][e]));
+                        v[3][e] = __fmul_rn(v[0][e], v[1][e]);
+                    }
                 }
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
@@ -267,11 +274,7 @@ __global__ void __launch_bounds__(RT, MAPS5 ? 3 : 4) ssim_ring_kernel(const Ssim
                     if (p < 1 || p > RK + 1) continue;  // positions 0 and 13 carry no tap
                     const f2_t w = pack2(tp.wp[p].x, tp.wp[p].y);
 #pragma unroll
-                    for (int q = 0; q < M; ++q) {
-                        float lo, hi;
-                        unpack2(mm[q], lo, hi);
-                        h[q] = fma2(bc2(e ? hi : lo), w, h[q]);
-                    }
+                    for (int q = 0; q < M; ++q) h[q] = fma2(bc2(v[q][e]), w, h[q]);
                 }
             }
             __syncwarp();
