@@ -246,9 +246,10 @@ int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const float *y, 
  * E[x^2] - mu^2 cancels), and it is applied in closed form: moments scale by r = ratio^2, central moments become
  * r (var - (r - 1) mu^2).  Measured against a float64 evaluation with the second window: <= 3e-9 relative.
  *   out_sum    [n * c] doubles, first policy over h x w;  out_sum_b [n * c] doubles over (h - 10) x (w - 10)
- * llie_ssim_stats_dual_eligible: 1 when this pair of tensors can take the call (11 taps, W % 4 == 0, 16-byte aligned
- * planes, host copy of the taps, reflect padding, clamp_var, no input clamp / luma / interior), else 0: make two
- * llie_ssim_stats calls. */
+ * llie_ssim_stats_dual_eligible: 1 when this pair of tensors can take the call (11 taps, reflect padding, clamp_var,
+ * no input clamp / luma / interior, images larger than the window), else 0: make two llie_ssim_stats calls.  W % 4 == 0
+ * with 16-byte aligned planes and a host copy of the taps runs on the TMA ring kernel, everything else on the
+ * two-column cp.async kernel. */
 int llie_ssim_stats_dual_eligible(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d_host);
 int llie_ssim_stats_dual(const llie_ssim_desc *desc, float c1_b, float c2_b, double tap_sum_ratio, const float *x,
                          const float *y, const float *win1d, const float *win1d_host, double *out_sum,

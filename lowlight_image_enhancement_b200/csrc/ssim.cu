@@ -451,8 +451,9 @@ static int launch_ssim_stream(const SsimArgs &a, int grid, cudaStream_t st) {
 constexpr int S2W = 256;
 constexpr int S2T = 128;
 
-template <int K, bool MAPS5, bool COEF = false>
+template <int K, bool MAPS5, bool COEF = false, bool DUAL = false>
 __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) {
+    static_assert(!DUAL || (MAPS5 && !COEF), "the second policy is evaluated from the five-map statistics");
     constexpr int P = K / 2;
     constexpr int RW = S2W + 2 * P;  // even: row starts stay 8-byte aligned
     constexpr int M = MAPS5 ? 5 : 4;
@@ -525,6 +526,7 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
 #pragma unroll
             for (int j = 0; j < K; ++j) acc[q][c][j] = 0.f;
     float facc = 0.f, chk_x = 0.f, chk_y = 0.f;
+    float facc2 = 0.f;  // DUAL: the second (interior-crop) policy, see llie_ssim_stats_dual
     const long long cstride = (long long)d.n * a.co * plane_elems;
     long long off = ((long long)plane * H + y0) * W + gx;  // COEF: first element of the next completed row
     const bool vec2 = (W & 1) == 0;                         // even rows keep the column pair 8-byte aligned
@@ -607,6 +609,15 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
                             sx = fmaxf(sx, 0.f);
                             sy = fmaxf(sy, 0.f);
                         }
+                        if (DUAL) {  // same closed form as ssim_ring_kernel<.., DUAL>: M' = r M, var' = r (var - eps mu^2)
+                            const float su = (acc[2][c][sl] - mx2) + (acc[3][c][sl] - my2), B = mx2 + my2;
+                            const float cxy = acc[4][c][sl] - mxy;
+                            const float n1b = fmaf(mxy, a.dual_2r2, a.dual_c1), d1b = fmaf(B, a.dual_r2, a.dual_c1);
+                            const float n2b = fmaf(fmaf(mxy, a.dual_neg_eps, cxy), a.dual_2r, a.dual_c2);
+                            const float d2b = fmaf(fmaf(B, a.dual_neg_eps, su), a.dual_r, a.dual_c2);
+                            const float s2 = (n1b * n2b) / (d1b * d2b);
+                            if (gx + c < W && gx + c >= P && gx + c < W - P && gy >= P && gy < H - P) facc2 += s2;
+                        }
                         vsum = sx + sy;
                         sxy = acc[4][c][sl] - mxy;
                     } else {
@@ -652,6 +663,10 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
     }
     cp_async_wait<0>();
     const double bs = block_sum<double>((double)facc, red);
+    if (DUAL) {
+        const double bs2 = block_sum<double>((double)facc2, red);
+        if (tid == 0) a.part2[blockIdx.x] = bs2;
+    }
     int flag = 0;
     if (!(chk_x == 0.f)) flag |= 1;
     if (!(chk_y == 0.f)) flag |= 2;
@@ -663,6 +678,15 @@ __global__ void __launch_bounds__(S2T, 3) ssim_stream2_kernel(const SsimArgs a) 
     if (!last_block_done(a.ticket, gridDim.x)) return;
     const int lane = tid & 31, wrp = tid >> 5;
     const int planes = d.n * a.co;
+    if (DUAL) {
+        for (int pl = wrp; pl < planes; pl += S2T / 32) {
+            const double *p2 = a.part2 + (size_t)pl * tpp;
+            double t0 = 0.0;
+            for (int b2 = lane; b2 < tpp; b2 += 32) t0 += __ldcg(p2 + b2);
+            t0 = warp_sum(t0);
+            if (lane == 0) a.out_sum2[pl] = t0;
+        }
+    }
     for (int pl = wrp; pl < planes; pl += S2T / 32) {
         const double *p = a.part + (size_t)pl * tpp;
         double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -1355,10 +1379,17 @@ extern "C" int llie_ssim_stats(const llie_ssim_desc *desc, const float *x, const
     return ssim_forward(desc, x, y, win1d, win1d_host, out_sum, out_map, nullptr, 0.f, out_flags, workspace, stream);
 }
 
+// pairs the ring kernel does not take (W % 4 != 0, unaligned planes, no host taps): the two-column cp.async kernel
+static bool ssim_stream2_dual_eligible(const llie_ssim_desc &d) {
+    return d.ksize == 11 && !d.luma && d.clamp_var && !d.clamp_in && !d.interior && !d.loss_map &&
+           d.pad_mode == LLIE_PAD_REFLECT && d.h > 10 && d.w > 10;
+}
+
 extern "C" int llie_ssim_stats_dual_eligible(const llie_ssim_desc *desc, const float *x, const float *y,
                                             const float *win1d_host) {
-    return desc != nullptr && g_ssim_path_a.load(std::memory_order_relaxed) == 0 &&
-           ssim_ring_dual_eligible(*desc, x, y, win1d_host);
+    const int path = g_ssim_path_a.load(std::memory_order_relaxed);
+    return desc != nullptr && ((path == 0 && ssim_ring_dual_eligible(*desc, x, y, win1d_host)) ||
+                               ((path == 0 || path == 3) && ssim_stream2_dual_eligible(*desc)));
 }
 
 extern "C" int llie_ssim_stats_dual(const llie_ssim_desc *desc, float c1_b, float c2_b, double tap_sum_ratio,
@@ -1367,8 +1398,8 @@ extern "C" int llie_ssim_stats_dual(const llie_ssim_desc *desc, float c1_b, floa
                                     void *stream) {
     LLIE_REQUIRE(desc && x && y && win1d && out_sum && out_sum_b && out_flags && workspace, "ssim_stats_dual: null pointer");
     LLIE_REQUIRE(llie_ssim_stats_dual_eligible(desc, x, y, win1d_host),
-                 "ssim_stats_dual: needs the 11-tap ring kernel (W %% 4 == 0, 16-byte aligned planes, host taps), reflect "
-                 "padding, the variance clamp and images larger than the window; make two llie_ssim_stats calls instead");
+                 "ssim_stats_dual: needs the 11-tap window, reflect padding, the variance clamp, no luma / input clamp / "
+                 "interior flag and images larger than the window; make two llie_ssim_stats calls instead");
     LLIE_REQUIRE(tap_sum_ratio > 0.999 && tap_sum_ratio < 1.001, "ssim_stats_dual: the two windows must both be normalised");
     SsimArgs a{};
     a.d = *desc;
@@ -1379,7 +1410,26 @@ extern "C" int llie_ssim_stats_dual(const llie_ssim_desc *desc, float c1_b, floa
     a.dual_c1 = c1_b; a.dual_c2 = c2_b;
     a.dual_r = (float)r; a.dual_2r = (float)(2.0 * r); a.dual_r2 = (float)(r * r); a.dual_2r2 = (float)(2.0 * r * r);
     a.dual_neg_eps = (float)(1.0 - r);
-    return ssim_ring_forward(a, win1d_host, workspace, reinterpret_cast<cudaStream_t>(stream));
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (g_ssim_path_a.load(std::memory_order_relaxed) == 0 && ssim_ring_dual_eligible(*desc, x, y, win1d_host))
+        return ssim_ring_forward(a, win1d_host, workspace, st);
+    // two-column cp.async kernel, same geometry as the single-policy launch of ssim_forward
+    const llie_ssim_desc &d = *desc;
+    a.tiles_x = div_up(d.w, S2W);
+    const long long cols = (long long)d.n * a.co * a.tiles_x;
+    a.seg_rows = pick_seg_rows(cols, d.h, kNumSM * 3, 64, d.ksize - 1);
+    a.tiles_y = div_up(d.h, a.seg_rows);
+    const long long grid = cols * a.tiles_y;
+    Workspace ws(workspace);
+    LLIE_REQUIRE(grid <= 0x7fffffffLL && (size_t)grid * (2 * sizeof(double) + sizeof(int)) <= ws.scratch_bytes,
+                 "ssim_stats_dual: workspace too small for %lld tiles", grid);
+    a.part = reinterpret_cast<double *>(ws.scratch);
+    a.part2 = a.part + grid;
+    a.pflag = reinterpret_cast<int *>(ws.scratch + (size_t)grid * 2 * sizeof(double));
+    a.ticket = ws.tickets;
+    ssim_stream2_kernel<11, true, false, true><<<(int)grid, S2T, 0, st>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
 }
 
 extern "C" int llie_ssim_loss_forward(const llie_ssim_desc *desc, const float *x, const float *y, const float *win1d,
