@@ -728,8 +728,9 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
         auto do_slot = [&](auto kind_tag, int kb, const float *sp) {
             constexpr int KIND = decltype(kind_tag)::value;
             constexpr bool GENERAL = KIND == kSlotGeneral, WARM = KIND == kSlotWarm;
+            float *gslot = gp + (long long)(ja - 4 + kb) * W;  // grad row of entry kb; one 64-bit product per slot
 #pragma unroll(!FUSED || WARM ? kG : (GENERAL ? kUnrollG : kUnrollI))
-            for (int u = 0; u < kG; ++u) {
+            for (int u = 0; u < kG; ++u, gslot += W) {
                 const int k = kb + u;
                 if (GENERAL && k >= E) break;  // CTA-uniform
                 const int j = ja - 4 + k, qr = j + 1;
@@ -794,8 +795,7 @@ __global__ void __launch_bounds__(kRingThreads, kCtasPerSM) phys_bwd_ring(const 
                         if (i == tgt) gr[i] += ecol;
                 }
                 if (KIND == kSlotInterior) {
-                    if (active)
-                        *reinterpret_cast<float4 *>(gp + (long long)j * W) = make_float4(gr[0], gr[1], gr[2], gr[3]);
+                    if (active) *reinterpret_cast<float4 *>(gslot) = make_float4(gr[0], gr[1], gr[2], gr[3]);
                 } else if (GENERAL && k >= 4) {  // CTA-uniform: entries 0..3 are warm-up
                     if (j == -1) {
 #pragma unroll
