@@ -56,8 +56,15 @@ for it in range(cases):
         x = gen.to(dev).requires_grad_(True)
         lo = SSIMLoss(window_size=ws)(x, tgt.to(dev))
         lo.backward()
+        e_grad, e_f32 = rel(x.grad, xr.grad), 0.0
+        if e_grad >= 5e-5:
+            # small windows: sigma^2 = E[x^2] - mu^2 over 9 or 25 pixels cancels, and the float32 evaluation of the oracle
+            # itself is that far from float64 (tools/diag_ssim3_grad.py); judge against it
+            x32 = gen.clone().requires_grad_(True)
+            quality.ssim_loss_kornia(x32, tgt, ws, 1.0).backward()
+            e_f32 = rel(x32.grad, xr.grad)
         check("ssim_loss", abs(float(lo.detach()) - float(lr.detach())) <= 2e-5 * abs(float(lr.detach())) and
-              rel(x.grad, xr.grad) < 5e-5, ((n, c, h, w), ws, float(lo.detach()), float(lr.detach()), rel(x.grad, xr.grad)))
+              e_grad < max(5e-5, 3.0 * e_f32), ((n, c, h, w), ws, float(lo.detach()), float(lr.detach()), e_grad, e_f32))
     # ---- ssim_linear / torchmetrics policy
     n, c, h, w = shape(min_hw=26)
     k = rnd.choice([3, 7, 11, 11, 11, 15, 21])
@@ -85,7 +92,14 @@ for it in range(cases):
     chroma_ok = ((lab[:, 1] ** 2 + lab[:, 2] ** 2) > 1.0) & ((lab2[:, 1] ** 2 + lab2[:, 2] ** 2) > 1.0)
     d = (m.view_as(r64) - r64).abs()
     frac = float((d[chroma_ok] > 1e-4).double().mean()) if chroma_ok.any() else 0.0
-    check("de00_map", frac < 2e-3 and float(d.mean()) < 3e-5, ((n, h, w), frac, float(d.mean()), float(d.max())))
+    # CIEDE2000 is discontinuous where the hue difference crosses 180 degrees (the mean hue jumps by pi): a pixel pair
+    # on that branch changes by O(1) with the last bit of a', in float32 eager as here (seen once in ~900 cases: one pixel
+    # off by 2.9).  Such pixels are counted and reported, the mean is taken over the others.
+    jumps = int((d > 0.05).sum())
+    if jumps:
+        print("dE00 map: pixels on a formula discontinuity:", jumps, "of", d.numel(), "max", float(d.max()), flush=True)
+    check("de00_map", frac < 2e-3 and float(d[d <= 0.05].mean()) < 3e-5 and jumps <= 2 + d.numel() // 100000,
+          ((n, h, w), frac, float(d.mean()), float(d.max()), jumps))
     es, er = edge_deltaE2000_stats(pr8.to(dev), gt8.to(dev), q=0.85), colour.edge_stats(pr8, gt8, q=0.85)
     # the mask count is bit-exact GIVEN the L plane (stage test test_sobel_quantile_count_bit_exact); end to end it also
     # depends on the last bit of L = 116 f(Y) - 16, where this library's x^2.4 / cbrt (< 1 ulp) and the host libm of the
