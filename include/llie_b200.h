@@ -323,6 +323,17 @@ int llie_pixel_loss_grad(int32_t mode, const float *x, const float *y, const flo
                          int32_t accumulate, double *out_sum, float *out_grad, int32_t *out_flags, void *workspace,
                          void *stream);
 
+/* Epilogue of the fused hybrid loss (losses.py:249-345: `total = w_l1 L1 + w_de dE + w_ssim DSSIM + w_phys Phys`, the
+ * `logs` values): the four term values from the raw device sums of the loss kernels and their weighted total in ONE
+ * launch, in place of the dozen scalar tensor operations of the eager expression.
+ *   l1_sum [1] f64 / l1_count; de_sums [n_de] f64 / de_count; ssim_sums [n_ssim] f64 / ssim_count: term = float(sum / count)
+ *   phys_value: device float (batch mean from llie_phys_value_and_grad); a NULL pointer marks an absent term (NaN in
+ *   out_terms, left out of the total).  weights: HOST float[4] in the order L1, dE, SSIM, Phys.
+ *   out_terms [4] float, out_total [1] float (sum of float32 products in that order). */
+int llie_hybrid_combine(const double *l1_sum, double l1_count, const double *de_sums, int32_t n_de, double de_count,
+                        const double *ssim_sums, int32_t n_ssim, double ssim_count, const float *phys_value,
+                        const float *weights, float *out_terms, float *out_total, void *stream);
+
 /* g[0..n) *= *scale (device scalar), a no-op launch when *scale == 1: applies autograd's upstream scalar to a gradient
  * that a value + gradient kernel already produced in the forward pass.  replaces the `grad * grad_output` multiply of
  * the autograd graph behind NewBP_model/losses.py:92-372. */

@@ -792,7 +792,6 @@ def _one(dev: torch.device) -> Tensor:
     return t
 
 
-_wvec_cache: dict = {}
 
 
 class HybridFusedFn(torch.autograd.Function):
@@ -816,8 +815,7 @@ class HybridFusedFn(torch.autograd.Function):
         lib = nat.lib()
         ws = nat.ptr(nat.workspace(dev))
         flags = torch.empty(1, dtype=torch.int32, device=dev)
-        nan = torch.full((), float("nan"), dtype=torch.float32, device=dev)
-        vals = [nan, nan, nan, nan]
+        des = sss = phys_val = None   # raw device sums / value of the optional terms (llie_hybrid_combine forms the rest)
         g_raw = g_srgb = None
         launches = 0
         with torch.cuda.device(dev):
@@ -832,7 +830,7 @@ class HybridFusedFn(torch.autograd.Function):
                 else:
                     vec, _, _ = phys_forward(xr, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
                                              False)
-                vals[3] = vec[n]
+                phys_val = vec[n:n + 1]
             l1s = torch.empty(1, dtype=torch.float64, device=dev)
             acc = 1 if g_raw is not None else 0
             if need_raw and g_raw is None:
@@ -840,7 +838,6 @@ class HybridFusedFn(torch.autograd.Function):
             nat.check(lib.llie_l1_grad(nat.ptr(xr), nat.ptr(br), xr.numel(), w["l1"] / xr.numel(), acc, nat.ptr(l1s),
                                        nat.ptr(g_raw), nat.ptr(flags), ws, st), "llie_l1_grad")
             launches += 1
-            vals[0] = (l1s[0] / float(xr.numel())).to(torch.float32)
             # ---- sRGB side: dE00 (writes) then DSSIM backward (adds), then the sRGB physics term if any
             n, c, h, wd = xs.shape
             if spec["use_de"]:
@@ -855,7 +852,6 @@ class HybridFusedFn(torch.autograd.Function):
                     nat.check(lib.llie_deltae(dd, nat.ptr(xs), nat.ptr(bs), nat.ptr(des), None, None, nat.ptr(flags),
                                               ws, st), "llie_deltae")
                 launches += 1
-                vals[1] = (des.sum() / float(n * h * wd)).to(torch.float32)
             if spec["use_ssim"]:
                 k = int(spec["ssim_window"])
                 mv = float(spec["ssim_max_val"])
@@ -879,7 +875,6 @@ class HybridFusedFn(torch.autograd.Function):
                     nat.check(lib.llie_ssim_stats(sd, nat.ptr(xs), nat.ptr(bs), nat.ptr(win), win_host(win), nat.ptr(sss),
                                                   None, nat.ptr(flags), ws, st), "llie_ssim_stats")
                     launches += 1
-                vals[2] = (sss.sum() / float(xs.numel())).to(torch.float32)
             if ph is not None and ph["srgb"]:
                 if need_srgb:
                     vec, _, gp = phys_value_and_grad(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"],
@@ -888,23 +883,19 @@ class HybridFusedFn(torch.autograd.Function):
                 else:
                     vec, _, _ = phys_forward(xs, ph["a"], ph["psf"], ph["rho_t"], ph["rho_s"], ph["rho_st"], ph["cfg"],
                                              False)
-                vals[3] = vec[n]
+                phys_val = vec[n:n + 1]
+            # term values and the weighted total in one launch (the eager expression is a dozen scalar tensor ops whose
+            # launches sat between the loss kernels: 0.59 -> 0.5x ms per C3 step); weights are read from spec["w"] every call
+            terms = torch.empty(4, dtype=torch.float32, device=dev)
+            total = torch.empty((), dtype=torch.float32, device=dev)
+            wv = (nat.C.c_float * 4)(*[float(w.get(k_, 0.0)) for k_ in ("l1", "de", "ssim", "phys")])
+            nat.check(lib.llie_hybrid_combine(nat.ptr(l1s), float(xr.numel()), nat.ptr(des),
+                                              des.numel() if des is not None else 0, float(n * h * wd), nat.ptr(sss),
+                                              sss.numel() if sss is not None else 0, float(xs.numel()),
+                                              nat.ptr(phys_val), wv, nat.ptr(terms), nat.ptr(total), st),
+                      "llie_hybrid_combine")
+            launches += 1
         nat.count_launch(launches)
-        terms = torch.stack(vals)
-        present = [0] + ([1] if spec["use_de"] else []) + ([2] if spec["use_ssim"] else []) + ([3] if ph is not None else [])
-        names = ("l1", "de", "ssim", "phys")
-        # index / weight vectors depend on which terms are present THIS call (A_srgb01 may be None on some batches,
-        # image_restoration_model.py:300) and on the current weights (schedules may edit module.w): cached by value,
-        # never on the module's spec dict
-        key = (dev.index, tuple(present), tuple(float(w[names[i]]) for i in present))
-        cached = _wvec_cache.get(key)
-        if cached is None:
-            if len(_wvec_cache) > 64:
-                _wvec_cache.clear()
-            cached = _wvec_cache[key] = (torch.tensor(present, device=dev),
-                                         torch.tensor(key[2], dtype=torch.float32, device=dev))
-        idx, wvec = cached
-        total = (terms.index_select(0, idx) * wvec).sum()
         ctx.save_for_backward(*[t for t in (g_raw, g_srgb) if t is not None])
         ctx.have = (g_raw is not None, g_srgb is not None)
         ctx.mark_non_differentiable(terms)

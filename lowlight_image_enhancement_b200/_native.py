@@ -112,6 +112,8 @@ _SIGNATURES = {
     "llie_pixel_loss_grad": (C.c_int, [C.c_int32, _VP, _VP, _VP, C.c_int32, _VP, C.c_int32, C.c_int32, C.c_int64, C.c_float,
                                        C.c_float, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
     "llie_scale_inplace": (C.c_int, [_VP, C.c_int64, _VP, _VP]),
+    "llie_hybrid_combine": (C.c_int, [_VP, C.c_double, _VP, C.c_int32, C.c_double, _VP, C.c_int32, C.c_double, _VP,
+                                      C.POINTER(C.c_float), _VP, _VP, _VP]),
     "llie_tile_merge": (C.c_int, [_VP, _VP, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _VP, _VP]),
     "llie_decode_u16": (C.c_int, [C.POINTER(DecodeDesc), _VP, _VP, C.c_float, _VP, _VP, _VP]),
     "llie_linear_to_srgb": (C.c_int, [_VP, C.c_int64, _VP, _VP, _VP]),

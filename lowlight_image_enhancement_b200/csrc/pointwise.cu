@@ -728,6 +728,67 @@ __global__ void __launch_bounds__(256) scale_inplace_kernel(float *__restrict__ 
 }
 }  // namespace llie
 
+namespace llie {
+struct HybridCombineArgs {
+    const double *l1_sum, *de_sums, *ssim_sums;
+    const float *phys_value;
+    double l1_count, de_count, ssim_count;
+    int n_de, n_ssim;
+    float w[4];
+    float *out_terms, *out_total;
+};
+
+// one warp: term values from the raw device sums, weighted total in the order L1, dE, SSIM, Phys
+__global__ void __launch_bounds__(32) hybrid_combine_kernel(const HybridCombineArgs a) {
+    const int lane = threadIdx.x;
+    double de = 0.0, ss = 0.0;
+    if (a.de_sums)
+        for (int i = lane; i < a.n_de; i += 32) de += a.de_sums[i];
+    if (a.ssim_sums)
+        for (int i = lane; i < a.n_ssim; i += 32) ss += a.ssim_sums[i];
+    de = warp_sum(de);
+    ss = warp_sum(ss);
+    if (lane != 0) return;
+    const float nanv = __int_as_float(0x7fc00000);
+    float t[4];
+    t[0] = a.l1_sum ? (float)(a.l1_sum[0] / a.l1_count) : nanv;
+    t[1] = a.de_sums ? (float)(de / a.de_count) : nanv;
+    t[2] = a.ssim_sums ? (float)(ss / a.ssim_count) : nanv;
+    t[3] = a.phys_value ? a.phys_value[0] : nanv;
+    const bool have[4] = {a.l1_sum != nullptr, a.de_sums != nullptr, a.ssim_sums != nullptr, a.phys_value != nullptr};
+    float total = 0.f;
+    bool first = true;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        a.out_terms[i] = t[i];
+        if (!have[i]) continue;
+        const float p = __fmul_rn(t[i], a.w[i]);
+        total = first ? p : __fadd_rn(total, p);
+        first = false;
+    }
+    a.out_total[0] = total;
+}
+}  // namespace llie
+
+extern "C" int llie_hybrid_combine(const double *l1_sum, double l1_count, const double *de_sums, int32_t n_de,
+                                   double de_count, const double *ssim_sums, int32_t n_ssim, double ssim_count,
+                                   const float *phys_value, const float *weights, float *out_terms, float *out_total,
+                                   void *stream) {
+    LLIE_REQUIRE(weights && out_terms && out_total, "hybrid_combine: null pointer");
+    LLIE_REQUIRE((!l1_sum || l1_count > 0) && (!de_sums || (n_de > 0 && de_count > 0)) &&
+                     (!ssim_sums || (n_ssim > 0 && ssim_count > 0)),
+                 "hybrid_combine: a present term needs a positive element count");
+    llie::HybridCombineArgs a{};
+    a.l1_sum = l1_sum; a.de_sums = de_sums; a.ssim_sums = ssim_sums; a.phys_value = phys_value;
+    a.l1_count = l1_count; a.de_count = de_count; a.ssim_count = ssim_count;
+    a.n_de = n_de; a.n_ssim = n_ssim;
+    for (int i = 0; i < 4; ++i) a.w[i] = weights[i];
+    a.out_terms = out_terms; a.out_total = out_total;
+    llie::hybrid_combine_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    LLIE_CUDA_OK(cudaGetLastError());
+    return LLIE_OK;
+}
+
 extern "C" int llie_scale_inplace(float *g, int64_t n, const float *scale, void *stream) {
     LLIE_REQUIRE(g != nullptr && scale != nullptr && n >= 0, "scale_inplace: null pointer");
     if (n == 0) return LLIE_OK;

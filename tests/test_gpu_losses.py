@@ -404,3 +404,41 @@ def test_losses_under_autocast(dev, in_dtype):
         ref = xf.grad.to(in_dtype).float()
         tol = {torch.float32: 1e-6, torch.bfloat16: 2.0 ** -7, torch.float16: 2.0 ** -9}[in_dtype]
         assert float((xa.grad.float() - ref).abs().max()) <= tol * float(ref.abs().max()) + 1e-12, name
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("present", [(True, True, True), (False, True, False), (True, False, True), (False, False, False)])
+def test_hybrid_combine_equals_the_eager_expression(present):
+    """llie_hybrid_combine (term values + weighted total of the fused hybrid loss in one launch) against the scalar
+    tensor expression it replaces; absent terms are NaN in the term vector and left out of the total."""
+    from lowlight_image_enhancement_b200 import _native as nat
+    dev = torch.device("cuda:0")
+    g = torch.Generator().manual_seed(11)
+    use_de, use_ssim, use_phys = present
+    l1 = torch.rand(1, generator=g, dtype=torch.float64).to(dev) * 1e5
+    des = (torch.rand(37, generator=g, dtype=torch.float64) * 1e6).to(dev)
+    sss = (torch.rand(37 * 3, generator=g, dtype=torch.float64) * 1e5).to(dev)
+    vec = torch.rand(39, generator=g).to(dev)
+    w = [1.0, 0.02, 0.05, 0.07]
+    counts = (12345678.0, 4194304.0, 12582912.0)
+    terms = torch.empty(4, device=dev)
+    total = torch.empty((), device=dev)
+    wv = (nat.C.c_float * 4)(*w)
+    pv = vec[37:38]
+    with torch.cuda.device(dev):
+        rc = nat.lib().llie_hybrid_combine(nat.ptr(l1), counts[0], nat.ptr(des) if use_de else None, 37 if use_de else 0,
+                                           counts[1], nat.ptr(sss) if use_ssim else None, 111 if use_ssim else 0,
+                                           counts[2], nat.ptr(pv) if use_phys else None, wv, nat.ptr(terms),
+                                           nat.ptr(total), nat.stream_ptr(dev))
+    nat.check(rc, "llie_hybrid_combine")
+    want = [(l1[0] / counts[0]).float(), (des.sum() / counts[1]).float(), (sss.sum() / counts[2]).float(), vec[37]]
+    have = [True, use_de, use_ssim, use_phys]
+    t = terms.cpu()
+    ref_total = torch.zeros((), dtype=torch.float32)
+    for i in range(4):
+        if have[i]:
+            assert abs(float(t[i]) - float(want[i])) <= 1.2e-7 * abs(float(want[i]))
+            ref_total = ref_total + want[i].cpu() * torch.tensor(w[i], dtype=torch.float32)
+        else:
+            assert torch.isnan(t[i])
+    assert abs(float(total) - float(ref_total)) <= 2.4e-7 * abs(float(ref_total))
